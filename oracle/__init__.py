@@ -1,0 +1,376 @@
+"""ctypes front-end of the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+May be imported only by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  The product package (uavmvs_b200)
+never imports this module.
+
+  liboracle.so        oracle/uavmvs_oracle.cpp: our restatement (kind "port")
+  _ref/libref_acc.so  the reference's libs/acc headers compiled as they lie
+                      (kind "reference"; tree build / ray traversal / KD search)
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_REF = None
+
+NAI = 0xFFFFFFFF
+VIEW_FLOATS = 28  # pos[3], w2c[16], calib[9]
+
+_vp = C.c_void_p
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+_u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+
+def build(force=False):
+    """Compile liboracle.so (and _ref/ when /root/reference is present)."""
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "uavmvs_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    ref_so = os.path.join(_HERE, "_ref", "libref_acc.so")
+    if os.path.isdir("/root/reference/libs/acc") and (force or not os.path.exists(ref_so)):
+        subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+
+
+def _opt(ptr_type):
+    """ndpointer that also accepts None."""
+    base = ptr_type
+
+    class _Opt(base):
+        @classmethod
+        def from_param(cls, obj):
+            if obj is None:
+                return None
+            return base.from_param(obj)
+    return _Opt
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    build()
+    L = C.CDLL(os.path.join(_HERE, "liboracle.so"))
+    u32, u64, i32, f32 = C.c_uint32, C.c_uint64, C.c_int, C.c_float
+    L.orc_bvh_build.restype = _vp
+    L.orc_bvh_build.argtypes = [_f32p, u32, _u32p, u32, i32]
+    L.orc_bvh_from_arrays.restype = _vp
+    L.orc_bvh_from_arrays.argtypes = [_u32p, _f32p, _f32p, _u32p, u32, u32]
+    L.orc_bvh_num_nodes.restype = u32
+    L.orc_bvh_num_nodes.argtypes = [_vp]
+    L.orc_bvh_num_tris.restype = u32
+    L.orc_bvh_num_tris.argtypes = [_vp]
+    L.orc_bvh_export.argtypes = [_vp, _u32p, _f32p, _f32p, _u32p]
+    L.orc_bvh_destroy.argtypes = [_vp]
+    L.orc_bvh_intersect.argtypes = [_vp, _f32p, u64, i32, _opt(_u8p), _opt(_u32p), _opt(_f32p), _opt(_u64p)]
+    L.orc_kd_build.restype = _vp
+    L.orc_kd_build.argtypes = [_f32p, u32]
+    L.orc_kd_from_arrays.restype = _vp
+    L.orc_kd_from_arrays.argtypes = [_u32p, _f32p, u32, u32]
+    L.orc_kd_num_nodes.restype = u32
+    L.orc_kd_num_nodes.argtypes = [_vp]
+    L.orc_kd_export.argtypes = [_vp, _u32p, _f32p]
+    L.orc_kd_find_nn.argtypes = [_vp, _f32p, u64, _u32p, _opt(_f32p)]
+    L.orc_kd_destroy.argtypes = [_vp]
+    L.orc_sphere_vertices.restype = u32
+    L.orc_sphere_vertices.argtypes = [f32, u32, _opt(_f32p), u32]
+    L.orc_update_observation_rays.argtypes = [
+        _vp, i32, _f32p, u32, f32, i32, i32, _f32p, _f32p, u32,
+        _f32p, _u32p, u32, u64, _opt(_u8p), _opt(_u64p)]
+    L.orc_process_observation_rays.argtypes = [_f32p, _u32p, u32, u64, u32]
+    L.orc_evaluate_observation_rays.argtypes = [_f32p, _u32p, u32, u64, u32, _f32p, _f32p]
+    L.orc_calculate_func_recons.argtypes = [_f32p, f32, _f32p, u32]
+    L.orc_reduce.argtypes = [_f32p, u32, _f64p]
+    L.orc_populate_spherical_histogram.argtypes = [
+        _vp, _vp, _f32p, f32, _f32p, _f32p, _f32p, _f32p, u32, _f64p, _opt(_u32p), _opt(_f32p)]
+    L.orc_populate_spherical_histogram_recon.argtypes = [
+        _vp, _vp, _f32p, f32, f32, _f32p, _f32p, u32, _f32p, _u32p, u32, u64,
+        _f32p, _f32p, _f64p, _opt(_u32p), _opt(_f32p)]
+    L.orc_evaluate_spherical_histogram.argtypes = [_f32p, i32, i32, _f32p, u32, _f32p, _f32p, u32, u32]
+    L.orc_estimate_capture_difficulty.argtypes = [_vp, f32, u32, _f32p, u32, _f32p, _f32p, u32, _f32p, _f32p]
+    _LIB = L
+    return L
+
+
+def ref():
+    """The reference's own acc code (None when oracle/_ref was not built)."""
+    global _REF
+    if _REF is not None:
+        return _REF
+    build()
+    path = os.path.join(_HERE, "_ref", "libref_acc.so")
+    if not os.path.exists(path):
+        return None
+    R = C.CDLL(path)
+    u32, u64, i32 = C.c_uint32, C.c_uint64, C.c_int
+    R.ref_bvh_build.restype = _vp
+    R.ref_bvh_build.argtypes = [_f32p, u32, _u32p, u32, i32]
+    R.ref_bvh_num_nodes.restype = u32
+    R.ref_bvh_num_nodes.argtypes = [_vp]
+    R.ref_bvh_num_tris.restype = u32
+    R.ref_bvh_num_tris.argtypes = [_vp]
+    R.ref_bvh_export.argtypes = [_vp, _u32p, _f32p, _f32p, _u32p]
+    R.ref_bvh_intersect.argtypes = [_vp, _f32p, u64, _opt(_u8p), _opt(_u32p), _opt(_f32p)]
+    R.ref_bvh_destroy.argtypes = [_vp]
+    R.ref_kd_build.restype = _vp
+    R.ref_kd_build.argtypes = [_f32p, u32, i32]
+    R.ref_kd_num_nodes.restype = u32
+    R.ref_kd_num_nodes.argtypes = [_vp]
+    R.ref_kd_export.argtypes = [_vp, _u32p, _f32p]
+    R.ref_kd_find_nn.argtypes = [_vp, _f32p, u64, _u32p, _opt(_f32p)]
+    R.ref_kd_destroy.argtypes = [_vp]
+    _REF = R
+    return R
+
+
+def _c(a, dt):
+    return np.ascontiguousarray(a, dtype=dt)
+
+
+class TreeArrays:
+    """Flat export of a binary BVH in the reference's layout
+    (libs/cacc/bvh_tree.h:31-42, :86-93): nodes[n,4] = first,last,left,right."""
+
+    def __init__(self, nodes, aabbs, tris, indices):
+        self.nodes, self.aabbs, self.tris, self.indices = nodes, aabbs, tris, indices
+
+    @property
+    def num_nodes(self):
+        return self.nodes.shape[0]
+
+    @property
+    def num_tris(self):
+        return self.indices.shape[0]
+
+
+class BVH:
+    """Oracle BVH (our restatement of acc::BVHTree)."""
+
+    def __init__(self, handle):
+        self.h = handle
+
+    @classmethod
+    def build(cls, verts, faces, threads=0):
+        verts = _c(verts, np.float32).reshape(-1, 3)
+        faces = _c(faces, np.uint32).reshape(-1, 3)
+        threads = threads or os.cpu_count() or 1
+        return cls(lib().orc_bvh_build(verts, verts.shape[0], faces, faces.shape[0], threads))
+
+    @classmethod
+    def from_arrays(cls, t):
+        return cls(lib().orc_bvh_from_arrays(_c(t.nodes, np.uint32), _c(t.aabbs, np.float32),
+                                             _c(t.tris, np.float32), _c(t.indices, np.uint32),
+                                             t.num_nodes, t.num_tris))
+
+    def export(self):
+        L = lib()
+        n, t = L.orc_bvh_num_nodes(self.h), L.orc_bvh_num_tris(self.h)
+        nodes = np.empty((n, 4), np.uint32)
+        aabbs = np.empty((n, 6), np.float32)
+        tris = np.empty((t, 9), np.float32)
+        idx = np.empty(t, np.uint32)
+        L.orc_bvh_export(self.h, nodes, aabbs, tris, idx)
+        return TreeArrays(nodes, aabbs, tris, idx)
+
+    def intersect(self, rays, any_hit=True, counters=False):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        hit = np.empty(n, np.uint8)
+        face = np.empty(n, np.uint32)
+        t = np.empty(n, np.float32)
+        cnt = np.zeros(5, np.uint64) if counters else None
+        lib().orc_bvh_intersect(self.h, rays, n, 1 if any_hit else 0, hit, face, t, cnt)
+        return (hit, face, t, cnt) if counters else (hit, face, t)
+
+    def __del__(self):
+        if getattr(self, "h", None) and _LIB is not None:
+            _LIB.orc_bvh_destroy(self.h)
+            self.h = None
+
+
+class RefBVH:
+    """The reference's own acc::BVHTree (oracle/_ref)."""
+
+    def __init__(self, verts, faces, threads=0):
+        R = ref()
+        if R is None:
+            raise RuntimeError("oracle/_ref/libref_acc.so not built")
+        verts = _c(verts, np.float32).reshape(-1, 3)
+        faces = _c(faces, np.uint32).reshape(-1, 3)
+        self.h = R.ref_bvh_build(verts, verts.shape[0], faces, faces.shape[0], threads or os.cpu_count() or 1)
+
+    def export(self):
+        R = ref()
+        n, t = R.ref_bvh_num_nodes(self.h), R.ref_bvh_num_tris(self.h)
+        nodes = np.empty((n, 4), np.uint32)
+        aabbs = np.empty((n, 6), np.float32)
+        tris = np.empty((t, 9), np.float32)
+        idx = np.empty(t, np.uint32)
+        R.ref_bvh_export(self.h, nodes, aabbs, tris, idx)
+        return TreeArrays(nodes, aabbs, tris, idx)
+
+    def intersect(self, rays):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        hit = np.empty(n, np.uint8)
+        face = np.empty(n, np.uint32)
+        t = np.empty(n, np.float32)
+        ref().ref_bvh_intersect(self.h, rays, n, hit, face, t)
+        return hit, face, t
+
+    def __del__(self):
+        if getattr(self, "h", None) and _REF is not None:
+            _REF.ref_bvh_destroy(self.h)
+            self.h = None
+
+
+class KD:
+    def __init__(self, handle):
+        self.h = handle
+
+    @classmethod
+    def build(cls, verts):
+        verts = _c(verts, np.float32).reshape(-1, 3)
+        return cls(lib().orc_kd_build(verts, verts.shape[0]))
+
+    @classmethod
+    def from_arrays(cls, nodes, verts):
+        nodes = _c(nodes, np.uint32).reshape(-1, 4)
+        verts = _c(verts, np.float32).reshape(-1, 3)
+        return cls(lib().orc_kd_from_arrays(nodes, verts, nodes.shape[0], verts.shape[0]))
+
+    def export(self):
+        L = lib()
+        n = L.orc_kd_num_nodes(self.h)
+        nodes = np.empty((n, 4), np.uint32)
+        verts = np.empty((n, 3), np.float32)
+        L.orc_kd_export(self.h, nodes, verts)
+        return nodes, verts
+
+    def find_nn(self, q):
+        q = _c(q, np.float32).reshape(-1, 3)
+        idx = np.empty(q.shape[0], np.uint32)
+        dist = np.empty(q.shape[0], np.float32)
+        lib().orc_kd_find_nn(self.h, q, q.shape[0], idx, dist)
+        return idx, dist
+
+    def __del__(self):
+        if getattr(self, "h", None) and _LIB is not None:
+            _LIB.orc_kd_destroy(self.h)
+            self.h = None
+
+
+def sphere_vertices(radius=1.0, subdivisions=3):
+    n = lib().orc_sphere_vertices(radius, subdivisions, None, 0)
+    out = np.empty((n, 3), np.float32)
+    lib().orc_sphere_vertices(radius, subdivisions, out, n)
+    return out
+
+
+def pack_views(view_pos, w2c, calib):
+    """[V,3], [V,4,4], [V,3,3] -> [V,28] float32."""
+    V = len(view_pos)
+    out = np.empty((V, VIEW_FLOATS), np.float32)
+    out[:, 0:3] = np.asarray(view_pos, np.float32).reshape(V, 3)
+    out[:, 3:19] = np.asarray(w2c, np.float32).reshape(V, 16)
+    out[:, 19:28] = np.asarray(calib, np.float32).reshape(V, 9)
+    return out
+
+
+class ObsRays:
+    """Host mirror of cacc::VectorArray<Vec3f> (libs/cacc/vector_array.h:23-50):
+    data[max_rows, stride, 4] float32, num_rows[N] uint32."""
+
+    def __init__(self, n, max_rows=32, stride=None):
+        self.n, self.max_rows = n, max_rows
+        self.stride = stride or n
+        self.data = np.zeros((max_rows, self.stride, 4), np.float32)
+        self.num_rows = np.zeros(n, np.uint32)
+
+
+def update_observation_rays(bvh, populate, views, max_distance, width, height, verts, normals, obs,
+                            want_state=False, want_counters=False):
+    views = _c(views, np.float32).reshape(-1, VIEW_FLOATS)
+    verts = _c(verts, np.float32).reshape(-1, 3)
+    normals = _c(normals, np.float32).reshape(-1, 3)
+    n = verts.shape[0]
+    state = np.zeros((views.shape[0], n), np.uint8) if want_state else None
+    cnt = np.zeros(6, np.uint64) if want_counters else None
+    lib().orc_update_observation_rays(bvh.h, 1 if populate else 0, views, views.shape[0], max_distance,
+                                      width, height, verts, normals, n, obs.data, obs.num_rows,
+                                      obs.max_rows, obs.stride, state, cnt)
+    return state, cnt
+
+
+def process_observation_rays(obs):
+    lib().orc_process_observation_rays(obs.data, obs.num_rows, obs.max_rows, obs.stride, obs.n)
+
+
+def evaluate_observation_rays(obs, heur=(8.0, 4.0, 32.0, 16.0)):
+    recons = np.empty(obs.n, np.float32)
+    lib().orc_evaluate_observation_rays(obs.data, obs.num_rows, obs.max_rows, obs.stride, obs.n,
+                                        np.asarray(heur, np.float32), recons)
+    return recons
+
+
+def calculate_func_recons(recons, target):
+    out = np.empty_like(recons)
+    lib().orc_calculate_func_recons(_c(recons, np.float32), target, out, recons.shape[0])
+    return out
+
+
+def reduce(x):
+    out = np.zeros(3, np.float64)
+    lib().orc_reduce(_c(x, np.float32), x.shape[0], out)
+    return out
+
+
+def populate_spherical_histogram(bvh, kd, view_pos, max_distance, verts, normals, values, qualities, S):
+    n = len(verts)
+    hist = np.zeros(S, np.float64)
+    bins = np.empty(n, np.uint32)
+    scores = np.empty(n, np.float32)
+    lib().orc_populate_spherical_histogram(bvh.h, kd.h, _c(view_pos, np.float32), max_distance,
+                                           _c(verts, np.float32), _c(normals, np.float32),
+                                           _c(values, np.float32), _c(qualities, np.float32), n,
+                                           hist, bins, scores)
+    return hist, bins, scores
+
+
+def populate_spherical_histogram_recon(bvh, kd, view_pos, max_distance, target_recon, verts, normals,
+                                       obs, recons, S, heur=(8.0, 4.0, 32.0, 16.0)):
+    n = len(verts)
+    hist = np.zeros(S, np.float64)
+    bins = np.empty(n, np.uint32)
+    deltas = np.empty(n, np.float32)
+    lib().orc_populate_spherical_histogram_recon(
+        bvh.h, kd.h, _c(view_pos, np.float32), max_distance, target_recon,
+        _c(verts, np.float32), _c(normals, np.float32), n, obs.data, obs.num_rows, obs.max_rows,
+        obs.stride, _c(recons, np.float32), np.asarray(heur, np.float32), hist, bins, deltas)
+    return hist, bins, deltas
+
+
+def evaluate_spherical_histogram(calib, width, height, sphere_verts, sphere_hist, hist_w=128, hist_h=45):
+    sv = _c(sphere_verts, np.float32).reshape(-1, 3)
+    out = np.empty((hist_h, hist_w), np.float32)
+    lib().orc_evaluate_spherical_histogram(_c(calib, np.float32).reshape(9), width, height, sv, sv.shape[0],
+                                           _c(sphere_hist, np.float32), out, hist_w, hist_h)
+    return out
+
+
+def estimate_capture_difficulty(bvh, max_distance, mesh_size, sphere_verts, verts, normals):
+    sv = _c(sphere_verts, np.float32).reshape(-1, 3)
+    n = len(verts)
+    values = np.empty(n, np.float32)
+    qualities = np.empty(n, np.float32)
+    lib().orc_estimate_capture_difficulty(bvh.h, max_distance, mesh_size, sv, sv.shape[0],
+                                          _c(verts, np.float32), _c(normals, np.float32), n, values, qualities)
+    return values, qualities
