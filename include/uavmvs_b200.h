@@ -1,0 +1,167 @@
+/*
+ * uavmvs_b200.h -- C ABI of the B200-native visibility-and-reconstructability
+ * evaluation (drop-in for the libs/eval + libs/cacc path of nmoehrle/uavmvs).
+ *
+ * Every entry point cites the reference interface it replaces (paths relative
+ * to the reference checkout).  Conventions:
+ *   - plain pointers and sizes only; HOST pointers unless the name says device;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - every function returns 0 on success, non-zero on failure;
+ *     uavmvs_last_error() gives the message (thread local).  The reference's
+ *     convention is print-and-exit (CHECK(), libs/cacc/defines.h:20-29); the
+ *     C++ facade (include/uavmvs_b200/cacc.hpp) maps non-zero back to that.
+ *   - matrices are row-major float (libs/cacc/matrix.h:36-44);
+ *   - there is no CPU fallback: every call needs a CUDA device.
+ */
+#ifndef UAVMVS_B200_H
+#define UAVMVS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UAVMVS_NAI 0xffffffffu
+#define UAVMVS_VIEW_FLOATS 28 /* pos[3], w2c[16], calib[9] */
+
+typedef struct uavmvs_bvh uavmvs_bvh;         /* cacc::BVHTree<DEVICE>            */
+typedef struct uavmvs_kdtree uavmvs_kdtree;   /* cacc::KDTree<3, DEVICE>          */
+typedef struct uavmvs_cloud uavmvs_cloud;     /* cacc::PointCloud<DEVICE>         */
+typedef struct uavmvs_obs uavmvs_obs;         /* cacc::VectorArray<Vec3f, DEVICE> */
+typedef struct uavmvs_array uavmvs_array;     /* cacc::Array<float, DEVICE>       */
+typedef struct uavmvs_image uavmvs_image;     /* cacc::Image<float, DEVICE>       */
+
+const char * uavmvs_last_error(void);
+/* cacc::select_cuda_device / set_cuda_device, libs/cacc/util.h:36-100 */
+int uavmvs_set_device(int device);
+int uavmvs_device_count(int * count);
+int uavmvs_synchronize(void * stream);
+
+/* ---- BVH: cacc::BVHTree<DEVICE>::create(acc_tree), libs/cacc/bvh_tree.h:190-194,
+ * libs/cacc/bvh_tree.cu:17-57.  Arrays are exactly what convert<HOST> hands over:
+ * nodes[4n] = {first,last,left,right}, aabbs[6n] = {min,max}, tris[9t] (leaf order),
+ * indices[t] = original face ids. */
+int uavmvs_bvh_create_from_arrays(const uint32_t * nodes, const float * aabbs, const float * tris,
+    const uint32_t * indices, uint32_t num_nodes, uint32_t num_tris, uavmvs_bvh ** out);
+/* GPU LBVH build (Morton sort + bottom-up refit) from an indexed mesh; replaces the host
+ * acc::BVHTree constructor (libs/acc/bvh_tree.h:335-399) for large scenes. */
+int uavmvs_bvh_build_lbvh(const float * verts, uint32_t num_verts, const uint32_t * faces,
+    uint32_t num_faces, uavmvs_bvh ** out);
+int uavmvs_bvh_sizes(const uavmvs_bvh * bvh, uint32_t * num_nodes, uint32_t * num_tris);
+/* Export in the reference layout (for the oracle / for acc-side consumers). */
+int uavmvs_bvh_export(const uavmvs_bvh * bvh, uint32_t * nodes, float * aabbs, float * tris, uint32_t * indices);
+int uavmvs_bvh_destroy(uavmvs_bvh * bvh);
+/* cacc::tracing::trace, libs/cacc/tracing.h:37-116 -- batch form for tests and tools.
+ * rays[8n] = origin, dir, tmin, tmax.  any_hit != 0: hit flag only (face = first accepted).
+ * Otherwise closest hit; face[i] = original face id or UAVMVS_NAI. */
+int uavmvs_bvh_trace(void * stream, const uavmvs_bvh * bvh, const float * rays, uint64_t num_rays,
+    int any_hit, uint8_t * hit, uint32_t * face, float * t);
+
+/* ---- KD-tree: cacc::KDTree<3,DEVICE>::create(acc_kd), libs/cacc/kd_tree.h:150-154,
+ * libs/cacc/kd_tree.cu:15-45.  nodes[4n] = {vid,dim,left,right}, verts[3n]. */
+int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t num_nodes, uavmvs_kdtree ** out);
+int uavmvs_kdtree_destroy(uavmvs_kdtree * kd);
+
+/* ---- Point cloud: cacc::PointCloud<HOST>::create(n) + fill + <DEVICE>::create<HOST>,
+ * libs/cacc/point_cloud.h:26-32, :91-114.  values/qualities may be NULL
+ * (defaults 0 / 1, libs/util/cio.h:45-46). */
+int uavmvs_cloud_create(const float * vertices, const float * normals, const float * values,
+    const float * qualities, uint32_t n, uavmvs_cloud ** out);
+int uavmvs_cloud_download_attributes(const uavmvs_cloud * cloud, float * values, float * qualities);
+int uavmvs_cloud_upload_attributes(uavmvs_cloud * cloud, const float * values, const float * qualities);
+int uavmvs_cloud_size(const uavmvs_cloud * cloud, uint32_t * n);
+int uavmvs_cloud_destroy(uavmvs_cloud * cloud);
+
+/* ---- Observation rays: cacc::VectorArray<Vec3f,DEVICE>::create(num_cols, max_rows),
+ * libs/cacc/vector_array.h:23-50, :87-90.  Device layout kept: row-major float4 rows of
+ * `pitch` bytes, element (row r, col i) at data + r*pitch + 16*i; num_rows[num_cols]. */
+int uavmvs_obs_create(uint32_t num_cols, uint32_t max_rows, uavmvs_obs ** out);
+int uavmvs_obs_clear(void * stream, uavmvs_obs * obs);              /* VectorArray::null() */
+/* data: [max_rows][num_cols][4] float (dense), num_rows: [num_cols]; either may be NULL */
+int uavmvs_obs_download(const uavmvs_obs * obs, float * data, uint32_t * num_rows);
+int uavmvs_obs_upload(uavmvs_obs * obs, const float * data, const uint32_t * num_rows);
+int uavmvs_obs_destroy(uavmvs_obs * obs);
+
+/* ---- cacc::Array<float,DEVICE>, libs/cacc/array.h:73-128 */
+int uavmvs_array_create(uint32_t n, uavmvs_array ** out);
+int uavmvs_array_null(void * stream, uavmvs_array * a);
+int uavmvs_array_download(const uavmvs_array * a, float * host);
+int uavmvs_array_upload(uavmvs_array * a, const float * host);
+int uavmvs_array_destroy(uavmvs_array * a);
+
+/* ---- cacc::Image<float,DEVICE>, libs/cacc/image.h:84-86 */
+int uavmvs_image_create(uint32_t width, uint32_t height, uavmvs_image ** out);
+int uavmvs_image_download(const uavmvs_image * img, float * host); /* dense [h][w] */
+int uavmvs_image_destroy(uavmvs_image * img);
+
+/* ---- configure_heuristic, libs/eval/kernels.h:93, kernels.cu:93-103.
+ * Process-global like the reference's __constant__ symbols; defaults 8, 4, 32, 16. */
+int uavmvs_configure_heuristic(float m_k, float m_x0, float t_k, float t_x0);
+
+/* ---- K1 update_observation_rays, libs/eval/kernels.h:26-35, kernels.cu:138-202.
+ * One view, all points; same arguments as the kernel plus the stream. */
+int uavmvs_update_observation_rays(void * stream, int populate, const float view_pos[3],
+    float max_distance, const float w2c[16], const float calib[9], int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs);
+/* Batched form of the launch loop apps/evaluate_trajectory/evaluate_trajectory.cu:154-164:
+ * `num_views` views in stream order, views[28*k] = {pos, w2c, calib} (HOST memory).
+ * Result identical to num_views single calls in order. */
+int uavmvs_update_observation_rays_batch(void * stream, int populate, const float * views,
+    uint32_t num_views, float max_distance, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs);
+/* Same with the view array already on the device (device pointer). */
+int uavmvs_update_observation_rays_batch_device(void * stream, int populate, const float * d_views,
+    uint32_t num_views, float max_distance, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs);
+
+/* ---- K2 process_observation_rays, kernels.h:37-39, kernels.cu:204-264 */
+int uavmvs_process_observation_rays(void * stream, uavmvs_obs * obs);
+/* ---- K3 evaluate_observation_rays, kernels.h:41-44, kernels.cu:266-291 */
+int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavmvs_array * recons);
+/* ---- K8 calculate_func_recons, kernels.h:86-91, kernels.cu:496-510 */
+int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon,
+    uavmvs_array * wrecons);
+/* ---- K9 cacc::reduction::{sum,min,max}, libs/cacc/reduction.h:132-162.
+ * out3 = {sum, min, max} (HOST); synchronises the stream. */
+int uavmvs_reduce(void * stream, const uavmvs_array * a, float out3[3]);
+
+/* ---- Whole evaluation as apps/evaluate_trajectory/evaluate_trajectory.cu:125-202 runs it:
+ * clear obs, K1 over all views, K2, K3, K8, K9.  views are HOST memory (copied inside).
+ * stats (HOST, may be NULL): [0] = occlusion rays traced, [1] = visible observations,
+ * [2] = (point,view) pairs evaluated, [3] = pairs surviving the block-level cull.
+ * out3 = {sum(wrecon), min, max}; score = out3[0] / num_points. */
+int uavmvs_evaluate_trajectory(void * stream, const float * views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4]);
+int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4]);
+
+/* ---- K4 populate_spherical_histogram (6-arg), kernels.h:46-50, kernels.cu:293-336 */
+int uavmvs_populate_spherical_histogram(void * stream, const float view_pos[3], float max_distance,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd,
+    uavmvs_array * sphere_hist);
+/* ---- K5 populate_spherical_histogram (9-arg), kernels.h:52-67, kernels.cu:338-390 */
+int uavmvs_populate_spherical_histogram_recon(void * stream, const float view_pos[3],
+    float max_distance, float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    const uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons,
+    uavmvs_array * sphere_hist);
+/* ---- K6 evaluate_spherical_histogram, kernels.h:69-79, kernels.cu:392-446 */
+int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int width, int height,
+    const uavmvs_kdtree * kd, const uavmvs_array * sphere_hist, uavmvs_image * hist);
+/* ---- K7 estimate_capture_difficulty, kernels.h:81-84, kernels.cu:448-494 */
+int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const uavmvs_bvh * bvh,
+    uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud);
+
+/* Device pointer escape hatch for callers that launch their own kernels on the data
+ * (the reference's cdata()/accessor() PODs): which = 0 obs data, 1 obs num_rows,
+ * 2 cloud vertices (float4), 3 cloud normals (float4). */
+int uavmvs_obs_device_ptr(const uavmvs_obs * obs, int which, void ** ptr, uint64_t * pitch_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UAVMVS_B200_H */

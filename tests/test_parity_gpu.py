@@ -1,0 +1,223 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star): visibility flags and observation counts bit-exact;
+stored observation rays bit-exact (same operation order); heuristic scores within
+1e-5 relative (libm vs CUDA acosf/expf).
+"""
+import numpy as np
+import pytest
+
+from conftest import make_rays
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def api():
+    from uavmvs_b200 import api as a
+    assert a.device_count() >= 1
+    return a
+
+
+def _close(a, b, rel=REL, floor=0.0):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.all(np.abs(a - b) <= rel * np.maximum(np.abs(a), np.abs(b)) + floor)
+
+
+def _gpu_tree(api, arrays):
+    return api.BVHTree.create(arrays.nodes, arrays.aabbs, arrays.tris, arrays.indices)
+
+
+def test_trace_matches_oracle(api, oracle, tiny_scene, tiny_tree):
+    obvh, arrays = tiny_tree
+    gbvh = _gpu_tree(api, arrays)
+    rays = make_rays(tiny_scene, 100_000, seed=1)
+    h_o, f_o, t_o = obvh.intersect(rays, any_hit=False)
+    h_g, f_g, t_g = gbvh.trace(rays, any_hit=False)
+    assert np.array_equal(h_o, h_g)
+    assert np.array_equal(f_o, f_g)
+    assert np.array_equal(t_o.view(np.uint32), t_g.view(np.uint32))
+    h_a, _, _ = gbvh.trace(rays, any_hit=True)
+    assert np.array_equal(h_o, h_a)
+    assert 0.05 < h_o.mean() < 0.95
+
+
+def test_trace_degenerate_inputs(api, oracle):
+    """Single-triangle tree (root is a leaf), a degenerate triangle, axis-parallel rays."""
+    verts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [2, 2, 2], [2, 2, 2], [2, 2, 2]], np.float32)
+    for faces in (np.array([[0, 1, 2]], np.uint32), np.array([[0, 1, 2], [3, 4, 5]], np.uint32)):
+        obvh = oracle.BVH.build(verts, faces, threads=1)
+        gbvh = _gpu_tree(api, obvh.export())
+        rays = np.array([[0.2, 0.2, 1, 0, 0, -1, 0.001, 5.0],
+                         [0.2, 0.2, 1, 0, 0, 1, 0.001, 5.0],
+                         [1.0005, 0.0, 1, 0, 0, -1, 0.0, 5.0],     # inside the 1e-3 slack
+                         [1.01, 0.0, 1, 0, 0, -1, 0.0, 5.0],       # outside
+                         [2, 2, 3, 0, 0, -1, 0.0, 5.0]], np.float32)
+        for any_hit in (True, False):
+            h_o, f_o, _ = obvh.intersect(rays, any_hit=any_hit)
+            h_g, f_g, _ = gbvh.trace(rays, any_hit=any_hit)
+            assert np.array_equal(h_o, h_g)
+            if not any_hit:
+                assert np.array_equal(f_o, f_g)
+            # one triangle: root is a leaf, no box test, the slack-zone ray hits; two faces: the
+            # leaf's tight box rejects it first (tree-dependent visibility)
+            assert list(h_o[:4]) == ([1, 0, 1, 0] if len(faces) == 1 else [1, 0, 0, 0])
+
+
+def _run_oracle_eval(oracle, obvh, sc, views=None, max_rows=32):
+    obs = oracle.ObsRays(sc.num_points, max_rows)
+    v = sc.views28() if views is None else views
+    state, cnt = oracle.update_observation_rays(obvh, True, v, sc.max_distance, sc.width, sc.height,
+                                                sc.points, sc.normals, obs, want_state=True, want_counters=True)
+    return obs, state, cnt
+
+
+def _valid_rows_equal(d_o, d_g, rows, max_rows):
+    r = np.minimum(rows, max_rows)
+    mask = np.arange(max_rows)[:, None] < r[None, :]
+    return np.array_equal(d_o.view(np.uint32)[mask], d_g.view(np.uint32)[mask])
+
+
+def test_update_observation_rays_batch(api, oracle, tiny_scene, tiny_tree):
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    obs_o, state, cnt = _run_oracle_eval(oracle, obvh, sc)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    assert np.array_equal(rows, obs_o.num_rows)                 # observation counts: bit-exact
+    assert rows.sum() == (state == 2).sum() and rows.sum() > 1000
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)          # stored rays: bit-exact
+
+
+def test_single_view_calls_equal_batch(api, oracle, tiny_scene, tiny_tree):
+    """The per-view entry point (reference launch loop) gives the same rows as the batch."""
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    for k in range(sc.num_views):
+        api.update_observation_rays(True, sc.view_pos[k], sc.max_distance, sc.w2c[k], sc.calib[k],
+                                    sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    obs_o, _, _ = _run_oracle_eval(oracle, obvh, sc)
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def test_row_cap_and_overflow_counter(api, oracle, tiny_scene, tiny_tree):
+    """max_rows = 4: counters keep counting, rows beyond the cap are dropped (kernels.cu:176-178)."""
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    obs_o, _, _ = _run_oracle_eval(oracle, obvh, sc, max_rows=4)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 4)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    assert rows.max() > 4
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 4)
+
+
+def test_process_and_evaluate(api, oracle, tiny_scene, tiny_tree):
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    obs_o, _, _ = _run_oracle_eval(oracle, obvh, sc)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    api.process_observation_rays(obs)
+    oracle.process_observation_rays(obs_o)
+    data, rows = obs.download()
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)          # same sort network -> same order
+    recons, wrecons = api.Array.create(sc.num_points), api.Array.create(sc.num_points)
+    api.evaluate_observation_rays(obs, recons)
+    api.calculate_func_recons(recons, sc.target_recon, wrecons)
+    r_o = oracle.evaluate_observation_rays(obs_o)
+    w_o = oracle.calculate_func_recons(r_o, sc.target_recon)
+    r_g, w_g = recons.download(), wrecons.download()
+    assert np.array_equal(r_o == -1.0, r_g == -1.0)
+    assert _close(r_o, r_g)
+    assert _close(w_o, w_g, floor=1e-6)
+    s, mn, mx = api.reduce(wrecons)
+    ref = oracle.reduce(w_o)
+    assert _close(s, ref[0]) and mn == ref[1] and mx == ref[2]
+
+
+def test_remove_views(api, oracle, tiny_scene, tiny_tree):
+    """populate=false marks rays, K2 compacts (optimize_trajectory.cu:313-354)."""
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    views = sc.views28()
+    removed = views[[3, 11, 17]]
+    obs_o, _, _ = _run_oracle_eval(oracle, obvh, sc)
+    oracle.update_observation_rays(obvh, False, removed, sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, views, sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    before = obs.download(data=False)[1].sum()
+    api.update_observation_rays_batch(False, removed, sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    api.process_observation_rays(obs)
+    data, rows = obs.download()
+    assert rows.sum() < before
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def test_evaluate_trajectory_fused(api, oracle, tiny_scene, tiny_tree):
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    obs_o, state, cnt = _run_oracle_eval(oracle, obvh, sc)
+    oracle.process_observation_rays(obs_o)
+    r_o = oracle.evaluate_observation_rays(obs_o)
+    w_o = oracle.calculate_func_recons(r_o, sc.target_recon)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    recons, wrecons = api.Array.create(sc.num_points), api.Array.create(sc.num_points)
+    for views in (sc.views28(), api.DeviceViews(sc.views28())):
+        s, mn, mx, stats = api.evaluate_trajectory(views, sc.max_distance, sc.target_recon, sc.width, sc.height,
+                                                   gbvh, cloud, obs, recons, wrecons)
+        assert stats[0] == int(cnt[0])                         # occlusion rays traced
+        assert stats[1] == int((state == 2).sum())             # visible observations
+        assert np.array_equal(obs.download(data=False)[1], obs_o.num_rows)
+        assert _close(recons.download(), r_o)
+        assert _close(s / sc.num_points, w_o.astype(np.float64).mean())
+
+
+def test_lbvh_same_tree_parity(api, oracle, tiny_scene):
+    """GPU-built LBVH: the oracle walks the exported tree (parity is per tree)."""
+    sc = tiny_scene
+    gbvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
+    nodes, aabbs, tris, indices = gbvh.export()
+    n, t = gbvh.sizes()
+    assert t == sc.num_tris and n == 2 * t - 1
+    assert sorted(indices.tolist()) == list(range(t))
+    # every inner box is the exact union of its children
+    inner = nodes[:, 2] != 0xFFFFFFFF
+    l, r = nodes[inner, 2], nodes[inner, 3]
+    assert np.array_equal(aabbs[inner, :3], np.minimum(aabbs[l, :3], aabbs[r, :3]))
+    assert np.array_equal(aabbs[inner, 3:], np.maximum(aabbs[l, 3:], aabbs[r, 3:]))
+    obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    rays = make_rays(sc, 50_000, seed=2)
+    h_o, f_o, t_o = obvh.intersect(rays, any_hit=False)
+    h_g, f_g, t_g = gbvh.trace(rays, any_hit=False)
+    assert np.array_equal(h_o, h_g) and np.array_equal(f_o, f_g)
+    assert np.array_equal(gbvh.trace(rays, any_hit=True)[0], h_o)
+    obs_o, state, _ = _run_oracle_eval(oracle, obvh, sc)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)

@@ -1,0 +1,366 @@
+"""Host-side mirror of the reference's cacc:: / libs/eval interface over the C ABI.
+
+Class and function names follow the reference so that callers (and the parity
+tests) read like its apps:
+
+    cacc::BVHTree<DEVICE>::create(acc_tree)        -> BVHTree.create(nodes, aabbs, tris, indices)
+    cacc::KDTree<3,DEVICE>::create(acc_kd)         -> KDTree.create(nodes, verts)
+    cacc::PointCloud<DEVICE>::create<HOST>(cloud)  -> PointCloud.create(vertices, normals, ...)
+    cacc::VectorArray<Vec3f,DEVICE>::create(n, 32) -> VectorArray.create(n, 32)
+    cacc::Array<float,DEVICE>::create(n)           -> Array.create(n)
+    cacc::Image<float,DEVICE>::create(w, h)        -> Image.create(w, h)
+    update_observation_rays<<<...>>>(...)          -> update_observation_rays(...)   (etc.)
+
+There is no CPU fallback: loading this module without the compiled CUDA library,
+or calling anything without a CUDA device, raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libuavmvs_b200.so")
+VIEW_FLOATS = 28
+NAI = 0xFFFFFFFF
+
+
+class UavmvsError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(_SO):
+        raise UavmvsError(
+            f"{_SO} is missing: build it with `python -m uavmvs_b200.build` "
+            "(there is no CPU fallback for the evaluation path)")
+    return C.CDLL(_SO)
+
+
+_lib = _load()
+_lib.uavmvs_last_error.restype = C.c_char_p
+
+_vp, _u32, _u64, _i32, _f32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_float
+
+
+def _check(rc):
+    if rc != 0:
+        raise UavmvsError(_lib.uavmvs_last_error().decode())
+
+
+def _f(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+def _u(a):
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+def _stream_ptr(stream):
+    """Accepts None, an int (cudaStream_t) or a torch.cuda.Stream."""
+    if stream is None:
+        return _vp(0)
+    if hasattr(stream, "cuda_stream"):
+        return _vp(stream.cuda_stream)
+    return _vp(int(stream))
+
+
+def set_device(device):
+    _check(_lib.uavmvs_set_device(_i32(device)))
+
+
+def device_count():
+    n = _i32(0)
+    _check(_lib.uavmvs_device_count(C.byref(n)))
+    return n.value
+
+
+def synchronize(stream=None):
+    _check(_lib.uavmvs_synchronize(_stream_ptr(stream)))
+
+
+def configure_heuristic(m_k=8.0, m_x0=4.0, t_k=32.0, t_x0=16.0):
+    """libs/eval/kernels.h:93"""
+    _check(_lib.uavmvs_configure_heuristic(_f32(m_k), _f32(m_x0), _f32(t_k), _f32(t_x0)))
+
+
+class _Handle:
+    _destroy = None
+
+    def __init__(self, ptr):
+        self.ptr = ptr
+
+    def free(self):
+        if getattr(self, "ptr", None):
+            getattr(_lib, self._destroy)(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class BVHTree(_Handle):
+    """cacc::BVHTree<DEVICE> (libs/cacc/bvh_tree.h)."""
+    _destroy = "uavmvs_bvh_destroy"
+
+    @classmethod
+    def create(cls, nodes, aabbs, tris, indices):
+        """From an acc-built tree in the layout convert<HOST> produces
+        (libs/cacc/bvh_tree.cu:17-48)."""
+        nodes, aabbs, tris, indices = _u(nodes).reshape(-1, 4), _f(aabbs, (-1, 6)), _f(tris, (-1, 9)), _u(indices)
+        h = _vp()
+        _check(_lib.uavmvs_bvh_create_from_arrays(_p(nodes), _p(aabbs), _p(tris), _p(indices),
+                                                  _u32(nodes.shape[0]), _u32(indices.shape[0]), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def build_lbvh(cls, verts, faces):
+        """GPU LBVH build from an indexed mesh."""
+        verts, faces = _f(verts, (-1, 3)), _u(faces).reshape(-1, 3)
+        h = _vp()
+        _check(_lib.uavmvs_bvh_build_lbvh(_p(verts), _u32(verts.shape[0]), _p(faces), _u32(faces.shape[0]),
+                                          C.byref(h)))
+        return cls(h)
+
+    def sizes(self):
+        n, t = _u32(0), _u32(0)
+        _check(_lib.uavmvs_bvh_sizes(self.ptr, C.byref(n), C.byref(t)))
+        return n.value, t.value
+
+    def export(self):
+        n, t = self.sizes()
+        nodes, aabbs = np.empty((n, 4), np.uint32), np.empty((n, 6), np.float32)
+        tris, indices = np.empty((t, 9), np.float32), np.empty(t, np.uint32)
+        _check(_lib.uavmvs_bvh_export(self.ptr, _p(nodes), _p(aabbs), _p(tris), _p(indices)))
+        return nodes, aabbs, tris, indices
+
+    def trace(self, rays, any_hit=True, stream=None):
+        """cacc::tracing::trace over a batch of host rays [n,8]."""
+        rays = _f(rays, (-1, 8))
+        n = rays.shape[0]
+        hit, face, t = np.zeros(n, np.uint8), np.zeros(n, np.uint32), np.zeros(n, np.float32)
+        _check(_lib.uavmvs_bvh_trace(_stream_ptr(stream), self.ptr, _p(rays), _u64(n), _i32(1 if any_hit else 0),
+                                     _p(hit), _p(face), _p(t)))
+        return hit, face, t
+
+
+class KDTree(_Handle):
+    """cacc::KDTree<3, DEVICE> (libs/cacc/kd_tree.h)."""
+    _destroy = "uavmvs_kdtree_destroy"
+
+    @classmethod
+    def create(cls, nodes, verts):
+        nodes, verts = _u(nodes).reshape(-1, 4), _f(verts, (-1, 3))
+        h = _vp()
+        _check(_lib.uavmvs_kdtree_create(_p(nodes), _p(verts), _u32(nodes.shape[0]), C.byref(h)))
+        obj = cls(h)
+        obj.num_verts = nodes.shape[0]
+        return obj
+
+
+class PointCloud(_Handle):
+    """cacc::PointCloud<DEVICE> (libs/cacc/point_cloud.h)."""
+    _destroy = "uavmvs_cloud_destroy"
+
+    @classmethod
+    def create(cls, vertices, normals, values=None, qualities=None):
+        vertices, normals = _f(vertices, (-1, 3)), _f(normals, (-1, 3))
+        n = vertices.shape[0]
+        values = None if values is None else _f(values)
+        qualities = None if qualities is None else _f(qualities)
+        h = _vp()
+        _check(_lib.uavmvs_cloud_create(_p(vertices), _p(normals), _p(values), _p(qualities), _u32(n), C.byref(h)))
+        obj = cls(h)
+        obj.num_vertices = n
+        return obj
+
+    def download_attributes(self):
+        values, qualities = np.empty(self.num_vertices, np.float32), np.empty(self.num_vertices, np.float32)
+        _check(_lib.uavmvs_cloud_download_attributes(self.ptr, _p(values), _p(qualities)))
+        return values, qualities
+
+    def upload_attributes(self, values=None, qualities=None):
+        values = None if values is None else _f(values)
+        qualities = None if qualities is None else _f(qualities)
+        _check(_lib.uavmvs_cloud_upload_attributes(self.ptr, _p(values), _p(qualities)))
+
+
+class VectorArray(_Handle):
+    """cacc::VectorArray<cacc::Vec3f, DEVICE> (libs/cacc/vector_array.h)."""
+    _destroy = "uavmvs_obs_destroy"
+
+    @classmethod
+    def create(cls, num_cols, max_rows=32):
+        h = _vp()
+        _check(_lib.uavmvs_obs_create(_u32(num_cols), _u32(max_rows), C.byref(h)))
+        obj = cls(h)
+        obj.num_cols, obj.max_rows = num_cols, max_rows
+        return obj
+
+    def null(self, stream=None):
+        _check(_lib.uavmvs_obs_clear(_stream_ptr(stream), self.ptr))
+
+    def download(self, data=True):
+        d = np.empty((self.max_rows, self.num_cols, 4), np.float32) if data else None
+        r = np.empty(self.num_cols, np.uint32)
+        _check(_lib.uavmvs_obs_download(self.ptr, _p(d), _p(r)))
+        return d, r
+
+    def upload(self, data=None, num_rows=None):
+        d = None if data is None else _f(data, (self.max_rows, self.num_cols, 4))
+        r = None if num_rows is None else _u(num_rows)
+        _check(_lib.uavmvs_obs_upload(self.ptr, _p(d), _p(r)))
+
+
+class Array(_Handle):
+    """cacc::Array<float, DEVICE> (libs/cacc/array.h)."""
+    _destroy = "uavmvs_array_destroy"
+
+    @classmethod
+    def create(cls, n):
+        h = _vp()
+        _check(_lib.uavmvs_array_create(_u32(n), C.byref(h)))
+        obj = cls(h)
+        obj.n = n
+        return obj
+
+    def null(self, stream=None):
+        _check(_lib.uavmvs_array_null(_stream_ptr(stream), self.ptr))
+
+    def download(self):
+        out = np.empty(self.n, np.float32)
+        _check(_lib.uavmvs_array_download(self.ptr, _p(out)))
+        return out
+
+    def upload(self, host):
+        host = _f(host)
+        assert host.shape[0] == self.n
+        _check(_lib.uavmvs_array_upload(self.ptr, _p(host)))
+
+
+class Image(_Handle):
+    """cacc::Image<float, DEVICE> (libs/cacc/image.h)."""
+    _destroy = "uavmvs_image_destroy"
+
+    @classmethod
+    def create(cls, width, height):
+        h = _vp()
+        _check(_lib.uavmvs_image_create(_u32(width), _u32(height), C.byref(h)))
+        obj = cls(h)
+        obj.width, obj.height = width, height
+        return obj
+
+    def download(self):
+        out = np.empty((self.height, self.width), np.float32)
+        _check(_lib.uavmvs_image_download(self.ptr, _p(out)))
+        return out
+
+
+# ------------------------------------------------------------------ kernels.h
+def update_observation_rays(populate, view_pos, max_distance, w2c, calib, width, height,
+                            bvh_tree, cloud, obs_rays, stream=None):
+    """libs/eval/kernels.h:26-35 (one view)."""
+    vp, W, K = _f(view_pos, 3), _f(w2c, 16), _f(calib, 9)
+    _check(_lib.uavmvs_update_observation_rays(_stream_ptr(stream), _i32(1 if populate else 0), _p(vp),
+                                               _f32(max_distance), _p(W), _p(K), _i32(width), _i32(height),
+                                               bvh_tree.ptr, cloud.ptr, obs_rays.ptr))
+
+
+def update_observation_rays_batch(populate, views, max_distance, width, height, bvh_tree, cloud, obs_rays,
+                                  stream=None):
+    """The launch loop of apps/evaluate_trajectory/evaluate_trajectory.cu:154-164 as one call;
+    views [V,28] = pos, w2c, calib (host)."""
+    views = _f(views, (-1, VIEW_FLOATS))
+    _check(_lib.uavmvs_update_observation_rays_batch(_stream_ptr(stream), _i32(1 if populate else 0), _p(views),
+                                                     _u32(views.shape[0]), _f32(max_distance), _i32(width),
+                                                     _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr))
+
+
+def process_observation_rays(obs_rays, stream=None):
+    """libs/eval/kernels.h:37-39"""
+    _check(_lib.uavmvs_process_observation_rays(_stream_ptr(stream), obs_rays.ptr))
+
+
+def evaluate_observation_rays(obs_rays, recons, stream=None):
+    """libs/eval/kernels.h:41-44"""
+    _check(_lib.uavmvs_evaluate_observation_rays(_stream_ptr(stream), obs_rays.ptr, recons.ptr))
+
+
+def calculate_func_recons(recons, target_recon, wrecons, stream=None):
+    """libs/eval/kernels.h:86-91"""
+    _check(_lib.uavmvs_calculate_func_recons(_stream_ptr(stream), recons.ptr, _f32(target_recon), wrecons.ptr))
+
+
+def reduce(array, stream=None):
+    """cacc::reduction::{sum,min,max} (libs/cacc/reduction.h:132-162) -> (sum, min, max)."""
+    out = (C.c_float * 3)()
+    _check(_lib.uavmvs_reduce(_stream_ptr(stream), array.ptr, out))
+    return float(out[0]), float(out[1]), float(out[2])
+
+
+class DeviceViews:
+    """A trajectory resident on the device ([V,28] floats) for repeated evaluation."""
+
+    def __init__(self, views):
+        import torch  # device memory plumbing only
+        self.num_views = int(np.asarray(views).reshape(-1, VIEW_FLOATS).shape[0])
+        self.tensor = torch.from_numpy(_f(views, (-1, VIEW_FLOATS)).copy()).cuda()
+
+    @property
+    def ptr(self):
+        return _vp(self.tensor.data_ptr())
+
+
+def evaluate_trajectory(views, max_distance, target_recon, width, height, bvh_tree, cloud, obs_rays,
+                        recons, wrecons, stream=None, want_stats=True):
+    """apps/evaluate_trajectory/evaluate_trajectory.cu:125-202 as one call.
+    `views` is a host array [V,28] (copied inside the call) or a DeviceViews.
+    Returns (sum_wrecon, min, max, stats[4])."""
+    out = (C.c_float * 3)()
+    stats = (C.c_uint64 * 4)() if want_stats else None
+    if isinstance(views, DeviceViews):
+        _check(_lib.uavmvs_evaluate_trajectory_device(
+            _stream_ptr(stream), views.ptr, _u32(views.num_views), _f32(max_distance), _f32(target_recon),
+            _i32(width), _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr, recons.ptr, wrecons.ptr, out, stats))
+    else:
+        views = _f(views, (-1, VIEW_FLOATS))
+        _check(_lib.uavmvs_evaluate_trajectory(
+            _stream_ptr(stream), _p(views), _u32(views.shape[0]), _f32(max_distance), _f32(target_recon),
+            _i32(width), _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr, recons.ptr, wrecons.ptr, out, stats))
+    st = [int(x) for x in stats] if want_stats else None
+    return float(out[0]), float(out[1]), float(out[2]), st
+
+
+def populate_spherical_histogram(view_pos, max_distance, bvh_tree, cloud, kd_tree, sphere_hist, stream=None,
+                                 target_recon=None, obs_rays=None, recons=None):
+    """Both overloads of libs/eval/kernels.h:46-67: the 9-argument form is selected by passing
+    target_recon, obs_rays and recons."""
+    vp = _f(view_pos, 3)
+    if obs_rays is None:
+        _check(_lib.uavmvs_populate_spherical_histogram(_stream_ptr(stream), _p(vp), _f32(max_distance),
+                                                        bvh_tree.ptr, cloud.ptr, kd_tree.ptr, sphere_hist.ptr))
+    else:
+        _check(_lib.uavmvs_populate_spherical_histogram_recon(
+            _stream_ptr(stream), _p(vp), _f32(max_distance), _f32(target_recon), bvh_tree.ptr, cloud.ptr,
+            kd_tree.ptr, obs_rays.ptr, recons.ptr, sphere_hist.ptr))
+
+
+def evaluate_spherical_histogram(calib, width, height, kd_tree, sphere_hist, hist, stream=None):
+    """libs/eval/kernels.h:69-79"""
+    K = _f(calib, 9)
+    _check(_lib.uavmvs_evaluate_spherical_histogram(_stream_ptr(stream), _p(K), _i32(width), _i32(height),
+                                                    kd_tree.ptr, sphere_hist.ptr, hist.ptr))
+
+
+def estimate_capture_difficulty(max_distance, bvh_tree, mesh_size, kd_tree, cloud, stream=None):
+    """libs/eval/kernels.h:81-84"""
+    _check(_lib.uavmvs_estimate_capture_difficulty(_stream_ptr(stream), _f32(max_distance), bvh_tree.ptr,
+                                                   _u32(mesh_size), kd_tree.ptr, cloud.ptr))

@@ -1,0 +1,374 @@
+// BVH handles: upload of an acc-built tree (reference topology and boxes, bit for bit),
+// GPU LBVH build, conversion into the 64-byte traversal layouts, export, batch trace.
+#include <cub/cub.cuh>
+
+#include "common.cuh"
+#include "trace.cuh"
+
+namespace uav {
+
+static thread_local std::string g_error;
+
+void set_error(const char * file, int line, const char * what, const char * detail) {
+    char buf[1024];
+    snprintf(buf, sizeof(buf), "%s:%d (%s): %s", file, line, what, detail ? detail : "");
+    g_error = buf;
+}
+
+// ------------------------------------------------------------------ conversion
+__global__ void k_flag_inner(const uint4 * __restrict__ nodes, uint32_t n, uint32_t * __restrict__ flag)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 nd = nodes[i];
+    flag[i] = (nd.z != UAV_NAI && nd.w != UAV_NAI) ? 1u : 0u;
+}
+
+__global__ void k_build_inner(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs,
+    const uint32_t * __restrict__ flag, const uint32_t * __restrict__ slot, uint32_t n,
+    Node64 * __restrict__ inner)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !flag[i]) return;
+    uint4 nd = nodes[i];
+    uint32_t l = nd.z, r = nd.w;
+    const float * bl = aabbs + 6 * (size_t)l;
+    const float * br = aabbs + 6 * (size_t)r;
+    Node64 o;
+    o.q0 = make_float4(bl[0], bl[1], bl[2], bl[3]);
+    o.q1 = make_float4(bl[4], bl[5], br[0], br[1]);
+    o.q2 = make_float4(br[2], br[3], br[4], br[5]);
+    uint4 ln = nodes[l], rn = nodes[r];
+    uint4 q3;
+    if (flag[l]) { q3.x = slot[l]; q3.z = 0u; } else { q3.x = ln.x; q3.z = ln.y - ln.x; }
+    if (flag[r]) { q3.y = slot[r]; q3.w = 0u; } else { q3.y = rn.x; q3.w = rn.y - rn.x; }
+    o.q3 = q3;
+    inner[slot[i]] = o;
+}
+
+// Per-triangle constants with the reference's operation order (libs/acc/primitives.h:
+// 217-225 normal, :139-145 Gram terms).  Degenerate triangles (|N| < eps, rejected at
+// :222) get a zero normal, which the |cosine| < eps test rejects.
+__global__ void k_build_tris(const float * __restrict__ tris, uint32_t n, Tri64 * __restrict__ out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float * t = tris + 9 * (size_t)i;
+    V3 a = mk(t[0], t[1], t[2]), b = mk(t[3], t[4], t[5]), c = mk(t[6], t[7], t[8]);
+    V3 ab = b - a, ac = c - a;
+    V3 nrm = cross(ab, ac);
+    float len = norm(nrm);
+    V3 un = (len < FLT_EPSILON) ? mk(0.0f, 0.0f, 0.0f) : nrm / len;
+    float d00 = dot(ab, ab), d01 = dot(ab, ac), d11 = dot(ac, ac);
+    float denom = d00 * d11 - d01 * d01;
+    Tri64 o;
+    o.q0 = make_float4(a.x, a.y, a.z, ab.x);
+    o.q1 = make_float4(ab.y, ab.z, ac.x, ac.y);
+    o.q2 = make_float4(ac.z, un.x, un.y, un.z);
+    o.q3 = make_float4(d00, d01, d11, denom);
+    out[i] = o;
+}
+
+static int finalize_layout(uavmvs_bvh * b)
+{
+    uint32_t n = b->num_nodes, t = b->num_tris;
+    uint32_t * flag = nullptr, * slot = nullptr;
+    UAV_CUDA(cudaMalloc(&flag, sizeof(uint32_t) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&slot, sizeof(uint32_t) * (size_t)n));
+    k_flag_inner<<<divup(n, 256), 256>>>(b->nodes, n, flag);
+    size_t tmp_bytes = 0; void * tmp = nullptr;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag, slot, (int)n);
+    UAV_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flag, slot, (int)n);
+    uint32_t last_flag = 0, last_slot = 0;
+    UAV_CUDA(cudaMemcpy(&last_flag, flag + (n - 1), 4, cudaMemcpyDeviceToHost));
+    UAV_CUDA(cudaMemcpy(&last_slot, slot + (n - 1), 4, cudaMemcpyDeviceToHost));
+    b->num_inner = last_flag + last_slot;
+    uint4 root;
+    UAV_CUDA(cudaMemcpy(&root, b->nodes, sizeof(uint4), cudaMemcpyDeviceToHost));
+    b->root_is_leaf = !(root.z != UAV_NAI && root.w != UAV_NAI);
+    b->root_first = root.x; b->root_count = root.y - root.x;
+    UAV_CUDA(cudaMalloc(&b->inner, sizeof(Node64) * (size_t)(b->num_inner ? b->num_inner : 1)));
+    UAV_CUDA(cudaMalloc(&b->ptris, sizeof(Tri64) * (size_t)t));
+    k_build_inner<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->inner);
+    k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaDeviceSynchronize());
+    cudaFree(tmp); cudaFree(flag); cudaFree(slot);
+    return 0;
+}
+
+static int alloc_reference_arrays(uavmvs_bvh * b)
+{
+    UAV_CUDA(cudaMalloc(&b->nodes, sizeof(uint4) * (size_t)b->num_nodes));
+    UAV_CUDA(cudaMalloc(&b->aabbs, sizeof(float) * 6 * (size_t)b->num_nodes));
+    UAV_CUDA(cudaMalloc(&b->tris, sizeof(float) * 9 * (size_t)b->num_tris));
+    UAV_CUDA(cudaMalloc(&b->indices, sizeof(uint32_t) * (size_t)b->num_tris));
+    return 0;
+}
+
+// ------------------------------------------------------------------ LBVH build
+__device__ __forceinline__ uint64_t spread21(uint64_t x)
+{
+    x &= 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void k_scene_bounds(const float * __restrict__ verts, uint32_t nv, float * __restrict__ bounds)
+{
+    // bounds: min xyz as ordered ints [0..2], max xyz [3..5]; tiny, atomics are fine
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    for (int k = 0; k < 3; ++k) {
+        float v = verts[3 * (size_t)i + k];
+        int iv = __float_as_int(v);
+        int ord = iv >= 0 ? iv : iv ^ 0x7fffffff;
+        atomicMin((int *)bounds + k, ord);
+        atomicMax((int *)bounds + 3 + k, ord);
+    }
+}
+
+__global__ void k_morton(const float * __restrict__ verts, const uint32_t * __restrict__ faces,
+    uint32_t nf, const float * __restrict__ bounds, uint64_t * __restrict__ keys, uint32_t * __restrict__ ids)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nf) return;
+    float lo[3], ext = 0.0f;
+    for (int k = 0; k < 3; ++k) {
+        int a = ((const int *)bounds)[k], b = ((const int *)bounds)[3 + k];
+        float mn = __int_as_float(a >= 0 ? a : a ^ 0x7fffffff);
+        float mx = __int_as_float(b >= 0 ? b : b ^ 0x7fffffff);
+        lo[k] = mn; ext = fmaxf(ext, mx - mn);
+    }
+    ext = fmaxf(ext, 1e-20f);
+    uint64_t code = 0;
+    for (int k = 0; k < 3; ++k) {
+        float c = 0.0f;
+        for (int j = 0; j < 3; ++j) c += verts[3 * (size_t)faces[3 * (size_t)i + j] + k];
+        c = (c / 3.0f - lo[k]) / ext;
+        c = fminf(fmaxf(c, 0.0f), 1.0f);
+        uint64_t q = (uint64_t)(c * 2097151.0f);
+        code |= spread21(q) << k;
+    }
+    keys[i] = code; ids[i] = i;
+}
+
+__device__ __forceinline__ int lcp(const uint64_t * __restrict__ keys, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a != b) return __clzll(a ^ b);
+    return 64 + __clz((uint32_t)i ^ (uint32_t)j);   // duplicate codes: fall back to the position
+}
+
+// Karras 2012: one thread per internal node.  Node ids: internal i -> i (root 0),
+// leaf j -> (n-1)+j.
+__global__ void k_radix_tree(const uint64_t * __restrict__ keys, int n, uint4 * __restrict__ nodes,
+    uint32_t * __restrict__ parent)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (lcp(keys, n, i, i + 1) - lcp(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = lcp(keys, n, i, i - d);
+    int lmax = 2;
+    while (lcp(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lcp(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = lcp(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) / 2; ; t = (t + 1) / 2) {
+        if (lcp(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t <= 1) break;
+    }
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    uint32_t left = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
+    uint32_t right = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
+    nodes[i] = make_uint4((uint32_t)lo, (uint32_t)hi + 1u, left, right);
+    parent[left] = (uint32_t)i;
+    parent[right] = (uint32_t)i;
+    if (i == 0) parent[0] = UAV_NAI;
+}
+
+__global__ void k_leaves_refit(const float * __restrict__ verts, const uint32_t * __restrict__ faces,
+    const uint32_t * __restrict__ ids, int n, uint4 * __restrict__ nodes, float * __restrict__ aabbs,
+    float * __restrict__ tris, uint32_t * __restrict__ indices, const uint32_t * __restrict__ parent,
+    uint32_t * __restrict__ visits)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    uint32_t f = ids[j];
+    float t[9];
+    for (int k = 0; k < 3; ++k)
+        for (int c = 0; c < 3; ++c) t[3 * k + c] = verts[3 * (size_t)faces[3 * (size_t)f + k] + c];
+    for (int c = 0; c < 9; ++c) tris[9 * (size_t)j + c] = t[c];
+    indices[j] = f;
+    uint32_t me = (uint32_t)(n - 1 + j);
+    nodes[me] = make_uint4((uint32_t)j, (uint32_t)j + 1u, UAV_NAI, UAV_NAI);
+    float * bb = aabbs + 6 * (size_t)me;
+    for (int c = 0; c < 3; ++c) {   // libs/acc/primitives.h:74-81
+        bb[c] = fminf(t[c], fminf(t[3 + c], t[6 + c]));
+        bb[3 + c] = fmaxf(t[c], fmaxf(t[3 + c], t[6 + c]));
+    }
+    __threadfence();
+    uint32_t p = (n > 1) ? parent[me] : UAV_NAI;
+    while (p != UAV_NAI) {
+        if (atomicAdd(visits + p, 1u) == 0u) return;   // first child to arrive stops
+        __threadfence();
+        uint4 nd = nodes[p];
+        volatile const float * l = aabbs + 6 * (size_t)nd.z;
+        volatile const float * r = aabbs + 6 * (size_t)nd.w;
+        float * o = aabbs + 6 * (size_t)p;
+        for (int c = 0; c < 3; ++c) { o[c] = fminf(l[c], r[c]); o[3 + c] = fmaxf(l[3 + c], r[3 + c]); }
+        __threadfence();
+        p = parent[p];
+    }
+}
+
+// ------------------------------------------------------------------ batch trace
+__global__ void k_trace(BvhView bvh, const float * __restrict__ rays, uint64_t n, int any_hit,
+    uint8_t * __restrict__ hit, uint32_t * __restrict__ face, float * __restrict__ t)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float * r = rays + 8 * i;
+    Ray ray;
+    ray.o = mk(r[0], r[1], r[2]); ray.d = mk(r[3], r[4], r[5]); ray.tmin = r[6]; ray.tmax = r[7];
+    if (any_hit) {
+        bool h = trace_any(bvh, ray);
+        hit[i] = h ? 1 : 0;
+        if (face) face[i] = UAV_NAI;
+        if (t) t[i] = 0.0f;
+    } else {
+        uint32_t f; float tt;
+        bool h = trace_closest(bvh, ray, f, tt);
+        hit[i] = h ? 1 : 0;
+        if (face) face[i] = h ? f : UAV_NAI;
+        if (t) t[i] = h ? tt : 0.0f;
+    }
+}
+
+}  // namespace uav
+
+using namespace uav;
+
+extern "C" {
+
+const char * uavmvs_last_error(void) { return g_error.c_str(); }
+
+int uavmvs_set_device(int device) { UAV_CUDA(cudaSetDevice(device)); return 0; }
+int uavmvs_device_count(int * count) { UAV_CUDA(cudaGetDeviceCount(count)); return 0; }
+int uavmvs_synchronize(void * stream) { UAV_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); return 0; }
+
+int uavmvs_bvh_create_from_arrays(const uint32_t * nodes, const float * aabbs, const float * tris,
+    const uint32_t * indices, uint32_t num_nodes, uint32_t num_tris, uavmvs_bvh ** out)
+{
+    UAV_REQUIRE(nodes && aabbs && tris && indices && out, "null argument");
+    UAV_REQUIRE(num_nodes >= 1 && num_tris >= 1, "empty tree");
+    uavmvs_bvh * b = new uavmvs_bvh();
+    b->num_nodes = num_nodes; b->num_tris = num_tris;
+    if (alloc_reference_arrays(b)) return 1;
+    UAV_CUDA(cudaMemcpy(b->nodes, nodes, sizeof(uint4) * (size_t)num_nodes, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->aabbs, aabbs, sizeof(float) * 6 * (size_t)num_nodes, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->tris, tris, sizeof(float) * 9 * (size_t)num_tris, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->indices, indices, sizeof(uint32_t) * (size_t)num_tris, cudaMemcpyHostToDevice));
+    if (finalize_layout(b)) return 1;
+    *out = b;
+    return 0;
+}
+
+int uavmvs_bvh_build_lbvh(const float * verts, uint32_t num_verts, const uint32_t * faces,
+    uint32_t num_faces, uavmvs_bvh ** out)
+{
+    UAV_REQUIRE(verts && faces && out, "null argument");
+    UAV_REQUIRE(num_faces >= 1 && num_verts >= 1, "empty mesh");
+    int n = (int)num_faces;
+    uavmvs_bvh * b = new uavmvs_bvh();
+    b->num_nodes = 2 * num_faces - 1; b->num_tris = num_faces;
+    if (alloc_reference_arrays(b)) return 1;
+    float * d_verts; uint32_t * d_faces, * ids, * ids2, * parent, * visits; uint64_t * keys, * keys2; float * bounds;
+    UAV_CUDA(cudaMalloc(&d_verts, sizeof(float) * 3 * (size_t)num_verts));
+    UAV_CUDA(cudaMalloc(&d_faces, sizeof(uint32_t) * 3 * (size_t)num_faces));
+    UAV_CUDA(cudaMalloc(&ids, 4 * (size_t)n)); UAV_CUDA(cudaMalloc(&ids2, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&keys, 8 * (size_t)n)); UAV_CUDA(cudaMalloc(&keys2, 8 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&parent, 4 * (size_t)b->num_nodes));
+    UAV_CUDA(cudaMalloc(&visits, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&bounds, 6 * sizeof(float)));
+    UAV_CUDA(cudaMemcpy(d_verts, verts, sizeof(float) * 3 * (size_t)num_verts, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(d_faces, faces, sizeof(uint32_t) * 3 * (size_t)num_faces, cudaMemcpyHostToDevice));
+    int init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    UAV_CUDA(cudaMemcpy(bounds, init, sizeof(init), cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemset(visits, 0, 4 * (size_t)n));
+    k_scene_bounds<<<divup(num_verts, 256), 256>>>(d_verts, num_verts, bounds);
+    k_morton<<<divup(n, 256), 256>>>(d_verts, d_faces, num_faces, bounds, keys, ids);
+    size_t tmp_bytes = 0; void * tmp = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, ids, ids2, n, 0, 63);
+    UAV_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, ids, ids2, n, 0, 63);
+    if (n > 1) k_radix_tree<<<divup(n - 1, 256), 256>>>(keys2, n, b->nodes, parent);
+    k_leaves_refit<<<divup(n, 256), 256>>>(d_verts, d_faces, ids2, n, b->nodes, b->aabbs, b->tris,
+        b->indices, parent, visits);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaDeviceSynchronize());
+    cudaFree(tmp); cudaFree(d_verts); cudaFree(d_faces); cudaFree(ids); cudaFree(ids2);
+    cudaFree(keys); cudaFree(keys2); cudaFree(parent); cudaFree(visits); cudaFree(bounds);
+    if (finalize_layout(b)) return 1;
+    *out = b;
+    return 0;
+}
+
+int uavmvs_bvh_sizes(const uavmvs_bvh * b, uint32_t * num_nodes, uint32_t * num_tris)
+{
+    UAV_REQUIRE(b, "null bvh");
+    if (num_nodes) *num_nodes = b->num_nodes;
+    if (num_tris) *num_tris = b->num_tris;
+    return 0;
+}
+
+int uavmvs_bvh_export(const uavmvs_bvh * b, uint32_t * nodes, float * aabbs, float * tris, uint32_t * indices)
+{
+    UAV_REQUIRE(b, "null bvh");
+    if (nodes) UAV_CUDA(cudaMemcpy(nodes, b->nodes, sizeof(uint4) * (size_t)b->num_nodes, cudaMemcpyDeviceToHost));
+    if (aabbs) UAV_CUDA(cudaMemcpy(aabbs, b->aabbs, sizeof(float) * 6 * (size_t)b->num_nodes, cudaMemcpyDeviceToHost));
+    if (tris) UAV_CUDA(cudaMemcpy(tris, b->tris, sizeof(float) * 9 * (size_t)b->num_tris, cudaMemcpyDeviceToHost));
+    if (indices) UAV_CUDA(cudaMemcpy(indices, b->indices, sizeof(uint32_t) * (size_t)b->num_tris, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int uavmvs_bvh_destroy(uavmvs_bvh * b)
+{
+    if (!b) return 0;
+    cudaFree(b->nodes); cudaFree(b->aabbs); cudaFree(b->tris); cudaFree(b->indices);
+    cudaFree(b->inner); cudaFree(b->ptris);
+    delete b;
+    return 0;
+}
+
+int uavmvs_bvh_trace(void * stream, const uavmvs_bvh * b, const float * rays, uint64_t n,
+    int any_hit, uint8_t * hit, uint32_t * face, float * t)
+{
+    UAV_REQUIRE(b && rays && hit, "null argument");
+    if (n == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    float * d_rays, * d_t; uint8_t * d_hit; uint32_t * d_face;
+    UAV_CUDA(cudaMalloc(&d_rays, 32 * n)); UAV_CUDA(cudaMalloc(&d_t, 4 * n));
+    UAV_CUDA(cudaMalloc(&d_hit, n)); UAV_CUDA(cudaMalloc(&d_face, 4 * n));
+    UAV_CUDA(cudaMemcpyAsync(d_rays, rays, 32 * n, cudaMemcpyHostToDevice, s));
+    k_trace<<<divup(n, 128), 128, 0, s>>>(view_of(b), d_rays, n, any_hit, d_hit, d_face, d_t);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaMemcpyAsync(hit, d_hit, n, cudaMemcpyDeviceToHost, s));
+    if (face) UAV_CUDA(cudaMemcpyAsync(face, d_face, 4 * n, cudaMemcpyDeviceToHost, s));
+    if (t) UAV_CUDA(cudaMemcpyAsync(t, d_t, 4 * n, cudaMemcpyDeviceToHost, s));
+    UAV_CUDA(cudaStreamSynchronize(s));
+    cudaFree(d_rays); cudaFree(d_t); cudaFree(d_hit); cudaFree(d_face);
+    return 0;
+}
+
+}  // extern "C"

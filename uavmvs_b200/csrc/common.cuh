@@ -1,0 +1,126 @@
+// Shared types of libuavmvs_b200: opaque handle layouts, error plumbing and the
+// fp32 helpers that fix the operation order of the reference.
+// Compiled with --fmad=false, IEEE div/sqrt, no FTZ: every expression below is
+// evaluated exactly as written.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <cfloat>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/uavmvs_b200.h"
+
+#define UAV_NAI 0xffffffffu
+#define UAV_INF __int_as_float(0x7f800000)
+
+namespace uav {
+
+void set_error(const char * file, int line, const char * what, const char * detail);
+int fail(const char * file, int line, const char * what);
+
+#define UAV_CUDA(call)                                                              \
+    do {                                                                            \
+        cudaError_t e_ = (call);                                                    \
+        if (e_ != cudaSuccess) {                                                    \
+            uav::set_error(__FILE__, __LINE__, #call, cudaGetErrorString(e_));      \
+            return 1;                                                               \
+        }                                                                           \
+    } while (0)
+#define UAV_REQUIRE(cond, msg)                                                      \
+    do { if (!(cond)) { uav::set_error(__FILE__, __LINE__, #cond, msg); return 2; } } while (0)
+
+static inline unsigned divup(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+// ---------------------------------------------------------------- device layouts
+// Two-child node, 64 B, one aligned 4 x LDG.128: both child boxes (exact floats, the
+// reference's boxes bit for bit) and both child references.
+//   q0 = lmin.xyz, lmax.x   q1 = lmax.yz, rmin.xy   q2 = rmin.z, rmax.xyz
+//   q3 = {left_ref, right_ref, left_count, right_count}
+// count == 0: ref = index of an inner node;  count > 0: ref = first triangle of a leaf.
+struct __align__(64) Node64 { float4 q0, q1, q2; uint4 q3; };
+// Pre-reduced triangle, 64 B: a, ab, ac, unit normal (N/|N|), d00, d01, d11, denom.
+// All derived values are computed with the reference's operation order, so using them
+// gives bit-identical operands (libs/acc/primitives.h:214-248, :134-153).
+struct __align__(64) Tri64 { float4 q0, q1, q2, q3; };
+
+}  // namespace uav
+
+struct uavmvs_bvh {
+    uint32_t num_nodes, num_tris, num_inner;
+    // reference layout (kept for export and for the oracle)
+    uint4 * nodes;      // {first,last,left,right}
+    float * aabbs;      // 6 per node
+    float * tris;       // 9 per triangle, leaf order
+    uint32_t * indices; // face ids
+    // traversal layout
+    uav::Node64 * inner;
+    uav::Tri64 * ptris;
+    uint32_t root_is_leaf, root_first, root_count;
+};
+
+struct uavmvs_kdtree {
+    uint32_t num_nodes;
+    uint4 * nodes;   // {vid, dim, left, right}
+    float4 * verts;  // xyz
+};
+
+struct uavmvs_cloud {
+    uint32_t n;
+    float4 * vertices, * normals;
+    float * values, * qualities;
+    // per 32-point block: bounding sphere (xyz, r) for the conservative view cull
+    float4 * block_sphere;
+    uint32_t num_blocks;
+};
+
+struct uavmvs_obs {
+    uint32_t num_cols, max_rows;
+    uint64_t pitch;          // bytes
+    float4 * data;
+    uint32_t * num_rows;
+};
+
+struct uavmvs_array { uint32_t n; float * data; };
+struct uavmvs_image { uint32_t width, height; uint64_t pitch; float * data; };
+
+namespace uav {
+
+// ---------------------------------------------------------------- fp32 helpers
+struct V3 { float x, y, z; };
+
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+// libs/cacc/vector.h:189-198: accumulate from zero, left to right
+__device__ __forceinline__ float dot(V3 a, V3 b) {
+    float r = 0.0f;
+    r = r + a.x * b.x;
+    r = r + a.y * b.y;
+    r = r + a.z * b.z;
+    return r;
+}
+// same value up to the sign of a zero result; used where only comparisons consume it
+__device__ __forceinline__ float dot_nz(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ float norm(V3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ V3 normalized(V3 a) { return a / norm(a); }
+// std::min/std::max NaN semantics (libs/acc/primitives.h:127-128)
+__device__ __forceinline__ float smin(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float smax(float a, float b) { return (a < b) ? b : a; }
+__device__ __forceinline__ V3 ld3(float4 v) { return mk(v.x, v.y, v.z); }
+
+struct Ray { V3 o, d; float tmin, tmax; };
+
+// heuristic constants (configure_heuristic, libs/eval/kernels.cu:93-103); host-side global,
+// passed to kernels by value
+struct Heur { float m_k, m_x0, t_k, t_x0; };
+Heur current_heur();
+
+}  // namespace uav

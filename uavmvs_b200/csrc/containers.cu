@@ -1,0 +1,248 @@
+// Device containers behind the C ABI: point cloud, observation-ray array, float array,
+// image, KD-tree.  They mirror the memory layouts of the reference's cacc containers
+// (libs/cacc/point_cloud.h:26-32, vector_array.h:23-50, array.h, image.h, kd_tree.h).
+#include "common.cuh"
+
+namespace uav {
+
+// Bounding sphere of every 32-point block (centre = box centre, radius padded so that the
+// block-level range cull in eval.cu is conservative w.r.t. fp32 rounding).
+__global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, float4 * __restrict__ out)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t id = blk * 32 + lane;
+    if (blk * 32 >= n) return;
+    bool valid = id < n;
+    float4 v = verts[valid ? id : n - 1];
+    float mn[3] = {v.x, v.y, v.z}, mx[3] = {v.x, v.y, v.z};
+    for (int k = 0; k < 3; ++k)
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    float cx = 0.5f * (mn[0] + mx[0]), cy = 0.5f * (mn[1] + mx[1]), cz = 0.5f * (mn[2] + mx[2]);
+    float dx = v.x - cx, dy = v.y - cy, dz = v.z - cz;
+    float r = sqrtf(dx * dx + dy * dy + dz * dz);
+    for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+    if (lane == 0) out[blk] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
+}
+
+__global__ void k_pad3(const float * __restrict__ in, uint32_t n, float4 * __restrict__ out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = make_float4(in[3 * (size_t)i], in[3 * (size_t)i + 1], in[3 * (size_t)i + 2], 0.0f);
+}
+
+__global__ void k_fill(float * __restrict__ p, uint32_t n, float v)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+static int upload3(const float * host, uint32_t n, float4 * dst)
+{
+    float * tmp;
+    UAV_CUDA(cudaMalloc(&tmp, sizeof(float) * 3 * (size_t)n));
+    UAV_CUDA(cudaMemcpy(tmp, host, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice));
+    k_pad3<<<divup(n, 256), 256>>>(tmp, n, dst);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaDeviceSynchronize());
+    cudaFree(tmp);
+    return 0;
+}
+
+}  // namespace uav
+
+using namespace uav;
+
+extern "C" {
+
+int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n, uavmvs_kdtree ** out)
+{
+    UAV_REQUIRE(nodes && verts && out && n >= 1, "bad argument");
+    uavmvs_kdtree * k = new uavmvs_kdtree();
+    k->num_nodes = n;
+    UAV_CUDA(cudaMalloc(&k->nodes, sizeof(uint4) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&k->verts, sizeof(float4) * (size_t)n));
+    UAV_CUDA(cudaMemcpy(k->nodes, nodes, sizeof(uint4) * (size_t)n, cudaMemcpyHostToDevice));
+    if (upload3(verts, n, k->verts)) return 1;
+    *out = k;
+    return 0;
+}
+
+int uavmvs_kdtree_destroy(uavmvs_kdtree * k)
+{
+    if (!k) return 0;
+    cudaFree(k->nodes); cudaFree(k->verts);
+    delete k;
+    return 0;
+}
+
+int uavmvs_cloud_create(const float * vertices, const float * normals, const float * values,
+    const float * qualities, uint32_t n, uavmvs_cloud ** out)
+{
+    UAV_REQUIRE(vertices && normals && out, "null argument");
+    UAV_REQUIRE(n >= 1, "empty cloud");
+    uavmvs_cloud * c = new uavmvs_cloud();
+    c->n = n; c->num_blocks = divup(n, 32);
+    UAV_CUDA(cudaMalloc(&c->vertices, sizeof(float4) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&c->normals, sizeof(float4) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&c->values, sizeof(float) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&c->qualities, sizeof(float) * (size_t)n));
+    UAV_CUDA(cudaMalloc(&c->block_sphere, sizeof(float4) * (size_t)c->num_blocks));
+    if (upload3(vertices, n, c->vertices)) return 1;
+    if (upload3(normals, n, c->normals)) return 1;
+    if (values) UAV_CUDA(cudaMemcpy(c->values, values, 4 * (size_t)n, cudaMemcpyHostToDevice));
+    else k_fill<<<divup(n, 256), 256>>>(c->values, n, 0.0f);        /* libs/util/cio.h:45 */
+    if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)n, cudaMemcpyHostToDevice));
+    else k_fill<<<divup(n, 256), 256>>>(c->qualities, n, 1.0f);     /* libs/util/cio.h:46 */
+    k_block_spheres<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaDeviceSynchronize());
+    *out = c;
+    return 0;
+}
+
+int uavmvs_cloud_download_attributes(const uavmvs_cloud * c, float * values, float * qualities)
+{
+    UAV_REQUIRE(c, "null cloud");
+    if (values) UAV_CUDA(cudaMemcpy(values, c->values, 4 * (size_t)c->n, cudaMemcpyDeviceToHost));
+    if (qualities) UAV_CUDA(cudaMemcpy(qualities, c->qualities, 4 * (size_t)c->n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int uavmvs_cloud_upload_attributes(uavmvs_cloud * c, const float * values, const float * qualities)
+{
+    UAV_REQUIRE(c, "null cloud");
+    if (values) UAV_CUDA(cudaMemcpy(c->values, values, 4 * (size_t)c->n, cudaMemcpyHostToDevice));
+    if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)c->n, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int uavmvs_cloud_size(const uavmvs_cloud * c, uint32_t * n) { UAV_REQUIRE(c && n, "null"); *n = c->n; return 0; }
+
+int uavmvs_cloud_destroy(uavmvs_cloud * c)
+{
+    if (!c) return 0;
+    cudaFree(c->vertices); cudaFree(c->normals); cudaFree(c->values); cudaFree(c->qualities);
+    cudaFree(c->block_sphere);
+    delete c;
+    return 0;
+}
+
+int uavmvs_obs_create(uint32_t num_cols, uint32_t max_rows, uavmvs_obs ** out)
+{
+    UAV_REQUIRE(out && num_cols >= 1 && max_rows >= 1 && max_rows <= 32, "bad argument (max_rows must be 1..32)");
+    uavmvs_obs * o = new uavmvs_obs();
+    o->num_cols = num_cols; o->max_rows = max_rows;
+    o->pitch = (((uint64_t)num_cols * 16 + 511) / 512) * 512;   /* cudaMallocPitch-like row alignment */
+    UAV_CUDA(cudaMalloc(&o->data, o->pitch * max_rows));
+    UAV_CUDA(cudaMalloc(&o->num_rows, 4 * (size_t)num_cols));
+    UAV_CUDA(cudaMemset(o->data, 0, o->pitch * max_rows));
+    UAV_CUDA(cudaMemset(o->num_rows, 0, 4 * (size_t)num_cols));
+    *out = o;
+    return 0;
+}
+
+int uavmvs_obs_clear(void * stream, uavmvs_obs * o)
+{
+    UAV_REQUIRE(o, "null obs");
+    UAV_CUDA(cudaMemsetAsync(o->data, 0, o->pitch * o->max_rows, (cudaStream_t)stream));
+    UAV_CUDA(cudaMemsetAsync(o->num_rows, 0, 4 * (size_t)o->num_cols, (cudaStream_t)stream));
+    return 0;
+}
+
+int uavmvs_obs_download(const uavmvs_obs * o, float * data, uint32_t * num_rows)
+{
+    UAV_REQUIRE(o, "null obs");
+    if (data) UAV_CUDA(cudaMemcpy2D(data, (size_t)o->num_cols * 16, o->data, o->pitch,
+        (size_t)o->num_cols * 16, o->max_rows, cudaMemcpyDeviceToHost));
+    if (num_rows) UAV_CUDA(cudaMemcpy(num_rows, o->num_rows, 4 * (size_t)o->num_cols, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int uavmvs_obs_upload(uavmvs_obs * o, const float * data, const uint32_t * num_rows)
+{
+    UAV_REQUIRE(o, "null obs");
+    if (data) UAV_CUDA(cudaMemcpy2D(o->data, o->pitch, data, (size_t)o->num_cols * 16,
+        (size_t)o->num_cols * 16, o->max_rows, cudaMemcpyHostToDevice));
+    if (num_rows) UAV_CUDA(cudaMemcpy(o->num_rows, num_rows, 4 * (size_t)o->num_cols, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int uavmvs_obs_device_ptr(const uavmvs_obs * o, int which, void ** ptr, uint64_t * pitch_bytes)
+{
+    UAV_REQUIRE(o && ptr, "null argument");
+    if (which == 0) { *ptr = o->data; if (pitch_bytes) *pitch_bytes = o->pitch; }
+    else if (which == 1) { *ptr = o->num_rows; if (pitch_bytes) *pitch_bytes = 0; }
+    else UAV_REQUIRE(false, "which must be 0 or 1");
+    return 0;
+}
+
+int uavmvs_obs_destroy(uavmvs_obs * o)
+{
+    if (!o) return 0;
+    cudaFree(o->data); cudaFree(o->num_rows);
+    delete o;
+    return 0;
+}
+
+int uavmvs_array_create(uint32_t n, uavmvs_array ** out)
+{
+    UAV_REQUIRE(out && n >= 1, "bad argument");
+    uavmvs_array * a = new uavmvs_array();
+    a->n = n;
+    UAV_CUDA(cudaMalloc(&a->data, 4 * (size_t)n));
+    UAV_CUDA(cudaMemset(a->data, 0, 4 * (size_t)n));
+    *out = a;
+    return 0;
+}
+
+int uavmvs_array_null(void * stream, uavmvs_array * a)
+{
+    UAV_REQUIRE(a, "null array");
+    UAV_CUDA(cudaMemsetAsync(a->data, 0, 4 * (size_t)a->n, (cudaStream_t)stream));
+    return 0;
+}
+
+int uavmvs_array_download(const uavmvs_array * a, float * host)
+{
+    UAV_REQUIRE(a && host, "null argument");
+    UAV_CUDA(cudaMemcpy(host, a->data, 4 * (size_t)a->n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int uavmvs_array_upload(uavmvs_array * a, const float * host)
+{
+    UAV_REQUIRE(a && host, "null argument");
+    UAV_CUDA(cudaMemcpy(a->data, host, 4 * (size_t)a->n, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int uavmvs_array_destroy(uavmvs_array * a) { if (a) { cudaFree(a->data); delete a; } return 0; }
+
+int uavmvs_image_create(uint32_t width, uint32_t height, uavmvs_image ** out)
+{
+    UAV_REQUIRE(out && width >= 1 && height >= 1, "bad argument");
+    uavmvs_image * im = new uavmvs_image();
+    im->width = width; im->height = height;
+    im->pitch = (((uint64_t)width * 4 + 511) / 512) * 512;
+    UAV_CUDA(cudaMalloc(&im->data, im->pitch * height));
+    UAV_CUDA(cudaMemset(im->data, 0, im->pitch * height));
+    *out = im;
+    return 0;
+}
+
+int uavmvs_image_download(const uavmvs_image * im, float * host)
+{
+    UAV_REQUIRE(im && host, "null argument");
+    UAV_CUDA(cudaMemcpy2D(host, (size_t)im->width * 4, im->data, im->pitch, (size_t)im->width * 4,
+        im->height, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int uavmvs_image_destroy(uavmvs_image * im) { if (im) { cudaFree(im->data); delete im; } return 0; }
+
+}  // extern "C"

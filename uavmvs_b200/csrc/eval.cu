@@ -1,0 +1,513 @@
+// Observation-ray path: K1 update_observation_rays (single view and batched over a
+// trajectory), K2 process, K3 evaluate, K8 func, K9 reduction, and the fused
+// evaluate_trajectory entry point.  Reference: libs/eval/kernels.cu:21-291, :496-510.
+#include "common.cuh"
+#include "trace.cuh"
+
+namespace uav {
+
+static Heur g_heur = {8.0f, 4.0f, 32.0f, 16.0f};   // m_k, m_x0, t_k, t_x0 (kernels.cu:93-96)
+Heur current_heur() { return g_heur; }
+constexpr float kPi = 3.14159265f;                            // kernels.cu:78
+
+// ---- helpers restating kernels.cu:21-40, :63-91, :111-136 --------------------------
+__device__ __forceinline__ V3 orthogonal(V3 v) {
+    V3 n0 = mk(1.0f, 0.0f, 0.0f), n1 = mk(0.0f, 1.0f, 0.0f);
+    if (fabsf(dot(n0, v)) < fabsf(dot(n1, v))) return cross(n0, v);
+    return cross(n1, v);
+}
+__device__ __forceinline__ V3 relative_direction(V3 v2cn, V3 n) {
+    V3 rx = normalized(orthogonal(n));
+    V3 ry = normalized(cross(n, rx));
+    V3 rel = mk(dot(rx, v2cn), dot(ry, v2cn), dot(n, v2cn));
+    return normalized(rel);
+}
+// view: pos[3] w2c[16] calib[9]; returns true if the point projects inside the image
+__device__ __forceinline__ bool in_image(const float * __restrict__ view, V3 v, int width, int height) {
+    const float * W = view + 3; const float * K = view + 19;
+    float q[3];
+    #pragma unroll
+    for (int i = 0; i < 3; ++i) {           // mult(w2c, v, 1.0f), libs/cacc/matrix.h:112-126
+        float s = 0.0f;
+        s += W[4 * i + 0] * v.x; s += W[4 * i + 1] * v.y; s += W[4 * i + 2] * v.z;
+        q[i] = s + W[4 * i + 3] * 1.0f;
+    }
+    float p[3];
+    #pragma unroll
+    for (int i = 0; i < 3; ++i) {           // calib * q, libs/cacc/matrix.h:69-82
+        float s = 0.0f;
+        s += K[3 * i + 0] * q[0]; s += K[3 * i + 1] * q[1]; s += K[3 * i + 2] * q[2];
+        p[i] = s;
+    }
+    float x = p[0] / p[2] - 0.5f, y = p[1] / p[2] - 0.5f;   // project(), kernels.cu:21-27
+    return !(x < 0.0f || (float)width <= x || y < 0.0f || (float)height <= y);
+}
+__device__ __forceinline__ float logistic(float x, float k, float x0) {
+    return 1.0f / (1.0f + expf(-k * (x - x0)));
+}
+__device__ __forceinline__ float func(float recon, float target) {
+    float a = fabsf(fminf(recon - target, 0.0f));
+    return a * a;
+}
+__device__ __forceinline__ float pair_term(float4 a, float4 b, float mk_, float mx0, float tk, float tx0) {
+    float calpha = dot(mk(b.x, b.y, b.z), mk(a.x, a.y, a.z));
+    float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+    float scale = fminf(a.w, b.w);
+    float ctheta = fminf(a.z, b.z);
+    float matchability = (1.0f - logistic(alpha, mk_, mx0)) * ctheta;
+    float triangulation = logistic(alpha, tk, tx0) * scale;
+    return matchability * triangulation;
+}
+
+// ---- K1 ----------------------------------------------------------------------------
+struct K1Args {
+    BvhView bvh;
+    const float4 * __restrict__ verts; const float4 * __restrict__ normals;
+    const float4 * __restrict__ spheres;
+    uint32_t n;
+    const float * __restrict__ views; uint32_t num_views;
+    float max_distance; int width, height;
+    float4 * obs; uint32_t * num_rows; uint32_t max_rows; uint32_t stride;   // stride in float4
+    unsigned long long * stats;   // [rays, visible, pairs, pairs after block cull] or null
+};
+
+constexpr int K1_WARPS = 4;
+constexpr int K1_QUEUE = 64;
+
+// One warp owns 32 consecutive (Z-ordered) points and walks the trajectory in view order.
+// Pairs that survive the exact cull are appended to a per-warp FIFO of (lane, view); every
+// time it holds 32 entries the warp traces them with all lanes busy.  FIFO order keeps
+// each point's observations in view order, which is the row order the reference gets
+// from launching one kernel per view on one stream (kernels.cu:175-181).
+template <bool POPULATE>
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_update_observation_rays(K1Args a)
+{
+    __shared__ float4 s_v[K1_WARPS][32];
+    __shared__ float4 s_n[K1_WARPS][32];
+    __shared__ uint32_t s_cnt[K1_WARPS][32];
+    __shared__ uint2 s_q[K1_WARPS][K1_QUEUE];
+
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk * 32 >= a.n) return;
+    const uint32_t id = blk * 32 + lane;
+    const bool valid = id < a.n;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+    float4 v4 = a.verts[valid ? id : a.n - 1], n4 = a.normals[valid ? id : a.n - 1];
+    s_v[w][lane] = v4; s_n[w][lane] = n4;
+    s_cnt[w][lane] = valid ? a.num_rows[id] : 0u;
+    const V3 v = ld3(v4), nrm = ld3(n4);
+    const float4 sph = a.spheres[blk];
+    __syncwarp();
+
+    uint32_t head = 0, qn = 0;
+    unsigned long long st_rays = 0, st_vis = 0, st_pairs = 0;
+
+    auto process = [&](uint32_t count) {
+        bool active = lane < count;
+        uint2 e = s_q[w][(head + lane) & (K1_QUEUE - 1)];
+        uint32_t pt = active ? e.x : lane, k = active ? e.y : 0u;
+        bool vis = false;
+        V3 pv = ld3(s_v[w][pt]), pn = ld3(s_n[w][pt]);
+        const float * view = a.views + UAVMVS_VIEW_FLOATS * (size_t)k;
+        V3 v2c = mk(view[0], view[1], view[2]) - pv;
+        float l = norm(v2c);
+        V3 v2cn = v2c / l;
+        if (active) {
+            Ray ray; ray.o = pv; ray.d = v2cn; ray.tmin = l * 0.001f; ray.tmax = l;   // kernels.cu:54-58
+            vis = !trace_any(a.bvh, ray);
+        }
+        uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
+        uint32_t peers = __match_any_sync(0xffffffffu, pt) & vis_mask;
+        if (lane == 0) { st_rays += count; st_vis += __popc(vis_mask); }
+        uint32_t row_pt = id - lane + pt;
+        V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
+        if (vis) { rel = relative_direction(v2cn, pn); scale = 1.0f - (l / a.max_distance); }
+        if (POPULATE) {
+            if (vis) {
+                uint32_t row = s_cnt[w][pt] + __popc(peers & lt_mask);
+                if (row < a.max_rows)
+                    a.obs[(size_t)row * a.stride + row_pt] = make_float4(rel.x, rel.y, rel.z, scale);
+            }
+            __syncwarp();
+            if (vis && (peers >> lane) == 1u) s_cnt[w][pt] += __popc(peers);   // highest peer updates
+        } else {
+            // kernels.cu:183-200: mark the first stored ray equal within 1e-5; same-point entries
+            // of one batch are applied in view order.
+            uint32_t rank = __popc(peers & lt_mask);
+            uint32_t max_rank = 0;
+            for (uint32_t m = vis_mask; m; m &= m - 1) {
+                uint32_t r = __shfl_sync(0xffffffffu, rank, __ffs(m) - 1);
+                max_rank = max(max_rank, r);
+            }
+            for (uint32_t r = 0; r <= max_rank; ++r) {
+                if (vis && rank == r) {
+                    uint32_t rows = min(s_cnt[w][pt], a.max_rows);
+                    volatile float4 * col = a.obs + row_pt;
+                    for (uint32_t i = 0; i < rows; ++i) {
+                        volatile float4 * p = col + (size_t)i * a.stride;
+                        float ox = p->x, oy = p->y, oz = p->z, ow = p->w;
+                        bool equal = fabsf(rel.x - ox) < 1e-5f && fabsf(rel.y - oy) < 1e-5f
+                            && fabsf(rel.z - oz) < 1e-5f && fabsf(scale - ow) < 1e-5f;
+                        if (equal) { p->w = -1.0f; break; }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        __syncwarp();
+    };
+
+    for (uint32_t k = 0; k < a.num_views; ++k) {
+        const float * view = a.views + UAVMVS_VIEW_FLOATS * (size_t)k;
+        V3 pos = mk(view[0], view[1], view[2]);
+        // conservative block cull on range: every point of the block fails `l >= max_distance`
+        {
+            float dx = pos.x - sph.x, dy = pos.y - sph.y, dz = pos.z - sph.z;
+            float D = sqrtf(dx * dx + dy * dy + dz * dz);
+            if (D * 0.99999f - sph.w >= a.max_distance * 1.00001f) continue;
+        }
+        st_pairs += 1;   // counted per warp-view; scaled by 32 at the end
+        // exact cull, kernels.cu:156-167
+        V3 v2c = pos - v;
+        float l = norm(v2c);
+        V3 v2cn = v2c / l;
+        float ctheta = dot(v2cn, nrm);
+        bool pass = valid && !(ctheta < 0.087f) && !(l >= a.max_distance);
+        if (pass) pass = in_image(view, v, a.width, a.height);
+        uint32_t mask = __ballot_sync(0xffffffffu, pass);
+        if (!mask) continue;
+        if (pass) s_q[w][(head + qn + __popc(mask & lt_mask)) & (K1_QUEUE - 1)] = make_uint2(lane, k);
+        qn += __popc(mask);
+        __syncwarp();
+        if (qn >= 32) { process(32); head = (head + 32) & (K1_QUEUE - 1); qn -= 32; }
+    }
+    if (qn) process(qn);
+
+    if (POPULATE && valid) a.num_rows[id] = s_cnt[w][lane];
+    if (a.stats && lane == 0) {
+        atomicAdd(a.stats + 0, st_rays);
+        atomicAdd(a.stats + 1, st_vis);
+        atomicAdd(a.stats + 2, (unsigned long long)a.num_views * 32ull);
+        atomicAdd(a.stats + 3, st_pairs * 32ull);
+    }
+}
+
+// ---- K2: process_observation_rays, kernels.cu:204-264 (one warp per point) ----------
+__global__ void __launch_bounds__(128)
+k_process_observation_rays(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t stride, uint32_t n)
+{
+    const uint32_t tx = threadIdx.x & 31;
+    const uint32_t id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (id >= n) return;
+    uint32_t num_rows = min(num_rows_ptr[id], max_rows);
+    float4 * col = obs + id;
+    float4 ray = make_float4(0.f, 0.f, 0.f, 0.f);
+    int key = (int)tx;
+    float theta = -1.0f;
+    if (tx < num_rows) {
+        ray = col[(size_t)tx * stride];
+        theta = (ray.w >= 0.0f) ? ray.z : -1.0f;
+    }
+    for (int i = 0; (1u << i) < num_rows; ++i) {
+        bool asc = (tx >> (i + 1)) % 2;
+        for (int s = 1 << i; s > 0; s >>= 1) {
+            bool dir = (tx % (s << 1)) < s;
+            float otheta = __shfl_xor_sync(0xffffffffu, theta, s);
+            int okey = __shfl_xor_sync(0xffffffffu, key, s);
+            if (otheta != theta && ((otheta > theta) == (asc ^ dir))) { theta = otheta; key = okey; }
+        }
+    }
+    uint32_t num_valid = __popc(__ballot_sync(0xffffffffu, theta >= 0.0f));
+    if (num_valid < num_rows && tx == 0) num_rows_ptr[id] = num_valid;
+    ray.x = __shfl_sync(0xffffffffu, ray.x, key);
+    ray.y = __shfl_sync(0xffffffffu, ray.y, key);
+    ray.z = __shfl_sync(0xffffffffu, ray.z, key);
+    ray.w = __shfl_sync(0xffffffffu, ray.w, key);
+    if (tx < num_valid) col[(size_t)tx * stride] = ray;
+}
+
+// ---- K3: evaluate_observation_rays, kernels.cu:266-291 (one thread per point) -------
+// The point's column is staged in shared memory once; the pair sum keeps the reference's
+// order (inner j < i ascending, outer i ascending).
+constexpr int K3_THREADS = 128;
+__global__ void __launch_bounds__(K3_THREADS)
+k_evaluate_observation_rays(const float4 * __restrict__ obs, const uint32_t * __restrict__ num_rows_ptr,
+    uint32_t max_rows, uint32_t stride, uint32_t n, float * __restrict__ recons,
+    float target, float * __restrict__ wrecons, Heur h)
+{
+    extern __shared__ float4 s_col[];   // [max_rows][K3_THREADS]
+    const uint32_t id = blockIdx.x * K3_THREADS + threadIdx.x;
+    if (id >= n) return;
+    const uint32_t rows = min(num_rows_ptr[id], max_rows);
+    for (uint32_t i = 0; i < rows; ++i) s_col[i * K3_THREADS + threadIdx.x] = obs[(size_t)i * stride + id];
+    const float m_k = h.m_k, m_x0 = kPi / h.m_x0, t_k = h.t_k, t_x0 = kPi / h.t_x0;
+    float recon = rows >= 1 ? 0.0f : -1.0f;
+    for (uint32_t i = 1; i < rows; ++i) {
+        float4 ri = s_col[i * K3_THREADS + threadIdx.x];
+        float sum = 0.0f;
+        for (uint32_t j = 0; j < i; ++j)
+            sum += pair_term(s_col[j * K3_THREADS + threadIdx.x], ri, m_k, m_x0, t_k, t_x0);
+        recon += sum;
+    }
+    recons[id] = recon;
+    if (wrecons) wrecons[id] = func(recon, target);
+}
+
+// ---- K8: calculate_func_recons, kernels.cu:496-510 -----------------------------------
+__global__ void k_calculate_func_recons(const float * __restrict__ recons, uint32_t n, float target,
+    float * __restrict__ wrecons)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) wrecons[i] = func(recons[i], target);
+}
+
+// ---- K9: sum/min/max, libs/cacc/reduction.h:104-162 ----------------------------------
+// acc[0] = sum (double), acc[1] = min, acc[2] = max as order-preserving ints.
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__host__ __device__ __forceinline__ float ord2f(int i) {
+    int b = i >= 0 ? i : i ^ 0x7fffffff;
+#ifdef __CUDA_ARCH__
+    return __int_as_float(b);
+#else
+    float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+struct ReduceAcc { double sum; int mn, mx; int pad; };
+
+__global__ void k_reduce_init(ReduceAcc * acc) { acc->sum = 0.0; acc->mn = 0x7fffffff; acc->mx = (int)0x80000000; }
+
+__global__ void __launch_bounds__(256)
+k_reduce(const float * __restrict__ x, uint32_t n, ReduceAcc * acc)
+{
+    float s = 0.0f, mn = UAV_INF, mx = -UAV_INF;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float v = x[i]; s += v; mn = fminf(mn, v); mx = fmaxf(mx, v);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    __shared__ float ss[8], smn[8], smx[8];
+    uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { ss[w] = s; smn[w] = mn; smx[w] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < 8; ++i) { t += (double)ss[i]; mn = fminf(mn, smn[i]); mx = fmaxf(mx, smx[i]); }
+        atomicAdd(&acc->sum, t);
+        atomicMin(&acc->mn, f2ord(mn));
+        atomicMax(&acc->mx, f2ord(mx));
+    }
+}
+
+// ---- launch helpers --------------------------------------------------------------------
+struct Scratch {   // per-process scratch on the device (views, reduction accumulator, stats)
+    float * views = nullptr; size_t views_cap = 0;
+    ReduceAcc * acc = nullptr;
+    unsigned long long * stats = nullptr;
+    ReduceAcc * h_acc = nullptr; unsigned long long * h_stats = nullptr;   // pinned
+};
+static thread_local Scratch g_scratch;
+
+static int ensure_scratch(size_t view_floats)
+{
+    Scratch & s = g_scratch;
+    if (!s.acc) {
+        UAV_CUDA(cudaMalloc(&s.acc, sizeof(ReduceAcc)));
+        UAV_CUDA(cudaMalloc(&s.stats, 4 * sizeof(unsigned long long)));
+        UAV_CUDA(cudaMallocHost(&s.h_acc, sizeof(ReduceAcc)));
+        UAV_CUDA(cudaMallocHost(&s.h_stats, 4 * sizeof(unsigned long long)));
+    }
+    if (view_floats > s.views_cap) {
+        if (s.views) cudaFree(s.views);
+        UAV_CUDA(cudaMalloc(&s.views, view_floats * sizeof(float)));
+        s.views_cap = view_floats;
+    }
+    return 0;
+}
+
+static int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
+    float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    uavmvs_obs * obs, unsigned long long * d_stats)
+{
+    UAV_REQUIRE(bvh && cloud && obs, "null handle");
+    UAV_REQUIRE(obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
+    if (num_views == 0) return 0;
+    K1Args a;
+    a.bvh = view_of(bvh);
+    a.verts = cloud->vertices; a.normals = cloud->normals; a.spheres = cloud->block_sphere; a.n = cloud->n;
+    a.views = d_views; a.num_views = num_views;
+    a.max_distance = max_distance; a.width = width; a.height = height;
+    a.obs = obs->data; a.num_rows = obs->num_rows; a.max_rows = obs->max_rows;
+    a.stride = (uint32_t)(obs->pitch / sizeof(float4));
+    a.stats = d_stats;
+    unsigned grid = divup(cloud->num_blocks, K1_WARPS);
+    if (populate) k_update_observation_rays<true><<<grid, K1_WARPS * 32, 0, s>>>(a);
+    else k_update_observation_rays<false><<<grid, K1_WARPS * 32, 0, s>>>(a);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int launch_k3(cudaStream_t s, const uavmvs_obs * obs, uavmvs_array * recons, float target, uavmvs_array * wrecons)
+{
+    UAV_REQUIRE(obs && recons, "null handle");
+    UAV_REQUIRE(recons->n == obs->num_cols, "recons size != obs columns");
+    size_t smem = sizeof(float4) * obs->max_rows * K3_THREADS;
+    static bool attr_set = false;
+    if (!attr_set) {
+        UAV_CUDA(cudaFuncSetAttribute(k_evaluate_observation_rays, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+        attr_set = true;
+    }
+    k_evaluate_observation_rays<<<divup(obs->num_cols, K3_THREADS), K3_THREADS, smem, s>>>(
+        obs->data, obs->num_rows, obs->max_rows, (uint32_t)(obs->pitch / sizeof(float4)), obs->num_cols,
+        recons->data, target, wrecons ? wrecons->data : nullptr, g_heur);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int launch_reduce(cudaStream_t s, const uavmvs_array * a)
+{
+    k_reduce_init<<<1, 1, 0, s>>>(g_scratch.acc);
+    unsigned grid = min(divup(a->n, 256 * 8), 148u * 8u);
+    k_reduce<<<grid ? grid : 1, 256, 0, s>>>(a->data, a->n, g_scratch.acc);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaMemcpyAsync(g_scratch.h_acc, g_scratch.acc, sizeof(ReduceAcc), cudaMemcpyDeviceToHost, s));
+    return 0;
+}
+
+}  // namespace uav
+
+using namespace uav;
+
+extern "C" {
+
+int uavmvs_configure_heuristic(float m_k, float m_x0, float t_k, float t_x0)
+{
+    g_heur.m_k = m_k; g_heur.m_x0 = m_x0; g_heur.t_k = t_k; g_heur.t_x0 = t_x0;
+    return 0;
+}
+
+int uavmvs_update_observation_rays_batch_device(void * stream, int populate, const float * d_views,
+    uint32_t num_views, float max_distance, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs)
+{
+    return launch_k1((cudaStream_t)stream, populate, d_views, num_views, max_distance, width, height,
+        bvh, cloud, obs, nullptr);
+}
+
+int uavmvs_update_observation_rays_batch(void * stream, int populate, const float * views,
+    uint32_t num_views, float max_distance, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs)
+{
+    UAV_REQUIRE(views || num_views == 0, "null views");
+    if (num_views == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
+    UAV_CUDA(cudaMemcpyAsync(g_scratch.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views,
+        cudaMemcpyHostToDevice, s));
+    int rc = launch_k1(s, populate, g_scratch.views, num_views, max_distance, width, height, bvh, cloud, obs, nullptr);
+    if (rc) return rc;
+    // the scratch view buffer may be reused by the next call: keep stream order, no host sync needed
+    return 0;
+}
+
+int uavmvs_update_observation_rays(void * stream, int populate, const float view_pos[3],
+    float max_distance, const float w2c[16], const float calib[9], int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs)
+{
+    UAV_REQUIRE(view_pos && w2c && calib, "null argument");
+    float view[UAVMVS_VIEW_FLOATS];
+    for (int i = 0; i < 3; ++i) view[i] = view_pos[i];
+    for (int i = 0; i < 16; ++i) view[3 + i] = w2c[i];
+    for (int i = 0; i < 9; ++i) view[19 + i] = calib[i];
+    // one private device copy per call so concurrent streams never share the staging buffer
+    cudaStream_t s = (cudaStream_t)stream;
+    float * d_view;
+    UAV_CUDA(cudaMallocAsync(&d_view, sizeof(view), s));
+    UAV_CUDA(cudaMemcpyAsync(d_view, view, sizeof(view), cudaMemcpyHostToDevice, s));
+    int rc = launch_k1(s, populate, d_view, 1, max_distance, width, height, bvh, cloud, obs, nullptr);
+    UAV_CUDA(cudaFreeAsync(d_view, s));
+    return rc;
+}
+
+int uavmvs_process_observation_rays(void * stream, uavmvs_obs * obs)
+{
+    UAV_REQUIRE(obs, "null obs");
+    k_process_observation_rays<<<divup((uint64_t)obs->num_cols * 32, 128), 128, 0, (cudaStream_t)stream>>>(
+        obs->data, obs->num_rows, obs->max_rows, (uint32_t)(obs->pitch / sizeof(float4)), obs->num_cols);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavmvs_array * recons)
+{
+    return launch_k3((cudaStream_t)stream, obs, recons, 0.0f, nullptr);
+}
+
+int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon, uavmvs_array * wrecons)
+{
+    UAV_REQUIRE(recons && wrecons && recons->n == wrecons->n, "bad arrays");
+    k_calculate_func_recons<<<divup(recons->n, 256), 256, 0, (cudaStream_t)stream>>>(recons->data, recons->n,
+        target_recon, wrecons->data);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int uavmvs_reduce(void * stream, const uavmvs_array * a, float out3[3])
+{
+    UAV_REQUIRE(a && out3, "null argument");
+    if (ensure_scratch(0)) return 1;
+    if (launch_reduce((cudaStream_t)stream, a)) return 1;
+    UAV_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    out3[0] = (float)g_scratch.h_acc->sum; out3[1] = ord2f(g_scratch.h_acc->mn); out3[2] = ord2f(g_scratch.h_acc->mx);
+    return 0;
+}
+
+int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4])
+{
+    UAV_REQUIRE(bvh && cloud && obs && recons && wrecons, "null handle");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ensure_scratch(0)) return 1;
+    UAV_CUDA(cudaMemsetAsync(obs->num_rows, 0, 4 * (size_t)obs->num_cols, s));
+    if (stats) UAV_CUDA(cudaMemsetAsync(g_scratch.stats, 0, 4 * sizeof(unsigned long long), s));
+    int rc = launch_k1(s, 1, d_views, num_views, max_distance, width, height, bvh, cloud, obs,
+        stats ? g_scratch.stats : nullptr);
+    if (rc) return rc;
+    rc = uavmvs_process_observation_rays(stream, obs);
+    if (rc) return rc;
+    rc = launch_k3(s, obs, recons, target_recon, wrecons);
+    if (rc) return rc;
+    if (launch_reduce(s, wrecons)) return 1;
+    if (stats) UAV_CUDA(cudaMemcpyAsync(g_scratch.h_stats, g_scratch.stats, 4 * sizeof(unsigned long long),
+        cudaMemcpyDeviceToHost, s));
+    if (out3 || stats) {
+        UAV_CUDA(cudaStreamSynchronize(s));
+        if (out3) { out3[0] = (float)g_scratch.h_acc->sum; out3[1] = ord2f(g_scratch.h_acc->mn); out3[2] = ord2f(g_scratch.h_acc->mx); }
+        if (stats) for (int i = 0; i < 4; ++i) stats[i] = g_scratch.h_stats[i];
+    }
+    return 0;
+}
+
+int uavmvs_evaluate_trajectory(void * stream, const float * views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4])
+{
+    UAV_REQUIRE(views || num_views == 0, "null views");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
+    if (num_views)
+        UAV_CUDA(cudaMemcpyAsync(g_scratch.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views,
+            cudaMemcpyHostToDevice, s));
+    return uavmvs_evaluate_trajectory_device(stream, g_scratch.views, num_views, max_distance, target_recon,
+        width, height, bvh, cloud, obs, recons, wrecons, out3, stats);
+}
+
+}  // extern "C"

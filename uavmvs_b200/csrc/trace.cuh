@@ -1,0 +1,152 @@
+// BVH traversal device functions.  Canon = libs/acc/bvh_tree.h:419-467 with the ray
+// primitives of libs/acc/primitives.h:119-132 (slab) and :214-248 (triangle), which is
+// also what libs/cacc/tracing.h:37-116 walks on the device.
+//
+// Any-hit result is independent of the visiting order: a leaf is reached iff every box
+// on its root path (root excluded) passes the slab test against the ORIGINAL
+// [tmin,tmax], and the query is true iff some reached leaf holds an accepted triangle.
+// trace_any() exploits that (leaf children are tested at once, only inner nodes are
+// stacked); trace_closest() keeps the reference's near-first order and its shrinking
+// tmax because those decide which slack-zone hit wins.
+#pragma once
+#include "common.cuh"
+
+namespace uav {
+
+struct BvhView {
+    const Node64 * __restrict__ inner;
+    const Tri64 * __restrict__ tris;
+    const uint32_t * __restrict__ indices;
+    uint32_t root_is_leaf, root_first, root_count;
+};
+
+__host__ inline BvhView view_of(const uavmvs_bvh * b) {
+    BvhView v;
+    v.inner = b->inner; v.tris = b->ptris; v.indices = b->indices;
+    v.root_is_leaf = b->root_is_leaf; v.root_first = b->root_first; v.root_count = b->root_count;
+    return v;
+}
+
+// libs/acc/primitives.h:119-132, true divisions, std::min/max NaN behaviour
+__device__ __forceinline__ bool slab(const Ray & r, float mnx, float mny, float mnz,
+    float mxx, float mxy, float mxz, float & tmin_out)
+{
+    float tmin = r.tmin, tmax = r.tmax;
+    float t1, t2;
+    t1 = (mnx - r.o.x) / r.d.x; t2 = (mxx - r.o.x) / r.d.x;
+    tmin = smax(tmin, smin(smin(t1, t2), UAV_INF)); tmax = smin(tmax, smax(smax(t1, t2), -UAV_INF));
+    t1 = (mny - r.o.y) / r.d.y; t2 = (mxy - r.o.y) / r.d.y;
+    tmin = smax(tmin, smin(smin(t1, t2), UAV_INF)); tmax = smin(tmax, smax(smax(t1, t2), -UAV_INF));
+    t1 = (mnz - r.o.z) / r.d.z; t2 = (mxz - r.o.z) / r.d.z;
+    tmin = smax(tmin, smin(smin(t1, t2), UAV_INF)); tmax = smin(tmax, smax(smax(t1, t2), -UAV_INF));
+    tmin_out = tmin;
+    return tmax >= smax(tmin, 0.0f);
+}
+
+// libs/acc/primitives.h:214-248 on the pre-reduced triangle
+__device__ __forceinline__ bool hit_tri(const Ray & r, const Tri64 * __restrict__ tp, float & t_out)
+{
+    float4 q0 = __ldg(&tp->q0), q1 = __ldg(&tp->q1), q2 = __ldg(&tp->q2), q3 = __ldg(&tp->q3);
+    V3 a = mk(q0.x, q0.y, q0.z), ab = mk(q0.w, q1.x, q1.y), ac = mk(q1.z, q1.w, q2.x);
+    V3 n = mk(q2.y, q2.z, q2.w);
+    float d00 = q3.x, d01 = q3.y, d11 = q3.z, denom = q3.w;
+    float cosine = dot_nz(n, r.d);
+    if (fabsf(cosine) < FLT_EPSILON) return false;      // also rejects degenerate (n == 0)
+    float t = -dot_nz(n, r.o - a) / cosine;
+    if (t < r.tmin || r.tmax < t) return false;
+    V3 p = r.o + r.d * t;
+    V3 ap = p - a;
+    float d20 = dot_nz(ap, ab), d21 = dot_nz(ap, ac);
+    float b1 = (d11 * d20 - d01 * d21) / denom;
+    float b2 = (d00 * d21 - d01 * d20) / denom;
+    float b0 = 1.0f - b1 - b2;
+    const float eps = 1e-3f;
+    if (-eps > b0 || b0 > 1.0f + eps) return false;
+    if (-eps > b1 || b1 > 1.0f + eps) return false;
+    if (-eps > b2 || b2 > 1.0f + eps) return false;
+    t_out = t;
+    return true;
+}
+
+#ifndef UAV_STACK
+#define UAV_STACK 96
+#endif
+
+// Occlusion query.  Returns true iff the segment is blocked.
+__device__ __forceinline__ bool trace_any(const BvhView & bvh, const Ray & ray)
+{
+    float t;
+    if (bvh.root_is_leaf) {
+        for (uint32_t i = 0; i < bvh.root_count; ++i)
+            if (hit_tri(ray, bvh.tris + bvh.root_first + i, t)) return true;
+        return false;
+    }
+    uint32_t stack[UAV_STACK];
+    int sp = 0;
+    uint32_t cur = 0;
+    while (true) {
+        const Node64 * np = bvh.inner + cur;
+        float4 q0 = __ldg(&np->q0), q1 = __ldg(&np->q1), q2 = __ldg(&np->q2);
+        uint4 q3 = __ldg(&np->q3);
+        float tl, tr;
+        bool hl = slab(ray, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tl);
+        bool hr = slab(ray, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tr);
+        if (hl && q3.z) {
+            for (uint32_t i = 0; i < q3.z; ++i) if (hit_tri(ray, bvh.tris + q3.x + i, t)) return true;
+            hl = false;
+        }
+        if (hr && q3.w) {
+            for (uint32_t i = 0; i < q3.w; ++i) if (hit_tri(ray, bvh.tris + q3.y + i, t)) return true;
+            hr = false;
+        }
+        if (hl && hr) {
+            if (tl < tr) { stack[sp++] = q3.y; cur = q3.x; }
+            else { stack[sp++] = q3.x; cur = q3.y; }
+        } else if (hl) cur = q3.x;
+        else if (hr) cur = q3.y;
+        else { if (sp == 0) break; cur = stack[--sp]; }
+    }
+    return false;
+}
+
+// Closest hit in the reference's order; face id through indices[] (bvh_tree.h:409).
+__device__ __forceinline__ bool trace_closest(const BvhView & bvh, Ray ray, uint32_t & face, float & t_hit)
+{
+    float best = UAV_INF; uint32_t best_face = UAV_NAI;
+    uint2 stack[UAV_STACK];
+    int sp = 0;
+    uint2 cur = bvh.root_is_leaf ? make_uint2(bvh.root_first, bvh.root_count) : make_uint2(0u, 0u);
+    while (true) {
+        if (cur.y == 0) {
+            const Node64 * np = bvh.inner + cur.x;
+            float4 q0 = __ldg(&np->q0), q1 = __ldg(&np->q1), q2 = __ldg(&np->q2);
+            uint4 q3 = __ldg(&np->q3);
+            float tl, tr;
+            bool hl = slab(ray, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tl);
+            bool hr = slab(ray, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tr);
+            uint2 L = make_uint2(q3.x, q3.z), R = make_uint2(q3.y, q3.w);
+            if (hl && hr) {
+                if (tl < tr) { stack[sp++] = R; cur = L; }
+                else { stack[sp++] = L; cur = R; }
+            } else if (hl) cur = L;
+            else if (hr) cur = R;
+            else { if (sp == 0) break; cur = stack[--sp]; }
+        } else {
+            bool any = false;
+            for (uint32_t i = 0; i < cur.y; ++i) {
+                float t;
+                if (hit_tri(ray, bvh.tris + cur.x + i, t)) {
+                    if (t > best) continue;
+                    best = t; best_face = __ldg(bvh.indices + cur.x + i); any = true;
+                }
+            }
+            if (any) ray.tmax = best;
+            if (sp == 0) break;
+            cur = stack[--sp];
+        }
+    }
+    face = best_face; t_hit = best;
+    return best < UAV_INF;
+}
+
+}  // namespace uav
