@@ -237,18 +237,20 @@ __global__ void k_trace(BvhView bvh, const float * __restrict__ rays, uint64_t n
     uint8_t * __restrict__ hit, uint32_t * __restrict__ face, float * __restrict__ t)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float * r = rays + 8 * i;
+    const bool active = i < n;
+    const float * r = rays + 8 * (active ? i : 0);
     Ray ray;
     ray.o = mk(r[0], r[1], r[2]); ray.d = mk(r[3], r[4], r[5]); ray.tmin = r[6]; ray.tmax = r[7];
     if (any_hit) {
-        bool h = trace_any(bvh, ray);
+        bool h = trace_any_warp(bvh, ray, active);
+        if (!active) return;
         hit[i] = h ? 1 : 0;
         if (face) face[i] = UAV_NAI;
         if (t) t[i] = 0.0f;
     } else {
         uint32_t f; float tt;
-        bool h = trace_closest(bvh, ray, f, tt);
+        bool h = trace_closest_warp(bvh, ray, active, f, tt);
+        if (!active) return;
         hit[i] = h ? 1 : 0;
         if (face) face[i] = h ? f : UAV_NAI;
         if (t) t[i] = h ? tt : 0.0f;

@@ -73,6 +73,45 @@ struct K1Args {
 
 constexpr int K1_WARPS = 4;
 constexpr int K1_QUEUE = 64;
+constexpr int K1_VSTRIDE = 29;   // 28 floats per staged view, padded against bank conflicts
+
+// Conservative (block of points, view) test: false only if NO point inside the sphere
+// (centre c, radius r) can pass the exact cull of kernels.cu:164-167 (range, image bounds).
+// Margins are 100x above fp32 rounding of the exact test, so a rejected block is rejected
+// point by point by the exact arithmetic as well.
+__device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view, float4 sph,
+    float max_distance, int width, int height)
+{
+    float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
+    float D = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (D * 0.99999f - sph.w >= max_distance * 1.00001f) return false;
+    const float * W = view + 3; const float * K = view + 19;
+    float q[3], e2 = 0.0f, fro2 = 0.0f;
+    #pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float a = W[4 * i] * sph.x, b = W[4 * i + 1] * sph.y, c = W[4 * i + 2] * sph.z, d = W[4 * i + 3];
+        q[i] = a + b + c + d;
+        float e = 1e-6f * (fabsf(a) + fabsf(b) + fabsf(c) + fabsf(d));
+        e2 += e * e;
+        fro2 += W[4 * i] * W[4 * i] + W[4 * i + 1] * W[4 * i + 1] + W[4 * i + 2] * W[4 * i + 2];
+    }
+    float qn = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);
+    float rho = sph.w * sqrtf(fro2) * 1.001f + sqrtf(e2) + 1e-4f * (qn + 1.0f);
+    float k2n = sqrtf(K[6] * K[6] + K[7] * K[7] + K[8] * K[8]);
+    float p2 = K[6] * q[0] + K[7] * q[1] + K[8] * q[2];
+    if (!(p2 - k2n * rho > 0.0f)) return true;          // ball not entirely in front: undecided
+    float lim[4] = {0.5f, (float)width + 0.5f, 0.5f, (float)height + 0.5f};
+    #pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        int r = s >> 1;                                   // image row of K: 0 -> x, 1 -> y
+        float a0 = K[3 * r] - lim[s] * K[6], a1 = K[3 * r + 1] - lim[s] * K[7], a2 = K[3 * r + 2] - lim[s] * K[8];
+        float an = sqrtf(a0 * a0 + a1 * a1 + a2 * a2);
+        float v = a0 * q[0] + a1 * q[1] + a2 * q[2];
+        if ((s & 1) == 0) { if (v + an * rho < 0.0f) return false; }   // coordinate < 0 everywhere
+        else { if (v - an * rho > 0.0f) return false; }                // coordinate >= size everywhere
+    }
+    return true;
+}
 
 // One warp owns 32 consecutive (Z-ordered) points and walks the trajectory in view order.
 // Pairs that survive the exact cull are appended to a per-warp FIFO of (lane, view); every
@@ -87,6 +126,7 @@ k_update_observation_rays(K1Args a)
     __shared__ float4 s_n[K1_WARPS][32];
     __shared__ uint32_t s_cnt[K1_WARPS][32];
     __shared__ uint2 s_q[K1_WARPS][K1_QUEUE];
+    __shared__ float s_views[K1_WARPS][32 * K1_VSTRIDE];
 
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t blk = blockIdx.x * K1_WARPS + w;
@@ -115,9 +155,10 @@ k_update_observation_rays(K1Args a)
         V3 v2c = mk(view[0], view[1], view[2]) - pv;
         float l = norm(v2c);
         V3 v2cn = v2c / l;
-        if (active) {
+        {
             Ray ray; ray.o = pv; ray.d = v2cn; ray.tmin = l * 0.001f; ray.tmax = l;   // kernels.cu:54-58
-            vis = !trace_any(a.bvh, ray);
+            bool blocked = trace_any_warp(a.bvh, ray, active);   // collective: every lane calls
+            vis = active && !blocked;
         }
         uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
         uint32_t peers = __match_any_sync(0xffffffffu, pt) & vis_mask;
@@ -160,29 +201,40 @@ k_update_observation_rays(K1Args a)
         __syncwarp();
     };
 
-    for (uint32_t k = 0; k < a.num_views; ++k) {
-        const float * view = a.views + UAVMVS_VIEW_FLOATS * (size_t)k;
-        V3 pos = mk(view[0], view[1], view[2]);
-        // conservative block cull on range: every point of the block fails `l >= max_distance`
-        {
-            float dx = pos.x - sph.x, dy = pos.y - sph.y, dz = pos.z - sph.z;
-            float D = sqrtf(dx * dx + dy * dy + dz * dz);
-            if (D * 0.99999f - sph.w >= a.max_distance * 1.00001f) continue;
-        }
-        st_pairs += 1;   // counted per warp-view; scaled by 32 at the end
-        // exact cull, kernels.cu:156-167
-        V3 v2c = pos - v;
-        float l = norm(v2c);
-        V3 v2cn = v2c / l;
-        float ctheta = dot(v2cn, nrm);
-        bool pass = valid && !(ctheta < 0.087f) && !(l >= a.max_distance);
-        if (pass) pass = in_image(view, v, a.width, a.height);
-        uint32_t mask = __ballot_sync(0xffffffffu, pass);
-        if (!mask) continue;
-        if (pass) s_q[w][(head + qn + __popc(mask & lt_mask)) & (K1_QUEUE - 1)] = make_uint2(lane, k);
-        qn += __popc(mask);
+    for (uint32_t chunk = 0; chunk < a.num_views; chunk += 32) {
+        // stage 32 views in shared memory (coalesced), then test them lane-parallel against the block
+        const uint32_t nv = min(32u, a.num_views - chunk);
         __syncwarp();
-        if (qn >= 32) { process(32); head = (head + 32) & (K1_QUEUE - 1); qn -= 32; }
+        {   // element e = 28 * vw + col; advancing e by 32 is (vw + 1, col + 4) with carry
+            uint32_t vw = lane >= UAVMVS_VIEW_FLOATS ? 1u : 0u, col = lane - vw * UAVMVS_VIEW_FLOATS;
+            const float * src = a.views + (size_t)chunk * UAVMVS_VIEW_FLOATS;
+            for (uint32_t e = lane; e < nv * UAVMVS_VIEW_FLOATS; e += 32) {
+                s_views[w][vw * K1_VSTRIDE + col] = src[e];
+                col += 4; vw += 1;
+                if (col >= UAVMVS_VIEW_FLOATS) { col -= UAVMVS_VIEW_FLOATS; vw += 1; }
+            }
+        }
+        __syncwarp();
+        bool cand = lane < nv && block_view_maybe(&s_views[w][lane * K1_VSTRIDE], sph, a.max_distance, a.width, a.height);
+        uint32_t cmask = __ballot_sync(0xffffffffu, cand);
+        st_pairs += __popc(cmask);
+        while (cmask) {
+            const uint32_t j = __ffs(cmask) - 1; cmask &= cmask - 1;
+            const float * view = &s_views[w][j * K1_VSTRIDE];
+            // exact cull, kernels.cu:156-167
+            V3 v2c = mk(view[0], view[1], view[2]) - v;
+            float l = norm(v2c);
+            V3 v2cn = v2c / l;
+            float ctheta = dot(v2cn, nrm);
+            bool pass = valid && !(ctheta < 0.087f) && !(l >= a.max_distance);
+            if (pass) pass = in_image(view, v, a.width, a.height);
+            uint32_t mask = __ballot_sync(0xffffffffu, pass);
+            if (!mask) continue;
+            if (pass) s_q[w][(head + qn + __popc(mask & lt_mask)) & (K1_QUEUE - 1)] = make_uint2(lane, chunk + j);
+            qn += __popc(mask);
+            __syncwarp();
+            if (qn >= 32) { process(32); head = (head + 32) & (K1_QUEUE - 1); qn -= 32; }
+        }
     }
     if (qn) process(qn);
 

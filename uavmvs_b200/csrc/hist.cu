@@ -79,56 +79,54 @@ k_populate_spherical_histogram(HistArgs a)
     for (uint32_t i = threadIdx.x; i < a.kd.n; i += HIST_THREADS) s_hist[i] = 0.0f;
     __syncthreads();
     uint32_t id = blockIdx.x * HIST_THREADS + threadIdx.x;
-    if (id < a.n) {
-        V3 v = ld3(a.verts[id]), n = ld3(a.normals[id]);
-        V3 v2c = mk(a.px, a.py, a.pz) - v;
-        float l = norm(v2c);
-        float scale = 1.0f - (l / a.max_distance);
-        if (scale > 0.0f) {
-            V3 v2cn = v2c / l;
-            float ctheta = dot(v2cn, n);
-            if (!(ctheta < 0.087f)) {
-                Ray ray; ray.o = v; ray.d = v2cn; ray.tmin = l * 0.001f; ray.tmax = l;
-                if (!trace_any(a.bvh, ray)) {
-                    float contrib = 0.0f; bool add = true;
-                    if (!WITH_RECON) {
-                        float capture_difficulty = fmaxf(a.qualities[id], 0.0f);
-                        float min_theta = fminf(a.values[id], 1.484f);
-                        float scaling = (kPi / 2.0f) / ((kPi / 2.0f) - min_theta);
-                        float theta = acosf(__saturatef(ctheta));
-                        float rel_theta = fmaxf(theta - min_theta, 0.0f) * scaling;
-                        contrib = capture_difficulty * cosf(rel_theta) * scale;
-                    } else {
-                        uint32_t rows = a.num_rows[id];
-                        if (rows >= a.max_rows) add = false;
-                        else {
-                            float recon = a.recons[id];
-                            float new_recon = 0.0f;
-                            if (rows >= 1) {
-                                V3 rel = relative_direction(v2cn, n);
-                                const float m_k = a.heur.m_k, m_x0 = kPi / a.heur.m_x0, t_k = a.heur.t_k, t_x0 = kPi / a.heur.t_x0;
-                                float sum = 0.0f;
-                                for (uint32_t i = 0; i < rows; ++i) {       // heuristic(), kernels.cu:111-136
-                                    float4 r = a.obs[(size_t)i * a.stride + id];
-                                    float calpha = dot(rel, mk(r.x, r.y, r.z));
-                                    float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
-                                    float sc = fminf(r.w, scale);
-                                    float ct = fminf(r.z, rel.z);
-                                    float matchability = (1.0f - logistic(alpha, m_k, m_x0)) * ct;
-                                    float triangulation = logistic(alpha, t_k, t_x0) * sc;
-                                    sum += matchability * triangulation;
-                                }
-                                new_recon = recon + sum;
-                            }
-                            contrib = func(new_recon, a.target_recon) - func(recon, a.target_recon);
-                        }
+    const bool valid = id < a.n;
+    V3 v = ld3(a.verts[valid ? id : 0]), n = ld3(a.normals[valid ? id : 0]);
+    V3 v2c = mk(a.px, a.py, a.pz) - v;
+    float l = norm(v2c);
+    float scale = 1.0f - (l / a.max_distance);
+    V3 v2cn = v2c / l;
+    float ctheta = dot(v2cn, n);
+    bool cast = valid && scale > 0.0f && !(ctheta < 0.087f);
+    Ray ray; ray.o = v; ray.d = v2cn; ray.tmin = l * 0.001f; ray.tmax = l;
+    bool blocked = trace_any_warp(a.bvh, ray, cast);   // collective: every lane calls
+    bool visible = cast && !blocked;
+    if (visible) {
+        float contrib = 0.0f; bool add = true;
+        if (!WITH_RECON) {
+            float capture_difficulty = fmaxf(a.qualities[id], 0.0f);
+            float min_theta = fminf(a.values[id], 1.484f);
+            float scaling = (kPi / 2.0f) / ((kPi / 2.0f) - min_theta);
+            float theta = acosf(__saturatef(ctheta));
+            float rel_theta = fmaxf(theta - min_theta, 0.0f) * scaling;
+            contrib = capture_difficulty * cosf(rel_theta) * scale;
+        } else {
+            uint32_t rows = a.num_rows[id];
+            if (rows >= a.max_rows) add = false;
+            else {
+                float recon = a.recons[id];
+                float new_recon = 0.0f;
+                if (rows >= 1) {
+                    V3 rel = relative_direction(v2cn, n);
+                    const float m_k = a.heur.m_k, m_x0 = kPi / a.heur.m_x0, t_k = a.heur.t_k, t_x0 = kPi / a.heur.t_x0;
+                    float sum = 0.0f;
+                    for (uint32_t i = 0; i < rows; ++i) {       // heuristic(), kernels.cu:111-136
+                        float4 r = a.obs[(size_t)i * a.stride + id];
+                        float calpha = dot(rel, mk(r.x, r.y, r.z));
+                        float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+                        float sc = fminf(r.w, scale);
+                        float ct = fminf(r.z, rel.z);
+                        float matchability = (1.0f - logistic(alpha, m_k, m_x0)) * ct;
+                        float triangulation = logistic(alpha, t_k, t_x0) * sc;
+                        sum += matchability * triangulation;
                     }
-                    if (add) {
-                        uint32_t bin = kd_find_nn(a.kd, -v2cn);
-                        atomicAdd(&s_hist[bin], contrib);
-                    }
+                    new_recon = recon + sum;
                 }
+                contrib = func(new_recon, a.target_recon) - func(recon, a.target_recon);
             }
+        }
+        if (add) {
+            uint32_t bin = kd_find_nn(a.kd, -v2cn);
+            atomicAdd(&s_hist[bin], contrib);
         }
     }
     __syncthreads();
@@ -197,15 +195,19 @@ k_estimate_capture_difficulty(BvhView bvh, KdView kd, uint32_t mesh_size, float 
     V3 v = ld3(verts[id]), nrm = ld3(normals[id]);
     float l = max_distance;
     float sum = 0.0f, max_ctheta = 0.0f;
-    for (uint32_t i = lane; i < kd.n; i += 32) {
-        V3 dir = normalized(ld3(__ldg(kd.verts + i)));
+    for (uint32_t base = 0; base < kd.n; base += 32) {
+        uint32_t i = base + lane;
+        bool in = i < kd.n;
+        V3 dir = normalized(ld3(__ldg(kd.verts + (in ? i : 0))));
         float ctheta = dot(dir, nrm);
-        if (ctheta < 0.087f) continue;
+        bool cast = in && !(ctheta < 0.087f);
         Ray ray; ray.o = v; ray.d = dir; ray.tmin = l * 0.001f; ray.tmax = l;
         uint32_t face; float t;
-        bool hit = trace_closest(bvh, ray, face, t);
-        if (!hit || face >= mesh_size) { if (ctheta > max_ctheta) max_ctheta = ctheta; }
-        else sum += ctheta;
+        bool hit = trace_closest_warp(bvh, ray, cast, face, t);
+        if (cast) {
+            if (!hit || face >= mesh_size) { if (ctheta > max_ctheta) max_ctheta = ctheta; }
+            else sum += ctheta;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) {
         sum += __shfl_xor_sync(0xffffffffu, sum, o);
