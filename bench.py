@@ -1,0 +1,405 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the visibility-and-reconstructability evaluation.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): synthetic 1M-triangle urban block, 1M proxy points,
+2k-view trajectory, full heuristic evaluation (clear obs, K1 over all views, K2, K3+K8, K9).
+A "step" is one such evaluation.  At N > 1 every rank evaluates its own 1M-point share of an
+N x 1M-point cloud against the replicated mesh (weak scaling; interleaved Z-order chunks), and
+the trajectory score is combined by one all-reduce.
+
+  value  occlusion rays/s, whole job, inputs resident in HBM, CUDA events, max over ranks
+  e2e    the same through the C-ABI call with HOST buffers: trajectory H2D from pinned memory,
+         evaluation, D2H of score + per-point recon + per-point counts into pinned memory
+  --impl reference   the CPU path (oracle port of libs/eval math over the reference's acc tree
+         walk) on the host cores, a bounded sample of the same workload per step
+
+One JSON line on stdout (rank 0).  Nothing here reads /root/reference.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "occlusion_rays_per_s"
+UNIT = "rays/s"
+CHUNK = 4096          # points per interleaved shard chunk (multiple of the 32-point block)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--points", type=int, default=1_000_000, help="proxy points per GPU")
+    ap.add_argument("--views", type=int, default=2000)
+    ap.add_argument("--extent", type=float, default=256.0)
+    ap.add_argument("--tree", default="lbvh", choices=["lbvh"], help="GPU LBVH build (product path)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(a, world):
+    return ("config2: synthetic urban block %.0f m, %d-triangle mesh, %d proxy points per GPU x %d GPU, "
+            "%d views, max_distance 80, 1920x1080, full evaluation K1+K2+K3+K8+K9" %
+            (a.extent, a.tris, a.points, world, a.views))
+
+
+def make_scene(a, world):
+    from uavmvs_b200 import scenes
+    return scenes.urban(a.tris, a.points * world, a.views, a.extent, seed=1)
+
+
+def my_points(sc, rank, world):
+    """Interleaved Z-order chunks: chunk c belongs to rank c % world (balanced visible-pair density)."""
+    n = sc.num_points
+    if world == 1:
+        return np.arange(n)
+    chunks = np.arange((n + CHUNK - 1) // CHUNK)
+    mine = chunks[chunks % world == rank]
+    idx = (mine[:, None] * CHUNK + np.arange(CHUNK)[None, :]).reshape(-1)
+    return idx[idx < n]
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "nvml unavailable"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def visible_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:  # noqa: BLE001
+            return local_rank
+    return local_rank
+
+
+# --------------------------------------------------------------------------- CPU arm (oracle/)
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+def cpu_tree(orc, sc):
+    """The reference's CPU tree: acc::BVHTree built by oracle/_ref (the reference's own code)
+    when that library travelled with the repo, else by the bit-identical restatement."""
+    t0 = time.perf_counter()
+    if orc.ref() is not None:
+        arrays = orc.RefBVH(sc.verts, sc.faces).export()
+        tree, built_by = orc.BVH.from_arrays(arrays), "oracle/_ref acc::BVHTree (reference code)"
+    else:
+        tree, built_by = orc.BVH.build(sc.verts, sc.faces), "oracle port of acc::BVHTree"
+    return tree, built_by, time.perf_counter() - t0
+
+
+def cpu_step(orc, tree, sc, view_idx, pts, nrm):
+    """One CPU evaluation over a subset of views: K1 (OpenMP over points, views in order), K2, K3,
+    K8, K9 -- the reference's algorithm, per-pair cull included."""
+    views = sc.views28()[view_idx]
+    obs = orc.ObsRays(pts.shape[0], 32)
+    t0 = time.perf_counter()
+    _, cnt = orc.update_observation_rays(tree, True, views, sc.max_distance, sc.width, sc.height, pts, nrm, obs,
+                                         want_counters=True)
+    t1 = time.perf_counter()
+    orc.process_observation_rays(obs)
+    recons = orc.evaluate_observation_rays(obs)
+    w = orc.calculate_func_recons(recons, sc.target_recon)
+    red = orc.reduce(w)
+    t2 = time.perf_counter()
+    return {"rays": int(cnt[0]), "pairs": int(cnt[5]), "counters": [int(x) for x in cnt], "seconds": t2 - t0,
+            "k1_seconds": t1 - t0, "score": float(red[0]) / pts.shape[0]}
+
+
+def pick_views(num_views, count):
+    count = max(1, min(num_views, count))
+    return np.unique(np.linspace(0, num_views - 1, count).round().astype(int))
+
+
+def calibrate_cpu_sample(orc, tree, sc, pts, nrm, budget_s):
+    """Number of (evenly strided) views whose CPU evaluation takes about budget_s seconds."""
+    probe = pick_views(sc.num_views, 16)
+    r = cpu_step(orc, tree, sc, probe, pts, nrm)
+    per_view = max(r["seconds"] / len(probe), 1e-6)
+    return int(max(16, min(sc.num_views, budget_s / per_view)))
+
+
+def bytes_per_ray(counters):
+    """B_ray = 80 n_inner + 16 n_leaf + 48 n_tri + 4 n_hit, counters of the oracle's
+    instrumented reference traversal on the same tree."""
+    rays, inner, leaf, tri, hit = counters[:5]
+    if rays == 0:
+        return 0.0, {}
+    per = {"n_inner": inner / rays, "n_leaf": leaf / rays, "n_tri": tri / rays, "n_hit": hit / rays}
+    return 80.0 * per["n_inner"] + 16.0 * per["n_leaf"] + 48.0 * per["n_tri"] + 4.0 * per["n_hit"], per
+
+
+def run_reference(a, rank, world):
+    if rank != 0:
+        return
+    import oracle as orc
+    orc.build()
+    sc = make_scene(a, 1)
+    tree, built_by, build_s = cpu_tree(orc, sc)
+    pts, nrm = sc.points, sc.normals
+    total = max(1, a.steps + a.warmup)
+    budget = min(12.0, 150.0 / total)                 # whole run within a few minutes
+    nviews = calibrate_cpu_sample(orc, tree, sc, pts, nrm, budget)
+    vidx = pick_views(sc.num_views, nviews)
+    for _ in range(a.warmup):
+        cpu_step(orc, tree, sc, vidx, pts, nrm)
+    secs, rays, pairs = 0.0, 0, 0
+    for _ in range(a.steps):
+        r = cpu_step(orc, tree, sc, vidx, pts, nrm)
+        secs += r["seconds"]; rays += r["rays"]; pairs += r["pairs"]
+    cores = host_threads()
+    value = rays / secs
+    sample = ("%d of %d views (evenly strided) x all %d points per step; tree: %s (built in %.2f s, not timed); "
+              "kernel math: oracle port of libs/eval/kernels.cu (the reference has no CPU implementation of it), "
+              "OpenMP over points" % (len(vidx), sc.num_views, pts.shape[0], built_by, build_s))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * secs / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a, 1), "sample": sample},
+            "pairs_per_s": pairs / secs,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- B200 arm
+def ncu_traffic():
+    """dram bytes per K1 launch from the committed ncu --set full capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "k1_traffic.json")
+    try:
+        return json.load(open(p))
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def run_b200(a, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    from uavmvs_b200 import api, sharded
+
+    if not torch.cuda.is_available() or api.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device (the evaluation path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    api.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks \
+        else (6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)")
+
+    sc = make_scene(a, world)
+    idx = my_points(sc, rank, world)
+    pts, nrm = np.ascontiguousarray(sc.points[idx]), np.ascontiguousarray(sc.normals[idx])
+    n_local = pts.shape[0]
+    views_np = sc.views28()
+    V = views_np.shape[0]
+
+    t0 = time.perf_counter()
+    bvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
+    api.synchronize()
+    build_s = time.perf_counter() - t0
+    cloud = api.PointCloud.create(pts, nrm)
+    obs = api.VectorArray.create(n_local, 32)
+    recons, wrecons = api.Array.create(n_local), api.Array.create(n_local)
+    dviews = api.DeviceViews(views_np)
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
+    h_views = torch.from_numpy(views_np.copy()).pin_memory()
+    h_recons = torch.empty(n_local, dtype=torch.float32).pin_memory()
+    h_rows = torch.empty(n_local, dtype=torch.int32).pin_memory()
+    h_recons_np, h_rows_np = h_recons.numpy(), h_rows.numpy().view(np.uint32)
+
+    def resident_step():
+        return api.evaluate_trajectory(dviews, sc.max_distance, sc.target_recon, sc.width, sc.height, bvh, cloud,
+                                       obs, recons, wrecons, stream=stream)
+
+    def e2e_step():
+        # host trajectory -> C ABI (H2D inside) -> evaluation -> D2H of score, per-point recon and counts
+        r = api.evaluate_trajectory(h_views.numpy(), sc.max_distance, sc.target_recon, sc.width, sc.height, bvh,
+                                    cloud, obs, recons, wrecons, stream=stream)
+        recons.download(out=h_recons_np)
+        obs.download(data=False, rows_out=h_rows_np)
+        return r
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps, want_profile=False):
+        ms, k_ms, last = 0.0, np.zeros(4), None
+        for _ in range(steps):
+            flush.fill_(1)                                   # evict L2 between steps (outside the events)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            last = step_fn()
+            e1.record(stream)
+            e1.synchronize()
+            ms += e0.elapsed_time(e1)
+            if want_profile:
+                k_ms += np.array(api.profile_last())
+        return ms, k_ms, last
+
+    for _ in range(a.warmup):
+        flush.fill_(1)
+        resident_step()
+    sampler = ClockSampler(visible_gpu_index(local_rank))
+    barrier()
+    sampler.start()
+    ms, k_ms, last = timed(resident_step, a.steps, want_profile=True)
+    barrier()
+    clocks = sampler.stop()
+    s_sum, s_min, s_max, stats = last
+    for _ in range(min(a.warmup, 3)):
+        e2e_step()
+    barrier()
+    e2e_ms, _, _ = timed(e2e_step, a.steps)
+    barrier()
+
+    # max over ranks of the device time; sums of the work
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = t.tolist()
+    res = sharded.combine_scores(s_sum, s_min, s_max, n_local, stats)
+    rays, observations, pairs, pairs_after_block_cull = res["stats"]
+    pairs = res["points"] * V                                  # every (point, view) pair is evaluated
+    sec, e2e_sec = ms / 1e3, e2e_ms / 1e3
+    value = rays * a.steps / sec
+    k1_ms = float(k_ms[0]) / a.steps
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a, world), "tree": "GPU LBVH (uavmvs_bvh_build_lbvh, %.3f s, not timed)"
+                       % build_s, "l2": "flushed between steps (256 MiB fill)", "rays_per_step": rays,
+                       "observations_per_step": observations, "pairs_per_step": pairs,
+                       "sharding": "replicated mesh, interleaved %d-point Z-order chunks, 1 score all-reduce" % CHUNK},
+            "pairs_per_s": pairs * a.steps / sec, "score": res["score"],
+            "stage_ms": {"K1": k1_ms, "K2": float(k_ms[1]) / a.steps, "K3_K8": float(k_ms[2]) / a.steps,
+                         "K9": float(k_ms[3]) / a.steps},
+            "e2e": {"value": rays * a.steps / e2e_sec, "unit": UNIT, "ms_per_step": e2e_ms / a.steps,
+                    "h2d_bytes_per_step": int(views_np.nbytes), "d2h_bytes_per_step": int(8 * n_local + 12 + 32)},
+            "gpu_launches": 5 * a.steps, "clocks": clocks}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: CPU baseline + roofline of the dominant kernel (K1) ------------------------
+    import oracle as orc
+    orc.build()
+    nodes, aabbs, tris, indices = bvh.export()
+    same_tree = orc.BVH.from_arrays(orc.TreeArrays(nodes, aabbs, tris, indices))
+    probe = cpu_step(orc, same_tree, sc, pick_views(V, 24), pts, nrm)      # instrumented walk of the SAME tree
+    b_ray, per_ray = bytes_per_ray(probe["counters"])
+    stored = min(observations, 32 * res["points"])
+    alg_bytes = (rays / world) * b_ray + n_local * (32 + 4) + (stored / world) * 16 + V * 112
+    achieved = alg_bytes / (k1_ms / 1e3) / 1e9 if k1_ms > 0 else 0.0
+    traffic = ncu_traffic()
+    line["roofline"] = {"bound": "hbm", "kernel": "k_update_observation_rays<true> (K1, all views in one launch)",
+                        "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                        "traffic": None if traffic is None else traffic.get("dram_bytes_per_launch"),
+                        "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                        "bytes_per_ray": b_ray, "per_ray": per_ray, "kernel_ms": k1_ms,
+                        "note": "per-ray counters from the oracle's instrumented reference traversal of the same "
+                                "(exported) tree on a 24-view sample; the tree (%.0f MB) is L2-resident, so "
+                                "algorithmic bytes exceed DRAM traffic" % ((nodes.nbytes + aabbs.nbytes + tris.nbytes) / 1e6)}
+    if world == 1 and not a.no_cpu_baseline:
+        tree, built_by, tree_s = cpu_tree(orc, sc)
+        nviews = calibrate_cpu_sample(orc, tree, sc, pts, nrm, a.cpu_seconds)
+        vidx = pick_views(V, nviews)
+        r = cpu_step(orc, tree, sc, vidx, pts, nrm)
+        line["cpu_baseline"] = {
+            "value": r["rays"] / r["seconds"], "unit": UNIT, "cores": host_threads(), "kind": "port",
+            "pairs_per_s": r["pairs"] / r["seconds"],
+            "sample": "%d of %d views (evenly strided) x all %d points, %.1f s; tree: %s (%.2f s, not timed); kernel "
+                      "math: oracle port of libs/eval/kernels.cu, OpenMP over points" %
+                      (len(vidx), V, n_local, r["seconds"], built_by, tree_s)}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if a.impl == "reference":
+        run_reference(a, rank, world)
+        return
+    run_b200(a, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -140,6 +140,11 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
     uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4]);
 
+/* Device time (ms, CUDA events on the call's stream) of the stages of the calling thread's last
+ * uavmvs_evaluate_trajectory*: ms[0] = K1 (all views), [1] = K2, [2] = K3+K8, [3] = K9.  The
+ * reference only wall-clocks the K1 loop (apps/evaluate_trajectory/evaluate_trajectory.cu:144-171). */
+int uavmvs_profile_last(float ms[4]);
+
 /* ---- K4 populate_spherical_histogram (6-arg), kernels.h:46-50, kernels.cu:293-336 */
 int uavmvs_populate_spherical_histogram(void * stream, const float view_pos[3], float max_distance,
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd,

@@ -1,0 +1,132 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/uavmvs_b200.h
+declares (no compute calls without a GPU), the host mirror fails loudly without a device,
+scene generators are deterministic, and the N>1 sharding logic under gloo (world size 2)."""
+import ctypes
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    from uavmvs_b200 import build
+    return build.build()
+
+
+def test_library_exports_every_declared_symbol(built):
+    from uavmvs_b200 import abi
+    names = abi.declared_symbols()
+    assert len(names) >= 40 and "uavmvs_update_observation_rays" in names and "uavmvs_evaluate_trajectory" in names
+    assert abi.missing_symbols() == []
+
+
+def test_header_compiles_as_c(tmp_path):
+    src = tmp_path / "t.c"
+    src.write_text('#include "uavmvs_b200.h"\nint main(void) { return UAVMVS_VIEW_FLOATS == 28 ? 0 : 1; }\n')
+    import subprocess
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-c", str(src),
+                           "-o", str(tmp_path / "t.o")])
+
+
+def test_no_cpu_fallback(built):
+    """Without a device every entry point reports an error instead of computing on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from uavmvs_b200 import api
+    with pytest.raises(api.UavmvsError):
+        api.PointCloud.create(np.zeros((4, 3), np.float32), np.zeros((4, 3), np.float32))
+    with pytest.raises(api.UavmvsError):
+        api.VectorArray.create(4, 32)
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "uavmvs_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".hpp")):
+                text = open(os.path.join(dirpath, fn)).read()
+                assert "import oracle" not in text and "liboracle" not in text and "libref_acc" not in text, fn
+
+
+def test_scenes_are_deterministic():
+    from uavmvs_b200 import scenes
+    a, b = scenes.tiny(), scenes.tiny()
+    for name in ("verts", "faces", "points", "normals", "view_pos", "w2c", "calib"):
+        assert np.array_equal(getattr(a, name), getattr(b, name))
+    assert a.views28().shape == (a.num_views, 28) and a.views28().dtype == np.float32
+    assert np.allclose(np.linalg.norm(a.normals, axis=1), 1.0, atol=1e-5)
+    c = scenes.config1(num_points=2000)
+    assert c.num_tris == 20482 and 150 <= c.num_views <= 260
+
+
+def test_shard_ranges_cover_the_cloud():
+    from uavmvs_b200.sharded import shard_range
+    for n in (1, 7, 1000, 1_000_003):
+        for world in (1, 2, 3, 8):
+            r = [shard_range(n, k, world) for k in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
+            assert max(hi - lo for lo, hi in r) - min(hi - lo for lo, hi in r) <= (n + world - 1) // world
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _gloo_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    import oracle
+    from uavmvs_b200 import scenes, sharded
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    sc = scenes.tiny()
+    obvh = oracle.BVH.build(sc.verts, sc.faces, threads=1)      # replicated mesh
+    lo, hi = sharded.shard_range(sc.num_points, rank, world)
+    obs = oracle.ObsRays(hi - lo, 32)                           # the oracle stands in for the GPU shard here
+    _, cnt = oracle.update_observation_rays(obvh, True, sc.views28(), sc.max_distance, sc.width, sc.height,
+                                            sc.points[lo:hi], sc.normals[lo:hi], obs, want_counters=True)
+    oracle.process_observation_rays(obs)
+    recons = oracle.evaluate_observation_rays(obs)
+    w = oracle.calculate_func_recons(recons, sc.target_recon)
+    red = oracle.reduce(w)
+    res = sharded.combine_scores(red[0], red[1], red[2], hi - lo, [int(cnt[0]), int(obs.num_rows.sum()), 0, 0])
+    full = sharded.gather_point_vector(recons, sc.num_points)
+    counts = sharded.gather_point_vector(obs.num_rows, sc.num_points)
+    import torch
+    h = torch.full((2, 8), float(rank + 1), dtype=torch.float32)
+    sharded.allreduce_histograms(h)
+    if rank == 0:
+        np.savez(os.path.join(out_dir, "r.npz"), score=res["score"], mn=res["min"], mx=res["max"], pts=res["points"],
+                 rays=res["stats"][0], obs=res["stats"][1], full=full, counts=counts, h=h.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_point_sharding_world2_gloo(tmp_path, oracle, tiny_scene, tiny_tree):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r = np.load(tmp_path / "r.npz")
+    sc = tiny_scene
+    obvh, _ = tiny_tree
+    obs = oracle.ObsRays(sc.num_points, 32)
+    _, cnt = oracle.update_observation_rays(obvh, True, sc.views28(), sc.max_distance, sc.width, sc.height,
+                                            sc.points, sc.normals, obs, want_counters=True)
+    oracle.process_observation_rays(obs)
+    recons = oracle.evaluate_observation_rays(obs)
+    w = oracle.calculate_func_recons(recons, sc.target_recon)
+    assert int(r["pts"]) == sc.num_points and int(r["rays"]) == int(cnt[0]) and int(r["obs"]) == int(obs.num_rows.sum())
+    assert np.array_equal(r["full"].view(np.uint32), recons.view(np.uint32))     # shards are independent
+    assert np.array_equal(r["counts"], obs.num_rows)
+    assert abs(float(r["score"]) - float(w.astype(np.float64).mean())) < 1e-9
+    assert float(r["mn"]) == float(w.min()) and float(r["mx"]) == float(w.max())
+    assert np.all(r["h"] == 3.0)

@@ -208,9 +208,10 @@ class VectorArray(_Handle):
     def null(self, stream=None):
         _check(_lib.uavmvs_obs_clear(_stream_ptr(stream), self.ptr))
 
-    def download(self, data=True):
+    def download(self, data=True, rows_out=None):
         d = np.empty((self.max_rows, self.num_cols, 4), np.float32) if data else None
-        r = np.empty(self.num_cols, np.uint32)
+        r = np.empty(self.num_cols, np.uint32) if rows_out is None else rows_out
+        assert r.dtype == np.uint32 and r.size == self.num_cols
         _check(_lib.uavmvs_obs_download(self.ptr, _p(d), _p(r)))
         return d, r
 
@@ -235,8 +236,11 @@ class Array(_Handle):
     def null(self, stream=None):
         _check(_lib.uavmvs_array_null(_stream_ptr(stream), self.ptr))
 
-    def download(self):
-        out = np.empty(self.n, np.float32)
+    def download(self, out=None):
+        """`out`: optional host float32 array of n elements (e.g. a view of pinned memory)."""
+        if out is None:
+            out = np.empty(self.n, np.float32)
+        assert out.dtype == np.float32 and out.size == self.n and out.flags["C_CONTIGUOUS"]
         _check(_lib.uavmvs_array_download(self.ptr, _p(out)))
         return out
 
@@ -337,6 +341,13 @@ def evaluate_trajectory(views, max_distance, target_recon, width, height, bvh_tr
             _i32(width), _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr, recons.ptr, wrecons.ptr, out, stats))
     st = [int(x) for x in stats] if want_stats else None
     return float(out[0]), float(out[1]), float(out[2]), st
+
+
+def profile_last():
+    """Device ms of K1, K2, K3+K8, K9 of this thread's last evaluate_trajectory call."""
+    ms = (C.c_float * 4)()
+    _check(_lib.uavmvs_profile_last(ms))
+    return [float(x) for x in ms]
 
 
 def populate_spherical_histogram(view_pos, max_distance, bvh_tree, cloud, kd_tree, sphere_hist, stream=None,

@@ -362,6 +362,8 @@ struct Scratch {   // per-process scratch on the device (views, reduction accumu
     ReduceAcc * acc = nullptr;
     unsigned long long * stats = nullptr;
     ReduceAcc * h_acc = nullptr; unsigned long long * h_stats = nullptr;   // pinned
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};     // K1 | K2 | K3+K8 | K9 boundaries
+    bool ev_valid = false;
 };
 static thread_local Scratch g_scratch;
 
@@ -373,6 +375,7 @@ static int ensure_scratch(size_t view_floats)
         UAV_CUDA(cudaMalloc(&s.stats, 4 * sizeof(unsigned long long)));
         UAV_CUDA(cudaMallocHost(&s.h_acc, sizeof(ReduceAcc)));
         UAV_CUDA(cudaMallocHost(&s.h_stats, 4 * sizeof(unsigned long long)));
+        for (int i = 0; i < 5; ++i) UAV_CUDA(cudaEventCreate(&s.ev[i]));
     }
     if (view_floats > s.views_cap) {
         if (s.views) cudaFree(s.views);
@@ -529,14 +532,21 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
     if (ensure_scratch(0)) return 1;
     UAV_CUDA(cudaMemsetAsync(obs->num_rows, 0, 4 * (size_t)obs->num_cols, s));
     if (stats) UAV_CUDA(cudaMemsetAsync(g_scratch.stats, 0, 4 * sizeof(unsigned long long), s));
+    g_scratch.ev_valid = false;
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[0], s));
     int rc = launch_k1(s, 1, d_views, num_views, max_distance, width, height, bvh, cloud, obs,
         stats ? g_scratch.stats : nullptr);
     if (rc) return rc;
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[1], s));
     rc = uavmvs_process_observation_rays(stream, obs);
     if (rc) return rc;
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[2], s));
     rc = launch_k3(s, obs, recons, target_recon, wrecons);
     if (rc) return rc;
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[3], s));
     if (launch_reduce(s, wrecons)) return 1;
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[4], s));
+    g_scratch.ev_valid = true;
     if (stats) UAV_CUDA(cudaMemcpyAsync(g_scratch.h_stats, g_scratch.stats, 4 * sizeof(unsigned long long),
         cudaMemcpyDeviceToHost, s));
     if (out3 || stats) {
@@ -544,6 +554,15 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
         if (out3) { out3[0] = (float)g_scratch.h_acc->sum; out3[1] = ord2f(g_scratch.h_acc->mn); out3[2] = ord2f(g_scratch.h_acc->mx); }
         if (stats) for (int i = 0; i < 4; ++i) stats[i] = g_scratch.h_stats[i];
     }
+    return 0;
+}
+
+int uavmvs_profile_last(float ms[4])
+{
+    UAV_REQUIRE(ms, "null argument");
+    UAV_REQUIRE(g_scratch.ev_valid, "no evaluate_trajectory call recorded on this thread");
+    UAV_CUDA(cudaEventSynchronize(g_scratch.ev[4]));
+    for (int i = 0; i < 4; ++i) UAV_CUDA(cudaEventElapsedTime(&ms[i], g_scratch.ev[i], g_scratch.ev[i + 1]));
     return 0;
 }
 

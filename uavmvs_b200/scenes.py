@@ -277,8 +277,8 @@ def config1(num_points=100_000, seed=7):
     verts = np.concatenate([sv, gv]).astype(np.float32)
     faces = np.concatenate([sf, gf]).astype(np.uint32)
     pts, nrm = sample_cloud(verts, faces, num_points, seed)
-    specs = lawnmower(-g, -g, g, g, 75.0, 0.70, 0.50, 0.0) + \
-        lawnmower(-g, -g, g, g, 75.0, 0.70, 0.50, 30.0, heading_deg=90.0)
+    specs = lawnmower(-g, -g, g, g, 75.0, 0.80, 0.50, 0.0) + \
+        lawnmower(-g, -g, g, g, 75.0, 0.80, 0.50, 30.0, heading_deg=90.0)
     pos, w2c, calib = _pack_views(specs)
     n = pts.shape[0]
     return Scene("config1_sphere", verts, faces, pts, nrm, np.zeros(n, np.float32), np.ones(n, np.float32),
@@ -315,3 +315,10 @@ def tiny(num_points=4096, num_views=24, seed=3):
     """Small urban patch for fast parity tests."""
     return urban(num_tris=6000, num_points=num_points, num_views=num_views, extent=96.0, seed=seed,
                  name="tiny_urban")
+
+
+def dense(num_points=8192, num_views=160, seed=5):
+    """Small block flown densely: ~15 observations per point, some beyond the 32-row cap
+    (exercises row order, the cap, the sort network and the pair sums)."""
+    return urban(num_tris=8000, num_points=num_points, num_views=num_views, extent=64.0, seed=seed,
+                 name="dense_urban")
