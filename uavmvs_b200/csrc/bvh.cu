@@ -46,6 +46,23 @@ __global__ void k_build_inner(const uint4 * __restrict__ nodes, const float * __
     inner[slot[i]] = o;
 }
 
+// nested[0] = 0 unless every child box lies inside its parent's box (NaNs count as not nested)
+__global__ void k_check_nested(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n,
+    uint32_t * __restrict__ violations)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 nd = nodes[i];
+    if (nd.z == UAV_NAI || nd.w == UAV_NAI) return;
+    const float * p = aabbs + 6 * (size_t)i;
+    bool ok = true;
+    for (int c = 0; c < 2; ++c) {
+        const float * q = aabbs + 6 * (size_t)(c ? nd.w : nd.z);
+        for (int k = 0; k < 3; ++k) ok = ok && (q[k] >= p[k]) && (q[3 + k] <= p[3 + k]) && (q[k] <= q[3 + k]);
+    }
+    if (!ok) atomicAdd(violations, 1u);
+}
+
 // Per-triangle constants with the reference's operation order (libs/acc/primitives.h:
 // 217-225 normal, :139-145 Gram terms).  Degenerate triangles (|N| < eps, rejected at
 // :222) get a zero normal, which the |cosine| < eps test rejects.
@@ -90,6 +107,15 @@ static int finalize_layout(uavmvs_bvh * b)
     b->root_first = root.x; b->root_count = root.y - root.x;
     UAV_CUDA(cudaMalloc(&b->inner, sizeof(Node64) * (size_t)(b->num_inner ? b->num_inner : 1)));
     UAV_CUDA(cudaMalloc(&b->ptris, sizeof(Tri64) * (size_t)t));
+    {
+        uint32_t * viol = nullptr, h_viol = 1;
+        UAV_CUDA(cudaMalloc(&viol, 4));
+        UAV_CUDA(cudaMemset(viol, 0, 4));
+        k_check_nested<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, n, viol);
+        UAV_CUDA(cudaMemcpy(&h_viol, viol, 4, cudaMemcpyDeviceToHost));
+        cudaFree(viol);
+        b->nested = h_viol == 0 ? 1u : 0u;
+    }
     k_build_inner<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->inner);
     k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
     UAV_CUDA(cudaGetLastError());

@@ -58,6 +58,7 @@ struct uavmvs_bvh {
     uav::Node64 * inner;
     uav::Tri64 * ptris;
     uint32_t root_is_leaf, root_first, root_count;
+    uint32_t nested;    // every child box lies inside its parent's box (checked at upload)
 };
 
 struct uavmvs_kdtree {
@@ -73,6 +74,9 @@ struct uavmvs_cloud {
     // per 32-point block: bounding sphere (xyz, r) for the conservative view cull
     float4 * block_sphere;
     uint32_t num_blocks;
+    // per super-block (32 blocks = 1024 points): sphere enclosing its block spheres
+    float4 * super_sphere;
+    uint32_t num_super;
 };
 
 struct uavmvs_obs {

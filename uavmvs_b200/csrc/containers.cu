@@ -28,6 +28,28 @@ __global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, f
     if (lane == 0) out[blk] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
 }
 
+// Sphere around the 32 block spheres of a super-block (centre = centre of the box of the block
+// centres; radius = max over blocks of |c - c_b| + r_b, padded against rounding).
+__global__ void k_super_spheres(const float4 * __restrict__ blocks, uint32_t num_blocks, float4 * __restrict__ out)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t sb = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (sb * 32 >= num_blocks) return;
+    uint32_t b = sb * 32 + lane;
+    float4 s = blocks[b < num_blocks ? b : num_blocks - 1];
+    float mn[3] = {s.x, s.y, s.z}, mx[3] = {s.x, s.y, s.z};
+    for (int k = 0; k < 3; ++k)
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    float cx = 0.5f * (mn[0] + mx[0]), cy = 0.5f * (mn[1] + mx[1]), cz = 0.5f * (mn[2] + mx[2]);
+    float dx = s.x - cx, dy = s.y - cy, dz = s.z - cz;
+    float r = sqrtf(dx * dx + dy * dy + dz * dz) * 1.0001f + s.w;
+    for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+    if (lane == 0) out[sb] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
+}
+
 __global__ void k_pad3(const float * __restrict__ in, uint32_t n, float4 * __restrict__ out)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -92,6 +114,8 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     UAV_CUDA(cudaMalloc(&c->values, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->qualities, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->block_sphere, sizeof(float4) * (size_t)c->num_blocks));
+    c->num_super = divup(c->num_blocks, 32);
+    UAV_CUDA(cudaMalloc(&c->super_sphere, sizeof(float4) * (size_t)c->num_super));
     if (upload3(vertices, n, c->vertices)) return 1;
     if (upload3(normals, n, c->normals)) return 1;
     if (values) UAV_CUDA(cudaMemcpy(c->values, values, 4 * (size_t)n, cudaMemcpyHostToDevice));
@@ -99,6 +123,7 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)n, cudaMemcpyHostToDevice));
     else k_fill<<<divup(n, 256), 256>>>(c->qualities, n, 1.0f);     /* libs/util/cio.h:46 */
     k_block_spheres<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere);
+    k_super_spheres<<<divup((uint64_t)c->num_super * 32, 128), 128>>>(c->block_sphere, c->num_blocks, c->super_sphere);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaDeviceSynchronize());
     *out = c;
@@ -127,7 +152,7 @@ int uavmvs_cloud_destroy(uavmvs_cloud * c)
 {
     if (!c) return 0;
     cudaFree(c->vertices); cudaFree(c->normals); cudaFree(c->values); cudaFree(c->qualities);
-    cudaFree(c->block_sphere);
+    cudaFree(c->block_sphere); cudaFree(c->super_sphere);
     delete c;
     return 0;
 }

@@ -212,3 +212,59 @@ __device__ __forceinline__ bool trace_closest_warp(const BvhView & bvh, Ray ray,
 }
 
 }  // namespace uav
+
+// ---- lean filtered node test (K1 traversal) ---------------------------------------------
+// Same idea as slab_bool() with one FFMA per plane: t~ = fma(b, rd, -(o * rd)).  Against the
+// reference's fl(fl(b - o) / d) this carries a relative error < 4 * 2^-24 plus an ABSOLUTE
+// error <= 2^-24 |o / d| (the rounding of o * rd is not cancelled when b is close to o), so
+// the undecided band is m = 1e-6 (|Tmin~| + |Tmax~|) + eabs with
+// eabs = 3e-7 (|o.x rd.x| + |o.y rd.y| + |o.z rd.z|) >= 2 * 2^-23 max_k |o_k rd_k|.
+// Rays that may not use the fast path get eabs = +inf: every test of theirs is "undecided".
+namespace uav {
+
+struct RayF {            // per-lane traversal constants
+    float rdx, rdy, rdz;       // fl(1 / d)
+    float nox, noy, noz;       // -(o * rd)
+    float tmin, tmax, eabs;
+};
+
+__device__ __forceinline__ RayF make_rayf(const Ray & r)
+{
+    RayF f;
+    f.rdx = 1.0f / r.d.x; f.rdy = 1.0f / r.d.y; f.rdz = 1.0f / r.d.z;
+    float ox = r.o.x * f.rdx, oy = r.o.y * f.rdy, oz = r.o.z * f.rdz;
+    f.nox = -ox; f.noy = -oy; f.noz = -oz;
+    f.tmin = r.tmin; f.tmax = r.tmax;
+    float m = fminf(fminf(fabsf(r.d.x), fabsf(r.d.y)), fabsf(r.d.z));
+    float M = fmaxf(fmaxf(fabsf(r.d.x), fabsf(r.d.y)), fabsf(r.d.z));
+    bool fast = (m > 1e-12f) && (M < 1e12f) && (fabsf(ox) + fabsf(oy) + fabsf(oz) < 1e30f);
+    f.eabs = fast ? 3e-7f * (fabsf(ox) + fabsf(oy) + fabsf(oz)) : UAV_INF;
+    return f;
+}
+
+// decided: hit is the reference's decision.  !decided: caller must run slab() (exact).
+__device__ __forceinline__ void slab_fast(const RayF & f, float mnx, float mny, float mnz,
+    float mxx, float mxy, float mxz, bool & hit, bool & decided, float & tnear)
+{
+    float ax = __fmaf_rn(mnx, f.rdx, f.nox), bx = __fmaf_rn(mxx, f.rdx, f.nox);
+    float ay = __fmaf_rn(mny, f.rdy, f.noy), by = __fmaf_rn(mxy, f.rdy, f.noy);
+    float az = __fmaf_rn(mnz, f.rdz, f.noz), bz = __fmaf_rn(mxz, f.rdz, f.noz);
+    float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), f.tmin));
+    float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), f.tmax));
+    float lo = fmaxf(tmin, 0.0f);
+    float g = tmax - lo;
+    float m = __fmaf_rn(1e-6f, fabsf(tmin) + fabsf(tmax), f.eabs);
+    hit = g > m;
+    decided = hit || (g < -m);     // NaN / inf anywhere: neither holds -> undecided
+    tnear = tmin;
+}
+
+static __device__ __noinline__ bool slab_exact_call(float ox, float oy, float oz, float dx, float dy, float dz,
+    float tmin, float tmax, float mnx, float mny, float mnz, float mxx, float mxy, float mxz)
+{
+    Ray r; r.o = mk(ox, oy, oz); r.d = mk(dx, dy, dz); r.tmin = tmin; r.tmax = tmax;
+    float t;
+    return slab(r, mnx, mny, mnz, mxx, mxy, mxz, t);
+}
+
+}  // namespace uav
