@@ -35,7 +35,8 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return SO
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
+    extra = os.environ.get("UAV_NVCC_EXTRA", "").split()
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
     subprocess.check_call(cmd)
     return SO
 

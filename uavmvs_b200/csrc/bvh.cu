@@ -46,6 +46,39 @@ __global__ void k_build_inner(const uint4 * __restrict__ nodes, const float * __
     inner[slot[i]] = o;
 }
 
+// One thread per inner binary node: its Node128 from the grandchildren.
+__global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs,
+    const uint32_t * __restrict__ flag, const uint32_t * __restrict__ slot, uint32_t n,
+    Node128 * __restrict__ wide)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !flag[i]) return;
+    uint4 nd = nodes[i];
+    uint32_t kids[4]; int nk = 0;
+    for (int c = 0; c < 2; ++c) {
+        uint32_t ch = c ? nd.w : nd.z;
+        if (flag[ch]) { uint4 cn = nodes[ch]; kids[nk++] = cn.z; kids[nk++] = cn.w; }
+        else kids[nk++] = ch;
+    }
+    float b[24]; uint32_t ref[4], cnt[4];
+    for (int k = 0; k < 4; ++k) {
+        if (k < nk) {
+            uint32_t ch = kids[k];
+            for (int j = 0; j < 6; ++j) b[6 * k + j] = aabbs[6 * (size_t)ch + j];
+            if (flag[ch]) { ref[k] = slot[ch]; cnt[k] = 0u; }
+            else { uint4 cn = nodes[ch]; ref[k] = cn.x; cnt[k] = cn.y - cn.x; }
+        } else {
+            for (int j = 0; j < 6; ++j) b[6 * k + j] = 0.0f;
+            ref[k] = 0u; cnt[k] = UAV_NAI;
+        }
+    }
+    Node128 o;
+    for (int j = 0; j < 6; ++j) o.q[j] = make_float4(b[4 * j], b[4 * j + 1], b[4 * j + 2], b[4 * j + 3]);
+    o.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
+    o.cnt = make_uint4(cnt[0], cnt[1], cnt[2], cnt[3]);
+    wide[slot[i]] = o;
+}
+
 // nested[0] = 0 unless every child box lies inside its parent's box (NaNs count as not nested)
 __global__ void k_check_nested(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n,
     uint32_t * __restrict__ violations)
@@ -106,6 +139,7 @@ static int finalize_layout(uavmvs_bvh * b)
     b->root_is_leaf = !(root.z != UAV_NAI && root.w != UAV_NAI);
     b->root_first = root.x; b->root_count = root.y - root.x;
     UAV_CUDA(cudaMalloc(&b->inner, sizeof(Node64) * (size_t)(b->num_inner ? b->num_inner : 1)));
+    UAV_CUDA(cudaMalloc(&b->wide, sizeof(Node128) * (size_t)(b->num_inner ? b->num_inner : 1)));
     UAV_CUDA(cudaMalloc(&b->ptris, sizeof(Tri64) * (size_t)t));
     {
         uint32_t * viol = nullptr, h_viol = 1;
@@ -117,6 +151,7 @@ static int finalize_layout(uavmvs_bvh * b)
         b->nested = h_viol == 0 ? 1u : 0u;
     }
     k_build_inner<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->inner);
+    k_build_wide<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->wide);
     k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaDeviceSynchronize());
@@ -374,7 +409,7 @@ int uavmvs_bvh_destroy(uavmvs_bvh * b)
 {
     if (!b) return 0;
     cudaFree(b->nodes); cudaFree(b->aabbs); cudaFree(b->tris); cudaFree(b->indices);
-    cudaFree(b->inner); cudaFree(b->ptris);
+    cudaFree(b->inner); cudaFree(b->wide); cudaFree(b->ptris);
     delete b;
     return 0;
 }

@@ -40,6 +40,14 @@ static inline unsigned divup(uint64_t a, uint64_t b) { return (unsigned)((a + b 
 //   q3 = {left_ref, right_ref, left_count, right_count}
 // count == 0: ref = index of an inner node;  count > 0: ref = first triangle of a leaf.
 struct __align__(64) Node64 { float4 q0, q1, q2; uint4 q3; };
+// Four-child node, 128 B (one cache line): the up-to-four GRANDCHILDREN of a binary node (a leaf
+// child stays one child), boxes as the reference's exact floats.
+//   q[0..2] = boxes of children 0,1 (same packing as Node64 q0..q2), q[3..5] = children 2,3
+//   ref[c]  = index of an inner node (cnt[c] == 0) or first triangle of a leaf (cnt[c] = its size)
+//   cnt[c]  = UAV_NAI: empty slot
+// Every inner binary node owns one (indexed like Node64); a traversal that starts at the root only
+// ever touches those of even depth.
+struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
 // Pre-reduced triangle, 64 B: a, ab, ac, unit normal (N/|N|), d00, d01, d11, denom.
 // All derived values are computed with the reference's operation order, so using them
 // gives bit-identical operands (libs/acc/primitives.h:214-248, :134-153).
@@ -56,6 +64,7 @@ struct uavmvs_bvh {
     uint32_t * indices; // face ids
     // traversal layout
     uav::Node64 * inner;
+    uav::Node128 * wide;
     uav::Tri64 * ptris;
     uint32_t root_is_leaf, root_first, root_count;
     uint32_t nested;    // every child box lies inside its parent's box (checked at upload)

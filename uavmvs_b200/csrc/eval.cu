@@ -85,10 +85,11 @@ struct K1Args {
 
 constexpr int K1_WARPS = 4;
 constexpr int K1_RING = 128;      // reorder ring entries per warp
-constexpr int K1_PEND = 4;        // deferred leaves per lane
+constexpr int K1_PEND = 6;        // deferred leaves per lane
 constexpr int K1_REFILL = 8;      // refill when at least this many lanes are idle
 constexpr int K1_TRI = 8;         // run the triangle phase when this many lanes hold a leaf
 constexpr int K1_SB_PER_WARP = 8;
+constexpr int K1_STACK = 160;     // <= 3 pushes per two binary levels; LBVH depth <= 96
 constexpr int K1_STEPS = 4;       // node steps between two rounds of warp-level bookkeeping
 
 // Conservative (group of points, view) test: false only if NO point inside the sphere
@@ -188,8 +189,11 @@ struct K1Warp {
 // its IEEE-division fallback, is needed for leaf boxes alone.  Rays for which the argument
 // does not hold (a zero / tiny / non-finite direction component: NaN in the slab chain) have
 // eabs = inf and take the exact test at every node.
+#ifndef K1_MIN_BLOCKS
+#define K1_MIN_BLOCKS 5
+#endif
 template <bool POPULATE, bool EXACT_INNER>
-__global__ void __launch_bounds__(K1_WARPS * 32)
+__global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS)
 k_update_observation_rays(K1Args a)
 {
     __shared__ K1Warp s_warp[K1_WARPS];
@@ -197,7 +201,7 @@ k_update_observation_rays(K1Args a)
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t V = a.num_views;
-    uint32_t stack[UAV_STACK];
+    uint32_t stack[K1_STACK];
     unsigned long long st_rays = 0, st_vis = 0;
 
     for (;;) {
@@ -363,35 +367,54 @@ k_update_observation_rays(K1Args a)
                 }
             }
 
-            // ---------------- K1_STEPS traversal steps ----------------
+            // ---------------- K1_STEPS traversal steps (4-wide nodes) ----------------
             #pragma unroll 1
             for (int step = 0; step < K1_STEPS; ++step) {
-                if (traversing && npend <= K1_PEND - 2) {
-                    const Node64 * np = a.bvh.inner + cur;
-                    float4 q0 = __ldg(&np->q0), q1 = __ldg(&np->q1), q2 = __ldg(&np->q2);
-                    uint4 q3 = __ldg(&np->q3);
-                    bool sl, sr, dl, dr; float tl, tr;        // sure hit, decided
-                    slab_fast(rf, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, sl, dl, tl);
-                    slab_fast(rf, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, sr, dr, tr);
-                    const bool leaf_l = q3.z != 0u, leaf_r = q3.w != 0u;
+                if (traversing && npend <= K1_PEND - 4) {
+                    const Node128 * np = a.bvh.wide + cur;
+                    const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
+                    const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
+                    const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
+                    bool s0, s1, s2, s3, d0, d1, d2, d3; float t0, t1, t2, t3;   // sure hit, decided, entry
+                    slab_fast(rf, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, s0, d0, t0);
+                    slab_fast(rf, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, s1, d1, t1);
+                    slab_fast(rf, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y, s2, d2, t2);
+                    slab_fast(rf, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w, s3, d3, t3);
+                    const bool always_exact = EXACT_INNER || rf.eabs == UAV_INF;
+                    const bool l0 = cnt.x != 0u, l1 = cnt.y != 0u, l2 = cnt.z != 0u, l3 = cnt.w != 0u;   // leaf (or empty)
                     // undecided boxes: exact test where the decision matters, conservative visit elsewhere
-                    const bool xl = !dl && (EXACT_INNER || leaf_l || rf.eabs == UAV_INF);
-                    const bool xr = !dr && (EXACT_INNER || leaf_r || rf.eabs == UAV_INF);
-                    bool hl = sl || !dl, hr = sr || !dr;
-                    if (xl || xr) {                           // rare
-                        if (xl) hl = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
+                    bool h0 = (s0 || !d0) && cnt.x != UAV_NAI, h1 = (s1 || !d1) && cnt.y != UAV_NAI;
+                    bool h2 = (s2 || !d2) && cnt.z != UAV_NAI, h3 = (s3 || !d3) && cnt.w != UAV_NAI;
+                    const bool x0 = h0 && !d0 && (always_exact || l0), x1 = h1 && !d1 && (always_exact || l1);
+                    const bool x2 = h2 && !d2 && (always_exact || l2), x3 = h3 && !d3 && (always_exact || l3);
+                    if (x0 || x1 || x2 || x3) {               // rare
+                        if (x0) h0 = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
                                                      q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-                        if (xr) hr = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
+                        if (x1) h1 = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
                                                      q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+                        if (x2) h2 = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
+                                                     q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
+                        if (x3) h3 = slab_exact_call(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, rf.tmin, rf.tmax,
+                                                     q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
                     }
                     // leaf children are deferred (any-hit is order independent)
-                    if (hl && leaf_l) { defer_leaf(q3.x, q3.z); hl = false; }
-                    if (hr && leaf_r) { defer_leaf(q3.y, q3.w); hr = false; }
-                    if (hl && hr) {
-                        bool lf = tl < tr;
-                        stack[sp++] = lf ? q3.y : q3.x;
-                        cur = lf ? q3.x : q3.y;
-                    } else if (hl || hr) cur = hl ? q3.x : q3.y;
+                    if (h0 && l0) defer_leaf(ref.x, cnt.x);
+                    if (h1 && l1) defer_leaf(ref.y, cnt.y);
+                    if (h2 && l2) defer_leaf(ref.z, cnt.z);
+                    if (h3 && l3) defer_leaf(ref.w, cnt.w);
+                    // inner children: nearest first, the others go on the stack
+                    const float k0 = (h0 && !l0) ? t0 : UAV_INF, k1 = (h1 && !l1) ? t1 : UAV_INF;
+                    const float k2 = (h2 && !l2) ? t2 : UAV_INF, k3 = (h3 && !l3) ? t3 : UAV_INF;
+                    // (an entry distance is never +inf for a box that can be hit: tmin <= tmax <= ray.tmax)
+                    float kb = k0; uint32_t rb = ref.x;
+                    if (k1 < kb) { kb = k1; rb = ref.y; }
+                    if (k2 < kb) { kb = k2; rb = ref.z; }
+                    if (k3 < kb) { kb = k3; rb = ref.w; }
+                    if (k0 < UAV_INF && ref.x != rb) stack[sp++] = ref.x;
+                    if (k1 < UAV_INF && ref.y != rb) stack[sp++] = ref.y;
+                    if (k2 < UAV_INF && ref.z != rb) stack[sp++] = ref.z;
+                    if (k3 < UAV_INF && ref.w != rb) stack[sp++] = ref.w;
+                    if (kb < UAV_INF) cur = rb;
                     else if (sp > 0) cur = stack[--sp];
                     else traversing = false;
                 }
@@ -401,7 +424,7 @@ k_update_observation_rays(K1Args a)
                 uint32_t pmask = __ballot_sync(0xffffffffu, npend > 0);
                 if (pmask) {
                     uint32_t tmask = __ballot_sync(0xffffffffu, traversing);
-                    uint32_t full = __ballot_sync(0xffffffffu, npend > K1_PEND - 2);
+                    uint32_t full = __ballot_sync(0xffffffffu, npend > K1_PEND - 4);
                     if (__popc(pmask) >= K1_TRI || full || !tmask) {
                         if (npend > 0) {
                             Ray ray; ray.o = ro; ray.d = rd; ray.tmin = rf.tmin; ray.tmax = rf.tmax;
