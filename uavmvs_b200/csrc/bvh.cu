@@ -68,8 +68,10 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
             if (flag[ch]) { ref[k] = slot[ch]; cnt[k] = 0u; }
             else { uint4 cn = nodes[ch]; ref[k] = cn.x; cnt[k] = cn.y - cn.x; }
         } else {
-            for (int j = 0; j < 6; ++j) b[6 * k + j] = 0.0f;
-            ref[k] = 0u; cnt[k] = UAV_NAI;
+            // empty slot: a far-away point box that every ray surely misses (|t| ~ 1e18 / |d|),
+            // flagged as "inner" so that no leaf logic ever looks at it
+            for (int j = 0; j < 6; ++j) b[6 * k + j] = 1e18f;
+            ref[k] = 0u; cnt[k] = 0u;
         }
     }
     Node128 o;

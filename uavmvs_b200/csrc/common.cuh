@@ -44,7 +44,7 @@ struct __align__(64) Node64 { float4 q0, q1, q2; uint4 q3; };
 // child stays one child), boxes as the reference's exact floats.
 //   q[0..2] = boxes of children 0,1 (same packing as Node64 q0..q2), q[3..5] = children 2,3
 //   ref[c]  = index of an inner node (cnt[c] == 0) or first triangle of a leaf (cnt[c] = its size)
-//   cnt[c]  = UAV_NAI: empty slot
+//   empty slot: point box at 1e18 (no segment reaches it), ref = 0, cnt = 0
 // Every inner binary node owns one (indexed like Node64); a traversal that starts at the root only
 // ever touches those of even depth.
 struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
@@ -135,5 +135,11 @@ struct Ray { V3 o, d; float tmin, tmax; };
 // passed to kernels by value
 struct Heur { float m_k, m_x0, t_k, t_x0; };
 Heur current_heur();
+
+// K1 pipeline (k1.cu).  d_stats (device, may be null): [0] += occlusion rays, [1] += visible
+// observations, [3] += (point, view) pairs that survive the block-level cull.
+int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
+    float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    uavmvs_obs * obs, unsigned long long * d_stats);
 
 }  // namespace uav

@@ -1,0 +1,567 @@
+// K1: update_observation_rays over a whole trajectory (libs/eval/kernels.cu:138-202 launched
+// once per view by apps/evaluate_trajectory/evaluate_trajectory.cu:154-164), as a pipeline of
+// small kernels over an explicit ray list:
+//
+//   k_view_masks   conservative (super-block, view) then (block, view) range/frustum cull
+//                  -> masks[sb * V + v], bit b = "view v may see a point of block 32 sb + b"
+//   k_block_caps   per block: 32 x candidate views = upper bound of its rays -> exclusive scan
+//   k_cull_emit    warp per 32-point block: exact cull of kernels.cu:156-167 for the candidate
+//                  views in view order; every surviving (point, view) pair becomes one ray
+//                  record (unit direction, distance, point, view) in the block's slice
+//   k_trace        persistent warps stream over the ray list; idle lanes are refilled while
+//                  the others keep traversing the 4-wide BVH; leaf triangles are deferred
+//                  until several lanes hold one; one visibility byte per ray
+//   k_retire       warp per block, rays in (view, point) order: visible rays become
+//                  observation rows.  In-order retirement reproduces the row order and the
+//                  un-clamped counters of the reference's serial launch loop (:175-181).
+//
+// The ray list is why lanes never wait for each other's rays (rays binned by camera: the
+// rays of one block towards one view are adjacent) and why the traversal kernel is small.
+#include <cub/cub.cuh>
+
+#include "common.cuh"
+#include "trace.cuh"
+#include "evalmath.cuh"
+
+namespace uav {
+
+constexpr int K1_WARPS = 4;
+constexpr int K1_SB_PER_WARP = 8;
+constexpr int K1_PEND = 6;        // deferred leaves per lane
+constexpr int K1_REFILL = 8;      // refill when at least this many lanes are idle
+constexpr int K1_TRI = 8;         // run the triangle phase when this many lanes hold a leaf
+constexpr int K1_STACK = 160;     // <= 3 pushes per two binary levels; LBVH depth <= 96
+constexpr int K1_STEPS = 4;       // node steps between two rounds of warp-level bookkeeping
+
+// Conservative (group of points, view) test: false only if NO point inside the sphere
+// (centre c, radius r) can pass the exact cull of kernels.cu:164-167 (range, image bounds).
+// Margins are 100x above fp32 rounding of the exact test, so a rejected group is rejected
+// point by point by the exact arithmetic as well.
+__device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view, float4 sph,
+    float max_distance, int width, int height)
+{
+    float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
+    float D = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (D * 0.99999f - sph.w >= max_distance * 1.00001f) return false;
+    const float * W = view + 3; const float * K = view + 19;
+    float q[3], e2 = 0.0f, fro2 = 0.0f;
+    #pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float a = W[4 * i] * sph.x, b = W[4 * i + 1] * sph.y, c = W[4 * i + 2] * sph.z, d = W[4 * i + 3];
+        q[i] = a + b + c + d;
+        float e = 1e-6f * (fabsf(a) + fabsf(b) + fabsf(c) + fabsf(d));
+        e2 += e * e;
+        fro2 += W[4 * i] * W[4 * i] + W[4 * i + 1] * W[4 * i + 1] + W[4 * i + 2] * W[4 * i + 2];
+    }
+    float qn = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);
+    float rho = sph.w * sqrtf(fro2) * 1.001f + sqrtf(e2) + 1e-4f * (qn + 1.0f);
+    float k2n = sqrtf(K[6] * K[6] + K[7] * K[7] + K[8] * K[8]);
+    float p2 = K[6] * q[0] + K[7] * q[1] + K[8] * q[2];
+    if (!(p2 - k2n * rho > 0.0f)) return true;          // ball not entirely in front: undecided
+    float lim[4] = {0.5f, (float)width + 0.5f, 0.5f, (float)height + 0.5f};
+    #pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        int r = s >> 1;                                   // image row of K: 0 -> x, 1 -> y
+        float a0 = K[3 * r] - lim[s] * K[6], a1 = K[3 * r + 1] - lim[s] * K[7], a2 = K[3 * r + 2] - lim[s] * K[8];
+        float an = sqrtf(a0 * a0 + a1 * a1 + a2 * a2);
+        float v = a0 * q[0] + a1 * q[1] + a2 * q[2];
+        if ((s & 1) == 0) { if (v + an * rho < 0.0f) return false; }   // coordinate < 0 everywhere
+        else { if (v - an * rho > 0.0f) return false; }                // coordinate >= size everywhere
+    }
+    return true;
+}
+
+// One warp = one chunk of 32 views (a view per lane, kept in registers) x K1_SB_PER_WARP
+// super-blocks.  Surviving views are re-tested against the 32 blocks (a block per lane).
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 * __restrict__ super_spheres,
+    uint32_t num_super, const float4 * __restrict__ block_spheres, uint32_t num_blocks,
+    float max_distance, int width, int height, uint32_t * __restrict__ masks)
+{
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t v = blockIdx.x * 32 + lane;
+    const uint32_t sb0 = (blockIdx.y * K1_WARPS + w) * K1_SB_PER_WARP;
+    if (sb0 >= num_super) return;
+    float view[UAVMVS_VIEW_FLOATS];
+    const float * src = views + (size_t)(v < num_views ? v : num_views - 1) * UAVMVS_VIEW_FLOATS;
+    #pragma unroll
+    for (int i = 0; i < UAVMVS_VIEW_FLOATS / 4; ++i) {
+        float4 t = __ldg(reinterpret_cast<const float4 *>(src) + i);
+        view[4 * i] = t.x; view[4 * i + 1] = t.y; view[4 * i + 2] = t.z; view[4 * i + 3] = t.w;
+    }
+    for (uint32_t sb = sb0; sb < min(sb0 + K1_SB_PER_WARP, num_super); ++sb) {
+        bool cand = v < num_views && block_view_maybe(view, __ldg(super_spheres + sb), max_distance, width, height);
+        uint32_t m = __ballot_sync(0xffffffffu, cand);
+        uint32_t mine = 0;
+        const uint32_t b = sb * 32 + lane;
+        const float4 bs = __ldg(block_spheres + (b < num_blocks ? b : num_blocks - 1));
+        while (m) {
+            const int j = __ffs(m) - 1; m &= m - 1;
+            const float * vj = views + (size_t)(blockIdx.x * 32 + j) * UAVMVS_VIEW_FLOATS;   // uniform address
+            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height);
+            uint32_t word = __ballot_sync(0xffffffffu, c);
+            if ((int)lane == j) mine = word;
+        }
+        if (v < num_views) masks[(size_t)sb * num_views + v] = mine;
+    }
+}
+
+// caps[b] = 32 * number of candidate views of block b within [v0, v1)
+__global__ void k_block_caps(const uint32_t * __restrict__ masks, uint32_t num_views, uint32_t v0, uint32_t v1,
+    uint32_t num_blocks, uint32_t * __restrict__ caps)
+{
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= num_blocks) return;
+    const uint32_t * row = masks + (size_t)(b >> 5) * num_views;     // the same word for the 32 lanes: broadcast
+    const uint32_t bit = b & 31;
+    uint32_t c = 0;
+    for (uint32_t v = v0; v < v1; ++v) c += (__ldg(row + v) >> bit) & 1u;
+    caps[b] = 32u * c;
+}
+
+__global__ void k_sum_caps(const uint32_t * __restrict__ caps, uint32_t n, unsigned long long * total)
+{
+    unsigned long long s = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += caps[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(total, s);
+}
+
+__global__ void k_add_u64(unsigned long long * dst, const unsigned long long * src) { *dst += *src; }
+
+struct RayList {
+    float4 * dirl;        // unit point->camera direction, w = distance l
+    uint2 * ent;          // x = point id, y = view index
+    uint8_t * vis;        // 0 not traced yet, 1 occluded, 2 visible
+    const uint32_t * off; // [num_blocks] first ray of each block's slice
+    uint32_t * cnt;       // [num_blocks] rays in the slice
+};
+
+// Exact cull (kernels.cu:153-167) + ray set-up values (:54-58).  One warp per block, views in
+// order; lanes = points.  A slice is filled in (view, point) order.
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
+    const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
+    const uint32_t * __restrict__ masks, float max_distance, int width, int height, RayList rl)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t blk = blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
+    if (blk >= num_blocks) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t id = blk * 32 + lane;
+    const bool valid = id < n;
+    const V3 v = ld3(verts[valid ? id : n - 1]), nrm = ld3(normals[valid ? id : n - 1]);
+    const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
+    const uint32_t mbit = blk & 31;
+    const uint32_t base = rl.off[blk];
+    uint32_t count = 0;
+    for (uint32_t c0 = v0; c0 < v1; c0 += 32) {
+        uint32_t vi = c0 + lane;
+        uint32_t mw = vi < v1 ? __ldg(mrow + vi) : 0u;
+        uint32_t word = __ballot_sync(0xffffffffu, (mw >> mbit) & 1u);
+        while (word) {
+            const uint32_t k = c0 + (__ffs(word) - 1); word &= word - 1;
+            const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
+            float vw[UAVMVS_VIEW_FLOATS];
+            #pragma unroll
+            for (int i = 0; i < UAVMVS_VIEW_FLOATS / 4; ++i) {          // uniform address: broadcast
+                float4 t = __ldg(reinterpret_cast<const float4 *>(view) + i);
+                vw[4 * i] = t.x; vw[4 * i + 1] = t.y; vw[4 * i + 2] = t.z; vw[4 * i + 3] = t.w;
+            }
+            V3 v2c = mk(vw[0], vw[1], vw[2]) - v;
+            float l = norm(v2c);
+            V3 v2cn = v2c / l;
+            float ctheta = dot(v2cn, nrm);
+            bool pass = valid && !(ctheta < 0.087f) && !(l >= max_distance);
+            if (pass) pass = in_image(vw, v, width, height);
+            uint32_t m = __ballot_sync(0xffffffffu, pass);
+            if (pass) {
+                uint32_t idx = base + count + __popc(m & lt_mask);
+                rl.dirl[idx] = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
+                rl.ent[idx] = make_uint2(id, k);
+                rl.vis[idx] = 0;
+            }
+            count += __popc(m);
+        }
+    }
+    if (lane == 0) rl.cnt[blk] = count;
+}
+
+struct TraceArgs {
+    BvhView bvh;
+    const float4 * __restrict__ verts;
+    RayList rl;
+    uint32_t num_blocks;
+    uint32_t * work;              // next block slice to hand out
+};
+
+#ifndef K1_MIN_BLOCKS
+#define K1_MIN_BLOCKS 6
+#endif
+
+// Occlusion rays against the 4-wide BVH.  On nested trees (every child box inside its parent's
+// box: exact-union trees such as acc's SAH tree and our LBVH; verified at upload) the slab test
+// is monotone in the box bounds (each of fl(b - o), fl(x / d), min, max is), so a ray that
+// passes a leaf's box passes every ancestor's box: the reference reaches a leaf iff the leaf's
+// OWN box passes.  Inner boxes therefore only have to be tested conservatively (never reject a
+// box the exact test accepts); the exact decision, with its IEEE-division fallback, is taken
+// for leaf boxes alone.  EXACT_INNER = true (non-nested user trees) decides every box exactly.
+template <bool EXACT_INNER>
+__global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS)
+k_trace(TraceArgs a)
+{
+    __shared__ uint32_t s_pend[K1_PEND][K1_WARPS * 32];     // deferred leaves: first << 5 | min(count, 31)
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t stack[K1_STACK];
+
+    uint32_t pos = 0, end = 0; bool drained = false;         // warp-uniform: current slice of the ray list
+    bool has_ray = false, traversing = false, hit = false;
+    uint32_t idx = 0, cur = 0, npend = 0; int sp = 0;
+    RayT rt; rt.ox = rt.oy = rt.oz = rt.rdx = rt.rdy = rt.rdz = rt.tmin = rt.tmax = 0.0f;
+    V3 rd = mk(0.f, 0.f, 0.f);
+    uint32_t serviced_idle = 0;
+
+    for (;;) {
+        uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (idle != serviced_idle && __popc(idle) >= K1_REFILL) {
+            // ---------------- refill idle lanes from the ray list ----------------
+            const uint32_t need = __popc(idle), rank = __popc(idle & lt_mask);
+            uint32_t given = 0; bool mine = false;
+            while (given < need && !drained) {
+                if (pos == end) {
+                    uint32_t b = 0;
+                    if (lane == 0) b = atomicAdd(a.work, 1u);
+                    b = __shfl_sync(0xffffffffu, b, 0);
+                    if (b >= a.num_blocks) { drained = true; break; }
+                    pos = __ldg(a.rl.off + b); end = pos + a.rl.cnt[b];
+                    continue;
+                }
+                const uint32_t take = min(need - given, end - pos);
+                if (!has_ray && rank >= given && rank < given + take) { idx = pos + (rank - given); mine = true; }
+                pos += take; given += take;
+            }
+            if (mine) {
+                const float4 d4 = a.rl.dirl[idx];
+                const V3 o = ld3(__ldg(a.verts + a.rl.ent[idx].x));
+                rd = ld3(d4);
+                rt.ox = o.x; rt.oy = o.y; rt.oz = o.z;
+                rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
+                const float mn = fminf(fminf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
+                const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
+                if (mn > 1e-12f && mx < 2.0f) {
+                    rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
+                    has_ray = true; hit = false; sp = 0; npend = 0;
+                    if (a.bvh.root_is_leaf) {
+                        traversing = false; npend = 1;
+                        s_pend[0][tid] = (a.bvh.root_first << 5) | min(a.bvh.root_count, 31u);
+                        float t; Ray ray; ray.o = o; ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
+                        for (uint32_t i = 31u; i < a.bvh.root_count; ++i) hit |= hit_tri(ray, a.bvh.tris + a.bvh.root_first + i, t);
+                    } else { traversing = true; cur = 0; }
+                } else {
+                    // axis-parallel (or degenerate) ray: the reference walk with exact tests, right away
+                    bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
+                    a.rl.vis[idx] = h ? 1 : 2;
+                }
+            }
+            serviced_idle = __ballot_sync(0xffffffffu, !has_ray);
+            if (serviced_idle == 0xffffffffu) {
+                if (drained) break;
+                serviced_idle = 0;        // only axis-parallel rays were handed out: refill again
+                continue;
+            }
+        }
+
+        // ---------------- K1_STEPS traversal steps (4-wide nodes) ----------------
+        #pragma unroll 1
+        for (int step = 0; step < K1_STEPS; ++step) {
+            if (traversing && npend <= K1_PEND - 4) {
+                const Node128 * np = a.bvh.wide + cur;
+                const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
+                const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
+                const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
+                float g0, g1, g2, g3, m0, m1, m2, m3;
+                slab_rel(rt, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, g0, m0);
+                slab_rel(rt, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, g1, m1);
+                slab_rel(rt, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y, g2, m2);
+                slab_rel(rt, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w, g3, m3);
+                bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);   // not surely missed
+                const bool l0 = cnt.x != 0u, l1 = cnt.y != 0u, l2 = cnt.z != 0u, l3 = cnt.w != 0u;   // leaf child
+                // undecided boxes whose decision matters: exact test (rare)
+                const bool x0 = h0 && !(g0 > m0) && (EXACT_INNER || l0), x1 = h1 && !(g1 > m1) && (EXACT_INNER || l1);
+                const bool x2 = h2 && !(g2 > m2) && (EXACT_INNER || l2), x3 = h3 && !(g3 > m3) && (EXACT_INNER || l3);
+                const bool big = (h0 && cnt.x > 31u) || (h1 && cnt.y > 31u) || (h2 && cnt.z > 31u) || (h3 && cnt.w > 31u);
+                if (x0 || x1 || x2 || x3 || big) {
+                    if (x0) h0 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
+                                                 q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                    if (x1) h1 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
+                                                 q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+                    if (x2) h2 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
+                                                 q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
+                    if (x3) h3 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
+                                                 q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
+                    if (big) {    // the part of a leaf beyond 31 triangles does not fit a reference: test it now
+                        Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
+                        float t;
+                        if (h0) for (uint32_t i = 31u; i < cnt.x; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.x + i, t);
+                        if (h1) for (uint32_t i = 31u; i < cnt.y; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.y + i, t);
+                        if (h2) for (uint32_t i = 31u; i < cnt.z; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.z + i, t);
+                        if (h3) for (uint32_t i = 31u; i < cnt.w; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.w + i, t);
+                    }
+                }
+                // leaf children are deferred (any-hit is order independent); inner children: one is
+                // visited next, the others go on the stack
+                uint32_t nxt = UAV_NAI;
+                if (h0) { if (l0) { s_pend[npend][tid] = (ref.x << 5) | min(cnt.x, 31u); ++npend; } else nxt = ref.x; }
+                if (h1) { if (l1) { s_pend[npend][tid] = (ref.y << 5) | min(cnt.y, 31u); ++npend; }
+                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.y; } }
+                if (h2) { if (l2) { s_pend[npend][tid] = (ref.z << 5) | min(cnt.z, 31u); ++npend; }
+                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.z; } }
+                if (h3) { if (l3) { s_pend[npend][tid] = (ref.w << 5) | min(cnt.w, 31u); ++npend; }
+                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.w; } }
+                if (nxt != UAV_NAI) cur = nxt;
+                else if (sp > 0) cur = stack[--sp];
+                else traversing = false;
+            }
+        }
+        // ---------------- triangle phase ----------------
+        {
+            const uint32_t pmask = __ballot_sync(0xffffffffu, npend > 0);
+            if (pmask) {
+                const uint32_t tmask = __ballot_sync(0xffffffffu, traversing);
+                const uint32_t full = __ballot_sync(0xffffffffu, npend > K1_PEND - 4);
+                if (__popc(pmask) >= K1_TRI || full || !tmask) {
+                    if (npend > 0) {
+                        Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
+                        for (uint32_t p = 0; p < npend && !hit; ++p) {
+                            const uint32_t r = s_pend[p][tid];
+                            const uint32_t first = r >> 5, count = r & 31u;
+                            float t;
+                            for (uint32_t i = 0; i < count; ++i) hit |= hit_tri(ray, a.bvh.tris + first + i, t);
+                        }
+                        npend = 0;
+                    }
+                }
+            }
+        }
+        // ---------------- finished lanes post their result ----------------
+        if (has_ray && (hit || (!traversing && npend == 0))) {
+            a.rl.vis[idx] = hit ? 1 : 2;
+            has_ray = false; traversing = false; npend = 0;
+        }
+    }
+}
+
+struct RetireArgs {
+    const float4 * __restrict__ verts; const float4 * __restrict__ normals;
+    uint32_t n, num_blocks;
+    RayList rl;
+    float max_distance;
+    float4 * obs; uint32_t * num_rows; uint32_t max_rows; uint32_t stride;   // stride in float4
+    unsigned long long * stats;
+};
+
+// Warp per block; the block's rays are walked in (view, point) order, 32 at a time.
+// POPULATE: kernels.cu:171-181 (row = running counter of the point, stored iff row < max_rows).
+// !POPULATE: kernels.cu:183-200 (mark the first stored ray equal within 1e-5).
+template <bool POPULATE>
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_retire(RetireArgs a)
+{
+    __shared__ float4 s_nrm[K1_WARPS][32], s_rx[K1_WARPS][32], s_ry[K1_WARPS][32];
+    __shared__ uint32_t s_cnt[K1_WARPS][32];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk >= a.num_blocks) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t id = blk * 32 + lane;
+    const bool valid = id < a.n;
+    const uint32_t count = a.rl.cnt[blk];
+    if (count == 0) return;
+    {
+        V3 nrm = ld3(a.normals[valid ? id : a.n - 1]);
+        V3 rx = normalized(orthogonal(nrm));              // relative_direction(), kernels.cu:63-76
+        V3 ry = normalized(cross(nrm, rx));
+        s_nrm[w][lane] = make_float4(nrm.x, nrm.y, nrm.z, 0.0f);
+        s_rx[w][lane] = make_float4(rx.x, rx.y, rx.z, 0.0f);
+        s_ry[w][lane] = make_float4(ry.x, ry.y, ry.z, 0.0f);
+        s_cnt[w][lane] = valid ? a.num_rows[id] : 0u;
+    }
+    __syncwarp();
+    const uint32_t base = a.rl.off[blk];
+    unsigned long long st_vis = 0;
+    for (uint32_t c0 = 0; c0 < count; c0 += 32) {
+        const uint32_t i = c0 + lane;
+        const bool in = i < count;
+        const bool vis = in && a.rl.vis[base + i] == 2;
+        const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
+        if (!vis_mask) continue;
+        uint32_t pt = lane;
+        V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
+        if (vis) {
+            const float4 d4 = a.rl.dirl[base + i];
+            pt = a.rl.ent[base + i].x & 31u;
+            const V3 v2cn = ld3(d4);
+            rel = normalized(mk(dot(ld3(s_rx[w][pt]), v2cn), dot(ld3(s_ry[w][pt]), v2cn), dot(ld3(s_nrm[w][pt]), v2cn)));
+            scale = 1.0f - (d4.w / a.max_distance);
+            ++st_vis;
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, pt) & vis_mask;
+        const uint32_t row_pt = blk * 32 + pt;
+        if (POPULATE) {
+            if (vis) {
+                uint32_t row = s_cnt[w][pt] + __popc(peers & lt_mask);
+                if (row < a.max_rows) a.obs[(size_t)row * a.stride + row_pt] = make_float4(rel.x, rel.y, rel.z, scale);
+            }
+            __syncwarp();
+            if (vis && (peers >> lane) == 1u) s_cnt[w][pt] += __popc(peers);   // highest peer updates
+            __syncwarp();
+        } else {
+            // entries of the same point are applied in view order
+            const uint32_t rank = __popc(peers & lt_mask);
+            uint32_t max_rank = 0;
+            for (uint32_t m = vis_mask; m; m &= m - 1)
+                max_rank = max(max_rank, __shfl_sync(0xffffffffu, rank, __ffs(m) - 1));
+            for (uint32_t r = 0; r <= max_rank; ++r) {
+                if (vis && rank == r) {
+                    const uint32_t rows = min(s_cnt[w][pt], a.max_rows);
+                    volatile float4 * col = a.obs + row_pt;
+                    for (uint32_t k = 0; k < rows; ++k) {
+                        volatile float4 * p = col + (size_t)k * a.stride;
+                        float ox = p->x, oy = p->y, oz = p->z, ow = p->w;
+                        bool equal = fabsf(rel.x - ox) < 1e-5f && fabsf(rel.y - oy) < 1e-5f
+                            && fabsf(rel.z - oz) < 1e-5f && fabsf(scale - ow) < 1e-5f;
+                        if (equal) { p->w = -1.0f; break; }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+    if (POPULATE && valid) a.num_rows[id] = s_cnt[w][lane];
+    if (a.stats) {
+        for (int o = 16; o > 0; o >>= 1) st_vis += __shfl_xor_sync(0xffffffffu, st_vis, o);
+        if (lane == 0) { atomicAdd(a.stats + 0, (unsigned long long)count); atomicAdd(a.stats + 1, st_vis); }
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+struct K1Scratch {
+    uint32_t * masks = nullptr; size_t masks_cap = 0;
+    uint32_t * caps = nullptr, * off = nullptr, * cnt = nullptr; size_t blocks_cap = 0;
+    void * cub_tmp = nullptr; size_t cub_cap = 0;
+    float4 * dirl = nullptr; uint2 * ent = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
+    int grid_trace = 0;
+};
+static thread_local K1Scratch g_k1;
+
+template <typename T>
+static int grow(T ** p, size_t * cap, size_t need, cudaStream_t s)
+{
+    if (need <= *cap) return 0;
+    if (*p) UAV_CUDA(cudaFreeAsync(*p, s));        // stream-ordered: earlier kernels finish first
+    UAV_CUDA(cudaMallocAsync(p, need * sizeof(T), s));
+    *cap = need;
+    return 0;
+}
+
+static size_t ray_budget()
+{
+    // upper bound of ray records (24 B + 1 B each) kept at a time; views are processed in
+    // batches when a whole trajectory would need more
+    static size_t v = 0;
+    if (!v) {
+        const char * e = getenv("UAVMVS_RAY_BUDGET");
+        v = e ? (size_t)strtoull(e, nullptr, 10) : ((size_t)1 << 28);
+        if (v < 1024) v = 1024;
+    }
+    return v;
+}
+
+int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
+    float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    uavmvs_obs * obs, unsigned long long * d_stats)
+{
+    UAV_REQUIRE(bvh && cloud && obs, "null handle");
+    UAV_REQUIRE(obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
+    UAV_REQUIRE(bvh->num_tris < (1u << 27), "more than 2^27 triangles");
+    if (num_views == 0) return 0;
+    K1Scratch & k = g_k1;
+    const uint32_t nb = cloud->num_blocks;
+    if (!k.work) {
+        UAV_CUDA(cudaMalloc(&k.work, sizeof(uint32_t)));
+        UAV_CUDA(cudaMalloc(&k.total, sizeof(unsigned long long)));
+        UAV_CUDA(cudaMallocHost(&k.h_total, sizeof(unsigned long long)));
+        int dev = 0, sms = 0, occ_a = 0, occ_b = 0;
+        UAV_CUDA(cudaGetDevice(&dev));
+        UAV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_trace<false>, K1_WARPS * 32, 0));
+        UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_trace<true>, K1_WARPS * 32, 0));
+        int occ = occ_a < occ_b ? occ_a : occ_b;
+        k.grid_trace = sms * (occ > 0 ? occ : 1);
+    }
+    if (grow(&k.masks, &k.masks_cap, (size_t)cloud->num_super * num_views, s)) return 1;
+    if (nb + 1 > k.blocks_cap) {
+        size_t c0 = k.blocks_cap, c1 = k.blocks_cap, c2 = k.blocks_cap;
+        if (grow(&k.caps, &c0, (size_t)nb + 1, s) || grow(&k.off, &c1, (size_t)nb + 1, s) || grow(&k.cnt, &c2, (size_t)nb + 1, s)) return 1;
+        k.blocks_cap = nb + 1;
+    }
+    size_t tmp_need = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_need, k.caps, k.off, (int)nb, s);
+    if (tmp_need > k.cub_cap) {
+        if (k.cub_tmp) UAV_CUDA(cudaFreeAsync(k.cub_tmp, s));
+        UAV_CUDA(cudaMallocAsync(&k.cub_tmp, tmp_need, s));
+        k.cub_cap = tmp_need;
+    }
+
+    dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
+    k_view_masks<<<mgrid, K1_WARPS * 32, 0, s>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
+        cloud->block_sphere, nb, max_distance, width, height, k.masks);
+    UAV_CUDA(cudaGetLastError());
+
+    // view batches: [v0, v1) such that the upper bound of ray records fits the budget
+    uint32_t v0 = 0, step = num_views;
+    while (v0 < num_views) {
+        uint32_t v1 = (uint32_t)min((uint64_t)num_views, (uint64_t)v0 + step);
+        UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
+        k_block_caps<<<divup(nb, 128), 128, 0, s>>>(k.masks, num_views, v0, v1, nb, k.caps);
+        k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, s>>>(k.caps, nb, k.total);
+        UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+        UAV_CUDA(cudaStreamSynchronize(s));
+        const unsigned long long total = *k.h_total;
+        if (total > ray_budget() && v1 - v0 > 1) {          // too many candidates: halve the batch
+            step = (v1 - v0 + 1) / 2;
+            continue;
+        }
+        UAV_REQUIRE(total < (1ull << 32), "a single view yields more than 2^32 candidate pairs");
+        if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
+        if (total > 0) {
+            if (total > k.rays_cap) {
+                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap;
+                if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.ent, &c1, (size_t)total, s) || grow(&k.vis, &c2, (size_t)total, s)) return 1;
+                k.rays_cap = (size_t)total;
+            }
+            cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
+            RayList rl; rl.dirl = k.dirl; rl.ent = k.ent; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt;
+            k_cull_emit<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+                d_views, num_views, v0, v1, k.masks, max_distance, width, height, rl);
+            UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
+            TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
+            unsigned grid = (unsigned)k.grid_trace;
+            if (bvh->nested) k_trace<false><<<grid, K1_WARPS * 32, 0, s>>>(ta);
+            else k_trace<true><<<grid, K1_WARPS * 32, 0, s>>>(ta);
+            RetireArgs ra; ra.verts = cloud->vertices; ra.normals = cloud->normals; ra.n = cloud->n; ra.num_blocks = nb;
+            ra.rl = rl; ra.max_distance = max_distance;
+            ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
+            ra.stride = (uint32_t)(obs->pitch / sizeof(float4)); ra.stats = d_stats;
+            if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
+            else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
+            UAV_CUDA(cudaGetLastError());
+        }
+        v0 = v1;
+    }
+    return 0;
+}
+
+}  // namespace uav

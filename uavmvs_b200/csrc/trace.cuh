@@ -269,3 +269,59 @@ static __device__ __noinline__ bool slab_exact_call(float ox, float oy, float oz
 }
 
 }  // namespace uav
+
+// ---- origin-relative filtered slab test (k1.cu traversal) ---------------------------------
+// t~ = fl(fl(b - o) * fl(1 / d)).  The first operation is the reference's own fl(b - o); only
+// the division is replaced, so |t~ - t_ref| <= 3 * 2^-24 |t~| and the undecided band is purely
+// relative: m = 1e-6 (|Tmin~| + |Tmax~|).  g > m proves the reference accepts the box, g < -m
+// proves it rejects; a box that only has to be tested conservatively is visited unless g < -m.
+// Only rays with |d_k| > 1e-12 on all axes may use it (no inf / NaN can arise).
+namespace uav {
+
+struct RayT { float ox, oy, oz, rdx, rdy, rdz, tmin, tmax; };
+
+__device__ __forceinline__ void slab_rel(const RayT & f, float mnx, float mny, float mnz,
+    float mxx, float mxy, float mxz, float & g, float & m)
+{
+    float ax = (mnx - f.ox) * f.rdx, bx = (mxx - f.ox) * f.rdx;
+    float ay = (mny - f.oy) * f.rdy, by = (mxy - f.oy) * f.rdy;
+    float az = (mnz - f.oz) * f.rdz, bz = (mxz - f.oz) * f.rdz;
+    float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), f.tmin));
+    float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), f.tmax));
+    g = tmax - fmaxf(tmin, 0.0f);
+    m = 1e-6f * (fabsf(tmin) + fabsf(tmax));
+}
+
+// The reference's any-hit walk with the exact test at every node (libs/acc/bvh_tree.h:419-467);
+// used for the rare rays the filtered test may not handle.
+static __device__ __noinline__ bool trace_any_exact(const BvhView bvh, float ox, float oy, float oz,
+    float dx, float dy, float dz, float tmin, float tmax)
+{
+    Ray ray; ray.o = mk(ox, oy, oz); ray.d = mk(dx, dy, dz); ray.tmin = tmin; ray.tmax = tmax;
+    float t;
+    if (bvh.root_is_leaf) {
+        for (uint32_t i = 0; i < bvh.root_count; ++i)
+            if (hit_tri(ray, bvh.tris + bvh.root_first + i, t)) return true;
+        return false;
+    }
+    uint32_t stack[UAV_STACK];
+    int sp = 0;
+    uint32_t cur = 0;
+    for (;;) {
+        const Node64 * np = bvh.inner + cur;
+        float4 q0 = __ldg(&np->q0), q1 = __ldg(&np->q1), q2 = __ldg(&np->q2);
+        uint4 q3 = __ldg(&np->q3);
+        float tl, tr;
+        bool hl = slab(ray, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tl);
+        bool hr = slab(ray, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tr);
+        if (hl && q3.z) { for (uint32_t i = 0; i < q3.z; ++i) if (hit_tri(ray, bvh.tris + q3.x + i, t)) return true; hl = false; }
+        if (hr && q3.w) { for (uint32_t i = 0; i < q3.w; ++i) if (hit_tri(ray, bvh.tris + q3.y + i, t)) return true; hr = false; }
+        if (hl && hr) { stack[sp++] = q3.y; cur = q3.x; }
+        else if (hl) cur = q3.x;
+        else if (hr) cur = q3.y;
+        else if (sp == 0) return false;
+        else cur = stack[--sp];
+    }
+}
+
+}  // namespace uav
