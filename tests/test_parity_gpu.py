@@ -221,3 +221,106 @@ def test_lbvh_same_tree_parity(api, oracle, tiny_scene):
     data, rows = obs.download()
     assert np.array_equal(rows, obs_o.num_rows)
     assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def _populate_both(api, oracle, sc, arrays):
+    obvh = oracle.BVH.from_arrays(arrays)
+    obs_o, state, _ = _run_oracle_eval(oracle, obvh, sc)
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    return obs_o, data, rows, state
+
+
+def test_dense_scene_rows_and_cap(api, oracle):
+    """~15 observations per point, some beyond the 32-row cap: row order, cap, un-clamped counters."""
+    from uavmvs_b200 import scenes
+    sc = scenes.dense()
+    arrays = oracle.BVH.build(sc.verts, sc.faces, threads=2).export()
+    obs_o, data, rows, state = _populate_both(api, oracle, sc, arrays)
+    assert rows.max() > 32 and rows.mean() > 8
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def test_non_nested_tree_takes_exact_path(api, oracle, tiny_scene, tiny_tree):
+    """User-supplied boxes that are not exact unions (here: some boxes SHRUNK, so rays the tight tree
+    would accept are rejected): the answer is tree dependent and must still equal the reference walk."""
+    sc = tiny_scene
+    _, arrays = tiny_tree
+    rng = np.random.default_rng(4)
+    aabbs = arrays.aabbs.copy()
+    pick = rng.random(aabbs.shape[0]) < 0.2
+    pick[0] = False
+    ext = aabbs[:, 3:] - aabbs[:, :3]
+    aabbs[pick, :3] += 0.2 * ext[pick]
+    aabbs[pick, 3:] -= 0.2 * ext[pick]
+    mod = oracle.TreeArrays(arrays.nodes, aabbs, arrays.tris, arrays.indices)
+    obs_o, data, rows, state = _populate_both(api, oracle, sc, mod)
+    obs_t, _, _ = _run_oracle_eval(oracle, oracle.BVH.from_arrays(arrays), sc)
+    assert not np.array_equal(obs_t.num_rows, obs_o.num_rows)      # the shrunk boxes do change visibility
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def test_large_leaves(api, oracle, tiny_scene):
+    """A hand-made tree whose leaves hold more than 31 triangles."""
+    sc = tiny_scene
+    t = sc.verts[sc.faces].reshape(-1, 9).astype(np.float32)
+    order = np.argsort(t[:, 0::3].mean(1), kind="stable")       # split along x into 2^k slabs
+    t, idx = t[order], order.astype(np.uint32)
+    nodes, aabbs = [], []
+
+    def box(lo, hi):
+        v = t[lo:hi].reshape(-1, 3)
+        return np.concatenate([v.min(0), v.max(0)])
+
+    def build(lo, hi, depth):
+        me = len(nodes)
+        nodes.append([lo, hi, 0xFFFFFFFF, 0xFFFFFFFF])
+        aabbs.append(box(lo, hi))
+        if depth < 5 and hi - lo > 80:
+            mid = (lo + hi) // 2
+            l = build(lo, mid, depth + 1)
+            r = build(mid, hi, depth + 1)
+            nodes[me][2], nodes[me][3] = l, r
+        return me
+
+    build(0, t.shape[0], 0)
+    arrays = oracle.TreeArrays(np.array(nodes, np.uint32), np.array(aabbs, np.float32), t, idx)
+    assert (arrays.nodes[arrays.nodes[:, 2] == 0xFFFFFFFF, 1] - arrays.nodes[arrays.nodes[:, 2] == 0xFFFFFFFF, 0]).max() > 31
+    obs_o, data, rows, state = _populate_both(api, oracle, sc, arrays)
+    assert np.array_equal(rows, obs_o.num_rows) and rows.sum() > 1000
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
+def test_axis_parallel_rays_and_flat_boxes(api, oracle):
+    """Cameras exactly above points (zero direction components) over axis-aligned flat geometry
+    (zero-thickness leaf boxes): the cases the filtered slab test hands to the exact path."""
+    from uavmvs_b200 import scenes
+    g = np.arange(0, 9, dtype=np.float32)
+    X, Y = np.meshgrid(g, g, indexing="ij")
+    gv = np.stack([X.ravel(), Y.ravel(), np.zeros(81, np.float32)], 1)
+    quads = [(i * 9 + j, (i + 1) * 9 + j, (i + 1) * 9 + j + 1, i * 9 + j + 1) for i in range(8) for j in range(8)]
+    gf = np.array([[a, b, c] for a, b, c, d in quads] + [[a, c, d] for a, b, c, d in quads], np.uint32)
+    # a flat roof plate 3 m above part of the ground
+    rv = np.array([[2, 2, 3], [5, 2, 3], [5, 5, 3], [2, 5, 3]], np.float32)
+    rf = np.array([[0, 1, 2], [0, 2, 3]], np.uint32) + 81
+    verts, faces = np.concatenate([gv, rv]), np.concatenate([gf, rf])
+    pts = np.stack([X.ravel() * 0.75 + 1.0, Y.ravel() * 0.75 + 1.0, np.zeros(81, np.float32)], 1).astype(np.float32)
+    nrm = np.tile(np.array([0, 0, 1], np.float32), (81, 1))
+    specs = [((float(p[0]), float(p[1]), 20.0), 0.0, 0.0) for p in pts[::4]]      # exactly above every 4th point
+    pos, w2c, calib = scenes._pack_views(specs)
+    sc = scenes.Scene("flat", verts, faces, pts, nrm, np.zeros(81, np.float32), np.ones(81, np.float32), pos, w2c, calib)
+    for arrays in (oracle.BVH.build(verts, faces, threads=1).export(),):
+        obs_o, data, rows, state = _populate_both(api, oracle, sc, arrays)
+        assert (state == 1).sum() > 0 and (state == 2).sum() > 0
+        assert np.array_equal(rows, obs_o.num_rows)
+        assert _valid_rows_equal(obs_o.data, data, rows, 32)
+    gb = api.BVHTree.build_lbvh(verts, faces)
+    nodes, aabbs, tris, indices = gb.export()
+    arrays = oracle.TreeArrays(nodes, aabbs, tris, indices)
+    obs_o, data, rows, state = _populate_both(api, oracle, sc, arrays)
+    assert np.array_equal(rows, obs_o.num_rows)

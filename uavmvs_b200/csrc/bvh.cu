@@ -66,7 +66,10 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
             uint32_t ch = kids[k];
             for (int j = 0; j < 6; ++j) b[6 * k + j] = aabbs[6 * (size_t)ch + j];
             if (flag[ch]) { ref[k] = slot[ch]; cnt[k] = 0u; }
-            else { uint4 cn = nodes[ch]; ref[k] = cn.x; cnt[k] = cn.y - cn.x; }
+            else {   // leaf: cnt = ready-made deferred-leaf reference, ref = first triangle
+                uint4 cn = nodes[ch]; uint32_t c = cn.y - cn.x;
+                ref[k] = cn.x; cnt[k] = (cn.x << 6) | (c < 31u ? c : 31u);
+            }
         } else {
             // empty slot: a far-away point box that every ray surely misses (|t| ~ 1e18 / |d|),
             // flagged as "inner" so that no leaf logic ever looks at it
@@ -81,21 +84,35 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
     wide[slot[i]] = o;
 }
 
-// nested[0] = 0 unless every child box lies inside its parent's box (NaNs count as not nested)
-__global__ void k_check_nested(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n,
-    uint32_t * __restrict__ violations)
+// out[0] += violations of "every child box lies inside its parent's box and every leaf box is the
+// exact bound of its triangles" (NaNs count as violations); out[1] = largest leaf
+__global__ void k_check_tree(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs,
+    const float * __restrict__ tris, uint32_t n, uint32_t * __restrict__ out)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint4 nd = nodes[i];
-    if (nd.z == UAV_NAI || nd.w == UAV_NAI) return;
     const float * p = aabbs + 6 * (size_t)i;
     bool ok = true;
-    for (int c = 0; c < 2; ++c) {
-        const float * q = aabbs + 6 * (size_t)(c ? nd.w : nd.z);
-        for (int k = 0; k < 3; ++k) ok = ok && (q[k] >= p[k]) && (q[3 + k] <= p[3 + k]) && (q[k] <= q[3 + k]);
+    if (nd.z == UAV_NAI || nd.w == UAV_NAI) {
+        float mn[3] = {UAV_INF, UAV_INF, UAV_INF}, mx[3] = {-UAV_INF, -UAV_INF, -UAV_INF};
+        for (uint32_t t = nd.x; t < nd.y; ++t)
+            for (int v = 0; v < 3; ++v)
+                for (int k = 0; k < 3; ++k) {
+                    float x = tris[9 * (size_t)t + 3 * v + k];
+                    mn[k] = fminf(mn[k], x); mx[k] = fmaxf(mx[k], x);
+                    ok = ok && (x == x);
+                }
+        for (int k = 0; k < 3; ++k) ok = ok && (p[k] == mn[k]) && (p[3 + k] == mx[k]);
+        ok = ok && nd.y > nd.x;
+        atomicMax(out + 1, nd.y - nd.x);
+    } else {
+        for (int c = 0; c < 2; ++c) {
+            const float * q = aabbs + 6 * (size_t)(c ? nd.w : nd.z);
+            for (int k = 0; k < 3; ++k) ok = ok && (q[k] >= p[k]) && (q[3 + k] <= p[3 + k]) && (q[k] <= q[3 + k]);
+        }
     }
-    if (!ok) atomicAdd(violations, 1u);
+    if (!ok) atomicAdd(out, 1u);
 }
 
 // Per-triangle constants with the reference's operation order (libs/acc/primitives.h:
@@ -144,13 +161,15 @@ static int finalize_layout(uavmvs_bvh * b)
     UAV_CUDA(cudaMalloc(&b->wide, sizeof(Node128) * (size_t)(b->num_inner ? b->num_inner : 1)));
     UAV_CUDA(cudaMalloc(&b->ptris, sizeof(Tri64) * (size_t)t));
     {
-        uint32_t * viol = nullptr, h_viol = 1;
-        UAV_CUDA(cudaMalloc(&viol, 4));
-        UAV_CUDA(cudaMemset(viol, 0, 4));
-        k_check_nested<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, n, viol);
-        UAV_CUDA(cudaMemcpy(&h_viol, viol, 4, cudaMemcpyDeviceToHost));
-        cudaFree(viol);
-        b->nested = h_viol == 0 ? 1u : 0u;
+        uint32_t * chk = nullptr, h_chk[2] = {1, 0};
+        UAV_CUDA(cudaMalloc(&chk, 8));
+        UAV_CUDA(cudaMemset(chk, 0, 8));
+        k_check_tree<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, b->tris, n, chk);
+        UAV_CUDA(cudaMemcpy(h_chk, chk, 8, cudaMemcpyDeviceToHost));
+        cudaFree(chk);
+        b->max_leaf = h_chk[1];
+        // the fast traversal needs nested inner boxes, tight leaf boxes and leaves of <= 31 triangles
+        b->nested = (h_chk[0] == 0 && h_chk[1] <= 31u) ? 1u : 0u;
     }
     k_build_inner<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->inner);
     k_build_wide<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->wide);

@@ -43,7 +43,9 @@ struct __align__(64) Node64 { float4 q0, q1, q2; uint4 q3; };
 // Four-child node, 128 B (one cache line): the up-to-four GRANDCHILDREN of a binary node (a leaf
 // child stays one child), boxes as the reference's exact floats.
 //   q[0..2] = boxes of children 0,1 (same packing as Node64 q0..q2), q[3..5] = children 2,3
-//   ref[c]  = index of an inner node (cnt[c] == 0) or first triangle of a leaf (cnt[c] = its size)
+//   cnt[c]  = 0: inner child, ref[c] = its node index
+//   cnt[c] != 0: leaf child, cnt[c] = first_triangle << 6 | min(size, 31) (bit 5 is left free for
+//             the traversal's "box not verified" flag), ref[c] = first triangle
 //   empty slot: point box at 1e18 (no segment reaches it), ref = 0, cnt = 0
 // Every inner binary node owns one (indexed like Node64); a traversal that starts at the root only
 // ever touches those of even depth.
@@ -67,7 +69,8 @@ struct uavmvs_bvh {
     uav::Node128 * wide;
     uav::Tri64 * ptris;
     uint32_t root_is_leaf, root_first, root_count;
-    uint32_t nested;    // every child box lies inside its parent's box (checked at upload)
+    uint32_t nested;    // child boxes inside parent boxes, leaf boxes tight, leaves <= 31 triangles (checked at upload)
+    uint32_t max_leaf;
 };
 
 struct uavmvs_kdtree {

@@ -199,18 +199,36 @@ struct TraceArgs {
 #define K1_MIN_BLOCKS 6
 #endif
 
-// Occlusion rays against the 4-wide BVH.  On nested trees (every child box inside its parent's
-// box: exact-union trees such as acc's SAH tree and our LBVH; verified at upload) the slab test
-// is monotone in the box bounds (each of fl(b - o), fl(x / d), min, max is), so a ray that
-// passes a leaf's box passes every ancestor's box: the reference reaches a leaf iff the leaf's
-// OWN box passes.  Inner boxes therefore only have to be tested conservatively (never reject a
-// box the exact test accepts); the exact decision, with its IEEE-division fallback, is taken
-// for leaf boxes alone.  EXACT_INNER = true (non-nested user trees) decides every box exactly.
-template <bool EXACT_INNER>
+// Exact leaf box (the tight bound of the leaf's triangles, verified at upload to equal the
+// reference's stored box) tested with the reference's own slab arithmetic.
+static __device__ __noinline__ bool leaf_box_exact(const float * __restrict__ raw_tris, uint32_t first, uint32_t count,
+    float ox, float oy, float oz, float dx, float dy, float dz, float tmin, float tmax)
+{
+    float mn[3] = {UAV_INF, UAV_INF, UAV_INF}, mx[3] = {-UAV_INF, -UAV_INF, -UAV_INF};
+    for (uint32_t t = first; t < first + count; ++t)
+        for (int v = 0; v < 3; ++v)
+            for (int k = 0; k < 3; ++k) {
+                float x = __ldg(raw_tris + 9 * (size_t)t + 3 * v + k);
+                mn[k] = fminf(mn[k], x); mx[k] = fmaxf(mx[k], x);
+            }
+    Ray r; r.o = mk(ox, oy, oz); r.d = mk(dx, dy, dz); r.tmin = tmin; r.tmax = tmax;
+    float t;
+    return slab(r, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2], t);
+}
+
+// Occlusion rays against the 4-wide BVH of a tree whose boxes are nested (every child box
+// inside its parent's box, every leaf box the tight bound of its triangles: exact-union trees
+// such as acc's SAH tree and our LBVH; verified at upload).  The slab test is monotone in the
+// box bounds (each of fl(b - o), fl(x / d), min, max is), so a ray that passes a leaf's box
+// passes every ancestor's box: the reference reaches a leaf iff the leaf's OWN box passes, and
+// its answer is  OR over leaves (leaf box passes AND some triangle of the leaf is accepted).
+// Inner boxes therefore only need a conservative test (never reject a box the exact test
+// accepts).  Leaf boxes the filtered test cannot decide are deferred with a flag; the exact
+// box test then runs only if a triangle of that leaf is accepted (both orders of the AND agree).
 __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS)
 k_trace(TraceArgs a)
 {
-    __shared__ uint32_t s_pend[K1_PEND][K1_WARPS * 32];     // deferred leaves: first << 5 | min(count, 31)
+    __shared__ uint32_t s_pend[K1_PEND][K1_WARPS * 32];     // deferred leaves: first << 6 | unverified << 5 | count
     const uint32_t tid = threadIdx.x, lane = tid & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t stack[K1_STACK];
@@ -249,17 +267,11 @@ k_trace(TraceArgs a)
                 rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
                 const float mn = fminf(fminf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
                 const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
-                if (mn > 1e-12f && mx < 2.0f) {
+                if (mn > 1e-12f && mx < 2.0f && !a.bvh.root_is_leaf) {
                     rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
-                    has_ray = true; hit = false; sp = 0; npend = 0;
-                    if (a.bvh.root_is_leaf) {
-                        traversing = false; npend = 1;
-                        s_pend[0][tid] = (a.bvh.root_first << 5) | min(a.bvh.root_count, 31u);
-                        float t; Ray ray; ray.o = o; ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
-                        for (uint32_t i = 31u; i < a.bvh.root_count; ++i) hit |= hit_tri(ray, a.bvh.tris + a.bvh.root_first + i, t);
-                    } else { traversing = true; cur = 0; }
+                    has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
                 } else {
-                    // axis-parallel (or degenerate) ray: the reference walk with exact tests, right away
+                    // axis-parallel (or degenerate) ray, single-leaf tree: the reference walk, right away
                     bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
                     a.rl.vis[idx] = h ? 1 : 2;
                 }
@@ -267,7 +279,7 @@ k_trace(TraceArgs a)
             serviced_idle = __ballot_sync(0xffffffffu, !has_ray);
             if (serviced_idle == 0xffffffffu) {
                 if (drained) break;
-                serviced_idle = 0;        // only axis-parallel rays were handed out: refill again
+                serviced_idle = 0;        // only such rays were handed out: refill again
                 continue;
             }
         }
@@ -285,43 +297,27 @@ k_trace(TraceArgs a)
                 slab_rel(rt, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, g1, m1);
                 slab_rel(rt, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y, g2, m2);
                 slab_rel(rt, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w, g3, m3);
-                bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);   // not surely missed
-                const bool l0 = cnt.x != 0u, l1 = cnt.y != 0u, l2 = cnt.z != 0u, l3 = cnt.w != 0u;   // leaf child
-                // undecided boxes whose decision matters: exact test (rare)
-                const bool x0 = h0 && !(g0 > m0) && (EXACT_INNER || l0), x1 = h1 && !(g1 > m1) && (EXACT_INNER || l1);
-                const bool x2 = h2 && !(g2 > m2) && (EXACT_INNER || l2), x3 = h3 && !(g3 > m3) && (EXACT_INNER || l3);
-                const bool big = (h0 && cnt.x > 31u) || (h1 && cnt.y > 31u) || (h2 && cnt.z > 31u) || (h3 && cnt.w > 31u);
-                if (x0 || x1 || x2 || x3 || big) {
-                    if (x0) h0 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
-                                                 q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-                    if (x1) h1 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
-                                                 q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
-                    if (x2) h2 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
-                                                 q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
-                    if (x3) h3 = slab_exact_call(rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax,
-                                                 q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
-                    if (big) {    // the part of a leaf beyond 31 triangles does not fit a reference: test it now
-                        Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
-                        float t;
-                        if (h0) for (uint32_t i = 31u; i < cnt.x; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.x + i, t);
-                        if (h1) for (uint32_t i = 31u; i < cnt.y; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.y + i, t);
-                        if (h2) for (uint32_t i = 31u; i < cnt.z; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.z + i, t);
-                        if (h3) for (uint32_t i = 31u; i < cnt.w; ++i) hit |= hit_tri(ray, a.bvh.tris + ref.w + i, t);
-                    }
+                // visit unless surely missed; leaf children are deferred (any-hit is order independent)
+                // with the "box not verified" flag when the filtered test cannot prove the hit
+                const bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);
+                const bool f0 = h0 && cnt.x != 0u, f1 = h1 && cnt.y != 0u, f2 = h2 && cnt.z != 0u, f3 = h3 && cnt.w != 0u;
+                const bool i0 = h0 && cnt.x == 0u, i1 = h1 && cnt.y == 0u, i2 = h2 && cnt.z == 0u, i3 = h3 && cnt.w == 0u;
+                if (f0) { s_pend[npend][tid] = cnt.x | (g0 > m0 ? 0u : 32u); ++npend; }
+                if (f1) { s_pend[npend][tid] = cnt.y | (g1 > m1 ? 0u : 32u); ++npend; }
+                if (f2) { s_pend[npend][tid] = cnt.z | (g2 > m2 ? 0u : 32u); ++npend; }
+                if (f3) { s_pend[npend][tid] = cnt.w | (g3 > m3 ? 0u : 32u); ++npend; }
+                // inner children: one is visited next, the others go on the stack
+                uint32_t nxt = i0 ? ref.x : UAV_NAI;
+                if (i1 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i1) nxt = ref.y;
+                if (i2 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i2) nxt = ref.z;
+                if (i3 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i3) nxt = ref.w;
+                if (nxt == UAV_NAI) {
+                    if (sp > 0) nxt = stack[--sp]; else traversing = false;
                 }
-                // leaf children are deferred (any-hit is order independent); inner children: one is
-                // visited next, the others go on the stack
-                uint32_t nxt = UAV_NAI;
-                if (h0) { if (l0) { s_pend[npend][tid] = (ref.x << 5) | min(cnt.x, 31u); ++npend; } else nxt = ref.x; }
-                if (h1) { if (l1) { s_pend[npend][tid] = (ref.y << 5) | min(cnt.y, 31u); ++npend; }
-                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.y; } }
-                if (h2) { if (l2) { s_pend[npend][tid] = (ref.z << 5) | min(cnt.z, 31u); ++npend; }
-                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.z; } }
-                if (h3) { if (l3) { s_pend[npend][tid] = (ref.w << 5) | min(cnt.w, 31u); ++npend; }
-                          else { if (nxt != UAV_NAI) stack[sp++] = nxt; nxt = ref.w; } }
-                if (nxt != UAV_NAI) cur = nxt;
-                else if (sp > 0) cur = stack[--sp];
-                else traversing = false;
+                cur = nxt;
             }
         }
         // ---------------- triangle phase ----------------
@@ -335,9 +331,12 @@ k_trace(TraceArgs a)
                         Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
                         for (uint32_t p = 0; p < npend && !hit; ++p) {
                             const uint32_t r = s_pend[p][tid];
-                            const uint32_t first = r >> 5, count = r & 31u;
-                            float t;
-                            for (uint32_t i = 0; i < count; ++i) hit |= hit_tri(ray, a.bvh.tris + first + i, t);
+                            const uint32_t first = r >> 6, count = r & 31u;
+                            float t; bool h = false;
+                            for (uint32_t i = 0; i < count; ++i) h |= hit_tri(ray, a.bvh.tris + first + i, t);
+                            if (h && (r & 32u))      // rare: the leaf's box still has to pass the exact test
+                                h = leaf_box_exact(a.bvh.raw_tris, first, count, rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
+                            hit = h;
                         }
                         npend = 0;
                     }
@@ -349,6 +348,22 @@ k_trace(TraceArgs a)
             a.rl.vis[idx] = hit ? 1 : 2;
             has_ray = false; traversing = false; npend = 0;
         }
+    }
+}
+
+// Trees that are not nested (user-supplied boxes) or hold leaves of more than 31 triangles:
+// every ray takes the reference walk with the exact test at every node.
+__global__ void k_trace_exact(TraceArgs a, uint32_t total)
+{
+    const uint32_t b = blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
+    if (b >= a.num_blocks) return;
+    const uint32_t base = a.rl.off[b], count = a.rl.cnt[b];
+    for (uint32_t i = threadIdx.x & 31; i < count; i += 32) {
+        const uint32_t idx = base + i;
+        const float4 d4 = a.rl.dirl[idx];
+        const V3 o = ld3(__ldg(a.verts + a.rl.ent[idx].x));
+        bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, d4.x, d4.y, d4.z, d4.w * 0.001f, d4.w);
+        a.rl.vis[idx] = h ? 1 : 2;
     }
 }
 
@@ -485,7 +500,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 {
     UAV_REQUIRE(bvh && cloud && obs, "null handle");
     UAV_REQUIRE(obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
-    UAV_REQUIRE(bvh->num_tris < (1u << 27), "more than 2^27 triangles");
+    UAV_REQUIRE(bvh->num_tris < (1u << 26), "more than 2^26 triangles");
     if (num_views == 0) return 0;
     K1Scratch & k = g_k1;
     const uint32_t nb = cloud->num_blocks;
@@ -496,8 +511,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         int dev = 0, sms = 0, occ_a = 0, occ_b = 0;
         UAV_CUDA(cudaGetDevice(&dev));
         UAV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_trace<false>, K1_WARPS * 32, 0));
-        UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_trace<true>, K1_WARPS * 32, 0));
+        UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_trace, K1_WARPS * 32, 0));
+        occ_b = occ_a;
         int occ = occ_a < occ_b ? occ_a : occ_b;
         k.grid_trace = sms * (occ > 0 ? occ : 1);
     }
@@ -549,8 +564,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
             unsigned grid = (unsigned)k.grid_trace;
-            if (bvh->nested) k_trace<false><<<grid, K1_WARPS * 32, 0, s>>>(ta);
-            else k_trace<true><<<grid, K1_WARPS * 32, 0, s>>>(ta);
+            if (bvh->nested) k_trace<<<grid, K1_WARPS * 32, 0, s>>>(ta);
+            else k_trace_exact<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ta, (uint32_t)total);
             RetireArgs ra; ra.verts = cloud->vertices; ra.normals = cloud->normals; ra.n = cloud->n; ra.num_blocks = nb;
             ra.rl = rl; ra.max_distance = max_distance;
             ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;

@@ -17,13 +17,14 @@ struct BvhView {
     const Node64 * __restrict__ inner;
     const Node128 * __restrict__ wide;
     const Tri64 * __restrict__ tris;
+    const float * __restrict__ raw_tris;     // 9 floats per triangle, leaf order (reference layout)
     const uint32_t * __restrict__ indices;
     uint32_t root_is_leaf, root_first, root_count;
 };
 
 __host__ inline BvhView view_of(const uavmvs_bvh * b) {
     BvhView v;
-    v.inner = b->inner; v.wide = b->wide; v.tris = b->ptris; v.indices = b->indices;
+    v.inner = b->inner; v.wide = b->wide; v.tris = b->ptris; v.raw_tris = b->tris; v.indices = b->indices;
     v.root_is_leaf = b->root_is_leaf; v.root_first = b->root_first; v.root_count = b->root_count;
     return v;
 }
