@@ -1,0 +1,121 @@
+"""Spherical-histogram path (K4/K5/K6/K7) through the C ABI against the CPU oracle.
+
+Bins (nearest sphere vertex through the same KD-tree) are integer work: bit-exact.  Histogram
+sums are float accumulations in a different order (shared-memory + global atomics vs the oracle's
+serial double sum): gated at 1e-5 relative to the magnitude of the summands, per bin.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    from uavmvs_b200 import api as a
+    assert a.device_count() >= 1
+    return a
+
+
+@pytest.fixture(scope="module")
+def setup(api, oracle):
+    from uavmvs_b200 import scenes
+    sc = scenes.dense()
+    obvh = oracle.BVH.build(sc.verts, sc.faces, threads=2)
+    arrays = obvh.export()
+    gbvh = api.BVHTree.create(arrays.nodes, arrays.aabbs, arrays.tris, arrays.indices)
+    sv = oracle.sphere_vertices(1.0, 3)
+    okd = oracle.KD.build(sv)
+    kn, kv = okd.export()
+    gkd = api.KDTree.create(kn, kv)
+    rng = np.random.default_rng(9)
+    values = rng.uniform(0.0, 1.2, sc.num_points).astype(np.float32)
+    quals = rng.uniform(-0.1, 1.0, sc.num_points).astype(np.float32)
+    cloud = api.PointCloud.create(sc.points, sc.normals, values, quals)
+    return dict(sc=sc, obvh=obvh, gbvh=gbvh, sv=sv, okd=okd, gkd=gkd, values=values, quals=quals, cloud=cloud)
+
+
+def _hist_close(h_gpu, h_ref, bins, contrib, S):
+    mag = np.zeros(S, np.float64)
+    ok = bins != 0xFFFFFFFF
+    np.add.at(mag, bins[ok], np.abs(contrib[ok].astype(np.float64)))
+    return np.all(np.abs(h_gpu.astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12)
+
+
+POSITIONS = [(32.0, 32.0, 45.0), (10.0, 50.0, 30.0), (60.0, 5.0, 70.0), (32.0, 32.0, 400.0)]
+
+
+def test_populate_spherical_histogram_k4(api, oracle, setup):
+    s = setup
+    sc, S = s["sc"], s["sv"].shape[0]
+    for pos in POSITIONS:
+        h_ref, bins, scores = oracle.populate_spherical_histogram(s["obvh"], s["okd"], np.array(pos, np.float32),
+                                                                  sc.max_distance, sc.points, sc.normals,
+                                                                  s["values"], s["quals"], S)
+        hist = api.Array.create(S)
+        hist.null()
+        api.populate_spherical_histogram(pos, sc.max_distance, s["gbvh"], s["cloud"], s["gkd"], hist)
+        h_gpu = hist.download()
+        assert np.array_equal(h_gpu != 0, h_ref != 0) or _hist_close(h_gpu, h_ref, bins, scores, S)
+        assert _hist_close(h_gpu, h_ref, bins, scores, S)
+        if pos[2] < 100:
+            assert (bins != 0xFFFFFFFF).sum() > 100
+        else:
+            assert not h_gpu.any()                               # beyond max_distance: nothing populated
+
+
+def test_populate_spherical_histogram_k5_and_image_k6(api, oracle, setup):
+    s = setup
+    sc, S = s["sc"], s["sv"].shape[0]
+    # state after a full evaluation: obs rows sorted, recons
+    obs_o = oracle.ObsRays(sc.num_points, 32)
+    oracle.update_observation_rays(s["obvh"], True, sc.views28(), sc.max_distance, sc.width, sc.height,
+                                   sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    r_o = oracle.evaluate_observation_rays(obs_o)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    recons, wrecons = api.Array.create(sc.num_points), api.Array.create(sc.num_points)
+    api.evaluate_trajectory(sc.views28(), sc.max_distance, sc.target_recon, sc.width, sc.height, s["gbvh"],
+                            s["cloud"], obs, recons, wrecons)
+    assert np.array_equal(obs.download(data=False)[1], obs_o.num_rows)
+    for pos in POSITIONS[:3]:
+        # the oracle consumes the GPU's recons so that the only differences are this kernel's
+        h_ref, bins, deltas = oracle.populate_spherical_histogram_recon(
+            s["obvh"], s["okd"], np.array(pos, np.float32), sc.max_distance, sc.target_recon, sc.points, sc.normals,
+            obs_o, recons.download(), S)
+        hist = api.Array.create(S)
+        hist.null()
+        api.populate_spherical_histogram(pos, sc.max_distance, s["gbvh"], s["cloud"], s["gkd"], hist,
+                                         target_recon=sc.target_recon, obs_rays=obs, recons=recons)
+        h_gpu = hist.download()
+        # deltas are differences of squares: 1e-5 of their operands' magnitude (func(new), func(old) <= 16)
+        mag = np.zeros(S, np.float64)
+        ok = bins != 0xFFFFFFFF
+        np.add.at(mag, bins[ok], 16.0)
+        assert np.all(np.abs(h_gpu.astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12)
+        assert ok.sum() > 100 and (h_ref < 0).any()
+        # K6 on the GPU histogram vs the oracle on the same histogram
+        img = api.Image.create(128, 45)
+        api.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["gkd"], hist, img)
+        i_gpu = img.download()
+        i_ref = oracle.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["sv"], h_gpu)
+        assert i_gpu.shape == (45, 128)
+        scale = np.abs(h_gpu).sum()
+        assert np.all(np.abs(i_gpu.astype(np.float64) - i_ref) <= 1e-5 * scale + 1e-12)
+        # the optimiser's argmin (apps/optimize_trajectory/optimize_trajectory.cu:415-428) agrees in value
+        assert abs(float(i_gpu.min()) - float(i_ref.min())) <= 1e-5 * scale + 1e-12
+
+
+def test_estimate_capture_difficulty_k7(api, oracle, setup):
+    s = setup
+    sc = s["sc"]
+    n = 512
+    pts, nrm = sc.points[:n], sc.normals[:n]
+    mesh_size = sc.num_tris // 2            # pretend the second half of the faces is "airspace"
+    v_o, q_o = oracle.estimate_capture_difficulty(s["obvh"], sc.max_distance, mesh_size, s["sv"], pts, nrm)
+    cloud = api.PointCloud.create(pts, nrm)
+    api.estimate_capture_difficulty(sc.max_distance, s["gbvh"], mesh_size, s["gkd"], cloud)
+    v_g, q_g = cloud.download_attributes()
+    assert np.allclose(v_g, v_o, rtol=1e-5, atol=1e-6)
+    assert np.allclose(q_g, q_o, rtol=1e-5, atol=1e-6)
+    assert q_o.max() > 0 and v_o.min() < 1.5
