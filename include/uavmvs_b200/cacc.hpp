@@ -1,0 +1,246 @@
+/*
+ * cacc.hpp -- header-compatible facade of the reference's device containers and of the
+ * libs/eval kernel entry points over the C ABI of libuavmvs_b200 (include/uavmvs_b200.h).
+ *
+ * An app of the reference (apps/evaluate_trajectory/evaluate_trajectory.cu and siblings)
+ * keeps its source: it includes this header instead of "cacc/..." and "eval/kernels.h",
+ * and a kernel launch
+ *
+ *     update_observation_rays<<<grid, block, 0, stream>>>(true, pos, max_distance, w2c, calib,
+ *         width, height, dbvh_tree->accessor(), dcloud->cdata(), dobs_rays->cdata());
+ *
+ * becomes the plain call
+ *
+ *     update_observation_rays(stream, true, pos, max_distance, w2c, calib,
+ *         width, height, dbvh_tree->accessor(), dcloud->cdata(), dobs_rays->cdata());
+ *
+ * (same argument list, the launch configuration replaced by the stream).  Ownership follows
+ * the reference: static create() returns a std::shared_ptr (libs/cacc/bvh_tree.h:190-194),
+ * accessor()/cdata() return non-owning PODs passed by value (bvh_tree.h:44-49,
+ * point_cloud.h:26-32, vector_array.h:23-29).  Errors keep the reference's convention:
+ * print "file:line (call): message" and exit (libs/cacc/defines.h:20-29).
+ *
+ * Host-side inputs are plain arrays (the acc tree's nodes/aabbs/tris/indices, exactly what
+ * cacc::BVHTree<HOST>::convert produces, libs/cacc/bvh_tree.cu:17-48); no MVE types appear.
+ * Plain C++11, no CUDA headers needed by the caller.
+ */
+#ifndef UAVMVS_B200_CACC_HPP
+#define UAVMVS_B200_CACC_HPP
+
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
+
+#include "../uavmvs_b200.h"
+
+#define UAVMVS_CHECK(call)                                                                  \
+    do {                                                                                    \
+        if ((call) != 0) {                                                                  \
+            std::fprintf(stderr, "%s:%d (%s): %s\n", __FILE__, __LINE__, #call, uavmvs_last_error()); \
+            std::exit(EXIT_FAILURE);                                                        \
+        }                                                                                   \
+    } while (0)
+
+namespace cacc {
+
+enum Location { HOST, DEVICE };
+typedef void * Stream;   /* cudaStream_t */
+
+struct Vec3f { float v[3]; float & operator[](int i) { return v[i]; } float operator[](int i) const { return v[i]; } };
+struct Mat3f { float m[9]; };    /* row-major, libs/cacc/matrix.h:36-44 */
+struct Mat4f { float m[16]; };
+
+inline void select_cuda_device(int, int) { UAVMVS_CHECK(uavmvs_set_device(0)); }   /* libs/cacc/util.h:82-87 */
+inline void set_cuda_device(int device) { UAVMVS_CHECK(uavmvs_set_device(device)); }
+inline void sync(Stream stream) { UAVMVS_CHECK(uavmvs_synchronize(stream)); }
+
+template <Location L> class BVHTree;
+template <> class BVHTree<DEVICE> {
+public:
+    typedef std::shared_ptr<BVHTree> Ptr;
+    struct Accessor { const uavmvs_bvh * h; };
+    /* cacc::BVHTree<DEVICE>::create(acc_tree): arrays as convert<HOST> lays them out */
+    static Ptr create(const uint32_t * nodes, const float * aabbs, const float * tris,
+        const uint32_t * indices, uint32_t num_nodes, uint32_t num_tris) {
+        Ptr p(new BVHTree());
+        UAVMVS_CHECK(uavmvs_bvh_create_from_arrays(nodes, aabbs, tris, indices, num_nodes, num_tris, &p->h));
+        return p;
+    }
+    /* B200-native alternative to the host SAH build: GPU LBVH from an indexed mesh */
+    static Ptr build(const float * verts, uint32_t num_verts, const uint32_t * faces, uint32_t num_faces) {
+        Ptr p(new BVHTree());
+        UAVMVS_CHECK(uavmvs_bvh_build_lbvh(verts, num_verts, faces, num_faces, &p->h));
+        return p;
+    }
+    Accessor accessor() const { Accessor a = {h}; return a; }
+    ~BVHTree() { uavmvs_bvh_destroy(h); }
+private:
+    BVHTree() : h(nullptr) {}
+    uavmvs_bvh * h;
+};
+
+template <unsigned K, Location L> class KDTree;
+template <> class KDTree<3u, DEVICE> {
+public:
+    typedef std::shared_ptr<KDTree> Ptr;
+    struct Accessor { const uavmvs_kdtree * h; };
+    static Ptr create(const uint32_t * nodes, const float * verts, uint32_t num_nodes) {
+        Ptr p(new KDTree());
+        UAVMVS_CHECK(uavmvs_kdtree_create(nodes, verts, num_nodes, &p->h));
+        return p;
+    }
+    Accessor accessor() const { Accessor a = {h}; return a; }
+    ~KDTree() { uavmvs_kdtree_destroy(h); }
+private:
+    KDTree() : h(nullptr) {}
+    uavmvs_kdtree * h;
+};
+
+template <Location L> class PointCloud;
+template <> class PointCloud<HOST> {
+public:
+    typedef std::shared_ptr<PointCloud> Ptr;
+    struct Data { float * vertices_ptr, * normals_ptr, * values_ptr, * qualities_ptr; uint32_t num_vertices; };
+    static Ptr create(uint32_t n) { return Ptr(new PointCloud(n)); }
+    Data cdata() { Data d = {v.data(), nrm.data(), val.data(), q.data(), n}; return d; }
+private:
+    explicit PointCloud(uint32_t n) : n(n), v(3 * (size_t)n), nrm(3 * (size_t)n), val(n, 0.0f), q(n, 1.0f) {}
+    uint32_t n; std::vector<float> v, nrm, val, q;   /* xyz packed; defaults of libs/util/cio.h:45-46 */
+};
+template <> class PointCloud<DEVICE> {
+public:
+    typedef std::shared_ptr<PointCloud> Ptr;
+    struct Data { uavmvs_cloud * h; };
+    template <Location O> static Ptr create(typename PointCloud<O>::Ptr host) {   /* point_cloud.h:95-114 */
+        typename PointCloud<O>::Data d = host->cdata();
+        Ptr p(new PointCloud());
+        UAVMVS_CHECK(uavmvs_cloud_create(d.vertices_ptr, d.normals_ptr, d.values_ptr, d.qualities_ptr, d.num_vertices, &p->h));
+        return p;
+    }
+    void download(PointCloud<HOST>::Ptr host) const {   /* values/qualities written by estimate_capture_difficulty */
+        PointCloud<HOST>::Data d = host->cdata();
+        UAVMVS_CHECK(uavmvs_cloud_download_attributes(h, d.values_ptr, d.qualities_ptr));
+    }
+    Data cdata() const { Data d = {h}; return d; }
+    ~PointCloud() { uavmvs_cloud_destroy(h); }
+private:
+    PointCloud() : h(nullptr) {}
+    uavmvs_cloud * h;
+};
+
+template <typename T, Location L> class VectorArray;
+template <> class VectorArray<Vec3f, DEVICE> {
+public:
+    typedef std::shared_ptr<VectorArray> Ptr;
+    struct Data { uavmvs_obs * h; };
+    static Ptr create(uint32_t num_cols, uint32_t max_rows, Stream = nullptr) {   /* vector_array.h:87-90 */
+        Ptr p(new VectorArray());
+        UAVMVS_CHECK(uavmvs_obs_create(num_cols, max_rows, &p->h));
+        return p;
+    }
+    void null(Stream stream = nullptr) { UAVMVS_CHECK(uavmvs_obs_clear(stream, h)); }
+    void download(float * data, uint32_t * num_rows) const { UAVMVS_CHECK(uavmvs_obs_download(h, data, num_rows)); }
+    Data cdata() const { Data d = {h}; return d; }
+    ~VectorArray() { uavmvs_obs_destroy(h); }
+private:
+    VectorArray() : h(nullptr) {}
+    uavmvs_obs * h;
+};
+
+template <typename T, Location L> class Array;
+template <> class Array<float, DEVICE> {
+public:
+    typedef std::shared_ptr<Array> Ptr;
+    struct Data { uavmvs_array * h; };
+    static Ptr create(uint32_t n, Stream = nullptr) {   /* array.h:73-76 */
+        Ptr p(new Array()); p->n = n;
+        UAVMVS_CHECK(uavmvs_array_create(n, &p->h));
+        return p;
+    }
+    void null(Stream stream = nullptr) { UAVMVS_CHECK(uavmvs_array_null(stream, h)); }   /* array.h:123-128 */
+    void download(float * host) const { UAVMVS_CHECK(uavmvs_array_download(h, host)); }   /* operator= HOST <- DEVICE */
+    void upload(const float * host) { UAVMVS_CHECK(uavmvs_array_upload(h, host)); }
+    uint32_t size() const { return n; }
+    Data cdata() const { Data d = {h}; return d; }
+    ~Array() { uavmvs_array_destroy(h); }
+private:
+    Array() : h(nullptr), n(0) {}
+    uavmvs_array * h; uint32_t n;
+};
+
+template <typename T, Location L> class Image;
+template <> class Image<float, DEVICE> {
+public:
+    typedef std::shared_ptr<Image> Ptr;
+    struct Data { uavmvs_image * h; };
+    static Ptr create(uint32_t width, uint32_t height, Stream = nullptr) {   /* image.h:84-86 */
+        Ptr p(new Image());
+        UAVMVS_CHECK(uavmvs_image_create(width, height, &p->h));
+        return p;
+    }
+    void download(float * host) const { UAVMVS_CHECK(uavmvs_image_download(h, host)); }
+    Data cdata() const { Data d = {h}; return d; }
+    ~Image() { uavmvs_image_destroy(h); }
+private:
+    Image() : h(nullptr) {}
+    uavmvs_image * h;
+};
+
+namespace reduction {   /* libs/cacc/reduction.h:132-162 */
+inline void all(Array<float, DEVICE>::Ptr a, float out3[3], Stream stream = nullptr) {
+    UAVMVS_CHECK(uavmvs_reduce(stream, a->cdata().h, out3));
+}
+inline float sum(Array<float, DEVICE>::Ptr a, Stream s = nullptr) { float o[3]; all(a, o, s); return o[0]; }
+inline float min(Array<float, DEVICE>::Ptr a, Stream s = nullptr) { float o[3]; all(a, o, s); return o[1]; }
+inline float max(Array<float, DEVICE>::Ptr a, Stream s = nullptr) { float o[3]; all(a, o, s); return o[2]; }
+}  // namespace reduction
+
+}  // namespace cacc
+
+/* ---- libs/eval/kernels.h:26-93, same argument lists, launch configuration -> stream ---- */
+inline void configure_heuristic(float m_k, float m_x0, float t_k, float t_x0) {
+    UAVMVS_CHECK(uavmvs_configure_heuristic(m_k, m_x0, t_k, t_x0));
+}
+inline void update_observation_rays(cacc::Stream stream, bool populate, cacc::Vec3f view_pos, float max_distance,
+    cacc::Mat4f w2c, cacc::Mat3f calib, int width, int height, cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree,
+    cacc::PointCloud<cacc::DEVICE>::Data cloud, cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays) {
+    UAVMVS_CHECK(uavmvs_update_observation_rays(stream, populate ? 1 : 0, view_pos.v, max_distance, w2c.m, calib.m,
+        width, height, bvh_tree.h, cloud.h, obs_rays.h));
+}
+inline void process_observation_rays(cacc::Stream stream, cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays) {
+    UAVMVS_CHECK(uavmvs_process_observation_rays(stream, obs_rays.h));
+}
+inline void evaluate_observation_rays(cacc::Stream stream, cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays,
+    cacc::Array<float, cacc::DEVICE>::Data recons) {
+    UAVMVS_CHECK(uavmvs_evaluate_observation_rays(stream, obs_rays.h, recons.h));
+}
+inline void populate_spherical_histogram(cacc::Stream stream, cacc::Vec3f view_pos, float max_distance,
+    cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, cacc::PointCloud<cacc::DEVICE>::Data cloud,
+    cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::Array<float, cacc::DEVICE>::Data sphere_hist) {
+    UAVMVS_CHECK(uavmvs_populate_spherical_histogram(stream, view_pos.v, max_distance, bvh_tree.h, cloud.h, kd_tree.h,
+        sphere_hist.h));
+}
+inline void populate_spherical_histogram(cacc::Stream stream, cacc::Vec3f view_pos, float max_distance,
+    float target_recon, cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, cacc::PointCloud<cacc::DEVICE>::Data cloud,
+    cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays,
+    cacc::Array<float, cacc::DEVICE>::Data recons, cacc::Array<float, cacc::DEVICE>::Data sphere_hist) {
+    UAVMVS_CHECK(uavmvs_populate_spherical_histogram_recon(stream, view_pos.v, max_distance, target_recon, bvh_tree.h,
+        cloud.h, kd_tree.h, obs_rays.h, recons.h, sphere_hist.h));
+}
+inline void evaluate_spherical_histogram(cacc::Stream stream, cacc::Mat3f calib, int width, int height,
+    cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::Array<float, cacc::DEVICE>::Data sphere_hist,
+    cacc::Image<float, cacc::DEVICE>::Data hist) {
+    UAVMVS_CHECK(uavmvs_evaluate_spherical_histogram(stream, calib.m, width, height, kd_tree.h, sphere_hist.h, hist.h));
+}
+inline void estimate_capture_difficulty(cacc::Stream stream, float max_distance,
+    cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, uint32_t mesh_size, cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree,
+    cacc::PointCloud<cacc::DEVICE>::Data cloud) {
+    UAVMVS_CHECK(uavmvs_estimate_capture_difficulty(stream, max_distance, bvh_tree.h, mesh_size, kd_tree.h, cloud.h));
+}
+inline void calculate_func_recons(cacc::Stream stream, cacc::Array<float, cacc::DEVICE>::Data recons, float target_recon,
+    cacc::Array<float, cacc::DEVICE>::Data wrecons) {
+    UAVMVS_CHECK(uavmvs_calculate_func_recons(stream, recons.h, target_recon, wrecons.h));
+}
+
+#endif /* UAVMVS_B200_CACC_HPP */
