@@ -238,6 +238,7 @@ def ncu_traffic():
 
 
 def run_b200(a, rank, local_rank, world):
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # keep stdout to the one JSON line
     import torch
     import torch.distributed as dist
     from uavmvs_b200 import api, sharded
@@ -349,7 +350,7 @@ def run_b200(a, rank, local_rank, world):
                          "K9": float(k_ms[3]) / a.steps},
             "e2e": {"value": rays * a.steps / e2e_sec, "unit": UNIT, "ms_per_step": e2e_ms / a.steps,
                     "h2d_bytes_per_step": int(views_np.nbytes), "d2h_bytes_per_step": int(8 * n_local + 12 + 32)},
-            "gpu_launches": 5 * a.steps, "clocks": clocks}
+            "gpu_launches": 11 * a.steps, "clocks": clocks}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

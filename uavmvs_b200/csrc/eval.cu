@@ -10,65 +10,102 @@ namespace uav {
 static Heur g_heur = {8.0f, 4.0f, 32.0f, 16.0f};   // m_k, m_x0, t_k, t_x0 (kernels.cu:93-96)
 Heur current_heur() { return g_heur; }
 
-// ---- K2: process_observation_rays, kernels.cu:204-264 (one warp per point) ----------
-__global__ void __launch_bounds__(128)
-k_process_observation_rays(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t stride, uint32_t n)
+// ---- K2 + K3 (+K8): process_observation_rays, kernels.cu:204-264, evaluate_observation_rays,
+// :266-291 (heuristic :111-136), calculate_func_recons :496-510 -------------------------------
+// One CTA = 32 consecutive points.  The [rows x 32 points] tile of the observation array is
+// moved through shared memory with coalesced 512-B row segments (the reference reads and writes
+// one 16-B element per lane at stride `pitch`); each warp then handles 8 points, one at a time:
+//   DO_SORT  lane = row: the reference's warp bitonic network (same compare/exchange sequence, so
+//            ties and the final order are those of kernels.cu:233-248), compaction of invalidated
+//            rows, counter rewritten only if something was invalid (:251-254)
+//   DO_EVAL  the n(n-1)/2 pairs are spread over the lanes (pair p -> lane p % 32), partial sums
+//            combined by a shuffle tree.  The summation order differs from the reference's
+//            serial double loop; scores are gated at 1e-5 relative (north_star), not bitwise.
+constexpr int SE_THREADS = 128;
+constexpr int SE_TILE_STRIDE = 33;      // float4 per tile row: padding against bank conflicts
+
+template <bool DO_SORT, bool DO_EVAL>
+__global__ void __launch_bounds__(SE_THREADS)
+k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t stride, uint32_t n,
+    float * __restrict__ recons, float target, float * __restrict__ wrecons, Heur h)
 {
-    const uint32_t tx = threadIdx.x & 31;
-    const uint32_t id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (id >= n) return;
-    uint32_t num_rows = min(num_rows_ptr[id], max_rows);
-    float4 * col = obs + id;
-    float4 ray = make_float4(0.f, 0.f, 0.f, 0.f);
-    int key = (int)tx;
-    float theta = -1.0f;
-    if (tx < num_rows) {
-        ray = col[(size_t)tx * stride];
-        theta = (ray.w >= 0.0f) ? ray.z : -1.0f;
+    __shared__ float4 s_tile[32 * SE_TILE_STRIDE];
+    __shared__ float4 s_col[SE_THREADS / 32][32];
+    __shared__ uint32_t s_rows[32], s_valid[32];
+    const uint32_t tx = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t pt0 = blockIdx.x * 32;
+    if (threadIdx.x < 32) {
+        uint32_t id = pt0 + threadIdx.x;
+        uint32_t r = id < n ? min(num_rows_ptr[id], max_rows) : 0u;
+        s_rows[threadIdx.x] = r; s_valid[threadIdx.x] = r;
     }
-    for (int i = 0; (1u << i) < num_rows; ++i) {
-        bool asc = (tx >> (i + 1)) % 2;
-        for (int s = 1 << i; s > 0; s >>= 1) {
-            bool dir = (tx % (s << 1)) < s;
-            float otheta = __shfl_xor_sync(0xffffffffu, theta, s);
-            int okey = __shfl_xor_sync(0xffffffffu, key, s);
-            if (otheta != theta && ((otheta > theta) == (asc ^ dir))) { theta = otheta; key = okey; }
+    __syncthreads();
+    uint32_t rmax = s_rows[tx];
+    for (int o = 16; o > 0; o >>= 1) rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    // coalesced load of rows [0, rmax): warp w takes rows w, w + 4, ...
+    for (uint32_t r = w; r < rmax; r += SE_THREADS / 32)
+        if (pt0 + tx < n) s_tile[r * SE_TILE_STRIDE + tx] = obs[(size_t)r * stride + pt0 + tx];
+    __syncthreads();
+
+    const float m_k = h.m_k, m_x0 = kPi / h.m_x0, t_k = h.t_k, t_x0 = kPi / h.t_x0;
+    for (uint32_t p = w * 8; p < w * 8 + 8; ++p) {
+        const uint32_t id = pt0 + p;
+        if (id >= n) break;                                   // warp-uniform
+        const uint32_t num_rows = s_rows[p];
+        float4 ray = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tx < num_rows) ray = s_tile[tx * SE_TILE_STRIDE + p];
+        uint32_t nv = num_rows;
+        if (DO_SORT) {
+            int key = (int)tx;
+            float theta = -1.0f;
+            if (tx < num_rows) theta = (ray.w >= 0.0f) ? ray.z : -1.0f;
+            for (int i = 0; (1u << i) < num_rows; ++i) {
+                bool asc = (tx >> (i + 1)) % 2;
+                for (int s = 1 << i; s > 0; s >>= 1) {
+                    bool dir = (tx % (s << 1)) < s;
+                    float otheta = __shfl_xor_sync(0xffffffffu, theta, s);
+                    int okey = __shfl_xor_sync(0xffffffffu, key, s);
+                    if (otheta != theta && ((otheta > theta) == (asc ^ dir))) { theta = otheta; key = okey; }
+                }
+            }
+            nv = __popc(__ballot_sync(0xffffffffu, theta >= 0.0f));
+            ray.x = __shfl_sync(0xffffffffu, ray.x, key);
+            ray.y = __shfl_sync(0xffffffffu, ray.y, key);
+            ray.z = __shfl_sync(0xffffffffu, ray.z, key);
+            ray.w = __shfl_sync(0xffffffffu, ray.w, key);
+            if (tx < nv) s_tile[tx * SE_TILE_STRIDE + p] = ray;      // rows >= nv keep their old content
+            if (tx == 0) s_valid[p] = nv;
+        }
+        if (DO_EVAL) {
+            __syncwarp();
+            s_col[w][tx] = ray;
+            __syncwarp();
+            const uint32_t rows = nv;
+            const uint32_t npairs = rows * (rows - (rows ? 1u : 0u)) / 2u;
+            float sum = 0.0f;
+            for (uint32_t q = tx; q < npairs; q += 32) {
+                // pair q -> (i, j), i > j:  i = floor((1 + sqrt(1 + 8 q)) / 2), fixed up exactly
+                uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
+                while (i * (i - 1) / 2 > q) --i;
+                while ((i + 1) * i / 2 <= q) ++i;
+                const uint32_t j = q - i * (i - 1) / 2;
+                sum += pair_term(s_col[w][j], s_col[w][i], m_k, m_x0, t_k, t_x0);
+            }
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (tx == 0) {
+                float recon = rows >= 1 ? sum : -1.0f;            // kernels.cu:283-288: none -> -1, one -> 0
+                recons[id] = recon;
+                if (wrecons) wrecons[id] = func(recon, target);
+            }
         }
     }
-    uint32_t num_valid = __popc(__ballot_sync(0xffffffffu, theta >= 0.0f));
-    if (num_valid < num_rows && tx == 0) num_rows_ptr[id] = num_valid;
-    ray.x = __shfl_sync(0xffffffffu, ray.x, key);
-    ray.y = __shfl_sync(0xffffffffu, ray.y, key);
-    ray.z = __shfl_sync(0xffffffffu, ray.z, key);
-    ray.w = __shfl_sync(0xffffffffu, ray.w, key);
-    if (tx < num_valid) col[(size_t)tx * stride] = ray;
-}
-
-// ---- K3: evaluate_observation_rays, kernels.cu:266-291 (one thread per point) -------
-// The point's column is staged in shared memory once; the pair sum keeps the reference's
-// order (inner j < i ascending, outer i ascending).
-constexpr int K3_THREADS = 128;
-__global__ void __launch_bounds__(K3_THREADS)
-k_evaluate_observation_rays(const float4 * __restrict__ obs, const uint32_t * __restrict__ num_rows_ptr,
-    uint32_t max_rows, uint32_t stride, uint32_t n, float * __restrict__ recons,
-    float target, float * __restrict__ wrecons, Heur h)
-{
-    extern __shared__ float4 s_col[];   // [max_rows][K3_THREADS]
-    const uint32_t id = blockIdx.x * K3_THREADS + threadIdx.x;
-    if (id >= n) return;
-    const uint32_t rows = min(num_rows_ptr[id], max_rows);
-    for (uint32_t i = 0; i < rows; ++i) s_col[i * K3_THREADS + threadIdx.x] = obs[(size_t)i * stride + id];
-    const float m_k = h.m_k, m_x0 = kPi / h.m_x0, t_k = h.t_k, t_x0 = kPi / h.t_x0;
-    float recon = rows >= 1 ? 0.0f : -1.0f;
-    for (uint32_t i = 1; i < rows; ++i) {
-        float4 ri = s_col[i * K3_THREADS + threadIdx.x];
-        float sum = 0.0f;
-        for (uint32_t j = 0; j < i; ++j)
-            sum += pair_term(s_col[j * K3_THREADS + threadIdx.x], ri, m_k, m_x0, t_k, t_x0);
-        recon += sum;
+    if (DO_SORT) {
+        __syncthreads();
+        for (uint32_t r = w; r < rmax; r += SE_THREADS / 32)
+            if (pt0 + tx < n && r < s_valid[tx]) obs[(size_t)r * stride + pt0 + tx] = s_tile[r * SE_TILE_STRIDE + tx];
+        if (threadIdx.x < 32 && pt0 + threadIdx.x < n && s_valid[threadIdx.x] < s_rows[threadIdx.x])
+            num_rows_ptr[pt0 + threadIdx.x] = s_valid[threadIdx.x];
     }
-    recons[id] = recon;
-    if (wrecons) wrecons[id] = func(recon, target);
 }
 
 // ---- K8: calculate_func_recons, kernels.cu:496-510 -----------------------------------
@@ -148,19 +185,21 @@ static int ensure_scratch(size_t view_floats)
     return 0;
 }
 
-static int launch_k3(cudaStream_t s, const uavmvs_obs * obs, uavmvs_array * recons, float target, uavmvs_array * wrecons)
+static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_obs * obs, uavmvs_array * recons,
+    float target, uavmvs_array * wrecons)
 {
-    UAV_REQUIRE(obs && recons, "null handle");
-    UAV_REQUIRE(recons->n == obs->num_cols, "recons size != obs columns");
-    size_t smem = sizeof(float4) * obs->max_rows * K3_THREADS;
-    static bool attr_set = false;
-    if (!attr_set) {
-        UAV_CUDA(cudaFuncSetAttribute(k_evaluate_observation_rays, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-        attr_set = true;
-    }
-    k_evaluate_observation_rays<<<divup(obs->num_cols, K3_THREADS), K3_THREADS, smem, s>>>(
-        obs->data, obs->num_rows, obs->max_rows, (uint32_t)(obs->pitch / sizeof(float4)), obs->num_cols,
-        recons->data, target, wrecons ? wrecons->data : nullptr, g_heur);
+    UAV_REQUIRE(obs, "null handle");
+    UAV_REQUIRE(!do_eval || (recons && recons->n == obs->num_cols), "recons size != obs columns");
+    UAV_REQUIRE(!wrecons || wrecons->n == obs->num_cols, "wrecons size != obs columns");
+    const unsigned grid = divup(obs->num_cols, 32);
+    const uint32_t stride = (uint32_t)(obs->pitch / sizeof(float4));
+    float * r = recons ? recons->data : nullptr, * wr = wrecons ? wrecons->data : nullptr;
+    if (do_sort && do_eval)
+        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
+    else if (do_sort)
+        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
+    else
+        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -233,15 +272,12 @@ int uavmvs_update_observation_rays(void * stream, int populate, const float view
 int uavmvs_process_observation_rays(void * stream, uavmvs_obs * obs)
 {
     UAV_REQUIRE(obs, "null obs");
-    k_process_observation_rays<<<divup((uint64_t)obs->num_cols * 32, 128), 128, 0, (cudaStream_t)stream>>>(
-        obs->data, obs->num_rows, obs->max_rows, (uint32_t)(obs->pitch / sizeof(float4)), obs->num_cols);
-    UAV_CUDA(cudaGetLastError());
-    return 0;
+    return launch_sort_eval((cudaStream_t)stream, true, false, obs, nullptr, 0.0f, nullptr);
 }
 
 int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavmvs_array * recons)
 {
-    return launch_k3((cudaStream_t)stream, obs, recons, 0.0f, nullptr);
+    return launch_sort_eval((cudaStream_t)stream, false, true, const_cast<uavmvs_obs *>(obs), recons, 0.0f, nullptr);
 }
 
 int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon, uavmvs_array * wrecons)
@@ -279,10 +315,8 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
         stats ? g_scratch.stats : nullptr);
     if (rc) return rc;
     UAV_CUDA(cudaEventRecord(g_scratch.ev[1], s));
-    rc = uavmvs_process_observation_rays(stream, obs);
-    if (rc) return rc;
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[2], s));
-    rc = launch_k3(s, obs, recons, target_recon, wrecons);
+    UAV_CUDA(cudaEventRecord(g_scratch.ev[2], s));      // K2 is fused into the next launch
+    rc = launch_sort_eval(s, true, true, obs, recons, target_recon, wrecons);
     if (rc) return rc;
     UAV_CUDA(cudaEventRecord(g_scratch.ev[3], s));
     if (launch_reduce(s, wrecons)) return 1;
