@@ -45,7 +45,7 @@ def parse():
     ap.add_argument("--points", type=int, default=1_000_000, help="proxy points per GPU")
     ap.add_argument("--views", type=int, default=2000)
     ap.add_argument("--extent", type=float, default=256.0)
-    ap.add_argument("--tree", default="lbvh", choices=["lbvh"], help="GPU LBVH build (product path)")
+    ap.add_argument("--tree", default="ploc", choices=["ploc", "lbvh"], help="GPU tree build (product path)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline sample")
     return ap.parse_args()
@@ -265,7 +265,7 @@ def run_b200(a, rank, local_rank, world):
     V = views_np.shape[0]
 
     t0 = time.perf_counter()
-    bvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
+    bvh = (api.BVHTree.build_ploc if a.tree == "ploc" else api.BVHTree.build_lbvh)(sc.verts, sc.faces)
     api.synchronize()
     build_s = time.perf_counter() - t0
     cloud = api.PointCloud.create(pts, nrm)
@@ -341,8 +341,8 @@ def run_b200(a, rank, local_rank, world):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a, world), "tree": "GPU LBVH (uavmvs_bvh_build_lbvh, %.3f s, not timed)"
-                       % build_s, "l2": "flushed between steps (256 MiB fill)", "rays_per_step": rays,
+            "config": {"workload": workload_name(a, world), "tree": "GPU %s (uavmvs_bvh_build_%s, %.3f s, not timed)"
+                       % (a.tree.upper(), a.tree, build_s), "l2": "flushed between steps (256 MiB fill)", "rays_per_step": rays,
                        "observations_per_step": observations, "pairs_per_step": pairs,
                        "sharding": "replicated mesh, interleaved %d-point Z-order chunks, 1 score all-reduce" % CHUNK},
             "pairs_per_s": pairs * a.steps / sec, "score": res["score"],

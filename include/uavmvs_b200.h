@@ -48,6 +48,10 @@ int uavmvs_bvh_create_from_arrays(const uint32_t * nodes, const float * aabbs, c
  * acc::BVHTree constructor (libs/acc/bvh_tree.h:335-399) for large scenes. */
 int uavmvs_bvh_build_lbvh(const float * verts, uint32_t num_verts, const uint32_t * faces,
     uint32_t num_faces, uavmvs_bvh ** out);
+/* Same inputs; the topology comes from parallel locally-ordered clustering over the Morton order
+ * (nearest neighbour by union surface area, mutual pairs merge): close to SAH quality, built on the GPU. */
+int uavmvs_bvh_build_ploc(const float * verts, uint32_t num_verts, const uint32_t * faces,
+    uint32_t num_faces, uavmvs_bvh ** out);
 int uavmvs_bvh_sizes(const uavmvs_bvh * bvh, uint32_t * num_nodes, uint32_t * num_tris);
 /* Export in the reference layout (for the oracle / for acc-side consumers). */
 int uavmvs_bvh_export(const uavmvs_bvh * bvh, uint32_t * nodes, float * aabbs, float * tris, uint32_t * indices);

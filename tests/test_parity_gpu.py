@@ -196,10 +196,11 @@ def test_evaluate_trajectory_fused(api, oracle, tiny_scene, tiny_tree):
         assert _close(s / sc.num_points, w_o.astype(np.float64).mean())
 
 
-def test_lbvh_same_tree_parity(api, oracle, tiny_scene):
-    """GPU-built LBVH: the oracle walks the exported tree (parity is per tree)."""
+@pytest.mark.parametrize("builder", ["build_lbvh", "build_ploc"])
+def test_gpu_built_tree_same_tree_parity(api, oracle, tiny_scene, builder):
+    """GPU-built trees (LBVH, PLOC): the oracle walks the exported tree (parity is per tree)."""
     sc = tiny_scene
-    gbvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
+    gbvh = getattr(api.BVHTree, builder)(sc.verts, sc.faces)
     nodes, aabbs, tris, indices = gbvh.export()
     n, t = gbvh.sizes()
     assert t == sc.num_tris and n == 2 * t - 1
@@ -209,6 +210,9 @@ def test_lbvh_same_tree_parity(api, oracle, tiny_scene):
     l, r = nodes[inner, 2], nodes[inner, 3]
     assert np.array_equal(aabbs[inner, :3], np.minimum(aabbs[l, :3], aabbs[r, :3]))
     assert np.array_equal(aabbs[inner, 3:], np.maximum(aabbs[l, 3:], aabbs[r, 3:]))
+    # a proper binary tree: every node except the root has exactly one parent, the root is node 0
+    kids = np.concatenate([l, r])
+    assert len(np.unique(kids)) == len(kids) == n - 1 and 0 not in kids
     obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
     rays = make_rays(sc, 50_000, seed=2)
     h_o, f_o, t_o = obvh.intersect(rays, any_hit=False)

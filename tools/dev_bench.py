@@ -16,6 +16,8 @@ ap.add_argument("--views", type=int, default=2000)
 ap.add_argument("--extent", type=float, default=256.0)
 ap.add_argument("--iters", type=int, default=5)
 ap.add_argument("--check", action="store_true")
+ap.add_argument("--ploc", action="store_true")
+ap.add_argument("--sah", action="store_true", help="dev experiment: tree from the oracle SAH builder (test infrastructure)")
 args = ap.parse_args()
 
 t = time.time()
@@ -23,7 +25,14 @@ sc = scenes.urban(args.tris, args.points, args.views, args.extent)
 print("scene", sc.name, "gen %.1fs" % (time.time() - t), flush=True)
 torch.cuda.init()
 t = time.time()
-bvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
+if args.sah:
+    import oracle
+    ta = oracle.BVH.build(sc.verts, sc.faces).export()
+    bvh = api.BVHTree.create(ta.nodes, ta.aabbs, ta.tris, ta.indices)
+elif args.ploc:
+    bvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+else:
+    bvh = api.BVHTree.build_lbvh(sc.verts, sc.faces)
 api.synchronize()
 print("lbvh build+upload %.3fs" % (time.time() - t), bvh.sizes(), flush=True)
 cloud = api.PointCloud.create(sc.points, sc.normals)
@@ -39,6 +48,7 @@ for it in range(args.iters):
     e1.record(stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
+    print("stages", ["%.3f" % x for x in api.profile_last()])
     print("iter %d: %.2f ms  rays %d vis %d pairs %d after_block_cull %d  -> %.3f Grays/s %.2f Gpairs/s score %.5f" % (
         it, ms, st[0], st[1], st[2], st[3], st[0] / ms / 1e6, st[2] / ms / 1e6, s / sc.num_points), flush=True)
 rows = obs.download(data=False)[1]

@@ -314,6 +314,97 @@ __global__ void k_leaves_refit(const float * __restrict__ verts, const uint32_t 
     }
 }
 
+// ------------------------------------------------------------------ PLOC build
+// Parallel locally-ordered clustering (Meister & Bittner 2017) over the Morton order: every round
+// each cluster looks at its PLOC_R neighbours on either side, picks the one whose union box has the
+// smallest surface area, and mutual pairs merge.  Bottom-up like the LBVH, but the topology follows
+// surface area instead of Morton-code bits, which brings the tree close to SAH quality.
+// Node ids as in the LBVH layout: inner nodes [0, n-1) with the root at 0 (ids are handed out from
+// n-2 downwards, the root is created last), leaf j = n-1+j (one triangle, Morton order).
+constexpr int PLOC_R = 24;
+
+__device__ __forceinline__ float union_area(const float * a, const float * b)
+{
+    float dx = fmaxf(a[3], b[3]) - fminf(a[0], b[0]);
+    float dy = fmaxf(a[4], b[4]) - fminf(a[1], b[1]);
+    float dz = fmaxf(a[5], b[5]) - fminf(a[2], b[2]);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_ploc_leaves(const float * __restrict__ verts, const uint32_t * __restrict__ faces,
+    const uint32_t * __restrict__ ids, int n, uint4 * __restrict__ nodes, float * __restrict__ aabbs,
+    float * __restrict__ tris, uint32_t * __restrict__ indices, uint32_t * __restrict__ cluster)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    uint32_t f = ids[j];
+    float t[9];
+    for (int k = 0; k < 3; ++k)
+        for (int c = 0; c < 3; ++c) t[3 * k + c] = verts[3 * (size_t)faces[3 * (size_t)f + k] + c];
+    for (int c = 0; c < 9; ++c) tris[9 * (size_t)j + c] = t[c];
+    indices[j] = f;
+    uint32_t me = (uint32_t)(n - 1 + j);
+    nodes[me] = make_uint4((uint32_t)j, (uint32_t)j + 1u, UAV_NAI, UAV_NAI);
+    float * bb = aabbs + 6 * (size_t)me;
+    for (int c = 0; c < 3; ++c) {   // libs/acc/primitives.h:74-81
+        bb[c] = fminf(t[c], fminf(t[3 + c], t[6 + c]));
+        bb[3 + c] = fmaxf(t[c], fmaxf(t[3 + c], t[6 + c]));
+    }
+    cluster[j] = me;
+}
+
+__global__ void k_ploc_nearest(const uint32_t * __restrict__ cluster, int n, const float * __restrict__ aabbs,
+    uint32_t * __restrict__ nn)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float bi[6];
+    const float * p = aabbs + 6 * (size_t)cluster[i];
+    for (int k = 0; k < 6; ++k) bi[k] = p[k];
+    float best = UAV_INF; int bj = -1;
+    int lo = max(0, i - PLOC_R), hi = min(n - 1, i + PLOC_R);
+    for (int j = lo; j <= hi; ++j) {
+        if (j == i) continue;
+        float a = union_area(bi, aabbs + 6 * (size_t)cluster[j]);
+        if (a < best) { best = a; bj = j; }          // ties: the lower position wins
+    }
+    nn[i] = (uint32_t)bj;
+}
+
+// keep[i] = 0 for the higher member of a mutual pair (absorbed), 1 otherwise; made[i] = 1 for the lower
+// member (creates a node)
+__global__ void k_ploc_flags(const uint32_t * __restrict__ nn, int n, uint32_t * __restrict__ keep,
+    uint32_t * __restrict__ made)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int j = (int)nn[i];
+    bool mutual = j >= 0 && (int)nn[j] == i;
+    keep[i] = (mutual && i > j) ? 0u : 1u;
+    made[i] = (mutual && i < j) ? 1u : 0u;
+}
+
+__global__ void k_ploc_merge(const uint32_t * __restrict__ cluster, const uint32_t * __restrict__ nn, int n,
+    const uint32_t * __restrict__ keep, const uint32_t * __restrict__ keep_pos,
+    const uint32_t * __restrict__ made, const uint32_t * __restrict__ made_pos, uint32_t id_base,
+    uint4 * __restrict__ nodes, float * __restrict__ aabbs, uint32_t * __restrict__ out_cluster)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !keep[i]) return;
+    uint32_t c = cluster[i];
+    if (made[i]) {
+        uint32_t l = c, r = cluster[nn[i]];
+        uint32_t id = id_base + made_pos[i];
+        const float * a = aabbs + 6 * (size_t)l, * b = aabbs + 6 * (size_t)r;
+        float * o = aabbs + 6 * (size_t)id;
+        for (int k = 0; k < 3; ++k) { o[k] = fminf(a[k], b[k]); o[3 + k] = fmaxf(a[3 + k], b[3 + k]); }
+        uint4 ln = nodes[l], rn = nodes[r];
+        nodes[id] = make_uint4(min(ln.x, rn.x), max(ln.y, rn.y), l, r);   // covering range (not a partition)
+        c = id;
+    }
+    out_cluster[keep_pos[i]] = c;
+}
+
 // ------------------------------------------------------------------ batch trace
 __global__ void k_trace(BvhView bvh, const float * __restrict__ rays, uint64_t n, int any_hit,
     uint8_t * __restrict__ hit, uint32_t * __restrict__ face, float * __restrict__ t)
@@ -403,6 +494,69 @@ int uavmvs_bvh_build_lbvh(const float * verts, uint32_t num_verts, const uint32_
     UAV_CUDA(cudaDeviceSynchronize());
     cudaFree(tmp); cudaFree(d_verts); cudaFree(d_faces); cudaFree(ids); cudaFree(ids2);
     cudaFree(keys); cudaFree(keys2); cudaFree(parent); cudaFree(visits); cudaFree(bounds);
+    if (finalize_layout(b)) return 1;
+    *out = b;
+    return 0;
+}
+
+int uavmvs_bvh_build_ploc(const float * verts, uint32_t num_verts, const uint32_t * faces,
+    uint32_t num_faces, uavmvs_bvh ** out)
+{
+    UAV_REQUIRE(verts && faces && out, "null argument");
+    UAV_REQUIRE(num_faces >= 1 && num_verts >= 1, "empty mesh");
+    int n = (int)num_faces;
+    uavmvs_bvh * b = new uavmvs_bvh();
+    b->num_nodes = 2 * num_faces - 1; b->num_tris = num_faces;
+    if (alloc_reference_arrays(b)) return 1;
+    float * d_verts; uint32_t * d_faces, * ids, * ids2; uint64_t * keys, * keys2; float * bounds;
+    uint32_t * cl_a, * cl_b, * nn, * keep, * keep_pos, * made, * made_pos;
+    UAV_CUDA(cudaMalloc(&d_verts, sizeof(float) * 3 * (size_t)num_verts));
+    UAV_CUDA(cudaMalloc(&d_faces, sizeof(uint32_t) * 3 * (size_t)num_faces));
+    UAV_CUDA(cudaMalloc(&ids, 4 * (size_t)n)); UAV_CUDA(cudaMalloc(&ids2, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&keys, 8 * (size_t)n)); UAV_CUDA(cudaMalloc(&keys2, 8 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&bounds, 6 * sizeof(float)));
+    UAV_CUDA(cudaMalloc(&cl_a, 4 * (size_t)n)); UAV_CUDA(cudaMalloc(&cl_b, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&nn, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&keep, 4 * (size_t)n)); UAV_CUDA(cudaMalloc(&keep_pos, 4 * (size_t)n));
+    UAV_CUDA(cudaMalloc(&made, 4 * (size_t)n)); UAV_CUDA(cudaMalloc(&made_pos, 4 * (size_t)n));
+    UAV_CUDA(cudaMemcpy(d_verts, verts, sizeof(float) * 3 * (size_t)num_verts, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(d_faces, faces, sizeof(uint32_t) * 3 * (size_t)num_faces, cudaMemcpyHostToDevice));
+    int init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    UAV_CUDA(cudaMemcpy(bounds, init, sizeof(init), cudaMemcpyHostToDevice));
+    k_scene_bounds<<<divup(num_verts, 256), 256>>>(d_verts, num_verts, bounds);
+    k_morton<<<divup(n, 256), 256>>>(d_verts, d_faces, num_faces, bounds, keys, ids);
+    size_t sort_bytes = 0, scan_bytes = 0; void * tmp = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys2, ids, ids2, n, 0, 63);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, keep, keep_pos, n);
+    size_t tmp_bytes = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
+    UAV_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, ids, ids2, n, 0, 63);
+    k_ploc_leaves<<<divup(n, 256), 256>>>(d_verts, d_faces, ids2, n, b->nodes, b->aabbs, b->tris, b->indices, cl_a);
+    UAV_CUDA(cudaGetLastError());
+    int count = n;
+    uint32_t next_id = (uint32_t)(n - 1);          // inner ids are handed out downwards; the root gets 0
+    while (count > 1) {
+        k_ploc_nearest<<<divup(count, 128), 128>>>(cl_a, count, b->aabbs, nn);
+        k_ploc_flags<<<divup(count, 256), 256>>>(nn, count, keep, made);
+        cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, keep, keep_pos, count);
+        cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, made, made_pos, count);
+        uint32_t last[2];
+        UAV_CUDA(cudaMemcpy(&last[0], made + (count - 1), 4, cudaMemcpyDeviceToHost));
+        UAV_CUDA(cudaMemcpy(&last[1], made_pos + (count - 1), 4, cudaMemcpyDeviceToHost));
+        uint32_t m = last[0] + last[1];
+        UAV_REQUIRE(m >= 1 && m <= next_id, "PLOC made no progress");   // the global nearest pair is always mutual
+        next_id -= m;
+        k_ploc_merge<<<divup(count, 256), 256>>>(cl_a, nn, count, keep, keep_pos, made, made_pos, next_id,
+            b->nodes, b->aabbs, cl_b);
+        UAV_CUDA(cudaGetLastError());
+        count -= (int)m;
+        uint32_t * t = cl_a; cl_a = cl_b; cl_b = t;
+    }
+    UAV_CUDA(cudaDeviceSynchronize());
+    UAV_REQUIRE(next_id == 0 || n == 1, "PLOC node count mismatch");
+    cudaFree(tmp); cudaFree(d_verts); cudaFree(d_faces); cudaFree(ids); cudaFree(ids2);
+    cudaFree(keys); cudaFree(keys2); cudaFree(bounds); cudaFree(cl_a); cudaFree(cl_b); cudaFree(nn);
+    cudaFree(keep); cudaFree(keep_pos); cudaFree(made); cudaFree(made_pos);
     if (finalize_layout(b)) return 1;
     *out = b;
     return 0;
