@@ -20,7 +20,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libuavmvs_b200.so")
+_SO = os.environ.get("UAVMVS_B200_LIB") or os.path.join(_HERE, "libuavmvs_b200.so")   # override: dev variants
 VIEW_FLOATS = 28
 NAI = 0xFFFFFFFF
 

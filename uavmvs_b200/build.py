@@ -36,9 +36,10 @@ def build(force=False, verbose=False):
         return SO
     nvcc = os.environ.get("NVCC", "nvcc")
     extra = os.environ.get("UAV_NVCC_EXTRA", "").split()
-    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
+    out = os.environ.get("UAV_SO", SO)
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", out] + sources()
     subprocess.check_call(cmd)
-    return SO
+    return out
 
 
 if __name__ == "__main__":

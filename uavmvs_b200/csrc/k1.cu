@@ -27,11 +27,23 @@ namespace uav {
 
 constexpr int K1_WARPS = 4;
 constexpr int K1_SB_PER_WARP = 8;
+#ifndef K1_REFILL_N
+#define K1_REFILL_N 20
+#endif
+#ifndef K1_TRI_N
+#define K1_TRI_N 12
+#endif
+#ifndef K1_STEPS_N
+#define K1_STEPS_N 6
+#endif
+#ifndef K1_PREFETCH
+#define K1_PREFETCH 0             // 0 none (measured best), 1 L1, 2 L2
+#endif
 constexpr int K1_PEND = 6;        // deferred leaves per lane
-constexpr int K1_REFILL = 8;      // refill when at least this many lanes are idle
-constexpr int K1_TRI = 8;         // run the triangle phase when this many lanes hold a leaf
+constexpr int K1_REFILL = K1_REFILL_N;   // refill when at least this many lanes are idle
+constexpr int K1_TRI = K1_TRI_N;  // run the triangle phase when this many lanes hold a leaf
 constexpr int K1_STACK = 160;     // <= 3 pushes per two binary levels; LBVH depth <= 96
-constexpr int K1_STEPS = 4;       // node steps between two rounds of warp-level bookkeeping
+constexpr int K1_STEPS = K1_STEPS_N;     // node steps between two rounds of warp-level bookkeeping
 
 // Conservative (group of points, view) test: false only if NO point inside the sphere
 // (centre c, radius r) can pass the exact cull of kernels.cu:164-167 (range, image bounds).
@@ -131,7 +143,7 @@ __global__ void k_add_u64(unsigned long long * dst, const unsigned long long * s
 
 struct RayList {
     float4 * dirl;        // unit point->camera direction, w = distance l
-    uint2 * ent;          // x = point id, y = view index
+    float4 * org;         // ray origin (the point), w = bits of the point's index within its block
     uint8_t * vis;        // 0 not traced yet, 1 occluded, 2 visible
     const uint32_t * off; // [num_blocks] first ray of each block's slice
     uint32_t * cnt;       // [num_blocks] rays in the slice
@@ -177,9 +189,8 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
             uint32_t m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
                 uint32_t idx = base + count + __popc(m & lt_mask);
-                rl.dirl[idx] = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
-                rl.ent[idx] = make_uint2(id, k);
-                rl.vis[idx] = 0;
+                __stcs(rl.dirl + idx, make_float4(v2cn.x, v2cn.y, v2cn.z, l));
+                __stcs(rl.org + idx, make_float4(v.x, v.y, v.z, __uint_as_float(lane)));
             }
             count += __popc(m);
         }
@@ -195,8 +206,17 @@ struct TraceArgs {
     uint32_t * work;              // next block slice to hand out
 };
 
+__device__ __forceinline__ void prefetch_l2(const void * p)
+{
+#if K1_PREFETCH == 2
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+#elif K1_PREFETCH == 1
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
+#endif
+}
+
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 6
+#define K1_MIN_BLOCKS 8
 #endif
 
 // Exact leaf box (the tight bound of the leaf's triangles, verified at upload to equal the
@@ -260,8 +280,8 @@ k_trace(TraceArgs a)
                 pos += take; given += take;
             }
             if (mine) {
-                const float4 d4 = a.rl.dirl[idx];
-                const V3 o = ld3(__ldg(a.verts + a.rl.ent[idx].x));
+                const float4 d4 = __ldcs(a.rl.dirl + idx);             // streamed once: keep L2 for the tree
+                const V3 o = ld3(__ldcs(a.rl.org + idx));
                 rd = ld3(d4);
                 rt.ox = o.x; rt.oy = o.y; rt.oz = o.z;
                 rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
@@ -302,17 +322,18 @@ k_trace(TraceArgs a)
                 const bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);
                 const bool f0 = h0 && cnt.x != 0u, f1 = h1 && cnt.y != 0u, f2 = h2 && cnt.z != 0u, f3 = h3 && cnt.w != 0u;
                 const bool i0 = h0 && cnt.x == 0u, i1 = h1 && cnt.y == 0u, i2 = h2 && cnt.z == 0u, i3 = h3 && cnt.w == 0u;
-                if (f0) { s_pend[npend][tid] = cnt.x | (g0 > m0 ? 0u : 32u); ++npend; }
-                if (f1) { s_pend[npend][tid] = cnt.y | (g1 > m1 ? 0u : 32u); ++npend; }
-                if (f2) { s_pend[npend][tid] = cnt.z | (g2 > m2 ? 0u : 32u); ++npend; }
-                if (f3) { s_pend[npend][tid] = cnt.w | (g3 > m3 ? 0u : 32u); ++npend; }
-                // inner children: one is visited next, the others go on the stack
+                if (f0) { s_pend[npend][tid] = cnt.x | (g0 > m0 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.x); }
+                if (f1) { s_pend[npend][tid] = cnt.y | (g1 > m1 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.y); }
+                if (f2) { s_pend[npend][tid] = cnt.z | (g2 > m2 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.z); }
+                if (f3) { s_pend[npend][tid] = cnt.w | (g3 > m3 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.w); }
+                // inner children: one is visited next, the others go on the stack (and are prefetched:
+                // on a visible ray every pushed node is popped later)
                 uint32_t nxt = i0 ? ref.x : UAV_NAI;
-                if (i1 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i1 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
                 if (i1) nxt = ref.y;
-                if (i2 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i2 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
                 if (i2) nxt = ref.z;
-                if (i3 && nxt != UAV_NAI) stack[sp++] = nxt;
+                if (i3 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
                 if (i3) nxt = ref.w;
                 if (nxt == UAV_NAI) {
                     if (sp > 0) nxt = stack[--sp]; else traversing = false;
@@ -345,7 +366,7 @@ k_trace(TraceArgs a)
         }
         // ---------------- finished lanes post their result ----------------
         if (has_ray && (hit || (!traversing && npend == 0))) {
-            a.rl.vis[idx] = hit ? 1 : 2;
+            __stcs(a.rl.vis + idx, (uint8_t)(hit ? 1 : 2));
             has_ray = false; traversing = false; npend = 0;
         }
     }
@@ -361,7 +382,7 @@ __global__ void k_trace_exact(TraceArgs a, uint32_t total)
     for (uint32_t i = threadIdx.x & 31; i < count; i += 32) {
         const uint32_t idx = base + i;
         const float4 d4 = a.rl.dirl[idx];
-        const V3 o = ld3(__ldg(a.verts + a.rl.ent[idx].x));
+        const V3 o = ld3(a.rl.org[idx]);
         bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, d4.x, d4.y, d4.z, d4.w * 0.001f, d4.w);
         a.rl.vis[idx] = h ? 1 : 2;
     }
@@ -408,14 +429,14 @@ k_retire(RetireArgs a)
     for (uint32_t c0 = 0; c0 < count; c0 += 32) {
         const uint32_t i = c0 + lane;
         const bool in = i < count;
-        const bool vis = in && a.rl.vis[base + i] == 2;
+        const bool vis = in && __ldcs(a.rl.vis + base + i) == 2;
         const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
         if (!vis_mask) continue;
         uint32_t pt = lane;
         V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
         if (vis) {
-            const float4 d4 = a.rl.dirl[base + i];
-            pt = a.rl.ent[base + i].x & 31u;
+            const float4 d4 = __ldcs(a.rl.dirl + base + i);
+            pt = __float_as_uint(__ldcs(a.rl.org + base + i).w) & 31u;
             const V3 v2cn = ld3(d4);
             rel = normalized(mk(dot(ld3(s_rx[w][pt]), v2cn), dot(ld3(s_ry[w][pt]), v2cn), dot(ld3(s_nrm[w][pt]), v2cn)));
             scale = 1.0f - (d4.w / a.max_distance);
@@ -465,7 +486,7 @@ struct K1Scratch {
     uint32_t * masks = nullptr; size_t masks_cap = 0;
     uint32_t * caps = nullptr, * off = nullptr, * cnt = nullptr; size_t blocks_cap = 0;
     void * cub_tmp = nullptr; size_t cub_cap = 0;
-    float4 * dirl = nullptr; uint2 * ent = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    float4 * dirl = nullptr, * org = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     int grid_trace = 0;
 };
@@ -554,11 +575,11 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         if (total > 0) {
             if (total > k.rays_cap) {
                 size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap;
-                if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.ent, &c1, (size_t)total, s) || grow(&k.vis, &c2, (size_t)total, s)) return 1;
+                if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.org, &c1, (size_t)total, s) || grow(&k.vis, &c2, (size_t)total, s)) return 1;
                 k.rays_cap = (size_t)total;
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
-            RayList rl; rl.dirl = k.dirl; rl.ent = k.ent; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt;
+            RayList rl; rl.dirl = k.dirl; rl.org = k.org; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt;
             k_cull_emit<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, max_distance, width, height, rl);
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
