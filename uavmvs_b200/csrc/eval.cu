@@ -83,13 +83,14 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
             const uint32_t rows = nv;
             const uint32_t npairs = rows * (rows - (rows ? 1u : 0u)) / 2u;
             float sum = 0.0f;
+            // pair q -> (i, j), i > j, enumerated row by row: q = i (i - 1) / 2 + j; advancing q by 32
+            // is j += 32 followed by carries into i
+            uint32_t i = 1, j = tx;
+            while (j >= i) { j -= i; ++i; }
             for (uint32_t q = tx; q < npairs; q += 32) {
-                // pair q -> (i, j), i > j:  i = floor((1 + sqrt(1 + 8 q)) / 2), fixed up exactly
-                uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
-                while (i * (i - 1) / 2 > q) --i;
-                while ((i + 1) * i / 2 <= q) ++i;
-                const uint32_t j = q - i * (i - 1) / 2;
-                sum += pair_term(s_col[w][j], s_col[w][i], m_k, m_x0, t_k, t_x0);
+                sum += pair_term_fast(s_col[w][j], s_col[w][i], m_k, m_x0, t_k, t_x0);
+                j += 32;
+                while (j >= i) { j -= i; ++i; }
             }
             for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
             if (tx == 0) {

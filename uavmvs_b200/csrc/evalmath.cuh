@@ -57,4 +57,20 @@ __device__ __forceinline__ float pair_term(float4 a, float4 b, float mk_, float 
     return matchability * triangulation;
 }
 
+// Same expression with the device intrinsics the reference's own logistic() uses (__expf,
+// libs/eval/kernels.cu:80-84) and an approximate reciprocal; relative error ~1e-6 per term, inside
+// the 1e-5 gate on scores.  acosf stays the full-precision one (the logistics amplify angle errors).
+__device__ __forceinline__ float logistic_fast(float x, float k, float x0) {
+    return __fdividef(1.0f, 1.0f + __expf(-k * (x - x0)));
+}
+__device__ __forceinline__ float pair_term_fast(float4 a, float4 b, float mk_, float mx0, float tk, float tx0) {
+    float calpha = b.x * a.x + b.y * a.y + b.z * a.z;
+    float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+    float scale = fminf(a.w, b.w);
+    float ctheta = fminf(a.z, b.z);
+    float matchability = (1.0f - logistic_fast(alpha, mk_, mx0)) * ctheta;
+    float triangulation = logistic_fast(alpha, tk, tx0) * scale;
+    return matchability * triangulation;
+}
+
 }  // namespace uav

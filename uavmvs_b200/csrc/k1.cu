@@ -144,7 +144,7 @@ __global__ void k_add_u64(unsigned long long * dst, const unsigned long long * s
 struct RayList {
     float4 * dirl;        // unit point->camera direction, w = distance l
     float4 * org;         // ray origin (the point), w = bits of the point's index within its block
-    uint8_t * vis;        // 0 not traced yet, 1 occluded, 2 visible
+    uint8_t * vis;        // (point's index within its block) << 2 | status: 1 occluded, 2 visible
     const uint32_t * off; // [num_blocks] first ray of each block's slice
     uint32_t * cnt;       // [num_blocks] rays in the slice
 };
@@ -255,7 +255,7 @@ k_trace(TraceArgs a)
 
     uint32_t pos = 0, end = 0; bool drained = false;         // warp-uniform: current slice of the ray list
     bool has_ray = false, traversing = false, hit = false;
-    uint32_t idx = 0, cur = 0, npend = 0; int sp = 0;
+    uint32_t idx = 0, cur = 0, npend = 0, ptl = 0; int sp = 0;
     RayT rt; rt.ox = rt.oy = rt.oz = rt.rdx = rt.rdy = rt.rdz = rt.tmin = rt.tmax = 0.0f;
     V3 rd = mk(0.f, 0.f, 0.f);
     uint32_t serviced_idle = 0;
@@ -281,7 +281,9 @@ k_trace(TraceArgs a)
             }
             if (mine) {
                 const float4 d4 = __ldcs(a.rl.dirl + idx);             // streamed once: keep L2 for the tree
-                const V3 o = ld3(__ldcs(a.rl.org + idx));
+                const float4 o4 = __ldcs(a.rl.org + idx);
+                const V3 o = ld3(o4);
+                ptl = __float_as_uint(o4.w) << 2;
                 rd = ld3(d4);
                 rt.ox = o.x; rt.oy = o.y; rt.oz = o.z;
                 rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
@@ -293,7 +295,7 @@ k_trace(TraceArgs a)
                 } else {
                     // axis-parallel (or degenerate) ray, single-leaf tree: the reference walk, right away
                     bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
-                    a.rl.vis[idx] = h ? 1 : 2;
+                    a.rl.vis[idx] = (uint8_t)(ptl | (h ? 1u : 2u));
                 }
             }
             serviced_idle = __ballot_sync(0xffffffffu, !has_ray);
@@ -366,7 +368,7 @@ k_trace(TraceArgs a)
         }
         // ---------------- finished lanes post their result ----------------
         if (has_ray && (hit || (!traversing && npend == 0))) {
-            __stcs(a.rl.vis + idx, (uint8_t)(hit ? 1 : 2));
+            __stcs(a.rl.vis + idx, (uint8_t)(ptl | (hit ? 1u : 2u)));
             has_ray = false; traversing = false; npend = 0;
         }
     }
@@ -382,9 +384,10 @@ __global__ void k_trace_exact(TraceArgs a, uint32_t total)
     for (uint32_t i = threadIdx.x & 31; i < count; i += 32) {
         const uint32_t idx = base + i;
         const float4 d4 = a.rl.dirl[idx];
-        const V3 o = ld3(a.rl.org[idx]);
+        const float4 o4 = a.rl.org[idx];
+        const V3 o = ld3(o4);
         bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, d4.x, d4.y, d4.z, d4.w * 0.001f, d4.w);
-        a.rl.vis[idx] = h ? 1 : 2;
+        a.rl.vis[idx] = (uint8_t)((__float_as_uint(o4.w) << 2) | (h ? 1u : 2u));
     }
 }
 
@@ -429,14 +432,15 @@ k_retire(RetireArgs a)
     for (uint32_t c0 = 0; c0 < count; c0 += 32) {
         const uint32_t i = c0 + lane;
         const bool in = i < count;
-        const bool vis = in && __ldcs(a.rl.vis + base + i) == 2;
+        const uint32_t vb = in ? (uint32_t)__ldcs(a.rl.vis + base + i) : 0u;
+        const bool vis = (vb & 3u) == 2u;
         const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
         if (!vis_mask) continue;
         uint32_t pt = lane;
         V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
         if (vis) {
             const float4 d4 = __ldcs(a.rl.dirl + base + i);
-            pt = __float_as_uint(__ldcs(a.rl.org + base + i).w) & 31u;
+            pt = vb >> 2;
             const V3 v2cn = ld3(d4);
             rel = normalized(mk(dot(ld3(s_rx[w][pt]), v2cn), dot(ld3(s_ry[w][pt]), v2cn), dot(ld3(s_nrm[w][pt]), v2cn)));
             scale = 1.0f - (d4.w / a.max_distance);
