@@ -85,6 +85,10 @@ struct uavmvs_cloud {
     float * values, * qualities;
     // per 32-point block: bounding sphere (xyz, r) for the conservative view cull
     float4 * block_sphere;
+    // per block: cone of its normals (unit axis xyz, half-angle w in radians; w >= pi: unusable)
+    // and the largest normal length, for the conservative back-face cull
+    float4 * block_cone;
+    float * block_nmax;
     uint32_t num_blocks;
     // per super-block (32 blocks = 1024 points): sphere enclosing its block spheres
     float4 * super_sphere;

@@ -28,6 +28,34 @@ __global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, f
     if (lane == 0) out[blk] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
 }
 
+// Cone of the block's normals: axis = normalised sum, half-angle = largest angle to the axis
+// (padded); blocks with a degenerate axis get half-angle 4 (> pi: the cull never uses them).
+__global__ void k_block_cones(const float4 * __restrict__ normals, uint32_t n, float4 * __restrict__ cone,
+    float * __restrict__ nmax)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t id = blk * 32 + lane;
+    if (blk * 32 >= n) return;
+    float4 v = normals[id < n ? id : n - 1];
+    float len = sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+    float ux = v.x / len, uy = v.y / len, uz = v.z / len;
+    bool bad = !(len > 1e-20f) || !(len < 1e20f);
+    float sx = bad ? 0.0f : ux, sy = bad ? 0.0f : uy, sz = bad ? 0.0f : uz, mx = len;
+    for (int o = 16; o > 0; o >>= 1) {
+        sx += __shfl_xor_sync(0xffffffffu, sx, o); sy += __shfl_xor_sync(0xffffffffu, sy, o);
+        sz += __shfl_xor_sync(0xffffffffu, sz, o); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    float sl = sqrtf(sx * sx + sy * sy + sz * sz);
+    float ax = sx / sl, ay = sy / sl, az = sz / sl;
+    float c = ax * ux + ay * uy + az * uz;
+    float ang = bad ? 4.0f : acosf(fminf(fmaxf(c, -1.0f), 1.0f));
+    for (int o = 16; o > 0; o >>= 1) ang = fmaxf(ang, __shfl_xor_sync(0xffffffffu, ang, o));
+    uint32_t anybad = __ballot_sync(0xffffffffu, bad);
+    if (!(sl > 1e-3f) || anybad) ang = 4.0f;
+    if (lane == 0) { cone[blk] = make_float4(ax, ay, az, ang * 1.0001f + 1e-4f); nmax[blk] = mx * 1.0001f; }
+}
+
 // Sphere around the 32 block spheres of a super-block (centre = centre of the box of the block
 // centres; radius = max over blocks of |c - c_b| + r_b, padded against rounding).
 __global__ void k_super_spheres(const float4 * __restrict__ blocks, uint32_t num_blocks, float4 * __restrict__ out)
@@ -114,6 +142,8 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     UAV_CUDA(cudaMalloc(&c->values, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->qualities, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->block_sphere, sizeof(float4) * (size_t)c->num_blocks));
+    UAV_CUDA(cudaMalloc(&c->block_cone, sizeof(float4) * (size_t)c->num_blocks));
+    UAV_CUDA(cudaMalloc(&c->block_nmax, sizeof(float) * (size_t)c->num_blocks));
     c->num_super = divup(c->num_blocks, 32);
     UAV_CUDA(cudaMalloc(&c->super_sphere, sizeof(float4) * (size_t)c->num_super));
     if (upload3(vertices, n, c->vertices)) return 1;
@@ -123,6 +153,7 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)n, cudaMemcpyHostToDevice));
     else k_fill<<<divup(n, 256), 256>>>(c->qualities, n, 1.0f);     /* libs/util/cio.h:46 */
     k_block_spheres<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere);
+    k_block_cones<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->normals, n, c->block_cone, c->block_nmax);
     k_super_spheres<<<divup((uint64_t)c->num_super * 32, 128), 128>>>(c->block_sphere, c->num_blocks, c->super_sphere);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaDeviceSynchronize());
@@ -152,7 +183,7 @@ int uavmvs_cloud_destroy(uavmvs_cloud * c)
 {
     if (!c) return 0;
     cudaFree(c->vertices); cudaFree(c->normals); cudaFree(c->values); cudaFree(c->qualities);
-    cudaFree(c->block_sphere); cudaFree(c->super_sphere);
+    cudaFree(c->block_sphere); cudaFree(c->super_sphere); cudaFree(c->block_cone); cudaFree(c->block_nmax);
     delete c;
     return 0;
 }

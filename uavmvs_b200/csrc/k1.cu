@@ -83,11 +83,30 @@ __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view
     return true;
 }
 
+// Conservative back-face test for a block: true only if EVERY point p in the sphere and every
+// normal n in the cone (|n| <= nmax) gives dot((c - p) / |c - p|, n) < 0.087 (kernels.cu:160-162).
+// The direction to the camera deviates from the centre's by at most asin(r / D); angles add up.
+__device__ __forceinline__ bool block_backfacing(const float * __restrict__ view, float4 sph, float4 cone, float nmax)
+{
+    if (!(cone.w < 3.2f)) return false;
+    float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
+    float D = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (!(D > sph.w * 1.001f + 1e-6f)) return false;
+    float c = (dx * cone.x + dy * cone.y + dz * cone.z) / D;
+    float theta = acosf(fminf(fmaxf(c, -1.0f), 1.0f));
+    float delta = asinf(fminf(sph.w * 1.001f / D, 1.0f));
+    float amin = theta - cone.w - delta - 0.002f;        // smallest possible angle between direction and normal
+    if (amin >= 1.5708f + 0.001f) return true;           // cos <= 0 for every pair
+    if (amin <= 0.0f) return false;
+    return nmax * cosf(amin) < 0.0865f;
+}
+
 // One warp = one chunk of 32 views (a view per lane, kept in registers) x K1_SB_PER_WARP
 // super-blocks.  Surviving views are re-tested against the 32 blocks (a block per lane).
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 * __restrict__ super_spheres,
-    uint32_t num_super, const float4 * __restrict__ block_spheres, uint32_t num_blocks,
+    uint32_t num_super, const float4 * __restrict__ block_spheres, const float4 * __restrict__ block_cones,
+    const float * __restrict__ block_nmax, uint32_t num_blocks,
     float max_distance, int width, int height, uint32_t * __restrict__ masks)
 {
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -107,10 +126,13 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
         uint32_t mine = 0;
         const uint32_t b = sb * 32 + lane;
         const float4 bs = __ldg(block_spheres + (b < num_blocks ? b : num_blocks - 1));
+        const float4 bc = __ldg(block_cones + (b < num_blocks ? b : num_blocks - 1));
+        const float bn = __ldg(block_nmax + (b < num_blocks ? b : num_blocks - 1));
         while (m) {
             const int j = __ffs(m) - 1; m &= m - 1;
             const float * vj = views + (size_t)(blockIdx.x * 32 + j) * UAVMVS_VIEW_FLOATS;   // uniform address
-            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height);
+            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height)
+                && !block_backfacing(vj, bs, bc, bn);
             uint32_t word = __ballot_sync(0xffffffffu, c);
             if ((int)lane == j) mine = word;
         }
@@ -557,7 +579,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 
     dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
     k_view_masks<<<mgrid, K1_WARPS * 32, 0, s>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
-        cloud->block_sphere, nb, max_distance, width, height, k.masks);
+        cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, max_distance, width, height, k.masks);
     UAV_CUDA(cudaGetLastError());
 
     // view batches: [v0, v1) such that the upper bound of ray records fits the budget
