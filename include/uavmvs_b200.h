@@ -149,6 +149,11 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
  * reference only wall-clocks the K1 loop (apps/evaluate_trajectory/evaluate_trajectory.cu:144-171). */
 int uavmvs_profile_last(float ms[4]);
 
+/* Diagnostics of the calling thread's K1 launches since the last reset (no reference counterpart):
+ * out[0] = (block, view) packets tested by the visibility-shaft pass, [1] = packets certified
+ * visible as a whole, [2] = occlusion rays answered by a certificate, [3] = occlusion rays traced. */
+int uavmvs_k1_counters(uint64_t out[4], int reset);
+
 /* ---- K4 populate_spherical_histogram (6-arg), kernels.h:46-50, kernels.cu:293-336 */
 int uavmvs_populate_spherical_histogram(void * stream, const float view_pos[3], float max_distance,
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd,

@@ -329,3 +329,36 @@ def test_axis_parallel_rays_and_flat_boxes(api, oracle):
     arrays = oracle.TreeArrays(nodes, aabbs, tris, indices)
     obs_o, data, rows, state = _populate_both(api, oracle, sc, arrays)
     assert np.array_equal(rows, obs_o.num_rows)
+
+
+@pytest.mark.parametrize("scene_name", ["tiny", "dense"])
+def test_visibility_shafts_opt_in_is_bit_exact(api, oracle, scene_name, monkeypatch):
+    """UAVMVS_SHAFTS=1: (block, view) packets certified visible by the shaft pass skip the per-ray
+    trace; counts and stored rows must stay bit-identical, and some packets must be certified."""
+    from uavmvs_b200 import scenes
+    sc = getattr(scenes, scene_name)()
+    monkeypatch.setenv("UAVMVS_SHAFTS", "1")
+    gbvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+    nodes, aabbs, tris, indices = gbvh.export()
+    obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    obs_o, state, _ = _run_oracle_eval(oracle, obvh, sc)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.k1_counters(reset=True)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    packets, certified, rays_cert, rays_traced = api.k1_counters()
+    assert packets > 0 and rays_cert + rays_traced == int((state != 0).sum()), (packets, certified, rays_cert, rays_traced)
+    if scene_name == "dense":
+        assert certified > 0 and rays_cert > 0, (packets, certified, rays_cert, rays_traced)
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+    # and the removal pass (populate = false) through the same packets
+    api.update_observation_rays_batch(False, sc.views28()[::3], sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    oracle.update_observation_rays(obvh, False, sc.views28()[::3], sc.max_distance, sc.width, sc.height,
+                                   sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    api.process_observation_rays(obs)
+    data2, rows2 = obs.download()
+    assert np.array_equal(rows2, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data2, rows2, 32)

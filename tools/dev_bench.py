@@ -48,7 +48,7 @@ for it in range(args.iters):
     e1.record(stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    print("stages", ["%.3f" % x for x in api.profile_last()])
+    print("stages", ["%.3f" % x for x in api.profile_last()], "k1 counters [packets, certified, rays certified, rays traced]", api.k1_counters())
     print("iter %d: %.2f ms  rays %d vis %d pairs %d after_block_cull %d  -> %.3f Grays/s %.2f Gpairs/s score %.5f" % (
         it, ms, st[0], st[1], st[2], st[3], st[0] / ms / 1e6, st[2] / ms / 1e6, s / sc.num_points), flush=True)
 rows = obs.download(data=False)[1]

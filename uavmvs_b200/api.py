@@ -359,6 +359,13 @@ def profile_last():
     return [float(x) for x in ms]
 
 
+def k1_counters(reset=True):
+    """[shaft packets tested, packets certified, rays certified, rays traced] since the last reset."""
+    out = (C.c_uint64 * 4)()
+    _check(_lib.uavmvs_k1_counters(out, _i32(1 if reset else 0)))
+    return [int(x) for x in out]
+
+
 def populate_spherical_histogram(view_pos, max_distance, bvh_tree, cloud, kd_tree, sphere_hist, stream=None,
                                  target_recon=None, obs_rays=None, recons=None):
     """Both overloads of libs/eval/kernels.h:46-67: the 9-argument form is selected by passing

@@ -85,6 +85,14 @@ struct uavmvs_cloud {
     float * values, * qualities;
     // per 32-point block: bounding sphere (xyz, r) for the conservative view cull
     float4 * block_sphere;
+    // per block: axis-aligned bounds of its points (exact min / max of the coordinates), the base
+    // of the visibility shaft towards a camera (k1.cu:k_shaft)
+    float4 * block_lo, * block_hi;
+    // per block: oriented bounds of its points, 5 float4: rows 0..2 = orthonormal frame vector f_i (xyz)
+    // and reference point c (w of rows 0..2 = c.x, c.y, c.z); row 3 = {lo0, hi0, lo1, hi1}, row 4 =
+    // {lo2, hi2, 0, 0}: f_i . (p - c) in [lo_i, hi_i] for every point p of the block (padded).  f_0 is the
+    // axis of the block's normal cone, so points sampled on one plane get a (near) zero-thickness slab.
+    float4 * block_obb;
     // per block: cone of its normals (unit axis xyz, half-angle w in radians; w >= pi: unusable)
     // and the largest normal length, for the conservative back-face cull
     float4 * block_cone;
@@ -148,5 +156,6 @@ Heur current_heur();
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
     uavmvs_obs * obs, unsigned long long * d_stats);
+int k1_counters(unsigned long long out[4], int reset);
 
 }  // namespace uav

@@ -7,7 +7,8 @@ namespace uav {
 
 // Bounding sphere of every 32-point block (centre = box centre, radius padded so that the
 // block-level range cull in eval.cu is conservative w.r.t. fp32 rounding).
-__global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, float4 * __restrict__ out)
+__global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, float4 * __restrict__ out,
+    float4 * __restrict__ lo, float4 * __restrict__ hi)
 {
     uint32_t lane = threadIdx.x & 31;
     uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -25,7 +26,11 @@ __global__ void k_block_spheres(const float4 * __restrict__ verts, uint32_t n, f
     float dx = v.x - cx, dy = v.y - cy, dz = v.z - cz;
     float r = sqrtf(dx * dx + dy * dy + dz * dz);
     for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
-    if (lane == 0) out[blk] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
+    if (lane == 0) {
+        out[blk] = make_float4(cx, cy, cz, r * 1.0001f + 1e-6f);
+        lo[blk] = make_float4(mn[0], mn[1], mn[2], 0.0f);
+        hi[blk] = make_float4(mx[0], mx[1], mx[2], 0.0f);
+    }
 }
 
 // Cone of the block's normals: axis = normalised sum, half-angle = largest angle to the axis
@@ -54,6 +59,48 @@ __global__ void k_block_cones(const float4 * __restrict__ normals, uint32_t n, f
     uint32_t anybad = __ballot_sync(0xffffffffu, bad);
     if (!(sl > 1e-3f) || anybad) ang = 4.0f;
     if (lane == 0) { cone[blk] = make_float4(ax, ay, az, ang * 1.0001f + 1e-4f); nmax[blk] = mx * 1.0001f; }
+}
+
+// Oriented bounds of every block in the frame of its normal cone (see common.cuh:block_obb).
+__global__ void k_block_obb(const float4 * __restrict__ verts, uint32_t n, const float4 * __restrict__ sphere,
+    const float4 * __restrict__ cone, float4 * __restrict__ obb)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t id = blk * 32 + lane;
+    if (blk * 32 >= n) return;
+    float4 v = verts[id < n ? id : n - 1];
+    float4 sp = sphere[blk], cn = cone[blk];
+    float ax = cn.x, ay = cn.y, az = cn.z;
+    float al = sqrtf(ax * ax + ay * ay + az * az);
+    if (!(fabsf(al - 1.0f) < 1e-3f)) { ax = 0.0f; ay = 0.0f; az = 1.0f; }     // degenerate cone: world frame
+    // f1 = unit vector orthogonal to the axis (cross with the world axis of the smallest component)
+    float bx, by, bz;
+    if (fabsf(ax) <= fabsf(ay) && fabsf(ax) <= fabsf(az)) { bx = 0.0f; by = -az; bz = ay; }
+    else if (fabsf(ay) <= fabsf(az)) { bx = az; by = 0.0f; bz = -ax; }
+    else { bx = -ay; by = ax; bz = 0.0f; }
+    float bl = sqrtf(bx * bx + by * by + bz * bz);
+    bx /= bl; by /= bl; bz /= bl;
+    float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+    float dx = v.x - sp.x, dy = v.y - sp.y, dz = v.z - sp.z;
+    float d[3] = {ax * dx + ay * dy + az * dz, bx * dx + by * dy + bz * dz, cx * dx + cy * dy + cz * dz};
+    float mn[3], mx[3];
+    for (int k = 0; k < 3; ++k) {
+        mn[k] = d[k]; mx[k] = d[k];
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    }
+    if (lane == 0) {
+        const float pad = 2e-6f * (1.0f + sp.w);      // rounding of p - c and of the dot products (|p - c| <= r)
+        float4 * o = obb + 5 * (size_t)blk;
+        o[0] = make_float4(ax, ay, az, sp.x);
+        o[1] = make_float4(bx, by, bz, sp.y);
+        o[2] = make_float4(cx, cy, cz, sp.z);
+        o[3] = make_float4(mn[0] - pad, mx[0] + pad, mn[1] - pad, mx[1] + pad);
+        o[4] = make_float4(mn[2] - pad, mx[2] + pad, 0.0f, 0.0f);
+    }
 }
 
 // Sphere around the 32 block spheres of a super-block (centre = centre of the box of the block
@@ -142,7 +189,10 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     UAV_CUDA(cudaMalloc(&c->values, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->qualities, sizeof(float) * (size_t)n));
     UAV_CUDA(cudaMalloc(&c->block_sphere, sizeof(float4) * (size_t)c->num_blocks));
+    UAV_CUDA(cudaMalloc(&c->block_lo, sizeof(float4) * (size_t)c->num_blocks));
+    UAV_CUDA(cudaMalloc(&c->block_hi, sizeof(float4) * (size_t)c->num_blocks));
     UAV_CUDA(cudaMalloc(&c->block_cone, sizeof(float4) * (size_t)c->num_blocks));
+    UAV_CUDA(cudaMalloc(&c->block_obb, sizeof(float4) * 5 * (size_t)c->num_blocks));
     UAV_CUDA(cudaMalloc(&c->block_nmax, sizeof(float) * (size_t)c->num_blocks));
     c->num_super = divup(c->num_blocks, 32);
     UAV_CUDA(cudaMalloc(&c->super_sphere, sizeof(float4) * (size_t)c->num_super));
@@ -152,8 +202,10 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     else k_fill<<<divup(n, 256), 256>>>(c->values, n, 0.0f);        /* libs/util/cio.h:45 */
     if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)n, cudaMemcpyHostToDevice));
     else k_fill<<<divup(n, 256), 256>>>(c->qualities, n, 1.0f);     /* libs/util/cio.h:46 */
-    k_block_spheres<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere);
+    k_block_spheres<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere,
+        c->block_lo, c->block_hi);
     k_block_cones<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->normals, n, c->block_cone, c->block_nmax);
+    k_block_obb<<<divup((uint64_t)c->num_blocks * 32, 128), 128>>>(c->vertices, n, c->block_sphere, c->block_cone, c->block_obb);
     k_super_spheres<<<divup((uint64_t)c->num_super * 32, 128), 128>>>(c->block_sphere, c->num_blocks, c->super_sphere);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaDeviceSynchronize());
@@ -183,7 +235,7 @@ int uavmvs_cloud_destroy(uavmvs_cloud * c)
 {
     if (!c) return 0;
     cudaFree(c->vertices); cudaFree(c->normals); cudaFree(c->values); cudaFree(c->qualities);
-    cudaFree(c->block_sphere); cudaFree(c->super_sphere); cudaFree(c->block_cone); cudaFree(c->block_nmax);
+    cudaFree(c->block_sphere); cudaFree(c->block_lo); cudaFree(c->block_hi); cudaFree(c->block_obb); cudaFree(c->super_sphere); cudaFree(c->block_cone); cudaFree(c->block_nmax);
     delete c;
     return 0;
 }

@@ -336,6 +336,15 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
     return 0;
 }
 
+int uavmvs_k1_counters(uint64_t out[4], int reset)
+{
+    UAV_REQUIRE(out, "null argument");
+    unsigned long long tmp[4];
+    if (uav::k1_counters(tmp, reset)) return 1;
+    for (int i = 0; i < 4; ++i) out[i] = tmp[i];
+    return 0;
+}
+
 int uavmvs_profile_last(float ms[4])
 {
     UAV_REQUIRE(ms, "null argument");

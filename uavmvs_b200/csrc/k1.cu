@@ -163,12 +163,211 @@ __global__ void k_sum_caps(const uint32_t * __restrict__ caps, uint32_t n, unsig
 
 __global__ void k_add_u64(unsigned long long * dst, const unsigned long long * src) { *dst += *src; }
 
+// ---- visibility shafts ----------------------------------------------------------------------
+// A (block, view) packet is CERTIFIED when no ray from any point of the block to the camera can be
+// occluded, proven without tracing the rays one by one:
+//   every ray of the packet lies in the shaft  S = { (1 - s) p + s a : p in [lo, hi], s in [s0, 1] }
+//   (a = camera position, [lo, hi] = bounds of the block's points, s = t / l, and the reference
+//   only accepts t in [0.001 l, l], kernels.cu:54-58).  At parameter s the cross-section of S is
+//   the box [lo + s (a - lo), hi + s (a - hi)], so S meets a box B iff six inequalities LINEAR in s
+//   share a solution in [s0, 1].  On a nested tree the reference reports "occluded" iff some leaf's
+//   own box passes its slab test and holds an accepted triangle (see k_trace); if S misses the
+//   eps-grown box of a node it misses every leaf box below it, and the exact fp32 slab test of any
+//   ray inside S rejects those leaves (eps = 2e-6 max|coordinate| + 1.4e-5 is > 10x the rounding of
+//   fl(fl(b - o) / d) and of the shaft arithmetic itself).  Hence: a traversal of the 4-wide tree
+//   with the shaft that never touches a leaf box proves all rays of the packet visible.
+// Packets that touch a leaf are left to k_trace (no claim is made about them).
+struct Shaft {
+    float lx, ly, lz, hx, hy, hz;         // lo - eps, hi + eps
+    float rux, ruy, ruz, rwx, rwy, rwz;   // 1 / (a - lo), 1 / (a - hi)   (|.| clamped to >= 1e-6)
+    bool upx, upy, upz, wpx, wpy, wpz;    // a - lo > 0, a - hi > 0
+};
+
+__device__ __forceinline__ float clamp_away(float u) { return fabsf(u) < 1e-6f ? 1e-6f : u; }
+
+__device__ __forceinline__ bool shaft_hits(const Shaft & f, float mnx, float mny, float mnz, float mxx, float mxy, float mxz)
+{
+    // lo + s u <= bmax + eps   and   hi + s w >= bmin - eps, per axis
+    const float ax = (mxx - f.lx) * f.rux, bx = (mnx - f.hx) * f.rwx;
+    const float ay = (mxy - f.ly) * f.ruy, by = (mny - f.hy) * f.rwy;
+    const float az = (mxz - f.lz) * f.ruz, bz = (mnz - f.hz) * f.rwz;
+    float s_lo = 0.0009f, s_hi = 1.0001f;
+    s_hi = fminf(s_hi, f.upx ? ax : UAV_INF); s_lo = fmaxf(s_lo, f.upx ? -UAV_INF : ax);
+    s_lo = fmaxf(s_lo, f.wpx ? bx : -UAV_INF); s_hi = fminf(s_hi, f.wpx ? UAV_INF : bx);
+    s_hi = fminf(s_hi, f.upy ? ay : UAV_INF); s_lo = fmaxf(s_lo, f.upy ? -UAV_INF : ay);
+    s_lo = fmaxf(s_lo, f.wpy ? by : -UAV_INF); s_hi = fminf(s_hi, f.wpy ? UAV_INF : by);
+    s_hi = fminf(s_hi, f.upz ? az : UAV_INF); s_lo = fmaxf(s_lo, f.upz ? -UAV_INF : az);
+    s_lo = fmaxf(s_lo, f.wpz ? bz : -UAV_INF); s_hi = fminf(s_hi, f.wpz ? UAV_INF : bz);
+    return !(s_lo > s_hi + 2e-6f);        // NaN (never produced: all operands finite) would count as a hit
+}
+
+// A triangle inside the shaft does no harm if its PLANE is not crossed by any ray of the packet
+// within the accepted parameter range: with h(p) = n . (p - a_tri) the signed height of an origin
+// and H that of the camera, the height along a ray is (1 - s) h + s H, and the reference rejects
+// the triangle when the crossing has t < 0.001 l or t > l (libs/acc/primitives.h:228-231).  The
+// block's oriented bounds give [h_lo, h_hi] over all its points; the triangle is cleared iff the
+// height keeps the sign of H, by more than mu, at s = 0.00099 and s = 1.0001 for both ends of the
+// interval (mu > 10x the rounding of the reference's own fl-dot(n, o - a) and t = -h / cos).
+// This is what lets packets leave the surface they were sampled on: coplanar and concave
+// neighbours have h >= 0 = sign of H.
+__device__ __forceinline__ bool tri_cleared(const Tri64 * __restrict__ tp, const float4 * ob, float px, float py, float pz, float eps)
+{
+    const float4 q0 = __ldg(&tp->q0), q2 = __ldg(&tp->q2);
+    const float ax = q0.x, ay = q0.y, az = q0.z, nx = q2.y, ny = q2.z, nz = q2.w;
+    const float4 o0 = ob[0], o1 = ob[1], o2 = ob[2], o3 = ob[3], o4 = ob[4];
+    const float g0 = nx * o0.x + ny * o0.y + nz * o0.z;
+    const float g1 = nx * o1.x + ny * o1.y + nz * o1.z;
+    const float g2 = nx * o2.x + ny * o2.y + nz * o2.z;
+    const float rx = o0.w - ax, ry = o1.w - ay, rz = o2.w - az;          // c - a_tri
+    const float base = nx * rx + ny * ry + nz * rz;
+    const float a0 = g0 * o3.x, b0 = g0 * o3.y, a1 = g1 * o3.z, b1 = g1 * o3.w, a2 = g2 * o4.x, b2 = g2 * o4.y;
+    const float h_lo = base + (fminf(a0, b0) + fminf(a1, b1) + fminf(a2, b2));
+    const float h_hi = base + (fmaxf(a0, b0) + fmaxf(a1, b1) + fmaxf(a2, b2));
+    const float ex = px - ax, ey = py - ay, ez = pz - az;
+    const float H = nx * ex + ny * ey + nz * ez;
+    const float d1 = (fabsf(rx) + fabsf(ry) + fabsf(rz)) + (fabsf(ex) + fabsf(ey) + fabsf(ez))
+        + ((o3.y - o3.x) + (o3.w - o3.z) + (o4.y - o4.x));
+    const float mu = eps + 1e-6f * d1;
+    const float n0 = 0.99901f, n1 = 0.00099f, f0 = 1.0001f, f1 = 0.0001f;
+    const bool pos = H > 0.0f && (n0 * h_lo + n1 * H > mu) && (f0 * H - f1 * h_hi > mu);
+    const bool neg = H < 0.0f && (n0 * h_hi + n1 * H < -mu) && (f0 * H - f1 * h_lo < -mu);
+    return pos || neg;                                                    // NaN anywhere: not cleared
+}
+
+constexpr int SH_STACK = 160;
+
+struct ShaftArgs {
+    const Node128 * __restrict__ wide; const Tri64 * __restrict__ tris;
+    const float4 * __restrict__ lo; const float4 * __restrict__ hi; const float4 * __restrict__ obb;
+    uint32_t num_blocks;
+    const float * __restrict__ views; uint32_t num_views, v0, v1;
+    const uint32_t * __restrict__ masks;
+    uint32_t * cert; uint32_t nchunks;       // cert[blk * nchunks + (v - v0) / 32], bit (v - v0) % 32
+    unsigned long long * counters;           // [0] packets tested, [1] packets certified
+    uint32_t max_steps;
+};
+
+// One warp per block; candidate views (bits of k_view_masks) are gathered 32 at a time and each
+// lane walks the tree with the shaft of its own view.
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_shaft(ShaftArgs a)
+{
+    __shared__ uint32_t s_q[K1_WARPS][64];
+    __shared__ float4 s_obb[K1_WARPS][5];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk >= a.num_blocks) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const float4 lo = __ldg(a.lo + blk), hi = __ldg(a.hi + blk);
+    if (lane < 5) s_obb[w][lane] = __ldg(a.obb + 5 * (size_t)blk + lane);
+    __syncwarp();
+    const uint32_t * mrow = a.masks + (size_t)(blk >> 5) * a.num_views;
+    const uint32_t mbit = blk & 31;
+    uint32_t stack[SH_STACK];
+    uint32_t qn = 0, tested = 0, certified = 0;
+    unsigned long long dbg_sc = 0, dbg_sf = 0, dbg_tt = 0;
+    for (uint32_t c0 = a.v0; c0 < a.v1 || qn > 0; c0 += 32) {
+        if (c0 < a.v1) {
+            const uint32_t vi = c0 + lane;
+            const bool cand = vi < a.v1 && ((__ldg(mrow + vi) >> mbit) & 1u);
+            const uint32_t m = __ballot_sync(0xffffffffu, cand);
+            if (cand) s_q[w][qn + __popc(m & lt_mask)] = vi;
+            qn += __popc(m);
+            __syncwarp();
+            if (qn < 32 && c0 + 32 < a.v1) continue;
+        }
+        // ---- up to 32 queued views: one shaft per lane ----
+        const uint32_t take = min(qn, 32u);
+        if (take == 0) continue;
+        const bool active = lane < take;
+        const uint32_t v = s_q[w][active ? lane : 0];
+        const float * vp = a.views + (size_t)v * UAVMVS_VIEW_FLOATS;
+        const float px = __ldg(vp), py = __ldg(vp + 1), pz = __ldg(vp + 2);
+        Shaft f; float eps;
+        {
+            float M = fmaxf(fmaxf(fabsf(px), fabsf(py)), fabsf(pz));
+            M = fmaxf(M, fmaxf(fmaxf(fabsf(lo.x), fabsf(lo.y)), fabsf(lo.z)));
+            M = fmaxf(M, fmaxf(fmaxf(fabsf(hi.x), fabsf(hi.y)), fabsf(hi.z)));
+            eps = 2e-6f * M + 1.4e-5f;
+            f.lx = lo.x - eps; f.ly = lo.y - eps; f.lz = lo.z - eps;
+            f.hx = hi.x + eps; f.hy = hi.y + eps; f.hz = hi.z + eps;
+            const float ux = clamp_away(px - lo.x), uy = clamp_away(py - lo.y), uz = clamp_away(pz - lo.z);
+            const float wx = clamp_away(px - hi.x), wy = clamp_away(py - hi.y), wz = clamp_away(pz - hi.z);
+            f.rux = 1.0f / ux; f.ruy = 1.0f / uy; f.ruz = 1.0f / uz;
+            f.rwx = 1.0f / wx; f.rwy = 1.0f / wy; f.rwz = 1.0f / wz;
+            f.upx = ux > 0.0f; f.upy = uy > 0.0f; f.upz = uz > 0.0f;
+            f.wpx = wx > 0.0f; f.wpy = wy > 0.0f; f.wpz = wz > 0.0f;
+        }
+        bool ok = active && (fabsf(px + py + pz) < 1e30f);
+        bool done = !ok;
+        uint32_t cur = 0; int sp = 0; uint32_t steps = 0, tt = 0;
+        while (__any_sync(0xffffffffu, !done)) {
+            if (!done) {
+                ++steps;
+                const Node128 * np = a.wide + cur;
+                const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
+                const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
+                const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
+                const bool h0 = shaft_hits(f, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                const bool h1 = shaft_hits(f, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+                const bool h2 = shaft_hits(f, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
+                const bool h3 = shaft_hits(f, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
+                // leaf boxes inside the shaft: every triangle of theirs has to be cleared by its plane
+                bool clear = sp <= SH_STACK - 4 && steps <= a.max_steps;
+                #pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const bool hc = c == 0 ? h0 : (c == 1 ? h1 : (c == 2 ? h2 : h3));
+                    const uint32_t cc = c == 0 ? cnt.x : (c == 1 ? cnt.y : (c == 2 ? cnt.z : cnt.w));
+                    if (hc && cc && clear) {
+                        const uint32_t first = cc >> 6, count = cc & 31u;
+                        for (uint32_t i = 0; i < count && clear; ++i, ++tt)
+                            clear = tri_cleared(a.tris + first + i, s_obb[w], px, py, pz, eps);
+                    }
+                }
+                if (!clear) {
+                    ok = false; done = true;              // no certificate
+                } else {
+                    if (h0 && !cnt.x) stack[sp++] = ref.x;
+                    if (h1 && !cnt.y) stack[sp++] = ref.y;
+                    if (h2 && !cnt.z) stack[sp++] = ref.z;
+                    if (h3 && !cnt.w) stack[sp++] = ref.w;
+                    if (sp > 0) cur = stack[--sp]; else done = true;
+                }
+            }
+        }
+        if (ok) atomicOr(a.cert + (size_t)blk * a.nchunks + ((v - a.v0) >> 5), 1u << ((v - a.v0) & 31u));
+        tested += take; certified += __popc(__ballot_sync(0xffffffffu, ok));
+        if (active) { if (ok) dbg_sc += steps; else dbg_sf += steps; dbg_tt += tt; }
+        // ---- keep the views that did not fit ----
+        __syncwarp();
+        const uint32_t rest = qn - take;
+        const uint32_t carry = lane < rest ? s_q[w][32 + lane] : 0u;
+        __syncwarp();
+        if (lane < rest) s_q[w][lane] = carry;
+        qn = rest;
+        __syncwarp();
+    }
+    if (a.counters && lane == 0 && tested) {
+        atomicAdd(a.counters + 0, (unsigned long long)tested);
+        atomicAdd(a.counters + 1, (unsigned long long)certified);
+    }
+    if (a.counters) {
+        for (int o = 16; o > 0; o >>= 1) {
+            dbg_sc += __shfl_xor_sync(0xffffffffu, dbg_sc, o); dbg_sf += __shfl_xor_sync(0xffffffffu, dbg_sf, o);
+            dbg_tt += __shfl_xor_sync(0xffffffffu, dbg_tt, o);
+        }
+        if (lane == 0) { atomicAdd(a.counters + 4, dbg_sc); atomicAdd(a.counters + 5, dbg_sf); atomicAdd(a.counters + 6, dbg_tt); }
+    }
+}
+
 struct RayList {
-    float4 * dirl;        // unit point->camera direction, w = distance l
-    float4 * org;         // ray origin (the point), w = bits of the point's index within its block
-    uint8_t * vis;        // (point's index within its block) << 2 | status: 1 occluded, 2 visible
-    const uint32_t * off; // [num_blocks] first ray of each block's slice
+    float4 * dirl;        // every ray, (view, point) order per block: unit point->camera direction, w = distance l
+    uint8_t * vis;        // every ray: (point's index within its block) << 2 | status: 1 occluded, 2 visible
+    float4 * tdir;        // rays that have to be traced (not certified by k_shaft): direction, w = l
+    float4 * torg;        // ... origin (the point), w = bits of (ray index << 5 | point's index within its block)
+    const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
+    uint32_t * tcnt;      // [num_blocks] rays of the slice that have to be traced
 };
 
 // Exact cull (kernels.cu:153-167) + ray set-up values (:54-58).  One warp per block, views in
@@ -176,7 +375,8 @@ struct RayList {
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
-    const uint32_t * __restrict__ masks, float max_distance, int width, int height, RayList rl)
+    const uint32_t * __restrict__ masks, const uint32_t * __restrict__ cert, uint32_t nchunks,
+    float max_distance, int width, int height, RayList rl, unsigned long long * counters)
 {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t blk = blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
@@ -188,13 +388,16 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
     const uint32_t mbit = blk & 31;
     const uint32_t base = rl.off[blk];
-    uint32_t count = 0;
+    uint32_t count = 0, tcount = 0;
     for (uint32_t c0 = v0; c0 < v1; c0 += 32) {
         uint32_t vi = c0 + lane;
         uint32_t mw = vi < v1 ? __ldg(mrow + vi) : 0u;
         uint32_t word = __ballot_sync(0xffffffffu, (mw >> mbit) & 1u);
+        const uint32_t cword = cert ? __ldg(cert + (size_t)blk * nchunks + ((c0 - v0) >> 5)) : 0u;
         while (word) {
-            const uint32_t k = c0 + (__ffs(word) - 1); word &= word - 1;
+            const uint32_t kb = __ffs(word) - 1;
+            const uint32_t k = c0 + kb; word &= word - 1;
+            const bool certified = (cword >> kb) & 1u;             // every ray of this packet is visible (k_shaft)
             const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
             float vw[UAVMVS_VIEW_FLOATS];
             #pragma unroll
@@ -210,14 +413,25 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
             if (pass) pass = in_image(vw, v, width, height);
             uint32_t m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
-                uint32_t idx = base + count + __popc(m & lt_mask);
-                __stcs(rl.dirl + idx, make_float4(v2cn.x, v2cn.y, v2cn.z, l));
-                __stcs(rl.org + idx, make_float4(v.x, v.y, v.z, __uint_as_float(lane)));
+                const uint32_t r = __popc(m & lt_mask);
+                const uint32_t idx = base + count + r;
+                const float4 d4 = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
+                __stcs(rl.dirl + idx, d4);
+                if (certified) rl.vis[idx] = (uint8_t)(lane << 2 | 2u);
+                else {
+                    const uint32_t j = base + tcount + r;
+                    __stcs(rl.tdir + j, d4);
+                    __stcs(rl.torg + j, make_float4(v.x, v.y, v.z, __uint_as_float(idx << 5 | lane)));
+                }
             }
             count += __popc(m);
+            if (!certified) tcount += __popc(m);
         }
     }
-    if (lane == 0) rl.cnt[blk] = count;
+    if (lane == 0) {
+        rl.cnt[blk] = count; rl.tcnt[blk] = tcount;
+        if (counters && count) { atomicAdd(counters + 2, (unsigned long long)(count - tcount)); atomicAdd(counters + 3, (unsigned long long)tcount); }
+    }
 }
 
 struct TraceArgs {
@@ -279,6 +493,7 @@ k_trace(TraceArgs a)
     bool has_ray = false, traversing = false, hit = false;
     uint32_t idx = 0, cur = 0, npend = 0, ptl = 0; int sp = 0;
     RayT rt; rt.ox = rt.oy = rt.oz = rt.rdx = rt.rdy = rt.rdz = rt.tmin = rt.tmax = 0.0f;
+    rt.nox = rt.noy = rt.noz = rt.em = 0.0f;
     V3 rd = mk(0.f, 0.f, 0.f);
     uint32_t serviced_idle = 0;
 
@@ -294,7 +509,7 @@ k_trace(TraceArgs a)
                     if (lane == 0) b = atomicAdd(a.work, 1u);
                     b = __shfl_sync(0xffffffffu, b, 0);
                     if (b >= a.num_blocks) { drained = true; break; }
-                    pos = __ldg(a.rl.off + b); end = pos + a.rl.cnt[b];
+                    pos = __ldg(a.rl.off + b); end = pos + a.rl.tcnt[b];
                     continue;
                 }
                 const uint32_t take = min(need - given, end - pos);
@@ -302,17 +517,19 @@ k_trace(TraceArgs a)
                 pos += take; given += take;
             }
             if (mine) {
-                const float4 d4 = __ldcs(a.rl.dirl + idx);             // streamed once: keep L2 for the tree
-                const float4 o4 = __ldcs(a.rl.org + idx);
+                const float4 d4 = __ldcs(a.rl.tdir + idx);             // streamed once: keep L2 for the tree
+                const float4 o4 = __ldcs(a.rl.torg + idx);
                 const V3 o = ld3(o4);
-                ptl = __float_as_uint(o4.w) << 2;
+                idx = __float_as_uint(o4.w) >> 5;                      // position in the ordered list
+                ptl = (__float_as_uint(o4.w) & 31u) << 2;
                 rd = ld3(d4);
                 rt.ox = o.x; rt.oy = o.y; rt.oz = o.z;
                 rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
                 const float mn = fminf(fminf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
                 const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
-                if (mn > 1e-12f && mx < 2.0f && !a.bvh.root_is_leaf) {
+                if (mn > 1e-4f && mx < 2.0f && !a.bvh.root_is_leaf) {     // below: em would be uselessly wide
                     rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
+                    ray_fma_setup(rt);
                     has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
                 } else {
                     // axis-parallel (or degenerate) ray, single-leaf tree: the reference walk, right away
@@ -336,11 +553,11 @@ k_trace(TraceArgs a)
                 const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
                 const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
                 const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
-                float g0, g1, g2, g3, m0, m1, m2, m3;
-                slab_rel(rt, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, g0, m0);
-                slab_rel(rt, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, g1, m1);
-                slab_rel(rt, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y, g2, m2);
-                slab_rel(rt, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w, g3, m3);
+                const float g0 = slab_fma(rt, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                const float g1 = slab_fma(rt, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+                const float g2 = slab_fma(rt, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
+                const float g3 = slab_fma(rt, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
+                const float m0 = rt.em, m1 = rt.em, m2 = rt.em, m3 = rt.em;
                 // visit unless surely missed; leaf children are deferred (any-hit is order independent)
                 // with the "box not verified" flag when the filtered test cannot prove the hit
                 const bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);
@@ -402,14 +619,13 @@ __global__ void k_trace_exact(TraceArgs a, uint32_t total)
 {
     const uint32_t b = blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
     if (b >= a.num_blocks) return;
-    const uint32_t base = a.rl.off[b], count = a.rl.cnt[b];
+    const uint32_t base = a.rl.off[b], count = a.rl.tcnt[b];
     for (uint32_t i = threadIdx.x & 31; i < count; i += 32) {
-        const uint32_t idx = base + i;
-        const float4 d4 = a.rl.dirl[idx];
-        const float4 o4 = a.rl.org[idx];
+        const float4 d4 = a.rl.tdir[base + i];
+        const float4 o4 = a.rl.torg[base + i];
         const V3 o = ld3(o4);
         bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, d4.x, d4.y, d4.z, d4.w * 0.001f, d4.w);
-        a.rl.vis[idx] = (uint8_t)((__float_as_uint(o4.w) << 2) | (h ? 1u : 2u));
+        a.rl.vis[__float_as_uint(o4.w) >> 5] = (uint8_t)(((__float_as_uint(o4.w) & 31u) << 2) | (h ? 1u : 2u));
     }
 }
 
@@ -512,8 +728,11 @@ struct K1Scratch {
     uint32_t * masks = nullptr; size_t masks_cap = 0;
     uint32_t * caps = nullptr, * off = nullptr, * cnt = nullptr; size_t blocks_cap = 0;
     void * cub_tmp = nullptr; size_t cub_cap = 0;
-    float4 * dirl = nullptr, * org = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    uint32_t * tcnt = nullptr;
+    uint32_t * cert = nullptr; size_t cert_cap = 0;
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
+    unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     int grid_trace = 0;
 };
 static thread_local K1Scratch g_k1;
@@ -528,6 +747,15 @@ static int grow(T ** p, size_t * cap, size_t need, cudaStream_t s)
     return 0;
 }
 
+// Opt-in (UAVMVS_SHAFTS=1, read at every call).  Measured on config 2 (profiles/r01_c_shafts.txt): 23 % of the
+// packets / 31 % of the rays are certified, but the shaft walk costs more than the tracing it saves
+// (K1 8.1 ms with shafts vs 5.3 ms without), so the default pipeline does not run it.
+static bool shafts_enabled()
+{
+    const char * e = getenv("UAVMVS_SHAFTS");
+    return e && e[0] == '1';
+}
+
 static size_t ray_budget()
 {
     // upper bound of ray records (24 B + 1 B each) kept at a time; views are processed in
@@ -535,8 +763,9 @@ static size_t ray_budget()
     static size_t v = 0;
     if (!v) {
         const char * e = getenv("UAVMVS_RAY_BUDGET");
-        v = e ? (size_t)strtoull(e, nullptr, 10) : ((size_t)1 << 28);
+        v = e ? (size_t)strtoull(e, nullptr, 10) : ((size_t)1 << 27);
         if (v < 1024) v = 1024;
+        if (v > ((size_t)1 << 27)) v = (size_t)1 << 27;      // ray index << 5 | lane must fit 32 bits
     }
     return v;
 }
@@ -554,6 +783,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     if (!k.work) {
         UAV_CUDA(cudaMalloc(&k.work, sizeof(uint32_t)));
         UAV_CUDA(cudaMalloc(&k.total, sizeof(unsigned long long)));
+        UAV_CUDA(cudaMalloc(&k.counters, 8 * sizeof(unsigned long long)));
+        UAV_CUDA(cudaMemset(k.counters, 0, 8 * sizeof(unsigned long long)));
         UAV_CUDA(cudaMallocHost(&k.h_total, sizeof(unsigned long long)));
         int dev = 0, sms = 0, occ_a = 0, occ_b = 0;
         UAV_CUDA(cudaGetDevice(&dev));
@@ -565,8 +796,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     }
     if (grow(&k.masks, &k.masks_cap, (size_t)cloud->num_super * num_views, s)) return 1;
     if (nb + 1 > k.blocks_cap) {
-        size_t c0 = k.blocks_cap, c1 = k.blocks_cap, c2 = k.blocks_cap;
-        if (grow(&k.caps, &c0, (size_t)nb + 1, s) || grow(&k.off, &c1, (size_t)nb + 1, s) || grow(&k.cnt, &c2, (size_t)nb + 1, s)) return 1;
+        size_t c0 = k.blocks_cap, c1 = k.blocks_cap, c2 = k.blocks_cap, c3 = k.blocks_cap;
+        if (grow(&k.caps, &c0, (size_t)nb + 1, s) || grow(&k.off, &c1, (size_t)nb + 1, s) || grow(&k.cnt, &c2, (size_t)nb + 1, s)
+            || grow(&k.tcnt, &c3, (size_t)nb + 1, s)) return 1;
         k.blocks_cap = nb + 1;
     }
     size_t tmp_need = 0;
@@ -596,18 +828,32 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             step = (v1 - v0 + 1) / 2;
             continue;
         }
-        UAV_REQUIRE(total < (1ull << 32), "a single view yields more than 2^32 candidate pairs");
+        UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
         if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
         if (total > 0) {
             if (total > k.rays_cap) {
-                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap;
-                if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.org, &c1, (size_t)total, s) || grow(&k.vis, &c2, (size_t)total, s)) return 1;
+                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap;
+                if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.tdir, &c1, (size_t)total, s) || grow(&k.torg, &c3, (size_t)total, s)
+                    || grow(&k.vis, &c2, (size_t)total, s)) return 1;
                 k.rays_cap = (size_t)total;
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
-            RayList rl; rl.dirl = k.dirl; rl.org = k.org; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt;
+            RayList rl; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
+            // shafts: whole (block, view) packets proven visible without tracing (nested trees only)
+            const uint32_t nchunks = divup(v1 - v0, 32);
+            const bool shafts = shafts_enabled() && bvh->nested && !bvh->root_is_leaf;
+            if (shafts) {
+                if (grow(&k.cert, &k.cert_cap, (size_t)nb * nchunks, s)) return 1;
+                UAV_CUDA(cudaMemsetAsync(k.cert, 0, sizeof(uint32_t) * (size_t)nb * nchunks, s));
+                ShaftArgs sa; sa.wide = bvh->wide; sa.tris = bvh->ptris; sa.lo = cloud->block_lo; sa.hi = cloud->block_hi;
+                sa.obb = cloud->block_obb; sa.num_blocks = nb;
+                sa.views = d_views; sa.num_views = num_views; sa.v0 = v0; sa.v1 = v1; sa.masks = k.masks;
+                sa.cert = k.cert; sa.nchunks = nchunks; sa.counters = k.counters;
+                { const char * e = getenv("UAVMVS_SHAFT_STEPS"); sa.max_steps = e ? (uint32_t)atoi(e) : 1000000u; }
+                k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
+            }
             k_cull_emit<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, max_distance, width, height, rl);
+                d_views, num_views, v0, v1, k.masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
             unsigned grid = (unsigned)k.grid_trace;
@@ -623,6 +869,21 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         }
         v0 = v1;
     }
+    return 0;
+}
+
+int k1_counters(unsigned long long out[4], int reset)
+{
+    K1Scratch & k = g_k1;
+    for (int i = 0; i < 4; ++i) out[i] = 0;
+    if (!k.counters) return 0;
+    UAV_CUDA(cudaMemcpy(out, k.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (getenv("UAVMVS_SHAFT_DEBUG")) {
+        unsigned long long d[8];
+        UAV_CUDA(cudaMemcpy(d, k.counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[shaft] node steps: certified %llu failed %llu, triangle tests %llu\n", d[4], d[5], d[6]);
+    }
+    if (reset) UAV_CUDA(cudaMemset(k.counters, 0, 8 * sizeof(unsigned long long)));
     return 0;
 }
 

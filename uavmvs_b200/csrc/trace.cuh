@@ -279,7 +279,32 @@ static __device__ __noinline__ bool slab_exact_call(float ox, float oy, float oz
 // Only rays with |d_k| > 1e-12 on all axes may use it (no inf / NaN can arise).
 namespace uav {
 
-struct RayT { float ox, oy, oz, rdx, rdy, rdz, tmin, tmax; };
+struct RayT { float ox, oy, oz, rdx, rdy, rdz, tmin, tmax; float nox, noy, noz, em; };
+
+// One FFMA per plane: t~ = fma(b, rd, -(o rd)).  Against the reference's fl(fl(b - o) / d) this has a
+// relative error < 4 * 2^-24 and an ABSOLUTE error <= 2^-24 |o_k rd_k| per axis (the rounding of
+// o rd does not cancel).  The min/max chain is monotone and 1-Lipschitz and clamps the results into
+// [ray.tmin, ...] and [..., ray.tmax] with ray.tmin > 0, so with
+//     em = 2.4e-7 (|o.x rd.x| + |o.y rd.y| + |o.z rd.z|) + 4e-6 ray.tmax          (one constant per ray)
+// g = Tmax~ - Tmin~ > em proves that the reference accepts the box and g < -em proves that it rejects
+// (if Tmin~ > 2 ray.tmax then |g| > Tmin~ / 2, which dominates the relative error of Tmin~ itself).
+__device__ __forceinline__ void ray_fma_setup(RayT & f)
+{
+    const float ax = f.ox * f.rdx, ay = f.oy * f.rdy, az = f.oz * f.rdz;
+    f.nox = -ax; f.noy = -ay; f.noz = -az;
+    f.em = 2.4e-7f * (fabsf(ax) + fabsf(ay) + fabsf(az)) + 4e-6f * f.tmax;
+}
+
+__device__ __forceinline__ float slab_fma(const RayT & f, float mnx, float mny, float mnz,
+    float mxx, float mxy, float mxz)
+{
+    const float ax = __fmaf_rn(mnx, f.rdx, f.nox), bx = __fmaf_rn(mxx, f.rdx, f.nox);
+    const float ay = __fmaf_rn(mny, f.rdy, f.noy), by = __fmaf_rn(mxy, f.rdy, f.noy);
+    const float az = __fmaf_rn(mnz, f.rdz, f.noz), bz = __fmaf_rn(mxz, f.rdz, f.noz);
+    const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), f.tmin));
+    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), f.tmax));
+    return tmax - tmin;
+}
 
 __device__ __forceinline__ void slab_rel(const RayT & f, float mnx, float mny, float mnz,
     float mxx, float mxy, float mxz, float & g, float & m)
