@@ -166,6 +166,26 @@ int uavmvs_populate_spherical_histogram_recon(void * stream, const float view_po
 /* ---- K6 evaluate_spherical_histogram, kernels.h:69-79, kernels.cu:392-446 */
 int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int width, int height,
     const uavmvs_kdtree * kd, const uavmvs_array * sphere_hist, uavmvs_image * hist);
+/* ---- batched K4 / K5: num_positions candidate camera positions in one call.  Replaces the per-candidate
+ * launch loops of apps/generate_guidance_volume/generate_guidance_volume.cu:236-253 (K4: obs = recons = NULL)
+ * and apps/optimize_trajectory/optimize_trajectory.cu:388-398 (K5).  positions: HOST [num_positions][3].
+ * sphere_hists: device array of >= num_positions * bins floats, row b = the sphere_hist of position b;
+ * contributions are ADDED (the caller nulls it first, like dcon_hist->null()).  Candidates go through the
+ * same ray-list pipeline as K1 (block-level range / back-face cull, compacted rays, persistent trace). */
+int uavmvs_populate_spherical_histogram_batch(void * stream, const float * positions, uint32_t num_positions,
+    float max_distance, float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    const uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons, uavmvs_array * sphere_hists);
+
+/* ---- batched K6 (+ the host arg-min loop of optimize_trajectory.cu:416-428 as a device reduction).
+ * For every position b: image[y][x] of kernels.cu:392-446 from row b of sphere_hists.  images: NULL or a
+ * device array of >= num_positions * image_height * image_width floats (dense [b][y][x]).  h_min / h_argmin /
+ * h_max / h_argmax: HOST [num_positions] or NULL; arg = y * image_width + x of the FIRST extremum in
+ * row-major order.  When any of them is given the call synchronises the stream.  The (pixel, bin) frustum
+ * matrix is cached in the KD-tree handle per (calib, width, height, image size). */
+int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9], int width, int height,
+    uavmvs_kdtree * kd, const uavmvs_array * sphere_hists, uint32_t num_positions, uint32_t image_width,
+    uint32_t image_height, uavmvs_array * images, float * h_min, uint32_t * h_argmin, float * h_max, uint32_t * h_argmax);
+
 /* ---- K7 estimate_capture_difficulty, kernels.h:81-84, kernels.cu:448-494 */
 int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const uavmvs_bvh * bvh,
     uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud);

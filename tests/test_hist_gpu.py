@@ -119,3 +119,86 @@ def test_estimate_capture_difficulty_k7(api, oracle, setup):
     assert np.allclose(v_g, v_o, rtol=1e-5, atol=1e-6)
     assert np.allclose(q_g, q_o, rtol=1e-5, atol=1e-6)
     assert q_o.max() > 0 and v_o.min() < 1.5
+
+
+def test_batched_k4_k6_equal_single_calls(api, oracle, setup):
+    """uavmvs_populate_spherical_histogram_batch / _evaluate_spherical_histogram_batch (config 4: one call per
+    batch of candidate voxels) against the per-position entry points and the oracle."""
+    s = setup
+    sc, S = s["sc"], s["sv"].shape[0]
+    rng = np.random.default_rng(21)
+    pos = np.concatenate([np.array(POSITIONS, np.float32),
+                          rng.uniform([0, 0, 15], [64, 64, 90], (28, 3)).astype(np.float32)])
+    B = pos.shape[0]
+    hists = api.Array.create(B * S)
+    hists.null()
+    api.populate_spherical_histogram_batch(pos, sc.max_distance, s["gbvh"], s["cloud"], s["gkd"], hists)
+    h_b = hists.download().reshape(B, S)
+    for b in range(B):
+        h_ref, bins, scores = oracle.populate_spherical_histogram(s["obvh"], s["okd"], pos[b], sc.max_distance,
+                                                                  sc.points, sc.normals, s["values"], s["quals"], S)
+        assert _hist_close(h_b[b], h_ref, bins, scores, S), b
+        assert np.array_equal(h_b[b] != 0, h_ref != 0) or _hist_close(h_b[b], h_ref, bins, scores, S)
+    assert not h_b[3].any() and (h_b != 0).sum() > 1000
+    # batched K6: images bit-identical to the per-position kernel on the same histogram rows (same additions,
+    # same order), extrema = first occurrence in row-major order
+    images = api.Array.create(B * 45 * 128)
+    vmin, imin, vmax, imax = api.evaluate_spherical_histogram_batch(sc.calib[0], sc.width, sc.height, s["gkd"], hists, B,
+                                                                    images=images)
+    img_b = images.download().reshape(B, 45, 128)
+    for b in (0, 1, 2, 7, B - 1):
+        row = api.Array.create(S)
+        row.upload(h_b[b])
+        img = api.Image.create(128, 45)
+        api.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["gkd"], row, img)
+        assert np.array_equal(img.download().view(np.uint32), img_b[b].view(np.uint32)), b
+        i_ref = oracle.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["sv"], h_b[b])
+        assert np.all(np.abs(img_b[b].astype(np.float64) - i_ref) <= 1e-5 * np.abs(h_b[b]).sum() + 1e-12)
+    flat = img_b.reshape(B, -1)
+    assert np.array_equal(vmin, flat.min(1)) and np.array_equal(vmax, flat.max(1))
+    assert np.array_equal(imin, flat.argmin(1).astype(np.uint32)) and np.array_equal(imax, flat.argmax(1).astype(np.uint32))
+    # without images, same extrema
+    v2 = api.evaluate_spherical_histogram_batch(sc.calib[0], sc.width, sc.height, s["gkd"], hists, B)
+    assert np.array_equal(v2[0], vmin) and np.array_equal(v2[3], imax)
+
+
+def test_batched_k5_optimizer_inner_loop(api, oracle, setup):
+    """Config 3: remove views -> K2 -> K3 -> candidate positions through batched K5 + K6 + arg-min
+    (apps/optimize_trajectory/optimize_trajectory.cu:313-428)."""
+    s = setup
+    sc, S = s["sc"], s["sv"].shape[0]
+    views = sc.views28()
+    removed = views[[5, 40, 90]]
+    obs_o = oracle.ObsRays(sc.num_points, 32)
+    oracle.update_observation_rays(s["obvh"], True, views, sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+    oracle.update_observation_rays(s["obvh"], False, removed, sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    recons = api.Array.create(sc.num_points)
+    api.update_observation_rays_batch(True, views, sc.max_distance, sc.width, sc.height, s["gbvh"], s["cloud"], obs)
+    api.update_observation_rays_batch(False, removed, sc.max_distance, sc.width, sc.height, s["gbvh"], s["cloud"], obs)
+    api.process_observation_rays(obs)
+    api.evaluate_observation_rays(obs, recons)
+    assert np.array_equal(obs.download(data=False)[1], obs_o.num_rows)
+    # 7 Nelder-Mead candidates around each removed view
+    rng = np.random.default_rng(4)
+    cand = (removed[:, None, :3] + rng.normal(0, 2.0, (3, 7, 3))).reshape(-1, 3).astype(np.float32)
+    B = cand.shape[0]
+    hists = api.Array.create(B * S)
+    hists.null()
+    api.populate_spherical_histogram_batch(cand, sc.max_distance, s["gbvh"], s["cloud"], s["gkd"], hists,
+                                           target_recon=sc.target_recon, obs_rays=obs, recons=recons)
+    h_b = hists.download().reshape(B, S)
+    r_g = recons.download()
+    for b in range(B):
+        h_ref, bins, deltas = oracle.populate_spherical_histogram_recon(
+            s["obvh"], s["okd"], cand[b], sc.max_distance, sc.target_recon, sc.points, sc.normals, obs_o, r_g, S)
+        mag = np.zeros(S, np.float64)
+        ok = bins != 0xFFFFFFFF
+        np.add.at(mag, bins[ok], 16.0)
+        assert np.all(np.abs(h_b[b].astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12), b
+    vmin, imin, vmax, imax = api.evaluate_spherical_histogram_batch(sc.calib[0], sc.width, sc.height, s["gkd"], hists, B)
+    for b in (0, 9, B - 1):
+        i_ref = oracle.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["sv"], h_b[b])
+        assert abs(float(vmin[b]) - float(i_ref.min())) <= 1e-5 * np.abs(h_b[b]).sum() + 1e-12
+    assert (vmin < 0).any()

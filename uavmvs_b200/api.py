@@ -387,6 +387,35 @@ def evaluate_spherical_histogram(calib, width, height, kd_tree, sphere_hist, his
                                                     kd_tree.ptr, sphere_hist.ptr, hist.ptr))
 
 
+def populate_spherical_histogram_batch(positions, max_distance, bvh_tree, cloud, kd_tree, sphere_hists, stream=None,
+                                       target_recon=0.0, obs_rays=None, recons=None):
+    """B candidate positions in one call; sphere_hists is an Array of >= B * bins floats (row per position).
+    K4 when obs_rays/recons are None, K5 otherwise.  Contributions are added (null the array first)."""
+    pos = _f(positions).reshape(-1, 3)
+    _check(_lib.uavmvs_populate_spherical_histogram_batch(
+        _stream_ptr(stream), _p(pos), _u32(pos.shape[0]), _f32(max_distance), _f32(target_recon), bvh_tree.ptr,
+        cloud.ptr, kd_tree.ptr, None if obs_rays is None else obs_rays.ptr, None if recons is None else recons.ptr,
+        sphere_hists.ptr))
+
+
+def evaluate_spherical_histogram_batch(calib, width, height, kd_tree, sphere_hists, num_positions, image_width=128,
+                                       image_height=45, images=None, want_best=True, stream=None):
+    """Batched K6 + device arg-min/arg-max.  Returns (min, argmin, max, argmax) arrays of length B
+    (arg = y * image_width + x, first extremum in row-major order) or None when want_best is False."""
+    K = _f(calib, 9)
+    B = int(num_positions)
+    if want_best:
+        vmin, vmax = np.empty(B, np.float32), np.empty(B, np.float32)
+        imin, imax = np.empty(B, np.uint32), np.empty(B, np.uint32)
+    else:
+        vmin = vmax = imin = imax = None
+    _check(_lib.uavmvs_evaluate_spherical_histogram_batch(
+        _stream_ptr(stream), _p(K), _i32(width), _i32(height), kd_tree.ptr, sphere_hists.ptr, _u32(B),
+        _u32(image_width), _u32(image_height), None if images is None else images.ptr,
+        _p(vmin), _p(imin), _p(vmax), _p(imax)))
+    return (vmin, imin, vmax, imax) if want_best else None
+
+
 def estimate_capture_difficulty(max_distance, bvh_tree, mesh_size, kd_tree, cloud, stream=None):
     """libs/eval/kernels.h:81-84"""
     _check(_lib.uavmvs_estimate_capture_difficulty(_stream_ptr(stream), _f32(max_distance), bvh_tree.ptr,

@@ -77,6 +77,10 @@ struct uavmvs_kdtree {
     uint32_t num_nodes;
     uint4 * nodes;   // {vid, dim, left, right}
     float4 * verts;  // xyz
+    // cache of the batched K6: bit (pixel, bin) = "sphere vertex bin projects inside the image of
+    // orientation pixel" (kernels.cu:409-441), valid for one (calib, width, height, image size)
+    uint32_t * fr_bits = nullptr;   // [words][pixels], words = ceil(num_nodes / 32)
+    float fr_calib[9] = {0}; int fr_w = 0, fr_h = 0; uint32_t fr_iw = 0, fr_ih = 0;
 };
 
 struct uavmvs_cloud {
@@ -151,11 +155,23 @@ struct Ray { V3 o, d; float tmin, tmax; };
 struct Heur { float m_k, m_x0, t_k, t_x0; };
 Heur current_heur();
 
+// Batched spherical-histogram job run through the K1 ray-list pipeline (k1.cu): the "views" are bare
+// candidate positions (no frustum), visible rays are binned into hist[view][bin] instead of becoming
+// observation rows.  with_recon = 0: K4 (kernels.cu:293-336); 1: K5 (kernels.cu:338-390).
+struct HistJob {
+    const uint4 * kd_nodes; const float4 * kd_verts; uint32_t kd_n;
+    const float * values; const float * qualities;
+    int with_recon; float target_recon;
+    const float4 * obs; const uint32_t * num_rows; uint32_t max_rows, stride; const float * recons;
+    float * hist;
+    Heur heur;
+};
+
 // K1 pipeline (k1.cu).  d_stats (device, may be null): [0] += occlusion rays, [1] += visible
 // observations, [3] += (point, view) pairs that survive the block-level cull.
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
-    uavmvs_obs * obs, unsigned long long * d_stats);
+    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hist_job = nullptr);
 int k1_counters(unsigned long long out[4], int reset);
 
 }  // namespace uav

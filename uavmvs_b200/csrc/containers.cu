@@ -172,7 +172,7 @@ int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n
 int uavmvs_kdtree_destroy(uavmvs_kdtree * k)
 {
     if (!k) return 0;
-    cudaFree(k->nodes); cudaFree(k->verts);
+    cudaFree(k->nodes); cudaFree(k->verts); cudaFree(k->fr_bits);
     delete k;
     return 0;
 }

@@ -3,43 +3,13 @@
 // Reference: libs/eval/kernels.cu:293-494, libs/cacc/nnsearch.h:67-155.
 #include "common.cuh"
 #include "trace.cuh"
+#include "kd.cuh"
+
+#include <vector>
 
 namespace uav {
 
 constexpr float kPi = 3.14159265f;
-
-struct KdView { const uint4 * __restrict__ nodes; const float4 * __restrict__ verts; uint32_t n; };
-
-// libs/cacc/nnsearch.h:67-155: depth-first nearest neighbour, strict '<' (first found wins)
-__device__ __forceinline__ uint32_t kd_find_nn(const KdView & kd, V3 q)
-{
-    uint32_t idx = UAV_NAI; float max_dist = UAV_INF;
-    uint32_t node_idx = 0; bool down = true;
-    uint32_t stack[40]; int sp = 0;
-    while (true) {
-        uint4 node = __ldg(kd.nodes + node_idx);          // vid, dim, left, right
-        float4 v4 = __ldg(kd.verts + node.x);
-        V3 vert = ld3(v4);
-        float qd = node.y == 0 ? q.x : (node.y == 1 ? q.y : q.z);
-        float vd = node.y == 0 ? vert.x : (node.y == 1 ? vert.y : vert.z);
-        float diff = qd - vd;
-        if (down) {
-            float dist = norm(q - vert);
-            if (dist < max_dist) { idx = node.x; max_dist = dist; }
-            if (node.z != UAV_NAI || node.w != UAV_NAI) {
-                if (node.z != UAV_NAI && node.w != UAV_NAI) stack[sp++] = node_idx;
-                uint32_t next = (diff < 0.0f) ? node.z : node.w;
-                uint32_t other = (diff < 0.0f) ? node.w : node.z;
-                node_idx = (next != UAV_NAI) ? next : other;
-            } else { down = false; node_idx = UAV_NAI; }
-        } else {
-            if (fabsf(diff) < max_dist) { down = true; node_idx = (diff < 0.0f) ? node.w : node.z; }
-            else { down = false; node_idx = UAV_NAI; }
-        }
-        if (node_idx == UAV_NAI) { if (sp == 0) break; node_idx = stack[--sp]; }
-    }
-    return idx;
-}
 
 __device__ __forceinline__ float logistic(float x, float k, float x0) { return 1.0f / (1.0f + expf(-k * (x - x0))); }
 __device__ __forceinline__ float func(float recon, float target) { float a = fabsf(fminf(recon - target, 0.0f)); return a * a; }
@@ -220,7 +190,105 @@ k_estimate_capture_difficulty(BvhView bvh, KdView kd, uint32_t mesh_size, float 
     }
 }
 
-static KdView kd_view(const uavmvs_kdtree * k) { KdView v; v.nodes = k->nodes; v.verts = k->verts; v.n = k->num_nodes; return v; }
+
+// ---- batched K6 ------------------------------------------------------------------------------
+// Whether sphere vertex i lies inside the image of orientation pixel (x, y) does not depend on the
+// histogram values (kernels.cu:409-441), so it is computed once per (calib, width, height) as a bit
+// matrix with exactly the arithmetic of k_evaluate_spherical_histogram; the per-position work is then
+// "sum the selected bins in ascending order" - the same additions in the same order as the reference.
+__global__ void k_frustum_bits(const float * __restrict__ K9, int width, int height, KdView kd,
+    uint32_t hw, uint32_t hh, uint32_t * __restrict__ bits)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x, npix = hw * hh;
+    if (pix >= npix) return;
+    const uint32_t x = pix % hw, y = pix / hw;
+    float K[9];
+    #pragma unroll
+    for (int i = 0; i < 9; ++i) K[i] = K9[i];
+    float phi = (x / (float)hw) * 2.0f * kPi;
+    float theta = (0.5f + (y / (float)hh) / 2.0f) * kPi;
+    float stheta = sinf(theta);
+    V3 view_dir = mk(stheta * cosf(phi), stheta * sinf(phi), cosf(theta));
+    V3 rz = -view_dir;
+    V3 up = mk(0.0f, 0.0f, 1.0f);
+    bool stable = fabsf(dot(up, rz)) < 0.99f;
+    if (!stable) up = mk(cosf(phi), sinf(phi), 0.0f);
+    V3 rx = normalized(cross(up, rz));
+    V3 ry = normalized(cross(rz, rx));
+    const uint32_t words = (kd.n + 31) / 32;
+    for (uint32_t wd = 0; wd < words; ++wd) {
+        uint32_t m = 0;
+        for (uint32_t b = 0; b < 32; ++b) {
+            const uint32_t i = wd * 32 + b;
+            if (i >= kd.n) break;
+            V3 dir = normalized(ld3(__ldg(kd.verts + i)));
+            if (dot(view_dir, dir) < 0.0f) continue;
+            V3 v = mk(dot(rx, dir), dot(ry, dir), dot(rz, dir));
+            float p[3];
+            #pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                float s = 0.0f;
+                s += K[3 * r + 0] * v.x; s += K[3 * r + 1] * v.y; s += K[3 * r + 2] * v.z;
+                p[r] = s;
+            }
+            float px = p[0] / p[2] - 0.5f, py = p[1] / p[2] - 0.5f;
+            if (px < 0.0f || (float)width <= px || py < 0.0f || (float)height <= py) continue;
+            m |= 1u << b;
+        }
+        bits[(size_t)wd * npix + pix] = m;
+    }
+}
+
+// One CTA per candidate position: histogram row staged in shared memory, a thread per orientation
+// pixel (strided), optional image output, first minimum / first maximum in row-major order (the
+// host loop of apps/optimize_trajectory/optimize_trajectory.cu:416-428 made a device reduction).
+constexpr int EVB_THREADS = 256;
+__global__ void __launch_bounds__(EVB_THREADS)
+k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_t words, uint32_t npix,
+    const float * __restrict__ sphere_hists, uint32_t S, float * __restrict__ images, float4 * __restrict__ best)
+{
+    extern __shared__ float s_h[];
+    __shared__ float s_v[2][EVB_THREADS / 32]; __shared__ uint32_t s_i[2][EVB_THREADS / 32];
+    const uint32_t b = blockIdx.x;
+    for (uint32_t i = threadIdx.x; i < words * 32; i += EVB_THREADS) s_h[i] = i < S ? sphere_hists[(size_t)b * S + i] : 0.0f;
+    __syncthreads();
+    float vmin = UAV_INF, vmax = -UAV_INF; uint32_t imin = UAV_NAI, imax = UAV_NAI;
+    for (uint32_t pix = threadIdx.x; pix < npix; pix += EVB_THREADS) {
+        float sum = 0.0f;
+        for (uint32_t wd = 0; wd < words; ++wd) {
+            uint32_t m = __ldg(bits + (size_t)wd * npix + pix);
+            while (m) { const uint32_t k = __ffs(m) - 1; m &= m - 1; sum += s_h[wd * 32 + k]; }
+        }
+        if (images) images[(size_t)b * npix + pix] = sum;
+        if (sum < vmin) { vmin = sum; imin = pix; }          // pixels ascend per thread: first occurrence
+        if (sum > vmax) { vmax = sum; imax = pix; }
+    }
+    // lexicographic (value, index) reduction keeps the first occurrence
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, vmin, o); uint32_t oi = __shfl_xor_sync(0xffffffffu, imin, o);
+        if (ov < vmin || (ov == vmin && oi < imin)) { vmin = ov; imin = oi; }
+        ov = __shfl_xor_sync(0xffffffffu, vmax, o); oi = __shfl_xor_sync(0xffffffffu, imax, o);
+        if (ov > vmax || (ov == vmax && oi < imax)) { vmax = ov; imax = oi; }
+    }
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { s_v[0][w] = vmin; s_i[0][w] = imin; s_v[1][w] = vmax; s_i[1][w] = imax; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < EVB_THREADS / 32; ++k) {
+            if (s_v[0][k] < vmin || (s_v[0][k] == vmin && s_i[0][k] < imin)) { vmin = s_v[0][k]; imin = s_i[0][k]; }
+            if (s_v[1][k] > vmax || (s_v[1][k] == vmax && s_i[1][k] < imax)) { vmax = s_v[1][k]; imax = s_i[1][k]; }
+        }
+        best[b] = make_float4(vmin, __uint_as_float(imin), vmax, __uint_as_float(imax));
+    }
+}
+
+__global__ void k_fill_positions(const float * __restrict__ pos, uint32_t n, float * __restrict__ views)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float * v = views + (size_t)i * UAVMVS_VIEW_FLOATS;
+    for (int k = 0; k < UAVMVS_VIEW_FLOATS; ++k) v[k] = k < 3 ? pos[3 * (size_t)i + k] : 0.0f;
+}
 
 static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos[3], float max_distance,
     float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd,
@@ -298,6 +366,84 @@ int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const 
         view_of(bvh), kd_view(kd), mesh_size, max_distance, cloud->vertices, cloud->normals, cloud->n,
         cloud->values, cloud->qualities);
     UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int uavmvs_populate_spherical_histogram_batch(void * stream, const float * positions, uint32_t num_positions,
+    float max_distance, float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
+    const uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons, uavmvs_array * sphere_hists)
+{
+    UAV_REQUIRE(positions && bvh && cloud && kd && sphere_hists, "null argument");
+    UAV_REQUIRE((obs == nullptr) == (recons == nullptr), "obs and recons go together (both NULL: K4, both set: K5)");
+    UAV_REQUIRE((uint64_t)sphere_hists->n >= (uint64_t)num_positions * kd->num_nodes, "sphere_hists smaller than [positions][bins]");
+    if (num_positions == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    HistJob hj;
+    hj.kd_nodes = kd->nodes; hj.kd_verts = kd->verts; hj.kd_n = kd->num_nodes;
+    hj.values = cloud->values; hj.qualities = cloud->qualities;
+    hj.with_recon = obs ? 1 : 0; hj.target_recon = target_recon;
+    hj.obs = nullptr; hj.num_rows = nullptr; hj.max_rows = 0; hj.stride = 0; hj.recons = nullptr;
+    if (obs) {
+        UAV_REQUIRE(obs->num_cols == cloud->n && recons->n == cloud->n, "size mismatch");
+        hj.obs = obs->data; hj.num_rows = obs->num_rows; hj.max_rows = obs->max_rows;
+        hj.stride = (uint32_t)(obs->pitch / sizeof(float4)); hj.recons = recons->data;
+    }
+    hj.hist = sphere_hists->data; hj.heur = current_heur();
+    float * d_pos = nullptr, * d_views = nullptr;
+    UAV_CUDA(cudaMallocAsync(&d_pos, sizeof(float) * 3 * (size_t)num_positions, s));
+    UAV_CUDA(cudaMallocAsync(&d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_positions, s));
+    UAV_CUDA(cudaMemcpyAsync(d_pos, positions, sizeof(float) * 3 * (size_t)num_positions, cudaMemcpyHostToDevice, s));
+    k_fill_positions<<<divup(num_positions, 256), 256, 0, s>>>(d_pos, num_positions, d_views);
+    UAV_CUDA(cudaGetLastError());
+    int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
+    cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s);
+    return rc;
+}
+
+int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9], int width, int height,
+    uavmvs_kdtree * kd, const uavmvs_array * sphere_hists, uint32_t num_positions, uint32_t image_width,
+    uint32_t image_height, uavmvs_array * images, float * h_min, uint32_t * h_argmin, float * h_max, uint32_t * h_argmax)
+{
+    UAV_REQUIRE(calib && kd && sphere_hists, "null argument");
+    UAV_REQUIRE(image_width >= 1 && image_height >= 1, "empty image");
+    UAV_REQUIRE((uint64_t)sphere_hists->n >= (uint64_t)num_positions * kd->num_nodes, "sphere_hists smaller than [positions][bins]");
+    const uint32_t npix = image_width * image_height, S = kd->num_nodes, words = (S + 31) / 32;
+    UAV_REQUIRE(!images || (uint64_t)images->n >= (uint64_t)num_positions * npix, "images smaller than [positions][h][w]");
+    UAV_REQUIRE(words * 32 * sizeof(float) <= 48 * 1024, "sphere histogram does not fit shared memory");
+    if (num_positions == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    bool same = kd->fr_bits && kd->fr_w == width && kd->fr_h == height && kd->fr_iw == image_width && kd->fr_ih == image_height
+        && memcmp(kd->fr_calib, calib, 9 * sizeof(float)) == 0;
+    if (!same) {
+        float * d_K;
+        UAV_CUDA(cudaStreamSynchronize(s));
+        if (kd->fr_bits) { UAV_CUDA(cudaFree(kd->fr_bits)); kd->fr_bits = nullptr; }
+        UAV_CUDA(cudaMalloc(&kd->fr_bits, sizeof(uint32_t) * (size_t)words * npix));
+        UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
+        UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
+        k_frustum_bits<<<divup(npix, 128), 128, 0, s>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
+        UAV_CUDA(cudaGetLastError());
+        UAV_CUDA(cudaStreamSynchronize(s));
+        UAV_CUDA(cudaFree(d_K));
+        memcpy(kd->fr_calib, calib, 9 * sizeof(float)); kd->fr_w = width; kd->fr_h = height;
+        kd->fr_iw = image_width; kd->fr_ih = image_height;
+    }
+    float4 * d_best;
+    UAV_CUDA(cudaMallocAsync(&d_best, sizeof(float4) * (size_t)num_positions, s));
+    k_evaluate_spherical_histogram_batch<<<num_positions, EVB_THREADS, words * 32 * sizeof(float), s>>>(kd->fr_bits, words, npix,
+        sphere_hists->data, S, images ? images->data : nullptr, d_best);
+    UAV_CUDA(cudaGetLastError());
+    if (h_min || h_argmin || h_max || h_argmax) {
+        std::vector<float4> hb(num_positions);
+        UAV_CUDA(cudaMemcpyAsync(hb.data(), d_best, sizeof(float4) * (size_t)num_positions, cudaMemcpyDeviceToHost, s));
+        UAV_CUDA(cudaStreamSynchronize(s));
+        for (uint32_t i = 0; i < num_positions; ++i) {
+            uint32_t a, b; memcpy(&a, &hb[i].y, 4); memcpy(&b, &hb[i].w, 4);
+            if (h_min) h_min[i] = hb[i].x; if (h_argmin) h_argmin[i] = a;
+            if (h_max) h_max[i] = hb[i].z; if (h_argmax) h_argmax[i] = b;
+        }
+    }
+    UAV_CUDA(cudaFreeAsync(d_best, s));
     return 0;
 }
 

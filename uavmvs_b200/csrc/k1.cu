@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "trace.cuh"
 #include "evalmath.cuh"
+#include "kd.cuh"
 
 namespace uav {
 
@@ -55,6 +56,7 @@ __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view
     float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
     float D = sqrtf(dx * dx + dy * dy + dz * dz);
     if (D * 0.99999f - sph.w >= max_distance * 1.00001f) return false;
+    if (width <= 0) return true;                          // bare candidate position (histogram jobs): no image test
     const float * W = view + 3; const float * K = view + 19;
     float q[3], e2 = 0.0f, fro2 = 0.0f;
     #pragma unroll
@@ -368,10 +370,12 @@ struct RayList {
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
     uint32_t * tcnt;      // [num_blocks] rays of the slice that have to be traced
+    uint32_t * rview;     // histogram jobs only: view (candidate position) index of every ray
 };
 
 // Exact cull (kernels.cu:153-167) + ray set-up values (:54-58).  One warp per block, views in
 // order; lanes = points.  A slice is filled in (view, point) order.
+template <bool HIST>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
@@ -409,14 +413,21 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
             float l = norm(v2c);
             V3 v2cn = v2c / l;
             float ctheta = dot(v2cn, nrm);
-            bool pass = valid && !(ctheta < 0.087f) && !(l >= max_distance);
-            if (pass) pass = in_image(vw, v, width, height);
+            bool pass;
+            if (HIST) {                                   // kernels.cu:310-316 / :358-364: scale first, no image test
+                const float scale = 1.0f - (l / max_distance);
+                pass = valid && !(scale <= 0.0f) && !(ctheta < 0.087f);
+            } else {
+                pass = valid && !(ctheta < 0.087f) && !(l >= max_distance);
+                if (pass) pass = in_image(vw, v, width, height);
+            }
             uint32_t m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
                 const uint32_t r = __popc(m & lt_mask);
                 const uint32_t idx = base + count + r;
                 const float4 d4 = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
                 __stcs(rl.dirl + idx, d4);
+                if (HIST) rl.rview[idx] = k;
                 if (certified) rl.vis[idx] = (uint8_t)(lane << 2 | 2u);
                 else {
                     const uint32_t j = base + tcount + r;
@@ -723,6 +734,72 @@ k_retire(RetireArgs a)
     }
 }
 
+// Histogram jobs: every visible ray adds its score to hist[view][nearest sphere bin].
+// WITH_RECON = false: K4, kernels.cu:318-335.  true: K5, kernels.cu:366-389.
+template <bool WITH_RECON>
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_retire_hist(RetireArgs a, HistJob h)
+{
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk >= a.num_blocks) return;
+    const uint32_t count = a.rl.cnt[blk];
+    if (count == 0) return;
+    const uint32_t base = a.rl.off[blk];
+    KdView kd; kd.nodes = h.kd_nodes; kd.verts = h.kd_verts; kd.n = h.kd_n;
+    unsigned long long st_vis = 0;
+    for (uint32_t c0 = 0; c0 < count; c0 += 32) {
+        const uint32_t i = c0 + lane;
+        const uint32_t vb = i < count ? (uint32_t)__ldcs(a.rl.vis + base + i) : 0u;
+        if ((vb & 3u) != 2u) continue;                    // occluded (or past the end)
+        ++st_vis;
+        const float4 d4 = __ldcs(a.rl.dirl + base + i);
+        const uint32_t view = a.rl.rview[base + i];
+        const uint32_t id = blk * 32 + (vb >> 2);
+        const V3 v2cn = ld3(d4), n = ld3(a.normals[id]);
+        const float l = d4.w;
+        const float scale = 1.0f - (l / a.max_distance);
+        const float ctheta = dot(v2cn, n);
+        float contrib = 0.0f;
+        if (!WITH_RECON) {
+            const float capture_difficulty = fmaxf(h.qualities[id], 0.0f);
+            const float min_theta = fminf(h.values[id], 1.484f);
+            const float scaling = (kPi / 2.0f) / ((kPi / 2.0f) - min_theta);
+            const float theta = acosf(__saturatef(ctheta));
+            const float rel_theta = fmaxf(theta - min_theta, 0.0f) * scaling;
+            contrib = capture_difficulty * cosf(rel_theta) * scale;
+        } else {
+            const uint32_t rows = h.num_rows[id];
+            if (rows >= h.max_rows) continue;             // kernels.cu:373
+            const float recon = h.recons[id];
+            float new_recon = 0.0f;
+            if (rows >= 1) {
+                const V3 rel = relative_direction(v2cn, n);
+                const float m_k = h.heur.m_k, m_x0 = kPi / h.heur.m_x0, t_k = h.heur.t_k, t_x0 = kPi / h.heur.t_x0;
+                float sum = 0.0f;
+                for (uint32_t r = 0; r < rows; ++r) {     // heuristic(), kernels.cu:111-136
+                    const float4 o = h.obs[(size_t)r * h.stride + id];
+                    const float calpha = dot(rel, mk(o.x, o.y, o.z));
+                    const float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+                    const float sc = fminf(o.w, scale);
+                    const float ct = fminf(o.z, rel.z);
+                    const float matchability = (1.0f - logistic(alpha, m_k, m_x0)) * ct;
+                    const float triangulation = logistic(alpha, t_k, t_x0) * sc;
+                    sum += matchability * triangulation;
+                }
+                new_recon = recon + sum;
+            }
+            contrib = func(new_recon, h.target_recon) - func(recon, h.target_recon);
+        }
+        const uint32_t bin = kd_find_nn(kd, -v2cn);
+        atomicAdd(h.hist + (size_t)view * h.kd_n + bin, contrib);
+    }
+    if (a.stats) {
+        for (int o = 16; o > 0; o >>= 1) st_vis += __shfl_xor_sync(0xffffffffu, st_vis, o);
+        if (lane == 0) { atomicAdd(a.stats + 0, (unsigned long long)count); atomicAdd(a.stats + 1, st_vis); }
+    }
+}
+
 // ---- host side ---------------------------------------------------------------------------
 struct K1Scratch {
     uint32_t * masks = nullptr; size_t masks_cap = 0;
@@ -730,6 +807,7 @@ struct K1Scratch {
     void * cub_tmp = nullptr; size_t cub_cap = 0;
     float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
     uint32_t * tcnt = nullptr;
+    uint32_t * rview = nullptr; size_t rview_cap = 0;
     uint32_t * cert = nullptr; size_t cert_cap = 0;
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
@@ -772,10 +850,11 @@ static size_t ray_budget()
 
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
-    uavmvs_obs * obs, unsigned long long * d_stats)
+    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hj)
 {
-    UAV_REQUIRE(bvh && cloud && obs, "null handle");
-    UAV_REQUIRE(obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
+    UAV_REQUIRE(bvh && cloud && (obs || hj), "null handle");
+    UAV_REQUIRE(hj || obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
+    if (hj) { width = 0; height = 0; }                   // bare positions: no image test anywhere
     UAV_REQUIRE(bvh->num_tris < (1u << 26), "more than 2^26 triangles");
     if (num_views == 0) return 0;
     K1Scratch & k = g_k1;
@@ -838,7 +917,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 k.rays_cap = (size_t)total;
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
-            RayList rl; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
+            if (hj && grow(&k.rview, &k.rview_cap, k.rays_cap, s)) return 1;
+            RayList rl; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
             // shafts: whole (block, view) packets proven visible without tracing (nested trees only)
             const uint32_t nchunks = divup(v1 - v0, 32);
             const bool shafts = shafts_enabled() && bvh->nested && !bvh->root_is_leaf;
@@ -852,7 +932,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 { const char * e = getenv("UAVMVS_SHAFT_STEPS"); sa.max_steps = e ? (uint32_t)atoi(e) : 1000000u; }
                 k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
             }
-            k_cull_emit<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+                d_views, num_views, v0, v1, k.masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
+            else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
@@ -861,8 +943,17 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             else k_trace_exact<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ta, (uint32_t)total);
             RetireArgs ra; ra.verts = cloud->vertices; ra.normals = cloud->normals; ra.n = cloud->n; ra.num_blocks = nb;
             ra.rl = rl; ra.max_distance = max_distance;
+            ra.stats = d_stats;
+            if (hj) {
+                ra.obs = nullptr; ra.num_rows = nullptr; ra.max_rows = 0; ra.stride = 0;
+                if (hj->with_recon) k_retire_hist<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
+                else k_retire_hist<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
+                UAV_CUDA(cudaGetLastError());
+                v0 = v1;
+                continue;
+            }
             ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
-            ra.stride = (uint32_t)(obs->pitch / sizeof(float4)); ra.stats = d_stats;
+            ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
             if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
             else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
             UAV_CUDA(cudaGetLastError());
