@@ -2,6 +2,7 @@
 // GPU LBVH build, conversion into the 64-byte traversal layouts, export, batch trace.
 #include <cub/cub.cuh>
 
+#include <cuda_fp16.h>
 #include "common.cuh"
 #include "trace.cuh"
 
@@ -65,7 +66,7 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
         if (k < nk) {
             uint32_t ch = kids[k];
             for (int j = 0; j < 6; ++j) b[6 * k + j] = aabbs[6 * (size_t)ch + j];
-            if (flag[ch]) { ref[k] = slot[ch]; cnt[k] = 0u; }
+            if (flag[ch]) { ref[k] = slot[ch]; cnt[k] = 0x80000000u | slot[ch]; }
             else {   // leaf: cnt = ready-made deferred-leaf reference, ref = first triangle
                 uint4 cn = nodes[ch]; uint32_t c = cn.y - cn.x;
                 ref[k] = cn.x; cnt[k] = (cn.x << 6) | (c < 31u ? c : 31u);
@@ -74,7 +75,7 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
             // empty slot: a far-away point box that every ray surely misses (|t| ~ 1e18 / |d|),
             // flagged as "inner" so that no leaf logic ever looks at it
             for (int j = 0; j < 6; ++j) b[6 * k + j] = 1e18f;
-            ref[k] = 0u; cnt[k] = 0u;
+            ref[k] = 0u; cnt[k] = 0x80000000u;
         }
     }
     Node128 o;
@@ -82,6 +83,42 @@ __global__ void k_build_wide(const uint4 * __restrict__ nodes, const float * __r
     o.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
     o.cnt = make_uint4(cnt[0], cnt[1], cnt[2], cnt[3]);
     wide[slot[i]] = o;
+}
+
+// Node80 from Node128: centre of the union of the occupied children, outward-rounded fp16 offsets.
+__global__ void k_build_wide80(const Node128 * __restrict__ wide, uint32_t n, Node80 * __restrict__ out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Node128 nd = wide[i];
+    const float * q = reinterpret_cast<const float *>(nd.q);          // 24 floats, 6 per child
+    const uint32_t cnt[4] = {nd.cnt.x, nd.cnt.y, nd.cnt.z, nd.cnt.w};
+    float mn[3] = {UAV_INF, UAV_INF, UAV_INF}, mx[3] = {-UAV_INF, -UAV_INF, -UAV_INF};
+    bool occ[4];
+    for (int k = 0; k < 4; ++k) {
+        occ[k] = !(cnt[k] == 0x80000000u && q[6 * k] == 1e18f);       // empty slots: inner index 0 at 1e18
+        if (!occ[k]) continue;
+        for (int a = 0; a < 3; ++a) { mn[a] = fminf(mn[a], q[6 * k + a]); mx[a] = fmaxf(mx[a], q[6 * k + 3 + a]); }
+    }
+    float c[3];
+    for (int a = 0; a < 3; ++a) { c[a] = 0.5f * mn[a] + 0.5f * mx[a]; if (!(fabsf(c[a]) < 1e30f)) c[a] = 0.0f; }
+    __half h[24];
+    for (int k = 0; k < 4; ++k)
+        for (int a = 0; a < 3; ++a) {
+            if (occ[k]) {
+                h[6 * k + a] = __float2half_rd(__fsub_rd(q[6 * k + a], c[a]));
+                h[6 * k + 3 + a] = __float2half_ru(__fsub_ru(q[6 * k + 3 + a], c[a]));
+            } else {
+                h[6 * k + a] = __ushort_as_half((unsigned short)0x7c00);      // +inf: no segment reaches it
+                h[6 * k + 3 + a] = __ushort_as_half((unsigned short)0x7c00);
+            }
+        }
+    Node80 o;
+    o.c = make_float4(c[0], c[1], c[2], 0.0f);
+    const uint32_t * hw = reinterpret_cast<const uint32_t *>(h);
+    for (int j = 0; j < 3; ++j) o.h[j] = make_uint4(hw[4 * j], hw[4 * j + 1], hw[4 * j + 2], hw[4 * j + 3]);
+    o.cnt = nd.cnt;
+    out[i] = o;
 }
 
 // out[0] += violations of "every child box lies inside its parent's box and every leaf box is the
@@ -173,6 +210,18 @@ static int finalize_layout(uavmvs_bvh * b)
     }
     k_build_inner<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->inner);
     k_build_wide<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, flag, slot, n, b->wide);
+    {
+        const uint32_t ni = b->num_inner ? b->num_inner : 1;
+        UAV_CUDA(cudaMalloc(&b->wide80, sizeof(Node80) * (size_t)ni));
+        UAV_CUDA(cudaMemset(b->wide80, 0, sizeof(Node80) * (size_t)ni));
+        if (b->num_inner) k_build_wide80<<<divup(b->num_inner, 256), 256>>>(b->wide, b->num_inner, b->wide80);
+        float root[6];
+        UAV_CUDA(cudaMemcpy(root, b->aabbs, sizeof(root), cudaMemcpyDeviceToHost));
+        for (int a = 0; a < 3; ++a) {
+            float m = fmaxf(fabsf(root[a]), fabsf(root[3 + a]));
+            b->bound_abs[a] = (m == m && m < 1e30f) ? m : 1e30f;
+        }
+    }
     k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaDeviceSynchronize());
@@ -584,7 +633,7 @@ int uavmvs_bvh_destroy(uavmvs_bvh * b)
 {
     if (!b) return 0;
     cudaFree(b->nodes); cudaFree(b->aabbs); cudaFree(b->tris); cudaFree(b->indices);
-    cudaFree(b->inner); cudaFree(b->wide); cudaFree(b->ptris);
+    cudaFree(b->inner); cudaFree(b->wide); cudaFree(b->wide80); cudaFree(b->ptris);
     delete b;
     return 0;
 }

@@ -43,13 +43,22 @@ struct __align__(64) Node64 { float4 q0, q1, q2; uint4 q3; };
 // Four-child node, 128 B (one cache line): the up-to-four GRANDCHILDREN of a binary node (a leaf
 // child stays one child), boxes as the reference's exact floats.
 //   q[0..2] = boxes of children 0,1 (same packing as Node64 q0..q2), q[3..5] = children 2,3
-//   cnt[c]  = 0: inner child, ref[c] = its node index
-//   cnt[c] != 0: leaf child, cnt[c] = first_triangle << 6 | min(size, 31) (bit 5 is left free for
-//             the traversal's "box not verified" flag), ref[c] = first triangle
-//   empty slot: point box at 1e18 (no segment reaches it), ref = 0, cnt = 0
+//   cnt[c] bit 31 set: inner child, cnt[c] & 0x7fffffff = ref[c] = its node index
+//   cnt[c] bit 31 clear: leaf child, cnt[c] = first_triangle << 6 | min(size, 31) (bit 5 is left free
+//             for the traversal's "box not verified" flag; < 2^25 triangles), ref[c] = first triangle
+//   empty slot: point box at 1e18 (no segment reaches it), ref = 0, cnt = 0x80000000
+// The traversal kernels read q[0..5] and cnt only (7 of the 8 quads).
 // Every inner binary node owns one (indexed like Node64); a traversal that starts at the root only
 // ever touches those of even depth.
 struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
+// Four-child node for k_trace, 80 B = 5 quads (the traversal is bound by the L1 data pipe: every quad
+// read per node step costs ~0.24 ms on config 2): child boxes as fp16 OFFSETS from the node's centre c,
+// rounded outwards (minima down, maxima up), so the decoded box contains the exact one.  That is all the
+// traversal needs: inner boxes only have to be conservative, and a leaf reached through a conservative
+// box is re-checked against its exact box once one of its triangles is accepted (see k_trace).
+//   c = {cx, cy, cz, unused};  h[0..2] = 24 halves: child k -> mn.x mn.y mn.z mx.x mx.y mx.z at 6k..6k+5
+//   cnt as in Node128;  empty slot: all offsets +inf
+struct __align__(16) Node80 { float4 c; uint4 h[3]; uint4 cnt; };
 // Pre-reduced triangle, 64 B: a, ab, ac, unit normal (N/|N|), d00, d01, d11, denom.
 // All derived values are computed with the reference's operation order, so using them
 // gives bit-identical operands (libs/acc/primitives.h:214-248, :134-153).
@@ -67,6 +76,8 @@ struct uavmvs_bvh {
     // traversal layout
     uav::Node64 * inner;
     uav::Node128 * wide;
+    uav::Node80 * wide80;
+    float bound_abs[3];   // max |coordinate| of the root box per axis (error band of the fp16 node test)
     uav::Tri64 * ptris;
     uint32_t root_is_leaf, root_first, root_count;
     uint32_t nested;    // child boxes inside parent boxes, leaf boxes tight, leaves <= 31 triangles (checked at upload)

@@ -309,7 +309,7 @@ k_shaft(ShaftArgs a)
                 const Node128 * np = a.wide + cur;
                 const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
                 const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
-                const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
+                const uint4 cnt = __ldg(&np->cnt);
                 const bool h0 = shaft_hits(f, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
                 const bool h1 = shaft_hits(f, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
                 const bool h2 = shaft_hits(f, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
@@ -320,7 +320,7 @@ k_shaft(ShaftArgs a)
                 for (int c = 0; c < 4; ++c) {
                     const bool hc = c == 0 ? h0 : (c == 1 ? h1 : (c == 2 ? h2 : h3));
                     const uint32_t cc = c == 0 ? cnt.x : (c == 1 ? cnt.y : (c == 2 ? cnt.z : cnt.w));
-                    if (hc && cc && clear) {
+                    if (hc && (int)cc >= 0 && clear) {
                         const uint32_t first = cc >> 6, count = cc & 31u;
                         for (uint32_t i = 0; i < count && clear; ++i, ++tt)
                             clear = tri_cleared(a.tris + first + i, s_obb[w], px, py, pz, eps);
@@ -329,10 +329,10 @@ k_shaft(ShaftArgs a)
                 if (!clear) {
                     ok = false; done = true;              // no certificate
                 } else {
-                    if (h0 && !cnt.x) stack[sp++] = ref.x;
-                    if (h1 && !cnt.y) stack[sp++] = ref.y;
-                    if (h2 && !cnt.z) stack[sp++] = ref.z;
-                    if (h3 && !cnt.w) stack[sp++] = ref.w;
+                    if (h0 && (int)cnt.x < 0) stack[sp++] = cnt.x & 0x7fffffffu;
+                    if (h1 && (int)cnt.y < 0) stack[sp++] = cnt.y & 0x7fffffffu;
+                    if (h2 && (int)cnt.z < 0) stack[sp++] = cnt.z & 0x7fffffffu;
+                    if (h3 && (int)cnt.w < 0) stack[sp++] = cnt.w & 0x7fffffffu;
                     if (sp > 0) cur = stack[--sp]; else done = true;
                 }
             }
@@ -540,7 +540,7 @@ k_trace(TraceArgs a)
                 const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
                 if (mn > 1e-4f && mx < 2.0f && !a.bvh.root_is_leaf) {     // below: em would be uselessly wide
                     rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
-                    ray_fma_setup(rt);
+                    ray_fma_setup80(rt, a.bvh.bx, a.bvh.by, a.bvh.bz);
                     has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
                 } else {
                     // axis-parallel (or degenerate) ray, single-leaf tree: the reference walk, right away
@@ -560,32 +560,39 @@ k_trace(TraceArgs a)
         #pragma unroll 1
         for (int step = 0; step < K1_STEPS; ++step) {
             if (traversing && npend <= K1_PEND - 4) {
-                const Node128 * np = a.bvh.wide + cur;
-                const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
-                const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
-                const uint4 ref = __ldg(&np->ref), cnt = __ldg(&np->cnt);
-                const float g0 = slab_fma(rt, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-                const float g1 = slab_fma(rt, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
-                const float g2 = slab_fma(rt, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
-                const float g3 = slab_fma(rt, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
+                const Node80 * np = a.bvh.wide80 + cur;
+                const float4 c4 = __ldg(&np->c);
+                const uint4 ha = __ldg(&np->h[0]), hb = __ldg(&np->h[1]), hc = __ldg(&np->h[2]);
+                const uint4 cnt = __ldg(&np->cnt);
+                const float crx = __fmaf_rn(c4.x, rt.rdx, rt.nox), cry = __fmaf_rn(c4.y, rt.rdy, rt.noy), crz = __fmaf_rn(c4.z, rt.rdz, rt.noz);
+                #define UAV_H2(w) __half22float2(*reinterpret_cast<const __half2 *>(&(w)))
+                const float2 p0 = UAV_H2(ha.x), p1 = UAV_H2(ha.y), p2 = UAV_H2(ha.z), p3 = UAV_H2(ha.w);
+                const float2 p4 = UAV_H2(hb.x), p5 = UAV_H2(hb.y), p6 = UAV_H2(hb.z), p7 = UAV_H2(hb.w);
+                const float2 p8 = UAV_H2(hc.x), p9 = UAV_H2(hc.y), p10 = UAV_H2(hc.z), p11 = UAV_H2(hc.w);
+                #undef UAV_H2
+                const float g0 = slab_fma80(rt, crx, cry, crz, p0.x, p0.y, p1.x, p1.y, p2.x, p2.y);
+                const float g1 = slab_fma80(rt, crx, cry, crz, p3.x, p3.y, p4.x, p4.y, p5.x, p5.y);
+                const float g2 = slab_fma80(rt, crx, cry, crz, p6.x, p6.y, p7.x, p7.y, p8.x, p8.y);
+                const float g3 = slab_fma80(rt, crx, cry, crz, p9.x, p9.y, p10.x, p10.y, p11.x, p11.y);
                 const float m0 = rt.em, m1 = rt.em, m2 = rt.em, m3 = rt.em;
                 // visit unless surely missed; leaf children are deferred (any-hit is order independent)
                 // with the "box not verified" flag when the filtered test cannot prove the hit
                 const bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);
-                const bool f0 = h0 && cnt.x != 0u, f1 = h1 && cnt.y != 0u, f2 = h2 && cnt.z != 0u, f3 = h3 && cnt.w != 0u;
-                const bool i0 = h0 && cnt.x == 0u, i1 = h1 && cnt.y == 0u, i2 = h2 && cnt.z == 0u, i3 = h3 && cnt.w == 0u;
-                if (f0) { s_pend[npend][tid] = cnt.x | (g0 > m0 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.x); }
-                if (f1) { s_pend[npend][tid] = cnt.y | (g1 > m1 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.y); }
-                if (f2) { s_pend[npend][tid] = cnt.z | (g2 > m2 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.z); }
-                if (f3) { s_pend[npend][tid] = cnt.w | (g3 > m3 ? 0u : 32u); ++npend; prefetch_l2(a.bvh.tris + ref.w); }
+                const bool f0 = h0 && (int)cnt.x >= 0, f1 = h1 && (int)cnt.y >= 0, f2 = h2 && (int)cnt.z >= 0, f3 = h3 && (int)cnt.w >= 0;
+                const bool i0 = h0 && (int)cnt.x < 0, i1 = h1 && (int)cnt.y < 0, i2 = h2 && (int)cnt.z < 0, i3 = h3 && (int)cnt.w < 0;
+                const uint4 ref = make_uint4(cnt.x & 0x7fffffffu, cnt.y & 0x7fffffffu, cnt.z & 0x7fffffffu, cnt.w & 0x7fffffffu);
+                if (f0) { s_pend[npend][tid] = cnt.x | 32u; ++npend; }
+                if (f1) { s_pend[npend][tid] = cnt.y | 32u; ++npend; }
+                if (f2) { s_pend[npend][tid] = cnt.z | 32u; ++npend; }
+                if (f3) { s_pend[npend][tid] = cnt.w | 32u; ++npend; }
                 // inner children: one is visited next, the others go on the stack (and are prefetched:
                 // on a visible ray every pushed node is popped later)
                 uint32_t nxt = i0 ? ref.x : UAV_NAI;
-                if (i1 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
+                if (i1 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide80 + nxt); }
                 if (i1) nxt = ref.y;
-                if (i2 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
+                if (i2 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide80 + nxt); }
                 if (i2) nxt = ref.z;
-                if (i3 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide + nxt); }
+                if (i3 && nxt != UAV_NAI) { stack[sp++] = nxt; prefetch_l2(a.bvh.wide80 + nxt); }
                 if (i3) nxt = ref.w;
                 if (nxt == UAV_NAI) {
                     if (sp > 0) nxt = stack[--sp]; else traversing = false;
@@ -855,7 +862,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     UAV_REQUIRE(bvh && cloud && (obs || hj), "null handle");
     UAV_REQUIRE(hj || obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
     if (hj) { width = 0; height = 0; }                   // bare positions: no image test anywhere
-    UAV_REQUIRE(bvh->num_tris < (1u << 26), "more than 2^26 triangles");
+    UAV_REQUIRE(bvh->num_tris < (1u << 25), "more than 2^25 triangles");
     if (num_views == 0) return 0;
     K1Scratch & k = g_k1;
     const uint32_t nb = cloud->num_blocks;

@@ -9,6 +9,7 @@
 // stacked); trace_closest() keeps the reference's near-first order and its shrinking
 // tmax because those decide which slack-zone hit wins.
 #pragma once
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace uav {
@@ -16,6 +17,8 @@ namespace uav {
 struct BvhView {
     const Node64 * __restrict__ inner;
     const Node128 * __restrict__ wide;
+    const Node80 * __restrict__ wide80;
+    float bx, by, bz;                         // max |coordinate| of the scene per axis
     const Tri64 * __restrict__ tris;
     const float * __restrict__ raw_tris;     // 9 floats per triangle, leaf order (reference layout)
     const uint32_t * __restrict__ indices;
@@ -24,7 +27,8 @@ struct BvhView {
 
 __host__ inline BvhView view_of(const uavmvs_bvh * b) {
     BvhView v;
-    v.inner = b->inner; v.wide = b->wide; v.tris = b->ptris; v.raw_tris = b->tris; v.indices = b->indices;
+    v.inner = b->inner; v.wide = b->wide; v.wide80 = b->wide80;
+    v.bx = b->bound_abs[0]; v.by = b->bound_abs[1]; v.bz = b->bound_abs[2]; v.tris = b->ptris; v.raw_tris = b->tris; v.indices = b->indices;
     v.root_is_leaf = b->root_is_leaf; v.root_first = b->root_first; v.root_count = b->root_count;
     return v;
 }
@@ -293,6 +297,30 @@ __device__ __forceinline__ void ray_fma_setup(RayT & f)
     const float ax = f.ox * f.rdx, ay = f.oy * f.rdy, az = f.oz * f.rdz;
     f.nox = -ax; f.noy = -ay; f.noz = -az;
     f.em = 2.4e-7f * (fabsf(ax) + fabsf(ay) + fabsf(az)) + 4e-6f * f.tmax;
+}
+
+// Node80 variant: the plane is c + off (off = outward-rounded fp16 offset), t~ = fma(off, rd, cr) with
+// cr = fma(c, rd, -(o rd)) once per node and axis.  cr carries the rounding of o rd and its own, both
+// <= 2^-24 (|o_k| + |c_k|) |rd_k| with |c_k| <= B_k = max |coordinate| of the scene on axis k, so the
+// per-ray band is  em80 = 4.8e-7 sum_k (|o_k| + B_k) |rd_k| + 4e-6 ray.tmax  (same argument as above).
+// The decoded box CONTAINS the exact one, so only "g < -em80 => the reference rejects" is ever used.
+__device__ __forceinline__ void ray_fma_setup80(RayT & f, float bx, float by, float bz)
+{
+    const float ax = f.ox * f.rdx, ay = f.oy * f.rdy, az = f.oz * f.rdz;
+    f.nox = -ax; f.noy = -ay; f.noz = -az;
+    f.em = 4.8e-7f * ((fabsf(f.ox) + bx) * fabsf(f.rdx) + (fabsf(f.oy) + by) * fabsf(f.rdy) + (fabsf(f.oz) + bz) * fabsf(f.rdz))
+        + 4e-6f * f.tmax;
+}
+
+__device__ __forceinline__ float slab_fma80(const RayT & f, float crx, float cry, float crz,
+    float mnx, float mny, float mnz, float mxx, float mxy, float mxz)
+{
+    const float ax = __fmaf_rn(mnx, f.rdx, crx), bx = __fmaf_rn(mxx, f.rdx, crx);
+    const float ay = __fmaf_rn(mny, f.rdy, cry), by = __fmaf_rn(mxy, f.rdy, cry);
+    const float az = __fmaf_rn(mnz, f.rdz, crz), bz = __fmaf_rn(mxz, f.rdz, crz);
+    const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), f.tmin));
+    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), f.tmax));
+    return tmax - tmin;
 }
 
 __device__ __forceinline__ float slab_fma(const RayT & f, float mnx, float mny, float mnz,
