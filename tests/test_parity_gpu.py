@@ -331,6 +331,25 @@ def test_axis_parallel_rays_and_flat_boxes(api, oracle):
     assert np.array_equal(rows, obs_o.num_rows)
 
 
+@pytest.mark.parametrize("tau", ["4", "32"])
+def test_packet_entry_points_opt_in_is_bit_exact(api, oracle, tau, monkeypatch):
+    """UAVMVS_ENTRY=1: rays start from their packet's frontier of wide nodes (k_entry) instead of the root."""
+    from uavmvs_b200 import scenes
+    sc = scenes.dense()
+    monkeypatch.setenv("UAVMVS_ENTRY", "1")
+    monkeypatch.setenv("UAVMVS_ENTRY_TAU", tau)
+    gbvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+    nodes, aabbs, tris, indices = gbvh.export()
+    obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    obs_o, state, _ = _run_oracle_eval(oracle, obvh, sc)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
 @pytest.mark.parametrize("scene_name", ["tiny", "dense"])
 def test_visibility_shafts_opt_in_is_bit_exact(api, oracle, scene_name, monkeypatch):
     """UAVMVS_SHAFTS=1: (block, view) packets certified visible by the shaft pass skip the per-ray

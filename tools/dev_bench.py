@@ -42,11 +42,13 @@ dviews = api.DeviceViews(sc.views28())
 stream = torch.cuda.current_stream()
 for it in range(args.iters):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); t_w = time.perf_counter()
     e0.record(stream)
     s, mn, mx, st = api.evaluate_trajectory(dviews, sc.max_distance, sc.target_recon, sc.width, sc.height,
                                             bvh, cloud, obs, recons, wrecons, stream=stream)
     e1.record(stream)
     torch.cuda.synchronize()
+    print("wall %.2f ms" % ((time.perf_counter() - t_w) * 1e3))
     ms = e0.elapsed_time(e1)
     print("stages", ["%.3f" % x for x in api.profile_last()], "k1 counters [packets, certified, rays certified, rays traced]", api.k1_counters())
     print("iter %d: %.2f ms  rays %d vis %d pairs %d after_block_cull %d  -> %.3f Grays/s %.2f Gpairs/s score %.5f" % (

@@ -362,6 +362,141 @@ k_shaft(ShaftArgs a)
     }
 }
 
+// ---- packet entry points ----------------------------------------------------------------------
+// The rays of one (block, view) packet all lie in the packet's shaft (see above), and they all walk
+// the same upper levels of the tree.  k_entry walks those levels ONCE per packet with the shaft and
+// records the frontier: a short list of wide nodes whose subtrees contain every leaf box the shaft
+// touches.  A ray of the packet then starts with that list on its stack instead of the root.  The
+// answer is unchanged: on a nested tree the reference's result is  OR over leaves (leaf box passes
+// the exact slab test AND a triangle is accepted); a leaf whose box passes for some ray of the packet
+// is touched by the shaft, so are all its ancestors, hence the walk below either emits one of them
+// or reaches the leaf's parent, which is emitted itself.  Subtrees outside the shaft hold no such leaf.
+//   rule: a touched inner child whose box is at most `tau` long is emitted, a longer one is expanded;
+//   a node with a touched LEAF child is emitted as a whole; more than ENTRY_MAX entries or ENTRY_STEPS
+//   expansions: the packet falls back to {root}.
+constexpr int ENTRY_MAX = 15;          // entries per packet; record = 16 words: count, entries
+constexpr int ENTRY_STEPS = 48;
+constexpr int ENTRY_STACK = 48;
+
+struct EntryArgs {
+    const Node128 * __restrict__ wide;
+    const float4 * __restrict__ lo; const float4 * __restrict__ hi;
+    uint32_t num_blocks;
+    const float * __restrict__ views; uint32_t num_views, v0, v1;
+    const uint32_t * __restrict__ masks;
+    const uint32_t * __restrict__ off;       // exclusive scan of 32 x candidate views: off[b] / 32 = first packet of block b
+    uint32_t * fr;                           // [packets][16]
+    float tau;
+    unsigned long long * counters;           // [4] += frontier entries, [5] += packets that fell back to the root
+};
+
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_entry(EntryArgs a)
+{
+    __shared__ uint32_t s_q[K1_WARPS][64];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk >= a.num_blocks) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const float4 lo = __ldg(a.lo + blk), hi = __ldg(a.hi + blk);
+    const uint32_t * mrow = a.masks + (size_t)(blk >> 5) * a.num_views;
+    const uint32_t mbit = blk & 31;
+    const uint32_t pk0 = __ldg(a.off + blk) >> 5;
+    uint32_t stack[ENTRY_STACK];
+    uint32_t qn = 0, pdone = 0;
+    unsigned long long n_entries = 0, n_fallback = 0;
+    for (uint32_t c0 = a.v0; c0 < a.v1 || qn > 0; c0 += 32) {
+        if (c0 < a.v1) {
+            const uint32_t vi = c0 + lane;
+            const bool cand = vi < a.v1 && ((__ldg(mrow + vi) >> mbit) & 1u);
+            const uint32_t m = __ballot_sync(0xffffffffu, cand);
+            if (cand) s_q[w][qn + __popc(m & lt_mask)] = vi;
+            qn += __popc(m);
+            __syncwarp();
+            if (qn < 32 && c0 + 32 < a.v1) continue;
+        }
+        const uint32_t take = min(qn, 32u);
+        if (take == 0) continue;
+        const bool active = lane < take;
+        const uint32_t v = s_q[w][active ? lane : 0];
+        const float * vp = a.views + (size_t)v * UAVMVS_VIEW_FLOATS;
+        const float px = __ldg(vp), py = __ldg(vp + 1), pz = __ldg(vp + 2);
+        Shaft f;
+        {
+            float M = fmaxf(fmaxf(fabsf(px), fabsf(py)), fabsf(pz));
+            M = fmaxf(M, fmaxf(fmaxf(fabsf(lo.x), fabsf(lo.y)), fabsf(lo.z)));
+            M = fmaxf(M, fmaxf(fmaxf(fabsf(hi.x), fabsf(hi.y)), fabsf(hi.z)));
+            const float eps = 2e-6f * M + 1.4e-5f;
+            f.lx = lo.x - eps; f.ly = lo.y - eps; f.lz = lo.z - eps;
+            f.hx = hi.x + eps; f.hy = hi.y + eps; f.hz = hi.z + eps;
+            const float ux = clamp_away(px - lo.x), uy = clamp_away(py - lo.y), uz = clamp_away(pz - lo.z);
+            const float wx = clamp_away(px - hi.x), wy = clamp_away(py - hi.y), wz = clamp_away(pz - hi.z);
+            f.rux = 1.0f / ux; f.ruy = 1.0f / uy; f.ruz = 1.0f / uz;
+            f.rwx = 1.0f / wx; f.rwy = 1.0f / wy; f.rwz = 1.0f / wz;
+            f.upx = ux > 0.0f; f.upy = uy > 0.0f; f.upz = uz > 0.0f;
+            f.wpx = wx > 0.0f; f.wpy = wy > 0.0f; f.wpz = wz > 0.0f;
+        }
+        uint32_t * rec = a.fr + ((size_t)(pk0 + pdone + lane) << 4);
+        bool fallback = active && !(fabsf(px + py + pz) < 1e30f);
+        bool done = !active || fallback;
+        uint32_t cur = 0, nout = 0, steps = 0; int sp = 0;
+        while (__any_sync(0xffffffffu, !done)) {
+            if (!done) {
+                const Node128 * np = a.wide + cur;
+                const float4 q0 = __ldg(&np->q[0]), q1 = __ldg(&np->q[1]), q2 = __ldg(&np->q[2]);
+                const float4 q3 = __ldg(&np->q[3]), q4 = __ldg(&np->q[4]), q5 = __ldg(&np->q[5]);
+                const uint4 cnt = __ldg(&np->cnt);
+                const bool h0 = shaft_hits(f, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                const bool h1 = shaft_hits(f, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+                const bool h2 = shaft_hits(f, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y);
+                const bool h3 = shaft_hits(f, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w);
+                const bool leaf_hit = (h0 && (int)cnt.x >= 0) || (h1 && (int)cnt.y >= 0) || (h2 && (int)cnt.z >= 0) || (h3 && (int)cnt.w >= 0);
+                if (leaf_hit) {
+                    if (nout < ENTRY_MAX) rec[1 + nout] = cur;
+                    ++nout;
+                } else {
+                    const float e0 = fmaxf(fmaxf(q0.w - q0.x, q1.x - q0.y), q1.y - q0.z);
+                    const float e1 = fmaxf(fmaxf(q2.y - q1.z, q2.z - q1.w), q2.w - q2.x);
+                    const float e2 = fmaxf(fmaxf(q3.w - q3.x, q4.x - q3.y), q4.y - q3.z);
+                    const float e3 = fmaxf(fmaxf(q5.y - q4.z, q5.z - q4.w), q5.w - q5.x);
+                    #pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const bool hc = c == 0 ? h0 : (c == 1 ? h1 : (c == 2 ? h2 : h3));
+                        const uint32_t cc = (c == 0 ? cnt.x : (c == 1 ? cnt.y : (c == 2 ? cnt.z : cnt.w))) & 0x7fffffffu;
+                        const float ec = c == 0 ? e0 : (c == 1 ? e1 : (c == 2 ? e2 : e3));
+                        if (hc) {
+                            if (ec <= a.tau) { if (nout < ENTRY_MAX) rec[1 + nout] = cc; ++nout; }
+                            else if (sp < ENTRY_STACK) stack[sp++] = cc;
+                            else nout = ENTRY_MAX + 1;
+                        }
+                    }
+                }
+                ++steps;
+                if (nout > ENTRY_MAX || steps > ENTRY_STEPS) { fallback = true; done = true; }
+                else if (sp > 0) cur = stack[--sp];
+                else done = true;
+            }
+        }
+        if (active) {
+            if (fallback) { rec[0] = 1u; rec[1] = 0u; ++n_fallback; n_entries += 1; }
+            else { rec[0] = nout; n_entries += nout; }
+        }
+        __syncwarp();
+        const uint32_t rest = qn - take;
+        const uint32_t carry = lane < rest ? s_q[w][32 + lane] : 0u;
+        __syncwarp();
+        if (lane < rest) s_q[w][lane] = carry;
+        qn = rest; pdone += take;
+        __syncwarp();
+    }
+    if (a.counters) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_entries += __shfl_xor_sync(0xffffffffu, n_entries, o); n_fallback += __shfl_xor_sync(0xffffffffu, n_fallback, o);
+        }
+        if (lane == 0 && n_entries) { atomicAdd(a.counters + 4, n_entries); atomicAdd(a.counters + 5, n_fallback); }
+    }
+}
+
 struct RayList {
     float4 * dirl;        // every ray, (view, point) order per block: unit point->camera direction, w = distance l
     uint8_t * vis;        // every ray: (point's index within its block) << 2 | status: 1 occluded, 2 visible
@@ -371,6 +506,8 @@ struct RayList {
     uint32_t * cnt;       // [num_blocks] rays in the slice
     uint32_t * tcnt;      // [num_blocks] rays of the slice that have to be traced
     uint32_t * rview;     // histogram jobs only: view (candidate position) index of every ray
+    uint32_t * tpk;       // packet (block, candidate view) of every ray that has to be traced; NULL: entry points off
+    const uint32_t * fr;  // [packets][16] entry points of k_entry: count, wide-node indices
 };
 
 // Exact cull (kernels.cu:153-167) + ray set-up values (:54-58).  One warp per block, views in
@@ -392,6 +529,7 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
     const uint32_t mbit = blk & 31;
     const uint32_t base = rl.off[blk];
+    uint32_t packet = base >> 5;                           // caps are 32 x candidate views: same numbering as k_entry
     uint32_t count = 0, tcount = 0;
     for (uint32_t c0 = v0; c0 < v1; c0 += 32) {
         uint32_t vi = c0 + lane;
@@ -433,8 +571,10 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
                     const uint32_t j = base + tcount + r;
                     __stcs(rl.tdir + j, d4);
                     __stcs(rl.torg + j, make_float4(v.x, v.y, v.z, __uint_as_float(idx << 5 | lane)));
+                    if (rl.tpk) rl.tpk[j] = packet;
                 }
             }
+            ++packet;
             count += __popc(m);
             if (!certified) tcount += __popc(m);
         }
@@ -528,6 +668,7 @@ k_trace(TraceArgs a)
                 pos += take; given += take;
             }
             if (mine) {
+                const uint32_t slot = idx;
                 const float4 d4 = __ldcs(a.rl.tdir + idx);             // streamed once: keep L2 for the tree
                 const float4 o4 = __ldcs(a.rl.torg + idx);
                 const V3 o = ld3(o4);
@@ -542,6 +683,12 @@ k_trace(TraceArgs a)
                     rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
                     ray_fma_setup80(rt, a.bvh.bx, a.bvh.by, a.bvh.bz);
                     has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
+                    if (a.rl.tpk) {                                      // start from the packet's entry points
+                        const uint32_t * rec = a.rl.fr + ((size_t)__ldg(a.rl.tpk + slot) << 4);
+                        const uint32_t ne = __ldg(rec);
+                        for (uint32_t e = 1; e <= ne; ++e) stack[sp++] = __ldg(rec + e);
+                        if (sp > 0) cur = stack[--sp]; else traversing = false;
+                    }
                 } else {
                     // axis-parallel (or degenerate) ray, single-leaf tree: the reference walk, right away
                     bool h = trace_any_exact(a.bvh, o.x, o.y, o.z, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
@@ -815,6 +962,8 @@ struct K1Scratch {
     float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
     uint32_t * tcnt = nullptr;
     uint32_t * rview = nullptr; size_t rview_cap = 0;
+    uint32_t * tpk = nullptr; size_t tpk_cap = 0;
+    uint32_t * fr = nullptr; size_t fr_cap = 0;
     uint32_t * cert = nullptr; size_t cert_cap = 0;
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
@@ -840,6 +989,11 @@ static bool shafts_enabled()
     const char * e = getenv("UAVMVS_SHAFTS");
     return e && e[0] == '1';
 }
+
+// Packet entry points (k_entry): opt-in (UAVMVS_ENTRY=1).  Measured on config 2 (profiles/r01_c_shafts.txt):
+// k_trace 3.4 -> 2.9 ms, but k_entry itself costs 0.8 ms (tau 32) to 1.1 ms (tau 8): a net loss.
+static bool entry_enabled() { const char * e = getenv("UAVMVS_ENTRY"); return e && e[0] == '1'; }
+static float entry_tau() { const char * e = getenv("UAVMVS_ENTRY_TAU"); return e ? (float)atof(e) : 32.0f; }
 
 static size_t ray_budget()
 {
@@ -878,6 +1032,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         UAV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_trace, K1_WARPS * 32, 0));
         occ_b = occ_a;
         int occ = occ_a < occ_b ? occ_a : occ_b;
+        { const char * e = getenv("UAVMVS_TRACE_CTAS"); if (e && atoi(e) > 0 && atoi(e) < occ) occ = atoi(e); }   // dev: leave room for co-running kernels
         k.grid_trace = sms * (occ > 0 ? occ : 1);
     }
     if (grow(&k.masks, &k.masks_cap, (size_t)cloud->num_super * num_views, s)) return 1;
@@ -925,7 +1080,15 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
             if (hj && grow(&k.rview, &k.rview_cap, k.rays_cap, s)) return 1;
-            RayList rl; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
+            const bool entry = entry_enabled() && bvh->nested && !bvh->root_is_leaf;
+            if (entry) {
+                if (grow(&k.tpk, &k.tpk_cap, k.rays_cap, s) || grow(&k.fr, &k.fr_cap, (size_t)(total / 32 + 1) * 16, s)) return 1;
+                EntryArgs ea; ea.wide = bvh->wide; ea.lo = cloud->block_lo; ea.hi = cloud->block_hi; ea.num_blocks = nb;
+                ea.views = d_views; ea.num_views = num_views; ea.v0 = v0; ea.v1 = v1; ea.masks = k.masks; ea.off = k.off;
+                ea.fr = k.fr; ea.tau = entry_tau(); ea.counters = k.counters;
+                k_entry<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ea);
+            }
+            RayList rl; rl.tpk = entry ? k.tpk : nullptr; rl.fr = k.fr; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
             // shafts: whole (block, view) packets proven visible without tracing (nested trees only)
             const uint32_t nchunks = divup(v1 - v0, 32);
             const bool shafts = shafts_enabled() && bvh->nested && !bvh->root_is_leaf;
@@ -979,7 +1142,7 @@ int k1_counters(unsigned long long out[4], int reset)
     if (getenv("UAVMVS_SHAFT_DEBUG")) {
         unsigned long long d[8];
         UAV_CUDA(cudaMemcpy(d, k.counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-        fprintf(stderr, "[shaft] node steps: certified %llu failed %llu, triangle tests %llu\n", d[4], d[5], d[6]);
+        fprintf(stderr, "[k1] counters 4..6: %llu %llu %llu (entry: frontier entries, root fallbacks; shaft: steps ok / failed, triangle tests)\n", d[4], d[5], d[6]);
     }
     if (reset) UAV_CUDA(cudaMemset(k.counters, 0, 8 * sizeof(unsigned long long)));
     return 0;
