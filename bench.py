@@ -224,7 +224,7 @@ def run_reference(a, rank, world):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------- B200 arm
@@ -386,12 +386,32 @@ def run_b200(a, rank, local_rank, world):
             "sample": "%d of %d views (evenly strided) x all %d points, %.1f s; tree: %s (%.2f s, not timed); kernel "
                       "math: oracle port of libs/eval/kernels.cu, OpenMP over points" %
                       (len(vidx), V, n_local, r["seconds"], built_by, tree_s)}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def guard_stdout():
+    """Keep stdout to the ONE JSON line: libraries (NCCL prints its version banner to stdout) get
+    stderr; the returned file object is the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w")
+    return real
+
+
+OUT = None
+
+
+def emit(line):
+    OUT.write(json.dumps(line) + "\n")
+    OUT.flush()
+
+
 def main():
+    global OUT
+    OUT = guard_stdout()
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -233,6 +233,32 @@ inline void evaluate_spherical_histogram(cacc::Stream stream, cacc::Mat3f calib,
     cacc::Image<float, cacc::DEVICE>::Data hist) {
     UAVMVS_CHECK(uavmvs_evaluate_spherical_histogram(stream, calib.m, width, height, kd_tree.h, sphere_hist.h, hist.h));
 }
+/* Batched forms (no reference counterpart: they replace the per-candidate launch loops of
+ * apps/generate_guidance_volume/generate_guidance_volume.cu:236-253 and
+ * apps/optimize_trajectory/optimize_trajectory.cu:388-428).  positions: host [n][3]; sphere_hists: [n][bins]. */
+inline void populate_spherical_histogram_batch(cacc::Stream stream, const float * positions, uint32_t n,
+    float max_distance, cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, cacc::PointCloud<cacc::DEVICE>::Data cloud,
+    cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::Array<float, cacc::DEVICE>::Data sphere_hists) {
+    UAVMVS_CHECK(uavmvs_populate_spherical_histogram_batch(stream, positions, n, max_distance, 0.0f, bvh_tree.h, cloud.h,
+        kd_tree.h, nullptr, nullptr, sphere_hists.h));
+}
+inline void populate_spherical_histogram_batch(cacc::Stream stream, const float * positions, uint32_t n,
+    float max_distance, float target_recon, cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree,
+    cacc::PointCloud<cacc::DEVICE>::Data cloud, cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree,
+    cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays, cacc::Array<float, cacc::DEVICE>::Data recons,
+    cacc::Array<float, cacc::DEVICE>::Data sphere_hists) {
+    UAVMVS_CHECK(uavmvs_populate_spherical_histogram_batch(stream, positions, n, max_distance, target_recon, bvh_tree.h,
+        cloud.h, kd_tree.h, obs_rays.h, recons.h, sphere_hists.h));
+}
+/* images may be a null Data ({nullptr}); h_* are host arrays of n entries or nullptr */
+inline void evaluate_spherical_histogram_batch(cacc::Stream stream, cacc::Mat3f calib, int width, int height,
+    cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::Array<float, cacc::DEVICE>::Data sphere_hists, uint32_t n,
+    uint32_t image_width, uint32_t image_height, cacc::Array<float, cacc::DEVICE>::Data images,
+    float * h_min, uint32_t * h_argmin, float * h_max, uint32_t * h_argmax) {
+    UAVMVS_CHECK(uavmvs_evaluate_spherical_histogram_batch(stream, calib.m, width, height,
+        const_cast<uavmvs_kdtree *>(kd_tree.h), sphere_hists.h, n, image_width, image_height, images.h,
+        h_min, h_argmin, h_max, h_argmax));
+}
 inline void estimate_capture_difficulty(cacc::Stream stream, float max_distance,
     cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, uint32_t mesh_size, cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree,
     cacc::PointCloud<cacc::DEVICE>::Data cloud) {

@@ -531,10 +531,16 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     const uint32_t base = rl.off[blk];
     uint32_t packet = base >> 5;                           // caps are 32 x candidate views: same numbering as k_entry
     uint32_t count = 0, tcount = 0;
-    for (uint32_t c0 = v0; c0 < v1; c0 += 32) {
-        uint32_t vi = c0 + lane;
-        uint32_t mw = vi < v1 ? __ldg(mrow + vi) : 0u;
-        uint32_t word = __ballot_sync(0xffffffffu, (mw >> mbit) & 1u);
+    for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
+      // four mask words per lane in flight: the scan of the block's row is latency bound otherwise
+      uint32_t mw4[4];
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) { const uint32_t vi = g0 + 32 * u + lane; mw4[u] = vi < v1 ? __ldg(mrow + vi) : 0u; }
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t c0 = g0 + 32 * u;
+        if (c0 >= v1) break;
+        uint32_t word = __ballot_sync(0xffffffffu, (mw4[u] >> mbit) & 1u);
         const uint32_t cword = cert ? __ldg(cert + (size_t)blk * nchunks + ((c0 - v0) >> 5)) : 0u;
         while (word) {
             const uint32_t kb = __ffs(word) - 1;
@@ -578,6 +584,7 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
             count += __popc(m);
             if (!certified) tcount += __popc(m);
         }
+      }
     }
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = tcount;
