@@ -1006,13 +1006,10 @@ static size_t ray_budget()
 {
     // upper bound of ray records (24 B + 1 B each) kept at a time; views are processed in
     // batches when a whole trajectory would need more
-    static size_t v = 0;
-    if (!v) {
-        const char * e = getenv("UAVMVS_RAY_BUDGET");
-        v = e ? (size_t)strtoull(e, nullptr, 10) : ((size_t)1 << 27);
-        if (v < 1024) v = 1024;
-        if (v > ((size_t)1 << 27)) v = (size_t)1 << 27;      // ray index << 5 | lane must fit 32 bits
-    }
+    const char * e = getenv("UAVMVS_RAY_BUDGET");             // read at every call (tests shrink it)
+    size_t v = e ? (size_t)strtoull(e, nullptr, 10) : ((size_t)1 << 27);
+    if (v < 1024) v = 1024;
+    if (v > ((size_t)1 << 27)) v = (size_t)1 << 27;          // ray index << 5 | lane must fit 32 bits
     return v;
 }
 
