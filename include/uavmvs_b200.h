@@ -62,6 +62,14 @@ int uavmvs_bvh_destroy(uavmvs_bvh * bvh);
 int uavmvs_bvh_trace(void * stream, const uavmvs_bvh * bvh, const float * rays, uint64_t num_rays,
     int any_hit, uint8_t * hit, uint32_t * face, float * t);
 
+/* Closest point on the mesh for num_points HOST queries [n][3]: acc::BVHTree::closest_point(vertex, &cp,
+ * max_dist), libs/acc/bvh_tree.h:492-548 (the optimiser's airspace test, apps/optimize_trajectory/
+ * optimize_trajectory.cu:370-386, :456).  found[i] = 1 iff a triangle lies closer than max_dist (pass INFINITY
+ * for none); tri_index[i] = its index in LEAF ORDER (acc's cp.first, the argument of get_triangle) or
+ * 0xffffffff; closest[i] = the point.  Bit-identical to the reference on the same tree.  Synchronises. */
+int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, const float * points, uint64_t num_points,
+    float max_dist, uint8_t * found, uint32_t * tri_index, float * closest);
+
 /* ---- KD-tree: cacc::KDTree<3,DEVICE>::create(acc_kd), libs/cacc/kd_tree.h:150-154,
  * libs/cacc/kd_tree.cu:15-45.  nodes[4n] = {vid,dim,left,right}, verts[3n]. */
 int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t num_nodes, uavmvs_kdtree ** out);

@@ -36,7 +36,9 @@ def build(force=False):
     if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     ref_so = os.path.join(_HERE, "_ref", "libref_acc.so")
-    if os.path.isdir("/root/reference/libs/acc") and (force or not os.path.exists(ref_so)):
+    shim = os.path.join(_HERE, "ref_shim", "ref_acc.cpp")
+    if os.path.isdir("/root/reference/libs/acc") and (force or not os.path.exists(ref_so)
+                                                      or os.path.getmtime(ref_so) < os.path.getmtime(shim)):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
 
 
@@ -72,6 +74,7 @@ def lib():
     L.orc_bvh_destroy.argtypes = [_vp]
     L.orc_bvh_intersect.argtypes = [_vp, _f32p, u64, i32, _opt(_u8p), _opt(_u32p), _opt(_f32p), _opt(_u64p)]
     L.orc_kd_build.restype = _vp
+    L.orc_bvh_closest_point.argtypes = [_vp, _f32p, u64, f32, _u8p, _u32p, _f32p]
     L.orc_kd_build.argtypes = [_f32p, u32]
     L.orc_kd_from_arrays.restype = _vp
     L.orc_kd_from_arrays.argtypes = [_u32p, _f32p, u32, u32]
@@ -119,6 +122,7 @@ def ref():
     R.ref_bvh_num_tris.argtypes = [_vp]
     R.ref_bvh_export.argtypes = [_vp, _u32p, _f32p, _f32p, _u32p]
     R.ref_bvh_intersect.argtypes = [_vp, _f32p, u64, _opt(_u8p), _opt(_u32p), _opt(_f32p)]
+    R.ref_bvh_closest_point.argtypes = [_vp, _f32p, u64, C.c_float, _u8p, _u32p, _f32p]
     R.ref_bvh_destroy.argtypes = [_vp]
     R.ref_kd_build.restype = _vp
     R.ref_kd_build.argtypes = [_f32p, u32, i32]
@@ -180,6 +184,14 @@ class BVH:
         L.orc_bvh_export(self.h, nodes, aabbs, tris, idx)
         return TreeArrays(nodes, aabbs, tris, idx)
 
+    def closest_point(self, points, max_dist=float("inf")):
+        """acc::BVHTree::closest_point (libs/acc/bvh_tree.h:492-548): found, leaf-order triangle index, point."""
+        pts = _c(points, np.float32).reshape(-1, 3)
+        n = pts.shape[0]
+        found, idx, cp = np.empty(n, np.uint8), np.empty(n, np.uint32), np.empty((n, 3), np.float32)
+        lib().orc_bvh_closest_point(self.h, pts, n, max_dist, found, idx, cp)
+        return found, idx, cp
+
     def intersect(self, rays, any_hit=True, counters=False):
         rays = _c(rays, np.float32).reshape(-1, 8)
         n = rays.shape[0]
@@ -216,6 +228,13 @@ class RefBVH:
         idx = np.empty(t, np.uint32)
         R.ref_bvh_export(self.h, nodes, aabbs, tris, idx)
         return TreeArrays(nodes, aabbs, tris, idx)
+
+    def closest_point(self, points, max_dist=float("inf")):
+        pts = _c(points, np.float32).reshape(-1, 3)
+        n = pts.shape[0]
+        found, idx, cp = np.empty(n, np.uint8), np.empty(n, np.uint32), np.empty((n, 3), np.float32)
+        ref().ref_bvh_closest_point(self.h, pts, n, max_dist, found, idx, cp)
+        return found, idx, cp
 
     def intersect(self, rays):
         rays = _c(rays, np.float32).reshape(-1, 8)

@@ -134,6 +134,21 @@ void ref_bvh_intersect(void * hp, float const * rays, uint64_t num_rays,
     }
 }
 
+/* acc::BVHTree::closest_point(vertex, &cp, max_dist), libs/acc/bvh_tree.h:492-548 */
+void ref_bvh_closest_point(void * hp, float const * points, uint64_t n, float max_dist,
+    uint8_t * found, uint32_t * idx, float * cp)
+{
+    RefBVH const & tree = *((RefBVHHandle *)hp)->tree;
+    #pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < (int64_t)n; ++i) {
+        std::pair<unsigned, math::Vec3f> r;
+        r.first = 0xffffffffu; r.second = math::Vec3f(0.0f);
+        bool f = tree.closest_point(math::Vec3f(points + 3 * i), &r, max_dist);
+        found[i] = f ? 1 : 0; idx[i] = f ? r.first : 0xffffffffu;
+        for (int k = 0; k < 3; ++k) cp[3 * i + k] = f ? r.second[k] : 0.0f;
+    }
+}
+
 void ref_bvh_destroy(void * hp) { delete (RefBVHHandle *)hp; }
 
 void * ref_kd_build(float const * verts, uint32_t num_verts, int threads)

@@ -373,6 +373,97 @@ inline bool hit_tri(Ray const & ray, float const * t9, float * t_out)
     return true;
 }
 
+
+/* ------------------------------------------------------------------ */
+/* closest point: libs/acc/primitives.h:155-163 (box), :174-212       */
+/* (triangle), libs/acc/bvh_tree.h:469-548 (tree search)               */
+/* ------------------------------------------------------------------ */
+inline V3 closest_on_box(V3 v, Box const & b)
+{
+    float r[3];
+    for (int i = 0; i < 3; ++i) r[i] = smax(b.mn[i], smin(get(v, i), b.mx[i]));
+    return V3{r[0], r[1], r[2]};
+}
+
+inline V3 closest_on_tri(V3 vertex, float const * t9)
+{
+    V3 a = {t9[0], t9[1], t9[2]}, b = {t9[3], t9[4], t9[5]}, c = {t9[6], t9[7], t9[8]};
+    V3 ab = sub(b, a), ac = sub(c, a);
+    V3 normal = cross(ab, ac);
+    float n = norm(normal);
+    normal = divs(normal, n);
+    V3 p = sub(vertex, mul(normal, dot(normal, sub(vertex, a))));
+    V3 ap = sub(p, a);
+    float d00 = dot(ab, ab), d01 = dot(ab, ac), d11 = dot(ac, ac);
+    float d20 = dot(ap, ab), d21 = dot(ap, ac);
+    double denom = d00 * d11 - d01 * d01;
+    float b1 = (d11 * d20 - d01 * d21) / denom;
+    float b2 = (d00 * d21 - d01 * d20) / denom;
+    float b0 = 1.0f - b1 - b2;
+    if (b0 < 0.0f) {
+        V3 bc = sub(c, b);
+        float len = norm(bc);
+        float t = smax(0.0f, smin(dot(bc, sub(p, b)) / len, len));
+        return add(b, mul(bc, t / len));
+    }
+    if (b1 < 0.0f) {
+        V3 ca = sub(a, c);
+        float len = norm(ca);
+        float t = smax(0.0f, smin(dot(ca, sub(p, c)) / len, len));
+        return add(c, mul(ca, t / len));
+    }
+    if (b2 < 0.0f) {
+        float len = norm(ab);
+        float t = smax(0.0f, smin(dot(ab, sub(p, a)) / len, len));
+        return add(a, mul(ab, t / len));
+    }
+    return add(add(mul(a, b0), mul(b, b1)), mul(c, b2));
+}
+
+inline float sqdist(V3 a, V3 b) { V3 d = sub(a, b); return dot(d, d); }
+
+inline bool tree_closest_point(Tree const & t, V3 vertex, float max_dist, u32 * idx_out, V3 * cp_out)
+{
+    float dist = max_dist * max_dist;
+    u32 idx = NAI; V3 cp = {0.0f, 0.0f, 0.0f};
+    u32 node_id = 0;
+    std::vector<u32> s;
+    while (true) {
+        Node const & node = t.nodes[node_id];
+        if (node.left != NAI && node.right != NAI) {
+            float dl = sqdist(closest_on_box(vertex, t.nodes[node.left].box), vertex);
+            float dr = sqdist(closest_on_box(vertex, t.nodes[node.right].box), vertex);
+            bool left = dl < dist, right = dr < dist;
+            if (left && right) {
+                if (dl < dr) { s.push_back(node.right); node_id = node.left; }
+                else { s.push_back(node.left); node_id = node.right; }
+            } else {
+                if (right) node_id = node.right;
+                if (left) node_id = node.left;
+            }
+            if (!left && !right) {
+                if (s.empty()) break;
+                node_id = s.back(); s.pop_back();
+            }
+        } else {
+            u32 idx_leaf = NAI; V3 cp_leaf = {0.0f, 0.0f, 0.0f}; float d_leaf = INF;
+            for (u32 i = node.first; i < node.last; ++i) {
+                V3 c = closest_on_tri(vertex, &t.tris[9 * (size_t)i]);
+                float d = sqdist(c, vertex);
+                if (d < d_leaf) { cp_leaf = c; d_leaf = d; idx_leaf = i; }
+            }
+            /* :530-536: the leaf's best is re-measured (NAI leaf result: cp is whatever, dist compares false for NaN/inf) */
+            float dist_leaf = idx_leaf == NAI ? INF : sqdist(cp_leaf, vertex);
+            if (dist_leaf < dist) { dist = dist_leaf; idx = idx_leaf; cp = cp_leaf; }
+            if (s.empty()) break;
+            node_id = s.back(); s.pop_back();
+        }
+    }
+    if (idx == NAI) return false;
+    *idx_out = idx; *cp_out = cp;
+    return true;
+}
+
 struct Counters { uint64_t rays, inner, leaf, tri, hit; };
 
 /* Traversal: libs/acc/bvh_tree.h:401-467.  any_hit stops at the first accepted
@@ -636,6 +727,20 @@ void orc_bvh_intersect(void * h, float const * rays, uint64_t n, int any_hit,
         { total.rays += c.rays; total.inner += c.inner; total.leaf += c.leaf; total.tri += c.tri; total.hit += c.hit; }
     }
     if (counters) { counters[0] = total.rays; counters[1] = total.inner; counters[2] = total.leaf; counters[3] = total.tri; counters[4] = total.hit; }
+}
+
+/* found[i] = 1/0, idx[i] = leaf-order triangle index (acc's cp.first) or NAI, cp = closest point */
+void orc_bvh_closest_point(void * h, float const * points, uint64_t n, float max_dist,
+    uint8_t * found, u32 * idx, float * cp)
+{
+    Tree const & t = *(Tree *)h;
+    #pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < (int64_t)n; ++i) {
+        u32 id = NAI; V3 c = {0.0f, 0.0f, 0.0f};
+        bool f = tree_closest_point(t, V3{points[3 * i], points[3 * i + 1], points[3 * i + 2]}, max_dist, &id, &c);
+        found[i] = f ? 1 : 0; idx[i] = f ? id : NAI;
+        cp[3 * i] = f ? c.x : 0.0f; cp[3 * i + 1] = f ? c.y : 0.0f; cp[3 * i + 2] = f ? c.z : 0.0f;
+    }
 }
 
 void * orc_kd_build(float const * verts, u32 n) { return build_kd(verts, n); }

@@ -154,3 +154,32 @@ def test_live_kdtree_equals_reference(oracle):
     R.ref_kd_destroy(rk)
     assert np.array_equal(dist.view(np.uint32), qd.view(np.uint32))
     assert np.array_equal(sv[idx], sv[qi])
+
+
+# ------------------------------------------------------------------ closest point (libs/acc/bvh_tree.h:492-548)
+def test_golden_closest_point(oracle, tiny_scene):
+    import make_golden_closest as mc
+    g = np.load(os.path.join(GOLD, "ref_acc_closest.npz"))
+    ob = oracle.BVH.build(tiny_scene.verts, tiny_scene.faces, threads=2)
+    q = mc.queries(tiny_scene)
+    for k, md in enumerate(mc.MAX_DISTS):
+        f, i, c = ob.closest_point(q, md)
+        assert np.array_equal(np.packbits(f), g["found%d" % k])
+        assert np.array_equal(i, g["idx%d" % k])                                  # leaf-order triangle index
+        assert np.array_equal(c.view(np.uint32), g["cp%d" % k].view(np.uint32))   # the point, bit for bit
+    assert 0 < np.unpackbits(g["found2"]).sum() < np.unpackbits(g["found1"]).sum() < len(q)
+
+
+def test_live_closest_point_equals_reference(oracle):
+    _need_ref(oracle)
+    from uavmvs_b200 import scenes
+    sc = scenes.dense()
+    ob = oracle.BVH.build(sc.verts, sc.faces, threads=2)
+    rb = oracle.RefBVH(sc.verts, sc.faces, 2)
+    rng = np.random.default_rng(3)
+    q = np.concatenate([rng.uniform([-5, -5, -5], [70, 70, 90], (20000, 3)),
+                        sc.points + rng.normal(0, 0.05, sc.points.shape)]).astype(np.float32)
+    for md in (float("inf"), 2.0):
+        a, b = ob.closest_point(q, md), rb.closest_point(q, md)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+        assert np.array_equal(a[2].view(np.uint32), b[2].view(np.uint32))

@@ -381,3 +381,39 @@ def test_visibility_shafts_opt_in_is_bit_exact(api, oracle, scene_name, monkeypa
     data2, rows2 = obs.download()
     assert np.array_equal(rows2, obs_o.num_rows)
     assert _valid_rows_equal(obs_o.data, data2, rows2, 32)
+
+
+@pytest.mark.parametrize("builder", ["sah", "build_ploc"])
+def test_closest_point_equals_oracle(api, oracle, tiny_scene, tiny_tree, builder):
+    """uavmvs_bvh_closest_point vs the oracle's acc::BVHTree::closest_point (pinned to the reference's own code
+    in tests/test_oracle_vs_ref.py) on the same tree: found flag, leaf-order triangle index, point bit for bit."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden_closest as mc
+    sc = tiny_scene
+    if builder == "sah":
+        obvh, arrays = tiny_tree
+        gbvh = _gpu_tree(api, arrays)
+    else:
+        gbvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+        nodes, aabbs, tris, indices = gbvh.export()
+        obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    q = mc.queries(sc)
+    for k, md in enumerate(mc.MAX_DISTS):
+        f_o, i_o, c_o = obvh.closest_point(q, md)
+        f_g, i_g, c_g = gbvh.closest_point(q, md)
+        assert np.array_equal(f_g, f_o) and np.array_equal(i_g, i_o)
+        assert np.array_equal(c_g.view(np.uint32), c_o.view(np.uint32))
+        if builder == "sah":                                       # and the committed reference output itself
+            g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_acc_closest.npz"))
+            assert np.array_equal(np.packbits(f_g), g["found%d" % k]) and np.array_equal(i_g, g["idx%d" % k])
+            assert np.array_equal(c_g.view(np.uint32), g["cp%d" % k].view(np.uint32))
+    # single-triangle tree (the root is a leaf) and an empty query list
+    v = np.array([[0, 0, 0], [2, 0, 0], [0, 2, 0]], np.float32)
+    one = oracle.BVH.build(v, np.array([[0, 1, 2]], np.uint32), threads=1)
+    g1 = _gpu_tree(api, one.export())
+    pts = np.array([[0.5, 0.5, 3.0], [5.0, 5.0, 0.0], [-1.0, -1.0, -1.0]], np.float32)
+    a, b = one.closest_point(pts), g1.closest_point(pts)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2].view(np.uint32), b[2].view(np.uint32))
+    assert g1.closest_point(np.zeros((0, 3), np.float32))[0].shape == (0,)

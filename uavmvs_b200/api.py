@@ -151,6 +151,15 @@ class BVHTree(_Handle):
         _check(_lib.uavmvs_bvh_export(self.ptr, _p(nodes), _p(aabbs), _p(tris), _p(indices)))
         return nodes, aabbs, tris, indices
 
+    def closest_point(self, points, max_dist=float("inf"), stream=None):
+        """acc::BVHTree::closest_point for a batch: (found u8[n], leaf-order triangle index u32[n], point f32[n,3])."""
+        pts = _f(points).reshape(-1, 3)
+        n = pts.shape[0]
+        found, idx, cp = np.empty(n, np.uint8), np.empty(n, np.uint32), np.empty((n, 3), np.float32)
+        _check(_lib.uavmvs_bvh_closest_point(_stream_ptr(stream), self.ptr, _p(pts), C.c_uint64(n), _f32(max_dist),
+                                             _p(found), _p(idx), _p(cp)))
+        return found, idx, cp
+
     def trace(self, rays, any_hit=True, stream=None):
         """cacc::tracing::trace over a batch of host rays [n,8]."""
         rays = _f(rays, (-1, 8))
