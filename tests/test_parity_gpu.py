@@ -417,3 +417,45 @@ def test_closest_point_equals_oracle(api, oracle, tiny_scene, tiny_tree, builder
     a, b = one.closest_point(pts), g1.closest_point(pts)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[2].view(np.uint32), b[2].view(np.uint32))
     assert g1.closest_point(np.zeros((0, 3), np.float32))[0].shape == (0,)
+
+
+def test_config1_bundled_mesh_full_evaluation(api, oracle, tmp_path):
+    """BASELINE.json configs[0]: the reference's bundled res/meshes/sphere.ply (x30, on a ground quad), 100k
+    proxy points, 200 views, evaluated on the tree of the reference's CPU path (acc SAH builder, pinned to the
+    reference's own code) - driven through the FILES a uavmvs user has (PLY mesh, PLY cloud, trajectory text)."""
+    from uavmvs_b200 import scenes, formats as F
+    sc = scenes.config1()
+    assert sc.num_tris == 20482 and sc.num_points == 100_000 and 150 <= sc.num_views <= 250
+    F.save_ply(str(tmp_path / "mesh.ply"), sc.verts, sc.faces)
+    F.save_ply(str(tmp_path / "cloud.ply"), sc.points, None, sc.normals)
+    F.save_trajectory(str(tmp_path / "t.traj"), sc.view_pos, sc.w2c[:, :3, :3], np.full(sc.num_views, scenes.FLEN, np.float32))
+    mesh = F.load_ply(str(tmp_path / "mesh.ply"))
+    pts, nrm, val, qual = F.load_point_cloud(str(tmp_path / "cloud.ply"))
+    views = F.views_from_trajectory(*F.load_trajectory(str(tmp_path / "t.traj")), sc.width, sc.height)
+    obvh = oracle.BVH.build(mesh["vertices"], mesh["faces"], threads=4)          # libs/acc/bvh_tree.h:335-399
+    gbvh = _gpu_tree(api, obvh.export())
+    cloud = api.PointCloud.create(pts, nrm, val, qual)
+    obs = api.VectorArray.create(len(pts), 32)
+    recons, wrecons = api.Array.create(len(pts)), api.Array.create(len(pts))
+    s_sum, s_min, s_max, stats = api.evaluate_trajectory(views, sc.max_distance, sc.target_recon, sc.width, sc.height,
+                                                         gbvh, cloud, obs, recons, wrecons)
+    obs_o = oracle.ObsRays(len(pts), 32)
+    _, cnt = oracle.update_observation_rays(obvh, True, views, sc.max_distance, sc.width, sc.height, pts, nrm, obs_o,
+                                            want_counters=True)
+    oracle.process_observation_rays(obs_o)
+    r_o = oracle.evaluate_observation_rays(obs_o)
+    data, rows = obs.download()
+    assert stats[0] == int(cnt[0]) > 300_000
+    assert np.array_equal(rows, obs_o.num_rows) and _valid_rows_equal(obs_o.data, data, rows, 32)
+    # recon: 1e-5 relative (north_star) plus half an ulp of 1.0 per pair: matchability is (1 - logistic), which
+    # cancels for wide-parallax pairs, so a point whose ONLY pair is such a pair (recon ~ 1e-5..1e-4 here) carries
+    # the rounding of the logistic itself (libm expf / IEEE division in the oracle, __expf in the reference and
+    # here) at ~1e-4 relative.  11 of the 100 000 points are in that regime; everything else passes 1e-5 alone.
+    r_g = recons.download().astype(np.float64)
+    n = np.minimum(rows, 32).astype(np.float64)
+    tol = 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o)) + 3e-8 * n * (n - 1) / 2
+    assert np.all(np.abs(r_g - r_o) <= tol)
+    strict = np.abs(r_g - r_o) <= 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o))
+    assert strict.mean() > 0.9995
+    w_o = oracle.calculate_func_recons(r_o, sc.target_recon).astype(np.float64)
+    assert abs(s_sum / len(pts) - w_o.mean()) <= 1e-5 * w_o.mean() + 1e-9

@@ -264,12 +264,23 @@ def _thin(specs, n):
     return [specs[i] for i in keep]
 
 
+def bundled_sphere():
+    """The reference's res/meshes/sphere.ply (10 242 vertices / 20 480 faces, unit sphere) from the committed
+    fixture tests/golden/ref_sphere_mesh.npz; the generated icosphere of the same counts if it is missing."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "ref_sphere_mesh.npz")
+    if os.path.exists(path):
+        g = np.load(path)
+        return g["vertices"].astype(np.float64), g["faces"].astype(np.int64)
+    return icosphere(5)
+
+
 # ---------------------------------------------------------------- configs
 def config1(num_points=100_000, seed=7):
     """BASELINE.json configs[0]: icosphere (res/meshes/sphere.ply topology: 20 480
     faces) x30 standing on a 200 m ground quad; ~200-view lawn-mower trajectory at
     0 and 30 degrees off nadir; 100k proxy points; max_distance 80."""
-    sv, sf = icosphere(5)
+    sv, sf = bundled_sphere()
     sv = sv * 30.0 + np.array([0.0, 0.0, 30.0])
     g = 100.0
     gv = np.array([[-g, -g, 0.0], [g, -g, 0.0], [g, g, 0.0], [-g, g, 0.0]])
