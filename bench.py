@@ -367,14 +367,18 @@ def run_b200(a, rank, local_rank, world):
     alg_bytes = (rays / world) * b_ray + n_local * (32 + 4) + (stored / world) * 16 + V * 112
     achieved = alg_bytes / (k1_ms / 1e3) / 1e9 if k1_ms > 0 else 0.0
     traffic = ncu_traffic()
-    line["roofline"] = {"bound": "hbm", "kernel": "k_update_observation_rays<true> (K1, all views in one launch)",
+    line["roofline"] = {"bound": "hbm", "kernel": "K1 = update_observation_rays over all views in one launch (pipeline "
+                        "k_view_masks, k_block_caps, k_cull_emit, k_trace, k_retire; k_trace is 2/3 of it)",
                         "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                         "traffic": None if traffic is None else traffic.get("dram_bytes_per_launch"),
                         "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                         "bytes_per_ray": b_ray, "per_ray": per_ray, "kernel_ms": k1_ms,
+                        "ncu_k_trace": None if traffic is None else traffic.get("k_trace_ncu"),
                         "note": "per-ray counters from the oracle's instrumented reference traversal of the same "
-                                "(exported) tree on a 24-view sample; the tree (%.0f MB) is L2-resident, so "
-                                "algorithmic bytes exceed DRAM traffic" % ((nodes.nbytes + aabbs.nbytes + tris.nbytes) / 1e6)}
+                                "(exported) tree on a 24-view sample; the tree (%.0f MB in the reference layout) is "
+                                "L2-resident, so algorithmic bytes exceed DRAM traffic (traffic = ray records and "
+                                "observation rows) and frac can exceed 1: K1 is bound by issue slots, not by HBM "
+                                "(ncu_k_trace, profiles/)" % ((nodes.nbytes + aabbs.nbytes + tris.nbytes) / 1e6)}
     if world == 1 and not a.no_cpu_baseline:
         tree, built_by, tree_s = cpu_tree(orc, sc)
         nviews = calibrate_cpu_sample(orc, tree, sc, pts, nrm, a.cpu_seconds)

@@ -14,7 +14,7 @@ want = ['gpu__time_duration.sum', 'smsp__inst_executed.sum', 'smsp__thread_inst_
         'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
         'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']
 kn = hdr.index('Kernel Name')
-seen, traffic = set(), {}
+seen, traffic, ktrace = set(), {}, {}
 with open(f"{pr}/{tag}_step_kernels.txt", "w") as f:
     f.write(f"# ncu --set full --clock-control none, one evaluation step of tools/dev_bench.py --ploc (config 2), commit {commit}\n")
     f.write(f"# command: tools/gpu_prof.sh {tag}; report gpurun_out/{tag}_step.ncu-rep (not committed)\n")
@@ -32,10 +32,21 @@ with open(f"{pr}/{tag}_step_kernels.txt", "w") as f:
             i = hdr.index(w); v = float(r[i].replace(',', ''))
             return v * {'Mbyte': 1e6, 'Kbyte': 1e3, 'Gbyte': 1e9, 'byte': 1}.get(units[i], 1)
         traffic[name] = int(mb('dram__bytes_read.sum') + mb('dram__bytes_write.sum'))
+        if name == 'k_trace':
+            def val(w):
+                return float(r[hdr.index(w)].replace(',', ''))
+            ktrace = {"ms_under_ncu": val('gpu__time_duration.sum'),
+                      "issue_slots_pct": val('smsp__issue_active.avg.pct_of_peak_sustained_active'),
+                      "alu_pipe_pct": val('sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active'),
+                      "l1_data_pipe_wavefronts_pct": val('l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed'),
+                      "dram_throughput_pct": val('gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'),
+                      "warp_instructions": val('smsp__inst_executed.sum'),
+                      "active_threads_per_instruction": val('smsp__thread_inst_executed_per_inst_executed.ratio')}
 k1 = [k for k in traffic if any(x in k for x in ('view_masks', 'block_caps', 'sum_caps', 'add_u64', 'cull_emit', 'k_trace', 'k_retire'))]
 json.dump({"dram_bytes_per_launch": sum(traffic[k] for k in k1),
            "source": f"ncu --set full --clock-control none, sum over the kernels of one K1 launch (config 2), profiles/{tag}_step_kernels.txt",
-           "kernel_version": f"{tag} (commit {commit})", "per_kernel": {k: traffic[k] for k in k1}},
+           "kernel_version": f"{tag} (commit {commit})", "per_kernel": {k: traffic[k] for k in k1},
+           "k_trace_ncu": ktrace},
           open(f"{pr}/k1_traffic.json", "w"), indent=1)
 out = subprocess.run([sys.executable, "tools/ncu_launches.py", f"{go}/{tag}_launches.csv", "6"], capture_output=True, text=True).stdout
 open(f"{pr}/{tag}_launches.txt", "w").write(

@@ -152,44 +152,41 @@ __global__ void k_evaluate_spherical_histogram(const float * __restrict__ K9, in
     hist[(size_t)y * hstride + x] = sum;
 }
 
-// K7: estimate_capture_difficulty, kernels.cu:448-494.  One warp per point, lanes stride
-// over the sphere directions; closest-hit traversal in the reference order.
-__global__ void __launch_bounds__(128)
+// K7: estimate_capture_difficulty, kernels.cu:448-494.  One thread per point like the reference, so a warp
+// holds 32 neighbouring points (the cloud is Z-order sorted) that all cast the SAME direction at a time:
+// parallel rays from nearby origins walk the same nodes (a warp per point with the directions over the
+// lanes, the earlier mapping, gave 32 unrelated rays per warp: 0.66 vs 1.43 Grays/s at 1 M points).  Small CTAs
+// keep small clouds spread over all SMs.  Closest-hit traversal
+// in the reference order; sums accumulate in the reference's order (ascending direction index).
+__global__ void __launch_bounds__(64)
 k_estimate_capture_difficulty(BvhView bvh, KdView kd, uint32_t mesh_size, float max_distance,
     const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n,
     float * __restrict__ values, float * __restrict__ qualities)
 {
-    uint32_t lane = threadIdx.x & 31;
-    uint32_t id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (id >= n) return;
-    V3 v = ld3(verts[id]), nrm = ld3(normals[id]);
-    float l = max_distance;
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = id < n;                                  // whole warps stay in the collective trace
+    const V3 v = ld3(verts[valid ? id : n - 1]), nrm = ld3(normals[valid ? id : n - 1]);
+    const float l = max_distance;
     float sum = 0.0f, max_ctheta = 0.0f;
-    for (uint32_t base = 0; base < kd.n; base += 32) {
-        uint32_t i = base + lane;
-        bool in = i < kd.n;
-        V3 dir = normalized(ld3(__ldg(kd.verts + (in ? i : 0))));
-        float ctheta = dot(dir, nrm);
-        bool cast = in && !(ctheta < 0.087f);
+    for (uint32_t i = 0; i < kd.n; ++i) {
+        const V3 dir = normalized(ld3(__ldg(kd.verts + i)));
+        const float ctheta = dot(dir, nrm);
+        const bool cast = valid && !(ctheta < 0.087f);
+        if (!__any_sync(0xffffffffu, cast)) continue;
         Ray ray; ray.o = v; ray.d = dir; ray.tmin = l * 0.001f; ray.tmax = l;
         uint32_t face; float t;
-        bool hit = trace_closest_warp(bvh, ray, cast, face, t);
+        const bool hit = trace_closest_warp(bvh, ray, cast, face, t);
         if (cast) {
             if (!hit || face >= mesh_size) { if (ctheta > max_ctheta) max_ctheta = ctheta; }
             else sum += ctheta;
         }
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        max_ctheta = fmaxf(max_ctheta, __shfl_xor_sync(0xffffffffu, max_ctheta, o));
-    }
-    if (lane == 0) {
-        float mx = (kd.n / 2.0f) * 0.5f;
+    if (valid) {
+        const float mx = (kd.n / 2.0f) * 0.5f;
         values[id] = acosf(__saturatef(max_ctheta));
         qualities[id] = sum / mx;
     }
 }
-
 
 // ---- batched K6 ------------------------------------------------------------------------------
 // Whether sphere vertex i lies inside the image of orientation pixel (x, y) does not depend on the
@@ -362,7 +359,7 @@ int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const 
     uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud)
 {
     UAV_REQUIRE(bvh && kd && cloud, "null argument");
-    k_estimate_capture_difficulty<<<divup((uint64_t)cloud->n * 32, 128), 128, 0, (cudaStream_t)stream>>>(
+    k_estimate_capture_difficulty<<<divup(cloud->n, 64), 64, 0, (cudaStream_t)stream>>>(
         view_of(bvh), kd_view(kd), mesh_size, max_distance, cloud->vertices, cloud->normals, cloud->n,
         cloud->values, cloud->qualities);
     UAV_CUDA(cudaGetLastError());
