@@ -32,8 +32,17 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
     __shared__ float4 s_tile[32 * SE_TILE_STRIDE];
     __shared__ float4 s_col[SE_THREADS / 32][32];
     __shared__ uint32_t s_rows[32], s_valid[32];
+    __shared__ uint16_t s_pairs[496];                      // pair q -> (i << 8 | j), i > j, q = i (i - 1) / 2 + j
     const uint32_t tx = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t pt0 = blockIdx.x * 32;
+    if (DO_EVAL) {
+        for (uint32_t q = threadIdx.x; q < 496; q += SE_THREADS) {
+            uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
+            while (i * (i - 1) / 2 > q) --i;
+            while ((i + 1) * i / 2 <= q) ++i;
+            s_pairs[q] = (uint16_t)(i << 8 | (q - i * (i - 1) / 2));
+        }
+    }
     if (threadIdx.x < 32) {
         uint32_t id = pt0 + threadIdx.x;
         uint32_t r = id < n ? min(num_rows_ptr[id], max_rows) : 0u;
@@ -47,7 +56,7 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
         if (pt0 + tx < n) s_tile[r * SE_TILE_STRIDE + tx] = obs[(size_t)r * stride + pt0 + tx];
     __syncthreads();
 
-    const float m_k = h.m_k, m_x0 = kPi / h.m_x0, t_k = h.t_k, t_x0 = kPi / h.t_x0;
+    const LogisticC lm = logistic_fold(h.m_k, kPi / h.m_x0), lt = logistic_fold(h.t_k, kPi / h.t_x0);
     for (uint32_t p = w * 8; p < w * 8 + 8; ++p) {
         const uint32_t id = pt0 + p;
         if (id >= n) break;                                   // warp-uniform
@@ -56,24 +65,43 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
         if (tx < num_rows) ray = s_tile[tx * SE_TILE_STRIDE + p];
         uint32_t nv = num_rows;
         if (DO_SORT) {
-            int key = (int)tx;
             float theta = -1.0f;
             if (tx < num_rows) theta = (ray.w >= 0.0f) ? ray.z : -1.0f;
-            for (int i = 0; (1u << i) < num_rows; ++i) {
-                bool asc = (tx >> (i + 1)) % 2;
-                for (int s = 1 << i; s > 0; s >>= 1) {
-                    bool dir = (tx % (s << 1)) < s;
-                    float otheta = __shfl_xor_sync(0xffffffffu, theta, s);
-                    int okey = __shfl_xor_sync(0xffffffffu, key, s);
-                    if (otheta != theta && ((otheta > theta) == (asc ^ dir))) { theta = otheta; key = okey; }
-                }
+            // Descending order of the valid rows by counting: rank = number of larger keys.  For distinct keys
+            // every correct sort gives the reference's order; only the arrangement of EQUAL keys depends on the
+            // reference's bitonic network (it never exchanges equal keys, kernels.cu:241), so a column with a
+            // tie among its valid rows runs that network instead.  Invalid rows and padding (-1) sort behind
+            // every valid row (cos(theta) >= 0.087) and are never written back.
+            uint32_t rank = 0; bool tie = !(theta == theta);          // a NaN key: leave it to the network
+            for (uint32_t k = 0; k < num_rows; ++k) {
+                const float o = __shfl_sync(0xffffffffu, theta, k);
+                rank += o > theta;
+                tie |= (o == theta) && (k != tx);
             }
-            nv = __popc(__ballot_sync(0xffffffffu, theta >= 0.0f));
-            ray.x = __shfl_sync(0xffffffffu, ray.x, key);
-            ray.y = __shfl_sync(0xffffffffu, ray.y, key);
-            ray.z = __shfl_sync(0xffffffffu, ray.z, key);
-            ray.w = __shfl_sync(0xffffffffu, ray.w, key);
-            if (tx < nv) s_tile[tx * SE_TILE_STRIDE + p] = ray;      // rows >= nv keep their old content
+            const bool valid_row = theta >= 0.0f;
+            nv = __popc(__ballot_sync(0xffffffffu, valid_row));
+            if (!__any_sync(0xffffffffu, tie && (valid_row || !(theta == theta)))) {
+                __syncwarp();
+                if (valid_row) { s_tile[rank * SE_TILE_STRIDE + p] = ray; if (DO_EVAL) s_col[w][rank] = ray; }
+                __syncwarp();
+                if (DO_EVAL) ray = s_col[w][tx];                      // rows >= nv: stale, never used
+            } else {
+                int key = (int)tx;
+                for (int i = 0; (1u << i) < num_rows; ++i) {
+                    bool asc = (tx >> (i + 1)) % 2;
+                    for (int s = 1 << i; s > 0; s >>= 1) {
+                        bool dir = (tx % (s << 1)) < s;
+                        float otheta = __shfl_xor_sync(0xffffffffu, theta, s);
+                        int okey = __shfl_xor_sync(0xffffffffu, key, s);
+                        if (otheta != theta && ((otheta > theta) == (asc ^ dir))) { theta = otheta; key = okey; }
+                    }
+                }
+                ray.x = __shfl_sync(0xffffffffu, ray.x, key);
+                ray.y = __shfl_sync(0xffffffffu, ray.y, key);
+                ray.z = __shfl_sync(0xffffffffu, ray.z, key);
+                ray.w = __shfl_sync(0xffffffffu, ray.w, key);
+                if (tx < nv) s_tile[tx * SE_TILE_STRIDE + p] = ray;      // rows >= nv keep their old content
+            }
             if (tx == 0) s_valid[p] = nv;
         }
         if (DO_EVAL) {
@@ -83,14 +111,11 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
             const uint32_t rows = nv;
             const uint32_t npairs = rows * (rows - (rows ? 1u : 0u)) / 2u;
             float sum = 0.0f;
-            // pair q -> (i, j), i > j, enumerated row by row: q = i (i - 1) / 2 + j; advancing q by 32
-            // is j += 32 followed by carries into i
-            uint32_t i = 1, j = tx;
-            while (j >= i) { j -= i; ++i; }
+            // pair q -> (i, j), i > j, enumerated row by row (table lookup: the carries of an incremental
+            // enumeration cost 11 % of the kernel)
             for (uint32_t q = tx; q < npairs; q += 32) {
-                sum += pair_term_fast(s_col[w][j], s_col[w][i], m_k, m_x0, t_k, t_x0);
-                j += 32;
-                while (j >= i) { j -= i; ++i; }
+                const uint32_t ij = s_pairs[q];
+                sum += pair_term_fast(s_col[w][ij & 255u], s_col[w][ij >> 8], lm, lt);
             }
             for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
             if (tx == 0) {

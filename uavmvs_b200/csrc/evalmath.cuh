@@ -63,13 +63,47 @@ __device__ __forceinline__ float pair_term(float4 a, float4 b, float mk_, float 
 __device__ __forceinline__ float logistic_fast(float x, float k, float x0) {
     return __fdividef(1.0f, 1.0f + __expf(-k * (x - x0)));
 }
-__device__ __forceinline__ float pair_term_fast(float4 a, float4 b, float mk_, float mx0, float tk, float tx0) {
+// acos(x) = sqrt(1 - |x|) P7(|x|), reflected for x < 0 (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 on [0, 1]);
+// the square root is MUFU.RSQ plus one Newton step.  Absolute error < 1e-7 rad: the same size as the 2 ulp of
+// CUDA's acosf at these magnitudes, at half the instructions.  x must already be clamped to [-1, 1].
+__device__ __forceinline__ float acos_fast(float x) {
+    const float a = fabsf(x);
+    const float y = fmaxf(1.0f - a, 1e-30f);
+    const float r = rsqrtf(y);
+    float s = y * r;
+    s = __fmaf_rn(0.5f * r, __fmaf_rn(-s, s, y), s);
+    float p = -0.0012624911f;
+    p = __fmaf_rn(p, a, 0.0066700901f);
+    p = __fmaf_rn(p, a, -0.0170881256f);
+    p = __fmaf_rn(p, a, 0.0308918810f);
+    p = __fmaf_rn(p, a, -0.0501743046f);
+    p = __fmaf_rn(p, a, 0.0889789874f);
+    p = __fmaf_rn(p, a, -0.2145988016f);
+    p = __fmaf_rn(p, a, 1.5707963050f);
+    const float v = s * p;
+    return x < 0.0f ? 3.14159265358979f - v : v;
+}
+// logistic(x; k, x0) = 1 / (1 + 2^(c1 x + c0)) with c1 = -k log2(e), c0 = k x0 log2(e) folded once per launch:
+// one FFMA, ex2.approx, one add, rcp.approx (the reference's own logistic is __expf + an approximate division,
+// libs/eval/kernels.cu:80-84 under --prec-div=false).  The rounding of the folded exponent is the same
+// half-ulp-of-the-argument that __expf's x * log2(e) carries.
+struct LogisticC { float c1, c0; };
+__host__ __device__ __forceinline__ LogisticC logistic_fold(float k, float x0) {
+    LogisticC c; c.c1 = -k * 1.4426950408889634f; c.c0 = k * x0 * 1.4426950408889634f; return c;
+}
+__device__ __forceinline__ float logistic_folded(float x, LogisticC c) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(__fmaf_rn(c.c1, x, c.c0)));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return r;
+}
+__device__ __forceinline__ float pair_term_fast(float4 a, float4 b, LogisticC m, LogisticC t) {
     float calpha = b.x * a.x + b.y * a.y + b.z * a.z;
-    float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+    float alpha = acos_fast(fmaxf(-1.0f, fminf(calpha, 1.0f)));
     float scale = fminf(a.w, b.w);
     float ctheta = fminf(a.z, b.z);
-    float matchability = (1.0f - logistic_fast(alpha, mk_, mx0)) * ctheta;
-    float triangulation = logistic_fast(alpha, tk, tx0) * scale;
+    float matchability = (1.0f - logistic_folded(alpha, m)) * ctheta;
+    float triangulation = logistic_folded(alpha, t) * scale;
     return matchability * triangulation;
 }
 
