@@ -51,8 +51,9 @@ constexpr int K1_STEPS = K1_STEPS_N;     // node steps between two rounds of war
 // Margins are 100x above fp32 rounding of the exact test, so a rejected group is rejected
 // point by point by the exact arithmetic as well.
 __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view, float4 sph,
-    float max_distance, int width, int height)
+    float max_distance, int width, int height, bool * inside = nullptr)
 {
+    if (inside) *inside = false;
     float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
     float D = sqrtf(dx * dx + dy * dy + dz * dz);
     if (D * 0.99999f - sph.w >= max_distance * 1.00001f) return false;
@@ -73,15 +74,17 @@ __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view
     float p2 = K[6] * q[0] + K[7] * q[1] + K[8] * q[2];
     if (!(p2 - k2n * rho > 0.0f)) return true;          // ball not entirely in front: undecided
     float lim[4] = {0.5f, (float)width + 0.5f, 0.5f, (float)height + 0.5f};
+    bool all_in = true;                                   // every point of the sphere surely projects inside the image
     #pragma unroll
     for (int s = 0; s < 4; ++s) {
         int r = s >> 1;                                   // image row of K: 0 -> x, 1 -> y
         float a0 = K[3 * r] - lim[s] * K[6], a1 = K[3 * r + 1] - lim[s] * K[7], a2 = K[3 * r + 2] - lim[s] * K[8];
         float an = sqrtf(a0 * a0 + a1 * a1 + a2 * a2);
         float v = a0 * q[0] + a1 * q[1] + a2 * q[2];
-        if ((s & 1) == 0) { if (v + an * rho < 0.0f) return false; }   // coordinate < 0 everywhere
-        else { if (v - an * rho > 0.0f) return false; }                // coordinate >= size everywhere
+        if ((s & 1) == 0) { if (v + an * rho < 0.0f) return false; all_in = all_in && (v - an * rho > 0.0f); }   // coordinate < 0 everywhere
+        else { if (v - an * rho > 0.0f) return false; all_in = all_in && (v + an * rho < 0.0f); }                // coordinate >= size everywhere
     }
+    if (inside) *inside = all_in;
     return true;
 }
 
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32)
 k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 * __restrict__ super_spheres,
     uint32_t num_super, const float4 * __restrict__ block_spheres, const float4 * __restrict__ block_cones,
     const float * __restrict__ block_nmax, uint32_t num_blocks,
-    float max_distance, int width, int height, uint32_t * __restrict__ masks)
+    float max_distance, int width, int height, uint32_t * __restrict__ masks, uint32_t * __restrict__ inside_masks)
 {
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t v = blockIdx.x * 32 + lane;
@@ -125,7 +128,7 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
     for (uint32_t sb = sb0; sb < min(sb0 + K1_SB_PER_WARP, num_super); ++sb) {
         bool cand = v < num_views && block_view_maybe(view, __ldg(super_spheres + sb), max_distance, width, height);
         uint32_t m = __ballot_sync(0xffffffffu, cand);
-        uint32_t mine = 0;
+        uint32_t mine = 0, mine_in = 0;
         const uint32_t b = sb * 32 + lane;
         const float4 bs = __ldg(block_spheres + (b < num_blocks ? b : num_blocks - 1));
         const float4 bc = __ldg(block_cones + (b < num_blocks ? b : num_blocks - 1));
@@ -133,12 +136,14 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
         while (m) {
             const int j = __ffs(m) - 1; m &= m - 1;
             const float * vj = views + (size_t)(blockIdx.x * 32 + j) * UAVMVS_VIEW_FLOATS;   // uniform address
-            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height)
+            bool in = false;
+            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height, &in)
                 && !block_backfacing(vj, bs, bc, bn);
             uint32_t word = __ballot_sync(0xffffffffu, c);
-            if ((int)lane == j) mine = word;
+            uint32_t word_in = __ballot_sync(0xffffffffu, c && in);
+            if ((int)lane == j) { mine = word; mine_in = word_in; }
         }
-        if (v < num_views) masks[(size_t)sb * num_views + v] = mine;
+        if (v < num_views) { masks[(size_t)sb * num_views + v] = mine; inside_masks[(size_t)sb * num_views + v] = mine_in; }
     }
 }
 
@@ -516,7 +521,8 @@ template <bool HIST>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
-    const uint32_t * __restrict__ masks, const uint32_t * __restrict__ cert, uint32_t nchunks,
+    const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
+    const uint32_t * __restrict__ cert, uint32_t nchunks,
     float max_distance, int width, int height, RayList rl, unsigned long long * counters)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -527,20 +533,26 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     const bool valid = id < n;
     const V3 v = ld3(verts[valid ? id : n - 1]), nrm = ld3(normals[valid ? id : n - 1]);
     const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
+    const uint32_t * irow = inside_masks + (size_t)(blk >> 5) * num_views;
     const uint32_t mbit = blk & 31;
     const uint32_t base = rl.off[blk];
     uint32_t packet = base >> 5;                           // caps are 32 x candidate views: same numbering as k_entry
     uint32_t count = 0, tcount = 0;
     for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
       // four mask words per lane in flight: the scan of the block's row is latency bound otherwise
-      uint32_t mw4[4];
+      uint32_t mw4[4], iw4[4];
       #pragma unroll
-      for (int u = 0; u < 4; ++u) { const uint32_t vi = g0 + 32 * u + lane; mw4[u] = vi < v1 ? __ldg(mrow + vi) : 0u; }
+      for (int u = 0; u < 4; ++u) {
+          const uint32_t vi = g0 + 32 * u + lane;
+          mw4[u] = vi < v1 ? __ldg(mrow + vi) : 0u;
+          iw4[u] = (!HIST && vi < v1) ? __ldg(irow + vi) : 0u;
+      }
       #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint32_t c0 = g0 + 32 * u;
         if (c0 >= v1) break;
         uint32_t word = __ballot_sync(0xffffffffu, (mw4[u] >> mbit) & 1u);
+        const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
         const uint32_t cword = cert ? __ldg(cert + (size_t)blk * nchunks + ((c0 - v0) >> 5)) : 0u;
         while (word) {
             const uint32_t kb = __ffs(word) - 1;
@@ -563,7 +575,7 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
                 pass = valid && !(scale <= 0.0f) && !(ctheta < 0.087f);
             } else {
                 pass = valid && !(ctheta < 0.087f) && !(l >= max_distance);
-                if (pass) pass = in_image(vw, v, width, height);
+                if (!((iword >> kb) & 1u) && pass) pass = in_image(vw, v, width, height);   // warp-uniform skip
             }
             uint32_t m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
@@ -1039,7 +1051,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         { const char * e = getenv("UAVMVS_TRACE_CTAS"); if (e && atoi(e) > 0 && atoi(e) < occ) occ = atoi(e); }   // dev: leave room for co-running kernels
         k.grid_trace = sms * (occ > 0 ? occ : 1);
     }
-    if (grow(&k.masks, &k.masks_cap, (size_t)cloud->num_super * num_views, s)) return 1;
+    if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
+    uint32_t * inside_masks = k.masks + (size_t)cloud->num_super * num_views;
     if (nb + 1 > k.blocks_cap) {
         size_t c0 = k.blocks_cap, c1 = k.blocks_cap, c2 = k.blocks_cap, c3 = k.blocks_cap;
         if (grow(&k.caps, &c0, (size_t)nb + 1, s) || grow(&k.off, &c1, (size_t)nb + 1, s) || grow(&k.cnt, &c2, (size_t)nb + 1, s)
@@ -1056,7 +1069,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 
     dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
     k_view_masks<<<mgrid, K1_WARPS * 32, 0, s>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
-        cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, max_distance, width, height, k.masks);
+        cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, max_distance, width, height, k.masks, inside_masks);
     UAV_CUDA(cudaGetLastError());
 
     // view batches: [v0, v1) such that the upper bound of ray records fits the budget
@@ -1107,9 +1120,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
             }
             if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
+                d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
+                d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
             unsigned grid = (unsigned)k.grid_trace;
