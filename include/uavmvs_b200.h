@@ -52,6 +52,12 @@ int uavmvs_bvh_build_lbvh(const float * verts, uint32_t num_verts, const uint32_
  * (nearest neighbour by union surface area, mutual pairs merge): close to SAH quality, built on the GPU. */
 int uavmvs_bvh_build_ploc(const float * verts, uint32_t num_verts, const uint32_t * faces,
     uint32_t num_faces, uavmvs_bvh ** out);
+/* Same inputs; full-sweep surface-area-heuristic build on the GPU: the reference builder's own cost model and
+ * termination rule (libs/acc/bvh_tree.h:277-333, cost = 1.2 + (A_l/A n_l + A_r/A n_r), leaf when not below n),
+ * evaluated for every split position of every axis of every node of a level at once (three pre-sorted orders,
+ * segmented box scans, stable segmented partition).  Best traversal quality of the three GPU builders. */
+int uavmvs_bvh_build_sah(const float * verts, uint32_t num_verts, const uint32_t * faces,
+    uint32_t num_faces, uavmvs_bvh ** out);
 int uavmvs_bvh_sizes(const uavmvs_bvh * bvh, uint32_t * num_nodes, uint32_t * num_tris);
 /* Export in the reference layout (for the oracle / for acc-side consumers). */
 int uavmvs_bvh_export(const uavmvs_bvh * bvh, uint32_t * nodes, float * aabbs, float * tris, uint32_t * indices);

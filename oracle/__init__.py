@@ -7,6 +7,9 @@ never imports this module.
   liboracle.so        oracle/uavmvs_oracle.cpp: our restatement (kind "port")
   _ref/libref_acc.so  the reference's libs/acc headers compiled as they lie
                       (kind "reference"; tree build / ray traversal / KD search)
+  _ref/libref_cuda_{exact,fast}.so
+                      the reference's own kernels (libs/eval/kernels.cu + libs/cacc)
+                      compiled for sm_100a as they lie; GPU box only (refcuda())
 """
 import ctypes as C
 import os
@@ -40,6 +43,11 @@ def build(force=False):
     if os.path.isdir("/root/reference/libs/acc") and (force or not os.path.exists(ref_so)
                                                       or os.path.getmtime(ref_so) < os.path.getmtime(shim)):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    cu_so = os.path.join(_HERE, "_ref", "libref_cuda_fast.so")
+    cu_shim = os.path.join(_HERE, "ref_shim", "ref_cuda.cu")
+    if os.path.isdir("/root/reference/libs/eval") and (force or not os.path.exists(cu_so)
+                                                       or os.path.getmtime(cu_so) < os.path.getmtime(cu_shim)):
+        subprocess.check_call(["make", "-C", _HERE, "refcuda"], stdout=subprocess.DEVNULL)
 
 
 def _opt(ptr_type):
@@ -133,6 +141,138 @@ def ref():
     R.ref_kd_destroy.argtypes = [_vp]
     _REF = R
     return R
+
+
+_REFCU = {}
+
+
+def refcuda(kind="exact"):
+    """The reference's own CUDA kernels compiled for sm_100a (None when oracle/_ref holds no such build or
+    there is no GPU).  kind: "exact" (IEEE, no FMA contraction) or "fast" (the reference's nvcc flags)."""
+    if kind in _REFCU:
+        return _REFCU[kind]
+    build()
+    path = os.path.join(_HERE, "_ref", "libref_cuda_%s.so" % kind)
+    if not os.path.exists(path):
+        return None
+    R = C.CDLL(path)
+    if R.refcu_device_count() <= 0:
+        return None
+    u32, i32, f32 = C.c_uint32, C.c_int, C.c_float
+    for name in ("refcu_bvh_create", "refcu_kd_create", "refcu_cloud_create", "refcu_obs_create"):
+        getattr(R, name).restype = _vp
+    R.refcu_bvh_create.argtypes = [_f32p, u32, _u32p, u32, i32]
+    R.refcu_kd_create.argtypes = [_f32p, u32]
+    R.refcu_cloud_create.argtypes = [u32, _f32p, _f32p, _opt(_f32p), _opt(_f32p)]
+    R.refcu_cloud_download.argtypes = [_vp, _opt(_f32p), _opt(_f32p)]
+    R.refcu_obs_create.argtypes = [u32, u32]
+    R.refcu_obs_clear.argtypes = [_vp]
+    R.refcu_obs_download.argtypes = [_vp, _opt(_u32p), _opt(_f32p)]
+    for name in ("refcu_bvh_destroy", "refcu_kd_destroy", "refcu_cloud_destroy", "refcu_obs_destroy",
+                 "refcu_process_observation_rays"):
+        getattr(R, name).argtypes = [_vp]
+    R.refcu_configure_heuristic.argtypes = [f32, f32, f32, f32]
+    R.refcu_update_observation_rays.argtypes = [i32, _f32p, u32, f32, i32, i32, _vp, _vp, _vp]
+    R.refcu_evaluate_observation_rays.argtypes = [_vp, _f32p]
+    R.refcu_calculate_func_recons.argtypes = [_f32p, u32, f32, _opt(_f32p), _opt(_f32p)]
+    R.refcu_populate_spherical_histogram.argtypes = [_f32p, f32, f32, _vp, _vp, _vp, _vp, _opt(_f32p), u32, _f32p]
+    R.refcu_evaluate_spherical_histogram.argtypes = [_f32p, i32, i32, _vp, _f32p, u32, _f32p]
+    R.refcu_estimate_capture_difficulty.argtypes = [f32, _vp, u32, _vp, _vp]
+    R.refcu_time_evaluate.restype = f32
+    R.refcu_time_evaluate.argtypes = [_f32p, u32, f32, i32, i32, f32, _vp, _vp, _vp]
+    _REFCU[kind] = R
+    return R
+
+
+class RefCuda:
+    """One scene held by the reference's own containers on the GPU (cacc::BVHTree / PointCloud / VectorArray /
+    KDTree), driven through the reference's kernels the way its apps drive them."""
+
+    def __init__(self, verts, faces, points, normals, values=None, qualities=None, sphere_verts=None,
+                 max_rows=32, kind="exact", threads=0):
+        self.R = refcuda(kind)
+        if self.R is None:
+            raise RuntimeError("oracle/_ref/libref_cuda_%s.so not available (no build, or no GPU)" % kind)
+        verts = _c(verts, np.float32).reshape(-1, 3)
+        faces = _c(faces, np.uint32).reshape(-1, 3)
+        self.n = len(points)
+        self.max_rows = max_rows
+        self.bvh = self.R.refcu_bvh_create(verts, verts.shape[0], faces, faces.shape[0], threads)
+        self.cloud = self.R.refcu_cloud_create(self.n, _c(points, np.float32), _c(normals, np.float32),
+                                               None if values is None else _c(values, np.float32),
+                                               None if qualities is None else _c(qualities, np.float32))
+        self.obs = self.R.refcu_obs_create(self.n, max_rows)
+        self.kd, self.S = None, 0
+        if sphere_verts is not None:
+            sv = _c(sphere_verts, np.float32).reshape(-1, 3)
+            self.kd, self.S = self.R.refcu_kd_create(sv, sv.shape[0]), sv.shape[0]
+
+    def configure_heuristic(self, m_k, m_x0, t_k, t_x0):
+        self.R.refcu_configure_heuristic(m_k, m_x0, t_k, t_x0)
+
+    def clear(self):
+        self.R.refcu_obs_clear(self.obs)
+
+    def update_observation_rays(self, populate, views, max_distance, width, height):
+        views = _c(views, np.float32).reshape(-1, VIEW_FLOATS)
+        self.R.refcu_update_observation_rays(1 if populate else 0, views, views.shape[0], max_distance, width, height,
+                                             self.bvh, self.cloud, self.obs)
+
+    def process_observation_rays(self):
+        self.R.refcu_process_observation_rays(self.obs)
+
+    def evaluate_observation_rays(self):
+        out = np.empty(self.n, np.float32)
+        self.R.refcu_evaluate_observation_rays(self.obs, out)
+        return out
+
+    def download(self):
+        """(num_rows[N] uint32, rows[max_rows, N, 4] float32)"""
+        num_rows = np.empty(self.n, np.uint32)
+        rows = np.empty((self.max_rows, self.n, 4), np.float32)
+        self.R.refcu_obs_download(self.obs, num_rows, rows)
+        return num_rows, rows
+
+    def calculate_func_recons(self, recons, target):
+        recons = _c(recons, np.float32)
+        w = np.empty_like(recons)
+        out3 = np.zeros(3, np.float32)
+        self.R.refcu_calculate_func_recons(recons, recons.shape[0], target, w, out3)
+        return w, out3
+
+    def populate_spherical_histogram(self, view_pos, max_distance, target_recon=0.0, recons=None):
+        hist = np.empty(self.S, np.float32)
+        self.R.refcu_populate_spherical_histogram(_c(view_pos, np.float32), max_distance, target_recon, self.bvh,
+                                                  self.cloud, self.kd, self.obs,
+                                                  None if recons is None else _c(recons, np.float32), self.S, hist)
+        return hist
+
+    def evaluate_spherical_histogram(self, calib, width, height, hist):
+        img = np.empty((45, 128), np.float32)
+        self.R.refcu_evaluate_spherical_histogram(_c(calib, np.float32).reshape(9), width, height, self.kd,
+                                                  _c(hist, np.float32), self.S, img)
+        return img
+
+    def estimate_capture_difficulty(self, max_distance, mesh_size):
+        self.R.refcu_estimate_capture_difficulty(max_distance, self.bvh, mesh_size, self.kd, self.cloud)
+        values, qualities = np.empty(self.n, np.float32), np.empty(self.n, np.float32)
+        self.R.refcu_cloud_download(self.cloud, values, qualities)
+        return values, qualities
+
+    def time_evaluate(self, views, max_distance, width, height, target_recon):
+        views = _c(views, np.float32).reshape(-1, VIEW_FLOATS)
+        return float(self.R.refcu_time_evaluate(views, views.shape[0], max_distance, width, height, target_recon,
+                                                self.bvh, self.cloud, self.obs))
+
+    def __del__(self):
+        try:
+            self.R.refcu_obs_destroy(self.obs)
+            self.R.refcu_cloud_destroy(self.cloud)
+            self.R.refcu_bvh_destroy(self.bvh)
+            if self.kd:
+                self.R.refcu_kd_destroy(self.kd)
+        except Exception:
+            pass
 
 
 def _c(a, dt):

@@ -196,14 +196,24 @@ def test_evaluate_trajectory_fused(api, oracle, tiny_scene, tiny_tree):
         assert _close(s / sc.num_points, w_o.astype(np.float64).mean())
 
 
-@pytest.mark.parametrize("builder", ["build_lbvh", "build_ploc"])
+@pytest.mark.parametrize("builder", ["build_lbvh", "build_ploc", "build_sah"])
 def test_gpu_built_tree_same_tree_parity(api, oracle, tiny_scene, builder):
-    """GPU-built trees (LBVH, PLOC): the oracle walks the exported tree (parity is per tree)."""
+    """GPU-built trees (LBVH, PLOC, sweep SAH): the oracle walks the exported tree (parity is per tree)."""
     sc = tiny_scene
     gbvh = getattr(api.BVHTree, builder)(sc.verts, sc.faces)
     nodes, aabbs, tris, indices = gbvh.export()
     n, t = gbvh.sizes()
-    assert t == sc.num_tris and n == 2 * t - 1
+    assert t == sc.num_tris
+    if builder == "build_sah":
+        # multi-triangle leaves like the reference's builder; every leaf range is covered exactly once
+        leaf = nodes[:, 2] == 0xFFFFFFFF
+        assert n % 2 == 1 and n < 2 * t - 1 and leaf.sum() == (n + 1) // 2
+        order = np.argsort(nodes[leaf, 0])
+        first, last = nodes[leaf, 0][order], nodes[leaf, 1][order]
+        assert first[0] == 0 and last[-1] == t and np.array_equal(first[1:], last[:-1])
+        assert (last - first).max() <= 8
+    else:
+        assert n == 2 * t - 1
     assert sorted(indices.tolist()) == list(range(t))
     # every inner box is the exact union of its children
     inner = nodes[:, 2] != 0xFFFFFFFF

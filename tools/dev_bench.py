@@ -17,6 +17,7 @@ ap.add_argument("--extent", type=float, default=256.0)
 ap.add_argument("--iters", type=int, default=5)
 ap.add_argument("--check", action="store_true")
 ap.add_argument("--ploc", action="store_true")
+ap.add_argument("--gsah", action="store_true", help="GPU sweep-SAH builder")
 ap.add_argument("--sah", action="store_true", help="dev experiment: tree from the oracle SAH builder (test infrastructure)")
 args = ap.parse_args()
 
@@ -29,6 +30,8 @@ if args.sah:
     import oracle
     ta = oracle.BVH.build(sc.verts, sc.faces).export()
     bvh = api.BVHTree.create(ta.nodes, ta.aabbs, ta.tris, ta.indices)
+elif args.gsah:
+    bvh = api.BVHTree.build_sah(sc.verts, sc.faces)
 elif args.ploc:
     bvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
 else:

@@ -139,6 +139,15 @@ class BVHTree(_Handle):
                                           C.byref(h)))
         return cls(h)
 
+    @classmethod
+    def build_sah(cls, verts, faces):
+        """GPU full-sweep SAH build (the reference builder's cost model, libs/acc/bvh_tree.h:277-333)."""
+        verts, faces = _f(verts, (-1, 3)), _u(faces).reshape(-1, 3)
+        h = _vp()
+        _check(_lib.uavmvs_bvh_build_sah(_p(verts), _u32(verts.shape[0]), _p(faces), _u32(faces.shape[0]),
+                                         C.byref(h)))
+        return cls(h)
+
     def sizes(self):
         n, t = _u32(0), _u32(0)
         _check(_lib.uavmvs_bvh_sizes(self.ptr, C.byref(n), C.byref(t)))

@@ -175,7 +175,7 @@ __global__ void k_build_tris(const float * __restrict__ tris, uint32_t n, Tri64 
     out[i] = o;
 }
 
-static int finalize_layout(uavmvs_bvh * b)
+int finalize_layout(uavmvs_bvh * b)
 {
     uint32_t n = b->num_nodes, t = b->num_tris;
     uint32_t * flag = nullptr, * slot = nullptr;
@@ -229,7 +229,7 @@ static int finalize_layout(uavmvs_bvh * b)
     return 0;
 }
 
-static int alloc_reference_arrays(uavmvs_bvh * b)
+int alloc_reference_arrays(uavmvs_bvh * b)
 {
     UAV_CUDA(cudaMalloc(&b->nodes, sizeof(uint4) * (size_t)b->num_nodes));
     UAV_CUDA(cudaMalloc(&b->aabbs, sizeof(float) * 6 * (size_t)b->num_nodes));
