@@ -45,7 +45,7 @@ def parse():
     ap.add_argument("--points", type=int, default=1_000_000, help="proxy points per GPU")
     ap.add_argument("--views", type=int, default=2000)
     ap.add_argument("--extent", type=float, default=256.0)
-    ap.add_argument("--tree", default="ploc", choices=["ploc", "lbvh"], help="GPU tree build (product path)")
+    ap.add_argument("--tree", default="sah", choices=["sah", "ploc", "lbvh"], help="GPU tree build (product path)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline sample")
     return ap.parse_args()
@@ -265,7 +265,7 @@ def run_b200(a, rank, local_rank, world):
     V = views_np.shape[0]
 
     t0 = time.perf_counter()
-    bvh = (api.BVHTree.build_ploc if a.tree == "ploc" else api.BVHTree.build_lbvh)(sc.verts, sc.faces)
+    bvh = getattr(api.BVHTree, "build_" + a.tree)(sc.verts, sc.faces)
     api.synchronize()
     build_s = time.perf_counter() - t0
     cloud = api.PointCloud.create(pts, nrm)

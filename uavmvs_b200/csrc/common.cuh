@@ -67,7 +67,7 @@ struct __align__(64) Tri64 { float4 q0, q1, q2, q3; };
 }  // namespace uav
 
 struct uavmvs_bvh {
-    uint32_t num_nodes, num_tris, num_inner;
+    uint32_t num_nodes, num_tris, num_inner, num_wide;
     // reference layout (kept for export and for the oracle)
     uint4 * nodes;      // {first,last,left,right}
     float * aabbs;      // 6 per node

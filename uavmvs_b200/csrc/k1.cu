@@ -604,6 +604,128 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     }
 }
 
+// Same result as k_cull_emit, fewer instructions: the exact cull costs ~400 instructions per 32 pairs
+// (IEEE sqrt, 8 IEEE divisions, unfused multiply-adds) and only ~40 % of the candidate pairs survive it,
+// most of the others failing the back-face test.  Phase 1 therefore proves rejections with a dozen
+// fast-math instructions from the view position alone (back-face and range tests with a margin three
+// orders of magnitude above the rounding error of either evaluation; NaNs never compare as rejected);
+// every pair it cannot reject is queued, and phase 2 runs the exact arithmetic on FULL warps of queued
+// pairs (lane = pair, not point).  The queue is filled in (view, point) order and drained in order, so
+// the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
+// passes keep using k_cull_emit.
+template <bool HIST>
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
+    const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
+    const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
+    float max_distance, int width, int height, RayList rl, unsigned long long * counters)
+{
+    __shared__ float4 s_v[K1_WARPS][32], s_n[K1_WARPS][32];
+    __shared__ uint32_t s_q[K1_WARPS][64];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    if (blk >= num_blocks) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t id = blk * 32 + lane;
+    const bool valid = id < n;
+    const float4 v4 = verts[valid ? id : n - 1], n4 = normals[valid ? id : n - 1];
+    s_v[w][lane] = v4; s_n[w][lane] = n4;
+    __syncwarp();
+    const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
+    const uint32_t * irow = inside_masks + (size_t)(blk >> 5) * num_views;
+    const uint32_t mbit = blk & 31;
+    const uint32_t base = rl.off[blk];
+    const float md2 = max_distance * max_distance * 1.00001f;
+    const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
+    uint32_t count = 0, qn = 0;
+
+    // exact cull + emit of the first min(qn, 32) queued pairs
+    auto flush = [&]() {
+        const uint32_t take = qn < 32u ? qn : 32u;
+        const uint32_t e = s_q[w][lane < take ? lane : 0];
+        const uint32_t pt = e & 31u, k = e >> 6;
+        const V3 v = ld3(s_v[w][pt]), nrm = ld3(s_n[w][pt]);
+        const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
+        float vw[UAVMVS_VIEW_FLOATS];
+        #pragma unroll
+        for (int i = 0; i < UAVMVS_VIEW_FLOATS / 4; ++i) {
+            float4 t = __ldg(reinterpret_cast<const float4 *>(view) + i);
+            vw[4 * i] = t.x; vw[4 * i + 1] = t.y; vw[4 * i + 2] = t.z; vw[4 * i + 3] = t.w;
+        }
+        V3 v2c = mk(vw[0], vw[1], vw[2]) - v;
+        float l = norm(v2c);
+        V3 v2cn = v2c / l;
+        float ctheta = dot(v2cn, nrm);
+        bool pass;
+        if (HIST) {                                   // kernels.cu:310-316 / :358-364: scale first, no image test
+            const float scale = 1.0f - (l / max_distance);
+            pass = lane < take && !(scale <= 0.0f) && !(ctheta < 0.087f);
+        } else {
+            pass = lane < take && !(ctheta < 0.087f) && !(l >= max_distance);
+            const bool need = pass && !((e >> 5) & 1u);               // block not surely inside this view's image
+            if (__any_sync(0xffffffffu, need)) { if (need) pass = in_image(vw, v, width, height); }
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, pass);
+        if (pass) {
+            const uint32_t idx = base + count + __popc(m & lt_mask);
+            const float4 d4 = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
+            __stcs(rl.dirl + idx, d4);
+            if (HIST) rl.rview[idx] = k;
+            __stcs(rl.tdir + idx, d4);
+            __stcs(rl.torg + idx, make_float4(v.x, v.y, v.z, __uint_as_float(idx << 5 | pt)));
+        }
+        count += __popc(m);
+        __syncwarp();
+        const uint32_t rest = qn - take;
+        const uint32_t carry = lane < rest ? s_q[w][32 + lane] : 0u;
+        __syncwarp();
+        if (lane < rest) s_q[w][lane] = carry;
+        qn = rest;
+        __syncwarp();
+    };
+
+    const V3 v = ld3(v4), nrm = ld3(n4);
+    for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
+      uint32_t mw4[4], iw4[4];
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+          const uint32_t vi = g0 + 32 * u + lane;
+          mw4[u] = vi < v1 ? __ldg(mrow + vi) : 0u;
+          iw4[u] = (!HIST && vi < v1) ? __ldg(irow + vi) : 0u;
+      }
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t c0 = g0 + 32 * u;
+        if (c0 >= v1) break;
+        uint32_t word = __ballot_sync(0xffffffffu, (mw4[u] >> mbit) & 1u);
+        const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
+        while (word) {
+            const uint32_t kb = __ffs(word) - 1;
+            const uint32_t k = c0 + kb; word &= word - 1;
+            const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
+            const float px = __ldg(view), py = __ldg(view + 1), pz = __ldg(view + 2);
+            // phase 1: fast-math proof of rejection (any doubt, any NaN -> queued for the exact test)
+            const float dx = px - v.x, dy = py - v.y, dz = pz - v.z;
+            const float l2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+            const float dn = __fmaf_rn(dz, nrm.z, __fmaf_rn(dy, nrm.y, dx * nrm.x));
+            const float c = dn * rsqrtf(l2);
+            const bool reject = (c < bf_lim) || (l2 > md2);
+            const bool maybe = valid && !reject;
+            const uint32_t m = __ballot_sync(0xffffffffu, maybe);
+            if (maybe) s_q[w][qn + __popc(m & lt_mask)] = (k << 6) | (((iword >> kb) & 1u) << 5) | lane;
+            qn += __popc(m);
+            __syncwarp();
+            if (qn >= 32u) flush();
+        }
+      }
+    }
+    while (qn) flush();
+    if (lane == 0) {
+        rl.cnt[blk] = count; rl.tcnt[blk] = count;
+        if (counters && count) atomicAdd(counters + 3, (unsigned long long)count);
+    }
+}
+
 struct TraceArgs {
     BvhView bvh;
     const float4 * __restrict__ verts;
@@ -1119,7 +1241,12 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 { const char * e = getenv("UAVMVS_SHAFT_STEPS"); sa.max_steps = e ? (uint32_t)atoi(e) : 1000000u; }
                 k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
             }
-            if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
+            if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, width, height, rl, k.counters);
+            else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, width, height, rl, k.counters);
+            else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
