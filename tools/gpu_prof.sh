@@ -10,6 +10,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" -c 200 --csv -
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $out/${tag}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 ncu --set full --clock-control none --import-source on -k "$K" -s 24 -c 12 -f -o $out/${tag}_step \
-    python tools/dev_bench.py --ploc --iters 4 > $out/${tag}_ncu_full.log 2>&1
+    python tools/dev_bench.py --gsah --iters 4 > $out/${tag}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 tail -3 $out/${tag}_ncu_full.log

@@ -27,7 +27,10 @@
 namespace uav {
 
 constexpr int K1_WARPS = 4;
-constexpr int K1_SB_PER_WARP = 8;
+#ifndef K1_SB_PER_WARP_N
+#define K1_SB_PER_WARP_N 1      // measured: 8 -> 0.26 ms, 4 -> 0.20, 2 -> 0.16, 1 -> 0.15 (the per-warp candidate loop is the critical path)
+#endif
+constexpr int K1_SB_PER_WARP = K1_SB_PER_WARP_N;
 #ifndef K1_REFILL_N
 #define K1_REFILL_N 20
 #endif
@@ -646,13 +649,8 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         const uint32_t pt = e & 31u, k = e >> 6;
         const V3 v = ld3(s_v[w][pt]), nrm = ld3(s_n[w][pt]);
         const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
-        float vw[UAVMVS_VIEW_FLOATS];
-        #pragma unroll
-        for (int i = 0; i < UAVMVS_VIEW_FLOATS / 4; ++i) {
-            float4 t = __ldg(reinterpret_cast<const float4 *>(view) + i);
-            vw[4 * i] = t.x; vw[4 * i + 1] = t.y; vw[4 * i + 2] = t.z; vw[4 * i + 3] = t.w;
-        }
-        V3 v2c = mk(vw[0], vw[1], vw[2]) - v;
+        const float4 p4 = __ldg(reinterpret_cast<const float4 *>(view));
+        V3 v2c = mk(p4.x, p4.y, p4.z) - v;
         float l = norm(v2c);
         V3 v2cn = v2c / l;
         float ctheta = dot(v2cn, nrm);
@@ -663,15 +661,24 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         } else {
             pass = lane < take && !(ctheta < 0.087f) && !(l >= max_distance);
             const bool need = pass && !((e >> 5) & 1u);               // block not surely inside this view's image
-            if (__any_sync(0xffffffffu, need)) { if (need) pass = in_image(vw, v, width, height); }
+            if (__any_sync(0xffffffffu, need)) {
+                if (need) {
+                    float vw[UAVMVS_VIEW_FLOATS];
+                    vw[0] = p4.x; vw[1] = p4.y; vw[2] = p4.z; vw[3] = p4.w;
+                    #pragma unroll
+                    for (int i = 1; i < UAVMVS_VIEW_FLOATS / 4; ++i) {
+                        float4 t = __ldg(reinterpret_cast<const float4 *>(view) + i);
+                        vw[4 * i] = t.x; vw[4 * i + 1] = t.y; vw[4 * i + 2] = t.z; vw[4 * i + 3] = t.w;
+                    }
+                    pass = in_image(vw, v, width, height);
+                }
+            }
         }
         const uint32_t m = __ballot_sync(0xffffffffu, pass);
         if (pass) {
             const uint32_t idx = base + count + __popc(m & lt_mask);
-            const float4 d4 = make_float4(v2cn.x, v2cn.y, v2cn.z, l);
-            __stcs(rl.dirl + idx, d4);
+            __stcs(rl.dirl + idx, make_float4(v2cn.x, v2cn.y, v2cn.z, l));      // rl.tdir aliases rl.dirl (nothing certified)
             if (HIST) rl.rview[idx] = k;
-            __stcs(rl.tdir + idx, d4);
             __stcs(rl.torg + idx, make_float4(v.x, v.y, v.z, __uint_as_float(idx << 5 | pt)));
         }
         count += __popc(m);
@@ -973,17 +980,24 @@ k_retire(RetireArgs a)
     __syncwarp();
     const uint32_t base = a.rl.off[blk];
     unsigned long long st_vis = 0;
+    // the next 32 records are fetched while the current ones are processed: an iteration is a chain of two
+    // DRAM round trips (status byte, then direction) otherwise, and the kernel is latency bound
+    uint32_t vb_next = lane < count ? (uint32_t)__ldcs(a.rl.vis + base + lane) : 0u;
+    float4 d4_next = lane < count ? __ldcs(a.rl.dirl + base + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
     for (uint32_t c0 = 0; c0 < count; c0 += 32) {
-        const uint32_t i = c0 + lane;
-        const bool in = i < count;
-        const uint32_t vb = in ? (uint32_t)__ldcs(a.rl.vis + base + i) : 0u;
+        const uint32_t vb = vb_next;
+        const float4 d4 = d4_next;
+        {
+            const uint32_t i_next = c0 + 32 + lane;
+            vb_next = 0u;
+            if (i_next < count) { vb_next = (uint32_t)__ldcs(a.rl.vis + base + i_next); d4_next = __ldcs(a.rl.dirl + base + i_next); }
+        }
         const bool vis = (vb & 3u) == 2u;
         const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
         if (!vis_mask) continue;
         uint32_t pt = lane;
         V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
         if (vis) {
-            const float4 d4 = __ldcs(a.rl.dirl + base + i);
             pt = vb >> 2;
             const V3 v2cn = ld3(d4);
             rel = normalized(mk(dot(ld3(s_rx[w][pt]), v2cn), dot(ld3(s_ry[w][pt]), v2cn), dot(ld3(s_nrm[w][pt]), v2cn)));
@@ -1242,6 +1256,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
             }
             const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
+            if (queued) rl.tdir = rl.dirl;            // one record per ray: every ray is traced, in list order
             if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, width, height, rl, k.counters);
             else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
