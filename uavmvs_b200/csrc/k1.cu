@@ -750,6 +750,9 @@ __device__ __forceinline__ void prefetch_l2(const void * p)
 #endif
 }
 
+#ifndef K1_RAY_PREFETCH
+#define K1_RAY_PREFETCH 0      // measured: no change (3.80-3.85 ms either way)
+#endif
 #ifndef K1_MIN_BLOCKS
 #define K1_MIN_BLOCKS 8
 #endif
@@ -815,6 +818,13 @@ k_trace(TraceArgs a)
                 if (!has_ray && rank >= given && rank < given + take) { idx = pos + (rank - given); mine = true; }
                 pos += take; given += take;
             }
+#if K1_RAY_PREFETCH
+            // the records the next refills will hand out: in L2 by then (DRAM latency otherwise stalls the whole warp)
+            if (pos + lane < end) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(a.rl.tdir + pos + lane));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(a.rl.torg + pos + lane));
+            }
+#endif
             if (mine) {
                 const uint32_t slot = idx;
                 const float4 d4 = __ldcs(a.rl.tdir + idx);             // streamed once: keep L2 for the tree
