@@ -390,6 +390,28 @@ def run_b200(a, rank, local_rank, world):
             "sample": "%d of %d views (evenly strided) x all %d points, %.1f s; tree: %s (%.2f s, not timed); kernel "
                       "math: oracle port of libs/eval/kernels.cu, OpenMP over points" %
                       (len(vidx), V, n_local, r["seconds"], built_by, tree_s)}
+        # SURVEY.md 8(d) "second side reference": the reference's own kernels (libs/eval/kernels.cu + libs/cacc,
+        # compiled for sm_100a with its own flags as oracle/_ref/libref_cuda_fast.so) driven through its per-view
+        # launch loop on the same GPU, same scene, all views.  Reported beside the CPU baseline; not the headline.
+        try:
+            if orc.refcuda("fast") is not None:
+                t0 = time.time()
+                refc = orc.RefCuda(sc.verts, sc.faces, pts, nrm, kind="fast")
+                setup_s = time.time() - t0
+                views_all = sc.views28()
+                ref_ms = min(refc.time_evaluate(views_all, sc.max_distance, sc.width, sc.height, sc.target_recon)
+                             for _ in range(3))
+                ref_rows = refc.download()[0]
+                line["reference_cuda"] = {
+                    "value": rays / (ref_ms / 1e3), "unit": UNIT, "ms_per_step": ref_ms,
+                    "kind": "reference kernels (update_observation_rays per view, process, evaluate, func), nvcc "
+                            "--ftz=true --prec-div=false --prec-sqrt=false for sm_100a, acc::BVHTree built on the host "
+                            "(%.2f s incl. upload, not timed)" % setup_s,
+                    "observations": int(np.minimum(ref_rows, 0xFFFFFFFF).sum()),
+                    "note": "best of 3, CUDA events; rays counted by the product on the same scene"}
+                del refc
+        except Exception as e:                      # the side reference must never break the bench line
+            line["reference_cuda"] = {"unavailable": str(e)[:200]}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

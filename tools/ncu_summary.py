@@ -21,7 +21,12 @@ for i, h in enumerate(hdr):
 rows = list(csv.reader(open(src)))
 hdr = rows[1]
 ia, isrc, ie, ns, it = (hdr.index(x) for x in ('Address', 'Source', 'Instructions Executed', '# Samples', 'Avg. Threads Executed'))
-data = [(r[ia], r[isrc], int(r[ie] or 0), int(r[ns] or 0), r[it]) for r in rows[2:] if len(r) > ie]
+data = [(r[ia], r[isrc], int(r[ie] or 0), int(r[ns] or 0), r[it]) for r in rows[2:]
+        if len(r) > ie and (r[ie] or '0').isdigit() and (r[ns] or '0').isdigit()]
+for j in range(1, len(data)):          # several instances of the kernel in one report: keep the first
+    if data[j][0] == data[0][0]:
+        data = data[:j]
+        break
 tot = sum(d[2] for d in data); tots = sum(d[3] for d in data)
 print('total inst', tot, 'samples', tots, 'n sass', len(data))
 seglen = int(sys.argv[3]) if len(sys.argv) > 3 else 80
