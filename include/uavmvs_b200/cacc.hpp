@@ -67,10 +67,11 @@ public:
         UAVMVS_CHECK(uavmvs_bvh_create_from_arrays(nodes, aabbs, tris, indices, num_nodes, num_tris, &p->h));
         return p;
     }
-    /* B200-native alternative to the host SAH build: GPU LBVH from an indexed mesh */
+    /* B200-native alternative to the host SAH build (acc::BVHTree constructor, libs/acc/bvh_tree.h:335-399):
+     * the same sweep-SAH cost model evaluated on the GPU, from an indexed mesh */
     static Ptr build(const float * verts, uint32_t num_verts, const uint32_t * faces, uint32_t num_faces) {
         Ptr p(new BVHTree());
-        UAVMVS_CHECK(uavmvs_bvh_build_lbvh(verts, num_verts, faces, num_faces, &p->h));
+        UAVMVS_CHECK(uavmvs_bvh_build_sah(verts, num_verts, faces, num_faces, &p->h));
         return p;
     }
     Accessor accessor() const { Accessor a = {h}; return a; }

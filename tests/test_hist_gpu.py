@@ -202,3 +202,26 @@ def test_batched_k5_optimizer_inner_loop(api, oracle, setup):
         i_ref = oracle.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["sv"], h_b[b])
         assert abs(float(vmin[b]) - float(i_ref.min())) <= 1e-5 * np.abs(h_b[b]).sum() + 1e-12
     assert (vmin < 0).any()
+
+
+@pytest.mark.parametrize("max_distance", [-7.5, 0.0])
+def test_batched_k4_non_positive_max_distance(api, oracle, setup, max_distance):
+    """`scale = 1 - l / max_distance` (kernels.cu:310-311) with max_distance <= 0: a negative value puts nothing out of
+    range (the planner's swapped arguments pass a negative average there, plan_trajectory.cu:270-274), zero
+    rejects every point at positive distance.  The conservative block culls must not interfere."""
+    s = setup
+    sc, S = s["sc"], s["sv"].shape[0]
+    pos = np.array(POSITIONS[:3], np.float32)
+    hists = api.Array.create(len(pos) * S)
+    hists.null()
+    api.populate_spherical_histogram_batch(pos, max_distance, s["gbvh"], s["cloud"], s["gkd"], hists)
+    h_b = hists.download().reshape(len(pos), S)
+    for b in range(len(pos)):
+        h_ref, bins, scores = oracle.populate_spherical_histogram(s["obvh"], s["okd"], pos[b], max_distance,
+                                                                  sc.points, sc.normals, s["values"], s["quals"], S)
+        assert _hist_close(h_b[b], h_ref, bins, scores, S), b
+        single = api.Array.create(S)
+        single.null()
+        api.populate_spherical_histogram(pos[b], max_distance, s["gbvh"], s["cloud"], s["gkd"], single)
+        assert _hist_close(single.download(), h_ref, bins, scores, S), b
+    assert (h_b != 0).any() == (max_distance < 0)

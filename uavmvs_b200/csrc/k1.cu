@@ -621,7 +621,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
     const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
-    float max_distance, int width, int height, RayList rl, unsigned long long * counters)
+    float max_distance, float cull_distance, int width, int height, RayList rl, unsigned long long * counters)
 {
     __shared__ float4 s_v[K1_WARPS][32], s_n[K1_WARPS][32];
     __shared__ uint32_t s_q[K1_WARPS][64];
@@ -638,7 +638,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t * irow = inside_masks + (size_t)(blk >> 5) * num_views;
     const uint32_t mbit = blk & 31;
     const uint32_t base = rl.off[blk];
-    const float md2 = max_distance * max_distance * 1.00001f;
+    const float md2 = cull_distance * cull_distance * 1.00001f;
     const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
     uint32_t count = 0, qn = 0;
 
@@ -1214,8 +1214,12 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     }
 
     dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
+    // Histogram jobs test `1 - l / max_distance <= 0` (kernels.cu:310-311): with max_distance <= 0 (the planner's
+    // swapped arguments can pass a negative average there, plan_trajectory.cu:270-274) nothing is out of range, so the
+    // conservative range culls are switched off and the exact test decides alone.
+    const float cull_distance = (hj && !(max_distance > 0.0f)) ? INFINITY : max_distance;
     k_view_masks<<<mgrid, K1_WARPS * 32, 0, s>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
-        cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, max_distance, width, height, k.masks, inside_masks);
+        cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, cull_distance, width, height, k.masks, inside_masks);
     UAV_CUDA(cudaGetLastError());
 
     // view batches: [v0, v1) such that the upper bound of ray records fits the budget
@@ -1268,9 +1272,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
             if (queued) rl.tdir = rl.dirl;            // one record per ray: every ray is traced, in list order
             if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, width, height, rl, k.counters);
+                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
             else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, width, height, rl, k.counters);
+                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
             else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
