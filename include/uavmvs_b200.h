@@ -81,6 +81,15 @@ int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, const float 
 int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t num_nodes, uavmvs_kdtree ** out);
 int uavmvs_kdtree_destroy(uavmvs_kdtree * kd);
 
+/* Proxy-cloud sampler on the device: apps/generate_proxy_cloud/generate_proxy_cloud.cpp:84-184 (area * density samples
+ * per face from std::mt19937 seeded with 3 * face, face normals, sorted by 20-bit Z-order index with a lexicographic
+ * tie-break).  Same samples, same order as the reference tool; feed them to uavmvs_cloud_create. */
+typedef struct uavmvs_samples uavmvs_samples;
+int uavmvs_proxy_cloud_sample(const float * verts, uint32_t num_verts, const uint32_t * faces, uint32_t num_faces,
+    float samples_per_unit_area, uavmvs_samples ** out, uint32_t * num_samples);
+int uavmvs_proxy_cloud_download(const uavmvs_samples * samples, float * verts, float * normals);
+int uavmvs_proxy_cloud_destroy(uavmvs_samples * samples);
+
 /* ---- Point cloud: cacc::PointCloud<HOST>::create(n) + fill + <DEVICE>::create<HOST>,
  * libs/cacc/point_cloud.h:26-32, :91-114.  values/qualities may be NULL
  * (defaults 0 / 1, libs/util/cio.h:45-46). */

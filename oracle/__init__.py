@@ -107,6 +107,8 @@ def lib():
         _f32p, _f32p, _f64p, _opt(_u32p), _opt(_f32p)]
     L.orc_evaluate_spherical_histogram.argtypes = [_f32p, i32, i32, _f32p, u32, _f32p, _f32p, u32, u32]
     L.orc_estimate_capture_difficulty.argtypes = [_vp, f32, u32, _f32p, u32, _f32p, _f32p, u32, _f32p, _f32p]
+    L.orc_sample_proxy_cloud.restype = u32
+    L.orc_sample_proxy_cloud.argtypes = [_f32p, _u32p, u32, f32, _opt(_f32p), _opt(_f32p), u32]
     _LIB = L
     return L
 
@@ -533,3 +535,14 @@ def estimate_capture_difficulty(bvh, max_distance, mesh_size, sphere_verts, vert
     lib().orc_estimate_capture_difficulty(bvh.h, max_distance, mesh_size, sv, sv.shape[0],
                                           _c(verts, np.float32), _c(normals, np.float32), n, values, qualities)
     return values, qualities
+
+
+def sample_proxy_cloud(verts, faces, samples):
+    """apps/generate_proxy_cloud/generate_proxy_cloud.cpp:84-184 -> (points [n,3], normals [n,3]), Z-order sorted."""
+    verts = _c(verts, np.float32).reshape(-1, 3)
+    faces = _c(faces, np.uint32).reshape(-1, 3)
+    n = lib().orc_sample_proxy_cloud(verts, faces, faces.shape[0], samples, None, None, 0)
+    pts, nrm = np.empty((n, 3), np.float32), np.empty((n, 3), np.float32)
+    if n:
+        lib().orc_sample_proxy_cloud(verts, faces, faces.shape[0], samples, pts, nrm, n)
+    return pts, nrm

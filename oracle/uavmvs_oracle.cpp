@@ -33,6 +33,7 @@
 #include <limits>
 #include <map>
 #include <numeric>
+#include <random>
 #include <utility>
 #include <vector>
 
@@ -1091,6 +1092,82 @@ void orc_estimate_capture_difficulty(void * bvh, float max_distance, u32 mesh_si
         values[id] = min_theta;
         qualities[id] = sum / mx;
     }
+}
+
+/* ---- proxy-cloud sampler: apps/generate_proxy_cloud/generate_proxy_cloud.cpp:84-184 ----
+ * std::mt19937 / std::uniform_real_distribution<float> are the library's own, as in the reference.
+ * math::geom::triangle_area is MVE's (not under /root/reference): |(b - a) x (c - a)| / 2.
+ * Returns the number of samples; writes them (Z-order sorted, :144-184) when capacity suffices. */
+typedef uint64_t u64;
+static inline u64 z_spread(u64 x, u64 mask) {          /* libs/acc/math.h:19-45 */
+    x &= mask;
+    x = (x * 0x100000001ull) & 0x003F00000000FFFFull;
+    x = (x * 0x10001ull) & 0x003F0000FF0000FFull;
+    x = (x * 0x101ull) & 0x300F00F00F00F00Full;
+    x = (x * 0x11ull) & 0x30C30C30C30C30C3ull;
+    return (x * 0x5ull) & 0x9249249249249249ull;
+}
+
+u32 orc_sample_proxy_cloud(float const * verts, u32 const * faces, u32 num_faces, float samples,
+    float * out_v, float * out_n, u32 capacity)
+{
+    std::uniform_real_distribution<float> dist(0.0f, 1.0f);
+    std::mt19937 gen;
+    std::vector<V3> pts, nrm;
+    for (std::size_t i = 0; i < 3 * (std::size_t)num_faces; i += 3) {
+        gen.seed(i);                                     /* :107 */
+        V3 v0 = ld3(verts, faces[i]), v1 = ld3(verts, faces[i + 1]), v2 = ld3(verts, faces[i + 2]);
+        V3 c = cross(sub(v1, v0), sub(v2, v0));
+        float len = norm(c);
+        V3 normal = divs(c, len);
+        float area = len / 2.0f;
+        float face_samples = area * samples;
+        unsigned num_face_samples = face_samples;
+        if (dist(gen) < (face_samples - static_cast<float>(num_face_samples))) num_face_samples += 1;
+        for (unsigned j = 0; j < num_face_samples; ++j) {
+            float r1 = dist(gen);
+            float r2 = dist(gen);
+            float tmp = std::sqrt(r1);
+            float u = 1.0f - tmp;
+            float v = r2 * tmp;
+            float w = 1.0f - v - u;
+            pts.push_back(add(add(mul(v0, u), mul(v1, v)), mul(v2, w)));
+            nrm.push_back(normal);
+        }
+    }
+    std::size_t n = pts.size();
+    if (n == 0 || n > capacity || !out_v || !out_n) return (u32)n;
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (std::size_t i = 0; i < n; ++i) {
+        float p[3] = {pts[i].x, pts[i].y, pts[i].z};
+        for (int j = 0; j < 3; ++j) { mn[j] = std::min(mn[j], p[j]); mx[j] = std::max(mx[j], p[j]); }
+    }
+    double scale[3], bias[3];
+    for (int i = 0; i < 3; ++i) {
+        double div = (mx[i] - mn[i]);
+        scale[i] = 1.0 / div * (double(1 << 20) - 1.0);
+        bias[i] = - mn[i] / div * (double(1 << 20) - 1.0);
+    }
+    std::vector<u64> zkey(n);
+    for (std::size_t i = 0; i < n; ++i) {
+        float p[3] = {pts[i].x, pts[i].y, pts[i].z};
+        u32 q[3];
+        for (int j = 0; j < 3; ++j) q[j] = scale[j] * p[j] + bias[j];
+        zkey[i] = z_spread(q[0], 0x3FFFFFull) | (z_spread(q[1], 0x1FFFFFull) << 1) | (z_spread(q[2], 0x1FFFFFull) << 2);
+    }
+    std::vector<std::size_t> idx(n);
+    std::iota(idx.begin(), idx.end(), 0);
+    std::stable_sort(idx.begin(), idx.end(), [&](std::size_t li, std::size_t ri) -> bool {
+        if (zkey[li] != zkey[ri]) return (zkey[li] < zkey[ri]);
+        float a[3] = {pts[li].x, pts[li].y, pts[li].z}, b[3] = {pts[ri].x, pts[ri].y, pts[ri].z};
+        return std::lexicographical_compare(a, a + 3, b, b + 3);
+    });
+    for (std::size_t i = 0; i < n; ++i) {
+        V3 p = pts[idx[i]], q = nrm[idx[i]];
+        out_v[3 * i] = p.x; out_v[3 * i + 1] = p.y; out_v[3 * i + 2] = p.z;
+        out_n[3 * i] = q.x; out_n[3 * i + 1] = q.y; out_n[3 * i + 2] = q.z;
+    }
+    return (u32)n;
 }
 
 }  // extern "C"

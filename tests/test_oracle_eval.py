@@ -144,3 +144,22 @@ def test_histogram_image_counts_bins_in_frustum(oracle):
     np.add.at(merged, first[inv.reshape(-1)], ones)
     img2 = oracle.evaluate_spherical_histogram(K.astype(np.float32), 1920, 1080, sv, merged)
     assert np.array_equal(img, img2)
+
+
+def test_oracle_sampler_known_answers(oracle):
+    """generate_proxy_cloud.cpp:84-184 restated: one unit-area triangle at density d yields floor(d) or floor(d) + 1
+    samples, all inside the triangle, with its normal; two identical meshes give identical clouds (seed = 3 * face)."""
+    verts = np.array([[0, 0, 0], [2, 0, 0], [0, 1, 0], [10, 0, 0], [12, 0, 0], [10, 1, 0]], np.float32)
+    faces = np.array([[0, 1, 2], [3, 4, 5]], np.uint32)
+    p, n = oracle.sample_proxy_cloud(verts, faces, 40.5)
+    assert 80 <= len(p) <= 82
+    assert np.array_equal(n, np.tile(np.array([0, 0, 1], np.float32), (len(p), 1)))
+    left = p[p[:, 0] < 5]
+    assert np.all(left[:, 0] >= 0) and np.all(left[:, 1] >= 0) and np.all(left[:, 0] / 2 + left[:, 1] <= 1 + 1e-6)
+    assert np.all(p[:, 2] == 0)
+    p2, _ = oracle.sample_proxy_cloud(verts, faces, 40.5)
+    assert np.array_equal(p, p2)
+    # the Z-order key (libs/acc/math.h:19-45) is monotone in x on a line: samples with y = z = 0 come out x-sorted
+    line = np.array([[0, 0, 0], [1, 0, 0], [0, 1e-9, 0]], np.float32)
+    q, _ = oracle.sample_proxy_cloud(line, np.array([[0, 1, 2]], np.uint32), 4e10)
+    assert len(q) > 5

@@ -438,3 +438,17 @@ def estimate_capture_difficulty(max_distance, bvh_tree, mesh_size, kd_tree, clou
     """libs/eval/kernels.h:81-84"""
     _check(_lib.uavmvs_estimate_capture_difficulty(_stream_ptr(stream), _f32(max_distance), bvh_tree.ptr,
                                                    _u32(mesh_size), kd_tree.ptr, cloud.ptr))
+
+
+def sample_proxy_cloud(verts, faces, samples_per_unit_area):
+    """generate_proxy_cloud.cpp:84-184 on the device -> (points [n,3], normals [n,3]) float32, Z-order sorted."""
+    verts, faces = _f(verts, (-1, 3)), _u(faces).reshape(-1, 3)
+    h, n = _vp(), _u32(0)
+    _check(_lib.uavmvs_proxy_cloud_sample(_p(verts), _u32(verts.shape[0]), _p(faces), _u32(faces.shape[0]),
+                                          _f32(samples_per_unit_area), C.byref(h), C.byref(n)))
+    pts, nrm = np.empty((n.value, 3), np.float32), np.empty((n.value, 3), np.float32)
+    try:
+        _check(_lib.uavmvs_proxy_cloud_download(h, _p(pts), _p(nrm)))
+    finally:
+        _lib.uavmvs_proxy_cloud_destroy(h)
+    return pts, nrm
