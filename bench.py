@@ -52,9 +52,9 @@ def parse():
 
 
 def workload_name(a, world):
-    return ("config2: synthetic urban block %.0f m, %d-triangle mesh, %d proxy points per GPU x %d GPU, "
+    return ("%s: synthetic urban block %.0f m, %d-triangle mesh, %d proxy points per GPU x %d GPU, "
             "%d views, max_distance 80, 1920x1080, full evaluation K1+K2+K3+K8+K9" %
-            (a.extent, a.tris, a.points, world, a.views))
+            ("config5" if a.tris >= 5_000_000 else "config2", a.extent, a.tris, a.points, world, a.views))
 
 
 def make_scene(a, world):
@@ -63,12 +63,16 @@ def make_scene(a, world):
 
 
 def my_points(sc, rank, world):
-    """Interleaved Z-order chunks: chunk c belongs to rank c % world (balanced visible-pair density)."""
+    """Interleaved Z-order chunks: every run of `world` consecutive chunks gives one chunk to each rank, and the
+    owner within the run rotates pseudo-randomly from run to run.  (Plain `chunk % world` aliases with the street
+    grid of the city scene: on config 5 one rank received the expensive street-canyon points and took 1.6x the
+    time of the others for the same number of rays.)"""
     n = sc.num_points
     if world == 1:
         return np.arange(n)
-    chunks = np.arange((n + CHUNK - 1) // CHUNK)
-    mine = chunks[chunks % world == rank]
+    chunks = np.arange((n + CHUNK - 1) // CHUNK, dtype=np.uint64)
+    rot = ((chunks // np.uint64(world)) * np.uint64(2654435761) >> np.uint64(7)) % np.uint64(world)
+    mine = chunks[(chunks + rot) % np.uint64(world) == np.uint64(rank)].astype(np.int64)
     idx = (mine[:, None] * CHUNK + np.arange(CHUNK)[None, :]).reshape(-1)
     return idx[idx < n]
 
@@ -327,10 +331,26 @@ def run_b200(a, rank, local_rank, world):
     barrier()
 
     # max over ranks of the device time; sums of the work
+    rank_ms = [ms / a.steps]
     if world > 1:
+        mine = torch.tensor([ms / a.steps, float(k_ms[0]) / a.steps, float(stats[0]), float(stats[3])], dtype=torch.float64, device="cuda")
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        rank_ms = [[round(float(x), 4) for x in e.tolist()] for e in every]     # per rank: step ms, K1 ms, rays, pairs after the block cull
         t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_ms = t.tolist()
+        # every rank watched its own GPU: the line reports the slowest clock and the union of the throttle reasons
+        bits = {"hw_slowdown": 1, "hw_thermal_slowdown": 2, "sw_thermal_slowdown": 4, "sw_power_cap": 8}
+        c = torch.tensor([clocks["sm_mhz"] or 0.0, float(sum(bits[r] for r in clocks["reasons"]))],
+                         dtype=torch.float64, device="cuda")
+        call = [torch.zeros_like(c) for _ in range(world)]
+        dist.all_gather(call, c)
+        mhz = [float(x[0]) for x in call]
+        mask = 0
+        for x in call:
+            mask |= int(x[1])
+        clocks = dict(clocks, sm_mhz=min(mhz), sm_mhz_per_rank=mhz, reasons=sorted(r for r, b in bits.items() if mask & b))
     res = sharded.combine_scores(s_sum, s_min, s_max, n_local, stats)
     rays, observations, pairs, pairs_after_block_cull = res["stats"]
     pairs = res["points"] * V                                  # every (point, view) pair is evaluated
@@ -344,8 +364,8 @@ def run_b200(a, rank, local_rank, world):
             "config": {"workload": workload_name(a, world), "tree": "GPU %s (uavmvs_bvh_build_%s, %.3f s, not timed)"
                        % (a.tree.upper(), a.tree, build_s), "l2": "flushed between steps (256 MiB fill)", "rays_per_step": rays,
                        "observations_per_step": observations, "pairs_per_step": pairs,
-                       "sharding": "replicated mesh, interleaved %d-point Z-order chunks, 1 score all-reduce" % CHUNK},
-            "pairs_per_s": pairs * a.steps / sec, "score": res["score"],
+                       "sharding": "replicated mesh, interleaved %d-point Z-order chunks (rotating owner), 1 score all-reduce" % CHUNK},
+            "pairs_per_s": pairs * a.steps / sec, "score": res["score"], "per_rank_ms_k1ms_rays_pairs": rank_ms,
             "stage_ms": {"K1": k1_ms, "K2": float(k_ms[1]) / a.steps, "K3_K8": float(k_ms[2]) / a.steps,
                          "K9": float(k_ms[3]) / a.steps},
             "e2e": {"value": rays * a.steps / e2e_sec, "unit": UNIT, "ms_per_step": e2e_ms / a.steps,
