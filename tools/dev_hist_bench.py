@@ -13,7 +13,7 @@ ap.add_argument("--single", type=int, default=64)
 args = ap.parse_args()
 sc = scenes.urban(1_000_000, 1_000_000, 2000, 256.0)
 torch.cuda.init()
-bvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+bvh = api.BVHTree.build_sah(sc.verts, sc.faces)
 rng = np.random.default_rng(4)
 values = rng.uniform(0.0, 1.2, sc.num_points).astype(np.float32)
 quals = rng.uniform(0.0, 1.0, sc.num_points).astype(np.float32)

@@ -12,7 +12,7 @@ ap.add_argument("--check", type=int, default=2000)
 args = ap.parse_args()
 sc = scenes.urban(1_000_000, 1_000_000, 16, 256.0)
 torch.cuda.init()
-bvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+bvh = api.BVHTree.build_sah(sc.verts, sc.faces)
 n = args.points
 idx = np.sort(np.random.default_rng(0).choice(sc.num_points, n, replace=False))
 pts, nrm = sc.points[idx], sc.normals[idx]

@@ -13,7 +13,7 @@ ap.add_argument("--interleave", type=int, default=4096)
 args = ap.parse_args()
 sc = scenes.urban(1_000_000, 1_000_000, 2000, 256.0)
 torch.cuda.init()
-bvh = api.BVHTree.build_ploc(sc.verts, sc.faces)
+bvh = api.BVHTree.build_sah(sc.verts, sc.faces)
 views = api.DeviceViews(sc.views28())
 K = args.shards
 n = sc.num_points
