@@ -146,6 +146,18 @@ int uavmvs_update_observation_rays_batch_device(void * stream, int populate, con
 int uavmvs_process_observation_rays(void * stream, uavmvs_obs * obs);
 /* ---- K3 evaluate_observation_rays, kernels.h:41-44, kernels.cu:266-291 */
 int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavmvs_array * recons);
+/* ---- K2 + K3 + K8 for the columns that changed: the optimiser's re-evaluation after it removed or re-added a few
+ * views (apps/optimize_trajectory/optimize_trajectory.cu:313-345 and :499-529 run process_observation_rays,
+ * evaluate_observation_rays and calculate_func_recons over ALL points every iteration).  Every observation array keeps
+ * one flag per 32 columns, set by update_observation_rays (either direction) when a column of the block received or
+ * lost a row, and by clear / upload / mark_dirty for all blocks; this call runs the three kernels on the flagged blocks
+ * only and clears the flags.  Result identical to the three full launches PROVIDED `recons` (and `wrecons`, may be NULL)
+ * are the arrays, and target_recon the value, of the previous call for this observation array (the first call after
+ * create / clear / upload evaluates everything). */
+int uavmvs_reevaluate_observation_rays(void * stream, uavmvs_obs * obs, uavmvs_array * recons, float target_recon,
+    uavmvs_array * wrecons);
+/* Flags every column as changed (after writing through uavmvs_obs_device_ptr pointers). */
+int uavmvs_obs_mark_dirty(void * stream, uavmvs_obs * obs);
 /* ---- K8 calculate_func_recons, kernels.h:86-91, kernels.cu:496-510 */
 int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon,
     uavmvs_array * wrecons);

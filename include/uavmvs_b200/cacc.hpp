@@ -216,6 +216,12 @@ inline void evaluate_observation_rays(cacc::Stream stream, cacc::VectorArray<cac
     cacc::Array<float, cacc::DEVICE>::Data recons) {
     UAVMVS_CHECK(uavmvs_evaluate_observation_rays(stream, obs_rays.h, recons.h));
 }
+/* process + evaluate + calculate_func_recons on the columns update_observation_rays changed since the last call
+ * (the optimiser's per-iteration re-evaluation, optimize_trajectory.cu:313-345, :499-529); same arrays every call. */
+inline void reevaluate_observation_rays(cacc::Stream stream, cacc::VectorArray<cacc::Vec3f, cacc::DEVICE>::Data obs_rays,
+    cacc::Array<float, cacc::DEVICE>::Data recons, float target_recon, cacc::Array<float, cacc::DEVICE>::Data wrecons) {
+    UAVMVS_CHECK(uavmvs_reevaluate_observation_rays(stream, obs_rays.h, recons.h, target_recon, wrecons.h));
+}
 inline void populate_spherical_histogram(cacc::Stream stream, cacc::Vec3f view_pos, float max_distance,
     cacc::BVHTree<cacc::DEVICE>::Accessor bvh_tree, cacc::PointCloud<cacc::DEVICE>::Data cloud,
     cacc::KDTree<3u, cacc::DEVICE>::Accessor kd_tree, cacc::Array<float, cacc::DEVICE>::Data sphere_hist) {

@@ -175,6 +175,60 @@ def test_remove_views(api, oracle, tiny_scene, tiny_tree):
     assert _valid_rows_equal(obs_o.data, data, rows, 32)
 
 
+def test_reevaluate_only_changed_columns(api, oracle, tiny_scene, tiny_tree):
+    """uavmvs_reevaluate_observation_rays = process + evaluate + calculate_func_recons on the blocks K1 touched
+    (the optimiser's per-iteration re-evaluation, optimize_trajectory.cu:313-345, :499-529): identical to the
+    three full launches after every step of remove -> re-evaluate -> re-add elsewhere -> re-evaluate."""
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    views = sc.views28()
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    n = sc.num_points
+    obs, obs_full = api.VectorArray.create(n, 32), api.VectorArray.create(n, 32)
+    rec, wrec = api.Array.create(n), api.Array.create(n)
+    rec_f, wrec_f = api.Array.create(n), api.Array.create(n)
+    obs_o = oracle.ObsRays(n, 32)
+
+    def step(populate, v):
+        oracle.update_observation_rays(obvh, populate, v, sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+        oracle.process_observation_rays(obs_o)
+        for o in (obs, obs_full):
+            api.update_observation_rays_batch(populate, v, sc.max_distance, sc.width, sc.height, gbvh, cloud, o)
+        api.reevaluate_observation_rays(obs, rec, sc.target_recon, wrec)
+        api.process_observation_rays(obs_full)
+        api.evaluate_observation_rays(obs_full, rec_f)
+        api.calculate_func_recons(rec_f, sc.target_recon, wrec_f)
+        d_i, r_i = obs.download()
+        d_f, r_f = obs_full.download()
+        assert np.array_equal(r_i, r_f) and np.array_equal(r_i, obs_o.num_rows)
+        assert _valid_rows_equal(d_f, d_i, r_i, 32) and _valid_rows_equal(obs_o.data, d_i, r_i, 32)
+        assert np.array_equal(rec.download().view(np.uint32), rec_f.download().view(np.uint32))     # same kernel, same bits
+        assert np.array_equal(wrec.download().view(np.uint32), wrec_f.download().view(np.uint32))
+        assert _close(rec.download(), oracle.evaluate_observation_rays(obs_o))
+
+    step(True, views)                       # first call: every block is flagged
+    step(False, views[[3, 11]])             # two views removed: few blocks flagged
+    moved = views[[3, 11]].copy()
+    moved[:, 0:3] += np.float32(1.5)
+    for k in range(2):                      # w2c translation column for the moved centre
+        w2c = moved[k, 3:19].reshape(4, 4).copy()
+        w2c[:3, 3] = -(w2c[:3, :3].astype(np.float64) @ moved[k, :3].astype(np.float64))
+        moved[k, 3:19] = w2c.reshape(16)
+    step(True, moved)
+    # nothing changed: a further call touches nothing and keeps the arrays
+    before = rec.download().copy()
+    api.reevaluate_observation_rays(obs, rec, sc.target_recon, wrec)
+    assert np.array_equal(before.view(np.uint32), rec.download().view(np.uint32))
+    # poisoned result arrays stay poisoned where no block is flagged, are rewritten after mark_dirty
+    rec.upload(np.full(n, 123.0, np.float32))
+    api.reevaluate_observation_rays(obs, rec, sc.target_recon, wrec)
+    assert np.all(rec.download() == 123.0)
+    obs.mark_dirty()
+    api.reevaluate_observation_rays(obs, rec, sc.target_recon, wrec)
+    assert np.array_equal(before.view(np.uint32), rec.download().view(np.uint32))
+
+
 def test_evaluate_trajectory_fused(api, oracle, tiny_scene, tiny_tree):
     sc = tiny_scene
     obvh, arrays = tiny_tree

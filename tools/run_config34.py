@@ -24,6 +24,7 @@ ap.add_argument("--grid", type=int, default=128)
 ap.add_argument("--batch", type=int, default=8192)
 ap.add_argument("--limit", type=int, default=0, help="config 4: stop after this many positions (0 = all)")
 ap.add_argument("--iters", type=int, default=10)
+ap.add_argument("--full-eval", action="store_true", help="config 3: K2/K3/K8 over all points (the reference's launches) instead of the changed blocks")
 ap.add_argument("--skip3", action="store_true")
 ap.add_argument("--skip4", action="store_true")
 args = ap.parse_args()
@@ -56,11 +57,18 @@ if not args.skip3:
     V = views.shape[0]
     obs = api.VectorArray.create(N, 32)
     recons, wrecons = api.Array.create(N), api.Array.create(N)
+
+    def reeval():
+        if args.full_eval:
+            api.process_observation_rays(obs)
+            api.evaluate_observation_rays(obs, recons)
+            api.calculate_func_recons(recons, sc.target_recon, wrecons)
+        else:
+            api.reevaluate_observation_rays(obs, recons, sc.target_recon, wrecons)
+
     obs.null()
     api.update_observation_rays_batch(True, views, sc.max_distance, sc.width, sc.height, bvh, cloud, obs)
-    api.process_observation_rays(obs)
-    api.evaluate_observation_rays(obs, recons)
-    api.calculate_func_recons(recons, sc.target_recon, wrecons)
+    reeval()
     score0 = api.reduce(wrecons)[0] / N
     gen = np.random.default_rng(7)
     iters_left = np.full(V, 100.0)
@@ -96,8 +104,7 @@ if not args.skip3:
         e[0].record()
         api.update_observation_rays_batch(False, views[sel], sc.max_distance, sc.width, sc.height, bvh, cloud, obs)
         e[1].record()
-        api.process_observation_rays(obs)
-        api.evaluate_observation_rays(obs, recons)
+        reeval()
         e[2].record()
         hists.null()
         api.populate_spherical_histogram_batch(cand, sc.max_distance, bvh, cloud, kd, hists,
@@ -116,9 +123,7 @@ if not args.skip3:
             w2c[:3, 3] = -(R.astype(np.float64) @ newpos[k].astype(np.float64))
             moved[k, 3:19] = w2c.reshape(16)
         api.update_observation_rays_batch(True, moved, sc.max_distance, sc.width, sc.height, bvh, cloud, obs)
-        api.process_observation_rays(obs)
-        api.evaluate_observation_rays(obs, recons)
-        api.calculate_func_recons(recons, sc.target_recon, wrecons)
+        reeval()
         score = api.reduce(wrecons)[0] / N
         e[5].record()
         torch.cuda.synchronize()
@@ -127,20 +132,21 @@ if not args.skip3:
         rays = api.k1_counters()[3]
         ms = [e[i].elapsed_time(e[i + 1]) for i in range(5)]
         rows.append({"views": len(sel), "candidates": B, "rays": rays, "ms_total": e[0].elapsed_time(e[5]),
-                     "ms_remove_K1": ms[0], "ms_K2_K3": ms[1], "ms_K5_batch": ms[2], "ms_K6_argmin": ms[3],
+                     "ms_remove_K1": ms[0], "ms_K2_K3_K8": ms[1], "ms_K5_batch": ms[2], "ms_K6_argmin": ms[3],
                      "ms_readd_K1_K2_K3_K8_K9": ms[4], "score": score})
-        print("config3 iter %d: %d views, %d candidates, %.2f ms (remove %.2f, K2+K3 %.2f, K5 %.2f, K6 %.3f, re-add+eval %.2f), "
+        print("config3 iter %d: %d views, %d candidates, %.2f ms (remove %.2f, K2+K3+K8 %.2f, K5 %.2f, K6 %.3f, re-add+eval %.2f), "
               "%d rays, score %.6f" % (it, len(sel), B, rows[-1]["ms_total"], *ms, rays, score), flush=True)
     timed = rows[2:]
     med = lambda k: float(np.median([r[k] for r in timed]))
     out3 = {"config": "3: optimiser inner loop on the config-2 state (1M triangles, 1M points, 2000 views resident)",
+            "re_evaluation": "all points (reference launches)" if args.full_eval else "changed 32-point blocks only (uavmvs_reevaluate_observation_rays)",
             "independence": independence, "views_per_iteration": med("views"), "candidates_per_iteration": med("candidates"),
             "iterations_timed": len(timed), "ms_per_iteration_median": med("ms_total"),
             "stage_ms_median": {k: med(k) for k in timed[0] if k.startswith("ms_") and k != "ms_total"},
             "rays_per_iteration_median": med("rays"),
             "rays_per_s": med("rays") / med("ms_total") * 1e3, "score_before": score0, "score_after": rows[-1]["score"],
             "tree_build_s": build_s, "iterations": rows}
-    json.dump(out3, open("gpurun_out/%s_config3.json" % args.tag, "w"), indent=1)
+    json.dump(out3, open("gpurun_out/%s_config3%s.json" % (args.tag, "_full" if args.full_eval else ""), "w"), indent=1)
     print("config3:", json.dumps({k: v for k, v in out3.items() if k != "iterations"}), flush=True)
     del obs, recons, wrecons, hists, cloud
 

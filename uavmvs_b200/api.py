@@ -235,6 +235,9 @@ class VectorArray(_Handle):
     def null(self, stream=None):
         _check(_lib.uavmvs_obs_clear(_stream_ptr(stream), self.ptr))
 
+    def mark_dirty(self, stream=None):
+        _check(_lib.uavmvs_obs_mark_dirty(_stream_ptr(stream), self.ptr))
+
     def download(self, data=True, rows_out=None):
         d = np.empty((self.max_rows, self.num_cols, 4), np.float32) if data else None
         r = np.empty(self.num_cols, np.uint32) if rows_out is None else rows_out
@@ -323,6 +326,13 @@ def process_observation_rays(obs_rays, stream=None):
 def evaluate_observation_rays(obs_rays, recons, stream=None):
     """libs/eval/kernels.h:41-44"""
     _check(_lib.uavmvs_evaluate_observation_rays(_stream_ptr(stream), obs_rays.ptr, recons.ptr))
+
+
+def reevaluate_observation_rays(obs_rays, recons, target_recon=0.0, wrecons=None, stream=None):
+    """K2 + K3 (+ K8) on the 32-column blocks update_observation_rays touched since the last call
+    (the re-evaluation of apps/optimize_trajectory/optimize_trajectory.cu:313-345, :499-529)."""
+    _check(_lib.uavmvs_reevaluate_observation_rays(_stream_ptr(stream), obs_rays.ptr, recons.ptr, _f32(target_recon),
+                                                   None if wrecons is None else wrecons.ptr))
 
 
 def calculate_func_recons(recons, target_recon, wrecons, stream=None):

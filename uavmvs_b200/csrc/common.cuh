@@ -123,6 +123,7 @@ struct uavmvs_obs {
     uint64_t pitch;          // bytes
     float4 * data;
     uint32_t * num_rows;
+    uint32_t * dirty;        // one word per 32 columns: a column of the block changed since the last incremental evaluation
 };
 
 struct uavmvs_array { uint32_t n; float * data; };

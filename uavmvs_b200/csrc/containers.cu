@@ -250,6 +250,8 @@ int uavmvs_obs_create(uint32_t num_cols, uint32_t max_rows, uavmvs_obs ** out)
     UAV_CUDA(cudaMalloc(&o->num_rows, 4 * (size_t)num_cols));
     UAV_CUDA(cudaMemset(o->data, 0, o->pitch * max_rows));
     UAV_CUDA(cudaMemset(o->num_rows, 0, 4 * (size_t)num_cols));
+    UAV_CUDA(cudaMalloc(&o->dirty, 4 * (size_t)divup(num_cols, 32)));
+    UAV_CUDA(cudaMemset(o->dirty, 0xff, 4 * (size_t)divup(num_cols, 32)));
     *out = o;
     return 0;
 }
@@ -259,6 +261,14 @@ int uavmvs_obs_clear(void * stream, uavmvs_obs * o)
     UAV_REQUIRE(o, "null obs");
     UAV_CUDA(cudaMemsetAsync(o->data, 0, o->pitch * o->max_rows, (cudaStream_t)stream));
     UAV_CUDA(cudaMemsetAsync(o->num_rows, 0, 4 * (size_t)o->num_cols, (cudaStream_t)stream));
+    UAV_CUDA(cudaMemsetAsync(o->dirty, 0xff, 4 * (size_t)divup(o->num_cols, 32), (cudaStream_t)stream));
+    return 0;
+}
+
+int uavmvs_obs_mark_dirty(void * stream, uavmvs_obs * o)
+{
+    UAV_REQUIRE(o, "null obs");
+    UAV_CUDA(cudaMemsetAsync(o->dirty, 0xff, 4 * (size_t)divup(o->num_cols, 32), (cudaStream_t)stream));
     return 0;
 }
 
@@ -277,6 +287,7 @@ int uavmvs_obs_upload(uavmvs_obs * o, const float * data, const uint32_t * num_r
     if (data) UAV_CUDA(cudaMemcpy2D(o->data, o->pitch, data, (size_t)o->num_cols * 16,
         (size_t)o->num_cols * 16, o->max_rows, cudaMemcpyHostToDevice));
     if (num_rows) UAV_CUDA(cudaMemcpy(o->num_rows, num_rows, 4 * (size_t)o->num_cols, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemset(o->dirty, 0xff, 4 * (size_t)divup(o->num_cols, 32)));
     return 0;
 }
 
@@ -292,7 +303,7 @@ int uavmvs_obs_device_ptr(const uavmvs_obs * o, int which, void ** ptr, uint64_t
 int uavmvs_obs_destroy(uavmvs_obs * o)
 {
     if (!o) return 0;
-    cudaFree(o->data); cudaFree(o->num_rows);
+    cudaFree(o->data); cudaFree(o->num_rows); cudaFree(o->dirty);
     delete o;
     return 0;
 }

@@ -27,8 +27,10 @@ constexpr int SE_TILE_STRIDE = 33;      // float4 per tile row: padding against 
 template <bool DO_SORT, bool DO_EVAL>
 __global__ void __launch_bounds__(SE_THREADS)
 k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t stride, uint32_t n,
-    float * __restrict__ recons, float target, float * __restrict__ wrecons, Heur h)
+    float * __restrict__ recons, float target, float * __restrict__ wrecons, Heur h, uint32_t * dirty)
 {
+    // incremental form: only blocks in which K1 added or invalidated a row since the last incremental pass
+    if (dirty && dirty[blockIdx.x] == 0u) return;
     __shared__ float4 s_tile[32 * SE_TILE_STRIDE];
     __shared__ float4 s_col[SE_THREADS / 32][32];
     __shared__ uint32_t s_rows[32], s_valid[32];
@@ -125,6 +127,7 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
             }
         }
     }
+    if (dirty && threadIdx.x == 0) dirty[blockIdx.x] = 0u;     // every thread read the flag before the first barrier
     if (DO_SORT) {
         __syncthreads();
         for (uint32_t r = w; r < rmax; r += SE_THREADS / 32)
@@ -212,8 +215,9 @@ static int ensure_scratch(size_t view_floats)
 }
 
 static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_obs * obs, uavmvs_array * recons,
-    float target, uavmvs_array * wrecons)
+    float target, uavmvs_array * wrecons, bool incremental = false)
 {
+    uint32_t * dirty = (incremental && obs) ? obs->dirty : nullptr;
     UAV_REQUIRE(obs, "null handle");
     UAV_REQUIRE(!do_eval || (recons && recons->n == obs->num_cols), "recons size != obs columns");
     UAV_REQUIRE(!wrecons || wrecons->n == obs->num_cols, "wrecons size != obs columns");
@@ -221,11 +225,11 @@ static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_o
     const uint32_t stride = (uint32_t)(obs->pitch / sizeof(float4));
     float * r = recons ? recons->data : nullptr, * wr = wrecons ? wrecons->data : nullptr;
     if (do_sort && do_eval)
-        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
+        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
     else if (do_sort)
-        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
+        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
     else
-        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur);
+        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -304,6 +308,13 @@ int uavmvs_process_observation_rays(void * stream, uavmvs_obs * obs)
 int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavmvs_array * recons)
 {
     return launch_sort_eval((cudaStream_t)stream, false, true, const_cast<uavmvs_obs *>(obs), recons, 0.0f, nullptr);
+}
+
+int uavmvs_reevaluate_observation_rays(void * stream, uavmvs_obs * obs, uavmvs_array * recons, float target_recon,
+    uavmvs_array * wrecons)
+{
+    UAV_REQUIRE(obs && recons, "null argument");
+    return launch_sort_eval((cudaStream_t)stream, true, true, obs, recons, target_recon, wrecons, true);
 }
 
 int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon, uavmvs_array * wrecons)

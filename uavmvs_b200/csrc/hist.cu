@@ -236,21 +236,29 @@ __global__ void k_frustum_bits(const float * __restrict__ K9, int width, int hei
     }
 }
 
-// One CTA per candidate position: histogram row staged in shared memory, a thread per orientation
-// pixel (strided), optional image output, first minimum / first maximum in row-major order (the
-// host loop of apps/optimize_trajectory/optimize_trajectory.cu:416-428 made a device reduction).
+// gridDim = (positions, parts): a CTA stages its position's histogram row in shared memory and takes one
+// contiguous part of the orientation pixels, a thread per pixel (strided); optional image output; first minimum /
+// first maximum in row-major order (the host loop of apps/optimize_trajectory/optimize_trajectory.cu:416-428 made a
+// device reduction).  Parts are combined by one 64-bit atomic per CTA on packed keys: min key = ordered(value) << 32 |
+// pixel (atomicMin: smallest value, then smallest pixel), max key = ordered(value) << 32 | ~pixel (atomicMax: largest
+// value, then smallest pixel).  Small batches (the optimiser's ~100 candidates) thus fill the GPU instead of
+// running 100 CTAs of 23 pixels per thread.
 constexpr int EVB_THREADS = 256;
+__device__ __forceinline__ uint32_t f2ord(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __global__ void __launch_bounds__(EVB_THREADS)
 k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_t words, uint32_t npix,
-    const float * __restrict__ sphere_hists, uint32_t S, float * __restrict__ images, float4 * __restrict__ best)
+    const float * __restrict__ sphere_hists, uint32_t S, float * __restrict__ images,
+    unsigned long long * __restrict__ best_min, unsigned long long * __restrict__ best_max)
 {
     extern __shared__ float s_h[];
     __shared__ float s_v[2][EVB_THREADS / 32]; __shared__ uint32_t s_i[2][EVB_THREADS / 32];
     const uint32_t b = blockIdx.x;
+    const uint32_t chunk = (npix + gridDim.y - 1) / gridDim.y;
+    const uint32_t p0 = blockIdx.y * chunk, p1 = min(npix, p0 + chunk);
     for (uint32_t i = threadIdx.x; i < words * 32; i += EVB_THREADS) s_h[i] = i < S ? sphere_hists[(size_t)b * S + i] : 0.0f;
     __syncthreads();
     float vmin = UAV_INF, vmax = -UAV_INF; uint32_t imin = UAV_NAI, imax = UAV_NAI;
-    for (uint32_t pix = threadIdx.x; pix < npix; pix += EVB_THREADS) {
+    for (uint32_t pix = p0 + threadIdx.x; pix < p1; pix += EVB_THREADS) {
         float sum = 0.0f;
         for (uint32_t wd = 0; wd < words; ++wd) {
             uint32_t m = __ldg(bits + (size_t)wd * npix + pix);
@@ -275,7 +283,9 @@ k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_
             if (s_v[0][k] < vmin || (s_v[0][k] == vmin && s_i[0][k] < imin)) { vmin = s_v[0][k]; imin = s_i[0][k]; }
             if (s_v[1][k] > vmax || (s_v[1][k] == vmax && s_i[1][k] < imax)) { vmax = s_v[1][k]; imax = s_i[1][k]; }
         }
-        best[b] = make_float4(vmin, __uint_as_float(imin), vmax, __uint_as_float(imax));
+        // a part without a comparable value (empty, NaN, or nothing below +inf / above -inf) leaves the initial key
+        if (imin != UAV_NAI) atomicMin(best_min + b, ((unsigned long long)f2ord(vmin + 0.0f) << 32) | imin);
+        if (imax != UAV_NAI) atomicMax(best_max + b, ((unsigned long long)f2ord(vmax + 0.0f) << 32) | (uint32_t)~imax);
     }
 }
 
@@ -425,19 +435,28 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
         memcpy(kd->fr_calib, calib, 9 * sizeof(float)); kd->fr_w = width; kd->fr_h = height;
         kd->fr_iw = image_width; kd->fr_ih = image_height;
     }
-    float4 * d_best;
-    UAV_CUDA(cudaMallocAsync(&d_best, sizeof(float4) * (size_t)num_positions, s));
-    k_evaluate_spherical_histogram_batch<<<num_positions, EVB_THREADS, words * 32 * sizeof(float), s>>>(kd->fr_bits, words, npix,
-        sphere_hists->data, S, images ? images->data : nullptr, d_best);
+    // pixel parts: enough CTAs for ~8 per SM when the batch is small; every thread keeps at least one pixel
+    uint32_t parts = divup(148u * 8u, num_positions);
+    parts = max(1u, min(parts, max(1u, npix / EVB_THREADS)));
+    unsigned long long * d_best;                      // [min keys | max keys]
+    UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long) * (size_t)num_positions, s));
+    UAV_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)num_positions, s));
+    UAV_CUDA(cudaMemsetAsync(d_best + num_positions, 0, sizeof(unsigned long long) * (size_t)num_positions, s));
+    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(kd->fr_bits, words, npix,
+        sphere_hists->data, S, images ? images->data : nullptr, d_best, d_best + num_positions);
     UAV_CUDA(cudaGetLastError());
     if (h_min || h_argmin || h_max || h_argmax) {
-        std::vector<float4> hb(num_positions);
-        UAV_CUDA(cudaMemcpyAsync(hb.data(), d_best, sizeof(float4) * (size_t)num_positions, cudaMemcpyDeviceToHost, s));
+        std::vector<unsigned long long> hb(2 * (size_t)num_positions);
+        UAV_CUDA(cudaMemcpyAsync(hb.data(), d_best, sizeof(unsigned long long) * hb.size(), cudaMemcpyDeviceToHost, s));
         UAV_CUDA(cudaStreamSynchronize(s));
+        auto ord2float = [](uint32_t o) { uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; float f; memcpy(&f, &u, 4); return f; };
         for (uint32_t i = 0; i < num_positions; ++i) {
-            uint32_t a, b; memcpy(&a, &hb[i].y, 4); memcpy(&b, &hb[i].w, 4);
-            if (h_min) h_min[i] = hb[i].x; if (h_argmin) h_argmin[i] = a;
-            if (h_max) h_max[i] = hb[i].z; if (h_argmax) h_argmax[i] = b;
+            const unsigned long long kmin = hb[i], kmax = hb[num_positions + i];
+            const bool has_min = kmin != ~0ull, has_max = kmax != 0ull;
+            if (h_min) h_min[i] = has_min ? ord2float((uint32_t)(kmin >> 32)) : INFINITY;
+            if (h_argmin) h_argmin[i] = has_min ? (uint32_t)kmin : 0xFFFFFFFFu;
+            if (h_max) h_max[i] = has_max ? ord2float((uint32_t)(kmax >> 32)) : -INFINITY;
+            if (h_argmax) h_argmax[i] = has_max ? ~(uint32_t)kmax : 0xFFFFFFFFu;
         }
     }
     UAV_CUDA(cudaFreeAsync(d_best, s));

@@ -958,6 +958,7 @@ struct RetireArgs {
     RayList rl;
     float max_distance;
     float4 * obs; uint32_t * num_rows; uint32_t max_rows; uint32_t stride;   // stride in float4
+    uint32_t * dirty;                // per 32-point block: some column received or lost a row (incremental K2/K3)
     unsigned long long * stats;
 };
 
@@ -990,6 +991,7 @@ k_retire(RetireArgs a)
     __syncwarp();
     const uint32_t base = a.rl.off[blk];
     unsigned long long st_vis = 0;
+    bool touched = false;
     // the next 32 records are fetched while the current ones are processed: an iteration is a chain of two
     // DRAM round trips (status byte, then direction) otherwise, and the kernel is latency bound
     uint32_t vb_next = lane < count ? (uint32_t)__ldcs(a.rl.vis + base + lane) : 0u;
@@ -1005,6 +1007,7 @@ k_retire(RetireArgs a)
         const bool vis = (vb & 3u) == 2u;
         const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
         if (!vis_mask) continue;
+        touched = true;
         uint32_t pt = lane;
         V3 rel = mk(0.f, 0.f, 0.f); float scale = 0.f;
         if (vis) {
@@ -1047,6 +1050,7 @@ k_retire(RetireArgs a)
         }
     }
     if (POPULATE && valid) a.num_rows[id] = s_cnt[w][lane];
+    if (touched && lane == 0 && a.dirty) a.dirty[blk] = 1u;
     if (a.stats) {
         for (int o = 16; o > 0; o >>= 1) st_vis += __shfl_xor_sync(0xffffffffu, st_vis, o);
         if (lane == 0) { atomicAdd(a.stats + 0, (unsigned long long)count); atomicAdd(a.stats + 1, st_vis); }
@@ -1288,7 +1292,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             ra.rl = rl; ra.max_distance = max_distance;
             ra.stats = d_stats;
             if (hj) {
-                ra.obs = nullptr; ra.num_rows = nullptr; ra.max_rows = 0; ra.stride = 0;
+                ra.obs = nullptr; ra.num_rows = nullptr; ra.max_rows = 0; ra.stride = 0; ra.dirty = nullptr;
                 if (hj->with_recon) k_retire_hist<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
                 else k_retire_hist<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
                 UAV_CUDA(cudaGetLastError());
@@ -1297,6 +1301,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             }
             ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
             ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
+            ra.dirty = obs->dirty;
             if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
             else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
             UAV_CUDA(cudaGetLastError());
