@@ -80,6 +80,11 @@ int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, const float 
  * libs/cacc/kd_tree.cu:15-45.  nodes[4n] = {vid,dim,left,right}, verts[3n]. */
 int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t num_nodes, uavmvs_kdtree ** out);
 int uavmvs_kdtree_destroy(uavmvs_kdtree * kd);
+/* cacc::nnsearch::find_nn<3> (libs/cacc/nnsearch.h:67-155) for n host queries [n][3] -> vertex indices (host).
+ * certified_lookup != 0 answers through the cube-map / neighbour-list shortcut the batched histogram path uses
+ * (kd.cuh); it must and does return the same indices, duplicates included - the parity tests compare the two. */
+int uavmvs_kdtree_find_nn(void * stream, uavmvs_kdtree * kd, const float * queries, uint64_t n, int certified_lookup,
+    uint32_t * out_idx);
 
 /* Proxy-cloud sampler on the device: apps/generate_proxy_cloud/generate_proxy_cloud.cpp:84-184 (area * density samples
  * per face from std::mt19937 seeded with 3 * face, face normals, sorted by 20-bit Z-order index with a lexicographic

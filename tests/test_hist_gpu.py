@@ -225,3 +225,62 @@ def test_batched_k4_non_positive_max_distance(api, oracle, setup, max_distance):
         api.populate_spherical_histogram(pos[b], max_distance, s["gbvh"], s["cloud"], s["gkd"], single)
         assert _hist_close(single.download(), h_ref, bins, scores, S), b
     assert (h_b != 0).any() == (max_distance < 0)
+
+
+def test_certified_nn_lookup_equals_kd_search(api, oracle, setup):
+    """The batched histogram path answers `find_nn` (libs/cacc/nnsearch.h:67-155) through a cube-map proposal certified
+    against neighbour lists, with a precomputed rule for which of two coincident icosphere vertices the depth-first
+    search meets first (kd.cuh).  It must return the SAME vertex index as the search, duplicates included."""
+    s = setup
+    kd, sv = s["gkd"], s["sv"].astype(np.float32)
+    rng = np.random.default_rng(11)
+    unit = lambda a: (a / np.linalg.norm(a, axis=1, keepdims=True)).astype(np.float32)
+    rand = unit(rng.normal(size=(3_000_000, 3)))
+    distinct = np.unique(sv, axis=0)
+    d = np.linalg.norm(distinct[:, None, :] - distinct[None, :, :], axis=2) + np.eye(len(distinct)) * 9.0
+    pairs = np.argwhere(d < 1.3 * d.min(axis=1, keepdims=True))                # neighbouring positions
+    mid = 0.5 * (distinct[pairs[:, 0]] + distinct[pairs[:, 1]])
+    bisector = unit(np.repeat(mid, 40, axis=0) + rng.normal(0, 2e-3, (len(mid) * 40, 3)))      # around the Voronoi edges
+    bisector_tight = unit(np.repeat(mid, 20, axis=0) + rng.normal(0, 1e-6, (len(mid) * 20, 3)))
+    at_vertex = np.concatenate([sv, unit(np.repeat(sv, 60, axis=0) + rng.normal(0, 5e-3, (len(sv) * 60, 3))),
+                                unit(np.repeat(sv, 20, axis=0) + rng.normal(0, 1e-7, (len(sv) * 20, 3)))])   # tie-break planes
+    axes = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1], [0, 0, 0],
+                     [1, 1, 1], [-1, 1, -1], [1e-30, 0, 0], [1e30, 0, 0], [np.nan, 0, 1]], np.float32)
+    scaled = np.concatenate([0.5 * rand[:200_000], 2.0 * rand[:200_000], 0.99 * rand[:200_000]])
+    q = np.concatenate([rand, bisector, bisector_tight, at_vertex, axes, scaled]).astype(np.float32)
+    plain = kd.find_nn(q, certified_lookup=False)
+    fast = kd.find_nn(q, certified_lookup=True)
+    assert np.array_equal(plain, fast)
+    # both duplicates of coincident positions occur as answers (the rule is query dependent), and the device search is
+    # the oracle's (reference acc::KDTree::find_nn restated) on a sample
+    _, inv, cnt = np.unique(sv, axis=0, return_inverse=True, return_counts=True)
+    inv = inv.reshape(-1)
+    assert (cnt == 2).sum() == 630 and (cnt == 1).sum() == 12           # SURVEY.md Appendix quirk 5
+    answered = np.zeros(len(sv), bool)
+    answered[np.unique(fast[fast < len(sv)])] = True                   # the NaN query answers NAI, as in the search
+    both = np.bincount(inv, weights=answered.astype(np.float64)) == 2   # positions whose two copies both win somewhere
+    assert both.sum() >= 20 and np.bincount(inv, weights=answered.astype(np.float64)).min() >= 1
+    sample = rng.choice(len(q) - len(axes) - len(scaled), 20_000, replace=False)
+    assert np.array_equal(s["okd"].find_nn(q[sample])[0], fast[sample])
+
+
+def test_certified_nn_lookup_refuses_unsuitable_sets(api, oracle):
+    """Three coincident vertices have no precomputed tie rule: the lookup is not built, the plain search answers."""
+    rng = np.random.default_rng(5)
+    pts = rng.normal(size=(50, 3)).astype(np.float32)
+    pts[7] = pts[3]; pts[9] = pts[3]
+    okd = oracle.KD.build(pts)
+    kn, kv = okd.export()
+    kd = api.KDTree.create(kn, kv)
+    q = rng.normal(size=(1000, 3)).astype(np.float32)
+    assert np.array_equal(kd.find_nn(q), okd.find_nn(q)[0])
+    with pytest.raises(RuntimeError):
+        kd.find_nn(q, certified_lookup=True)
+    # a generic set without triples: lookup available, same answers
+    pts2 = rng.normal(size=(300, 3)).astype(np.float32)
+    pts2[10] = pts2[20]
+    okd2 = oracle.KD.build(pts2)
+    kd2 = api.KDTree.create(*okd2.export())
+    q2 = np.concatenate([rng.normal(size=(200_000, 3)), np.repeat(pts2, 50, axis=0) + rng.normal(0, 1e-3, (15000, 3))]).astype(np.float32)
+    assert np.array_equal(kd2.find_nn(q2, certified_lookup=True), kd2.find_nn(q2))
+    assert np.array_equal(kd2.find_nn(q2[:5000], certified_lookup=True), okd2.find_nn(q2[:5000])[0])

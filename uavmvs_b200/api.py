@@ -193,6 +193,15 @@ class KDTree(_Handle):
         return obj
 
 
+    def find_nn(self, queries, certified_lookup=False, stream=None):
+        """cacc::nnsearch::find_nn<3> for a batch of queries [n,3] -> vertex indices."""
+        q = _f(queries).reshape(-1, 3)
+        out = np.empty(q.shape[0], np.uint32)
+        _check(_lib.uavmvs_kdtree_find_nn(_stream_ptr(stream), self.ptr, _p(q), _u64(q.shape[0]),
+                                          _i32(1 if certified_lookup else 0), _p(out)))
+        return out
+
+
 class PointCloud(_Handle):
     """cacc::PointCloud<DEVICE> (libs/cacc/point_cloud.h)."""
     _destroy = "uavmvs_cloud_destroy"

@@ -3,6 +3,7 @@
 // Compiled with --fmad=false, IEEE div/sqrt, no FTZ: every expression below is
 // evaluated exactly as written.
 #pragma once
+#include <vector>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <cfloat>
@@ -90,6 +91,14 @@ struct uavmvs_kdtree {
     float4 * verts;  // xyz
     // cache of the batched K6: bit (pixel, bin) = "sphere vertex bin projects inside the image of
     // orientation pixel" (kernels.cu:409-441), valid for one (calib, width, height, image size)
+    // certified nearest-vertex lookup (kd.cuh: kd_find_nn_fast), built lazily by kd_fast_ensure (containers.cu)
+    std::vector<uint32_t> h_nodes; std::vector<float> h_verts;     // host copies for that build
+    int fast_state = 0;                 // 0 not built yet, 1 ready, -1 unsuitable point set (plain search only)
+    uint32_t fast_m = 0, fast_res = 0;  // distinct positions, cube-map resolution per face
+    uint16_t * fast_table = nullptr;    // [6][res][res] -> distinct position nearest to the cell centre
+    float4 * fast_pos = nullptr;        // [m] xyz, w = half the certified radius
+    uint4 * fast_rule = nullptr;        // [m] {vertex id A, vertex id B, dim (3 = always A), coordinate bits}
+    uint16_t * fast_nbr = nullptr;      // [m][8] neighbouring distinct positions, 0xffff = none
     uint32_t * fr_bits = nullptr;   // [words][pixels], words = ceil(num_nodes / 32)
     float fr_calib[9] = {0}; int fr_w = 0, fr_h = 0; uint32_t fr_iw = 0, fr_ih = 0;
 };
@@ -170,8 +179,16 @@ Heur current_heur();
 // Batched spherical-histogram job run through the K1 ray-list pipeline (k1.cu): the "views" are bare
 // candidate positions (no frustum), visible rays are binned into hist[view][bin] instead of becoming
 // observation rows.  with_recon = 0: K4 (kernels.cu:293-336); 1: K5 (kernels.cu:338-390).
+struct KdFastView {               // null table = not available
+    const uint16_t * __restrict__ table; const float4 * __restrict__ pos; const uint4 * __restrict__ rule;
+    const uint16_t * __restrict__ nbr; uint32_t res;
+};
+int kd_fast_ensure(uavmvs_kdtree * kd);       // containers.cu; 0 on success (also when the set is unsuitable)
+KdFastView kd_fast_view(const uavmvs_kdtree * kd);
+
 struct HistJob {
     const uint4 * kd_nodes; const float4 * kd_verts; uint32_t kd_n;
+    KdFastView kd_fast;
     const float * values; const float * qualities;
     int with_recon; float target_recon;
     const float4 * obs; const uint32_t * num_rows; uint32_t max_rows, stride; const float * recons;

@@ -2,6 +2,9 @@
 // image, KD-tree.  They mirror the memory layouts of the reference's cacc containers
 // (libs/cacc/point_cloud.h:26-32, vector_array.h:23-50, array.h, image.h, kd_tree.h).
 #include "common.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 
 namespace uav {
 
@@ -150,6 +153,133 @@ static int upload3(const float * host, uint32_t n, float4 * dst)
     return 0;
 }
 
+
+// ---- certified nearest-vertex lookup tables (device side and the argument: kd.cuh, kd_find_nn_fast) ----------
+KdFastView kd_fast_view(const uavmvs_kdtree * kd)
+{
+    KdFastView v; v.table = nullptr; v.pos = nullptr; v.rule = nullptr; v.nbr = nullptr; v.res = 0;
+    if (kd && kd->fast_state == 1) { v.table = kd->fast_table; v.pos = kd->fast_pos; v.rule = kd->fast_rule; v.nbr = kd->fast_nbr; v.res = kd->fast_res; }
+    return v;
+}
+
+int kd_fast_ensure(uavmvs_kdtree * kd)
+{
+    if (!kd || kd->fast_state != 0) return 0;
+    kd->fast_state = -1;                                   // until proven suitable
+    if (getenv("UAVMVS_NO_KD_FAST")) return 0;
+    const uint32_t n = kd->num_nodes;
+    const std::vector<uint32_t> & nd = kd->h_nodes; const std::vector<float> & vt = kd->h_verts;
+    if (n < 2 || n > 60000 || nd.size() != 4 * (size_t)n) return 0;
+    // topology: every node reachable once from the root, vertex ids a permutation
+    std::vector<uint32_t> parent(n, UAV_NAI), depth(n, 0), node_of(n, UAV_NAI), order; order.reserve(n);
+    std::vector<char> seen(n, 0);
+    order.push_back(0); seen[0] = 1;
+    for (size_t h = 0; h < order.size(); ++h) {
+        const uint32_t i = order[h];
+        if (nd[4 * i + 1] > 2 || nd[4 * i] >= n || node_of[nd[4 * i]] != UAV_NAI) return 0;
+        node_of[nd[4 * i]] = i;
+        for (int c = 2; c < 4; ++c) {
+            const uint32_t ch = nd[4 * i + c];
+            if (ch == UAV_NAI) continue;
+            if (ch >= n || seen[ch]) return 0;
+            seen[ch] = 1; parent[ch] = i; depth[ch] = depth[i] + 1; order.push_back(ch);
+        }
+    }
+    if (order.size() != n) return 0;
+    // distinct positions (bitwise after -0 -> +0); at most two vertices per position
+    auto key = [&](uint32_t v, int k) { float f = vt[3 * (size_t)v + k] + 0.0f; uint32_t u; memcpy(&u, &f, 4); return u; };
+    for (size_t i = 0; i < 3 * (size_t)n; ++i) if (!(fabsf(vt[i]) < 1e18f)) return 0;
+    std::vector<uint32_t> ids(n);
+    for (uint32_t i = 0; i < n; ++i) ids[i] = i;
+    std::sort(ids.begin(), ids.end(), [&](uint32_t a, uint32_t b) {
+        for (int k = 0; k < 3; ++k) { if (key(a, k) != key(b, k)) return key(a, k) < key(b, k); }
+        return a < b; });
+    std::vector<float4> pos; std::vector<uint4> rule;
+    for (uint32_t i = 0; i < n;) {
+        uint32_t j = i + 1;
+        while (j < n && key(ids[j], 0) == key(ids[i], 0) && key(ids[j], 1) == key(ids[i], 1) && key(ids[j], 2) == key(ids[i], 2)) ++j;
+        if (j - i > 2) return 0;
+        const uint32_t a = ids[i];
+        uint4 r = make_uint4(a, a, 3u, 0u);
+        if (j - i == 2) {
+            const uint32_t b = ids[i + 1];
+            uint32_t na = node_of[a], nb = node_of[b], ca = UAV_NAI, cb = UAV_NAI;     // ca / cb: child of the meeting node
+            while (depth[na] > depth[nb]) { ca = na; na = parent[na]; }
+            while (depth[nb] > depth[na]) { cb = nb; nb = parent[nb]; }
+            while (na != nb) { ca = na; na = parent[na]; cb = nb; nb = parent[nb]; }
+            if (na == node_of[a]) r = make_uint4(a, a, 3u, 0u);              // a is b's ancestor: met first on the way down
+            else if (na == node_of[b]) r = make_uint4(b, b, 3u, 0u);
+            else {
+                const uint32_t dim = nd[4 * na + 1];
+                float coord = vt[3 * (size_t)nd[4 * na] + dim]; uint32_t cbits; memcpy(&cbits, &coord, 4);
+                const bool a_left = nd[4 * na + 2] == ca;
+                if (!a_left && nd[4 * na + 2] != cb) return 0;
+                r = a_left ? make_uint4(a, b, dim, cbits) : make_uint4(b, a, dim, cbits);
+            }
+        }
+        pos.push_back(make_float4(vt[3 * (size_t)a], vt[3 * (size_t)a + 1], vt[3 * (size_t)a + 2], 0.0f));
+        rule.push_back(r);
+        i = j;
+    }
+    const uint32_t m = (uint32_t)pos.size();
+    if (m < 2 || m > 65000) return 0;
+    // neighbour lists: everything closer than D = distance of the first position left out; at most 8 entries
+    std::vector<uint16_t> nbr(8 * (size_t)m, 0xffffu);
+    std::vector<std::pair<double, uint32_t>> ds(m);
+    for (uint32_t i = 0; i < m; ++i) {
+        for (uint32_t j = 0; j < m; ++j) {
+            const double dx = (double)pos[i].x - pos[j].x, dy = (double)pos[i].y - pos[j].y, dz = (double)pos[i].z - pos[j].z;
+            ds[j] = std::make_pair(j == i ? 1e300 : sqrt(dx * dx + dy * dy + dz * dz), j);
+        }
+        const uint32_t top = std::min<uint32_t>(m - 1, 9);
+        std::partial_sort(ds.begin(), ds.begin() + top, ds.end());
+        uint32_t k = 0;
+        while (k < top && k < 8 && ds[k].first <= 1.6 * ds[0].first) ++k;
+        const double D = k < top ? ds[k].first : (k < m - 1 ? ds[k].first : 1e30);
+        for (uint32_t t = 0; t < k; ++t) nbr[8 * (size_t)i + t] = (uint16_t)ds[t].second;
+        float halfD = (float)std::min(0.5 * D - 1e-5, 1e30);
+        halfD = nextafterf(halfD, -1.0f);
+        pos[i].w = halfD > 0.0f ? halfD : 0.0f;
+    }
+    // cube-map proposals: nearest distinct position of every cell centre
+    const uint32_t res = 128;
+    std::vector<uint16_t> table(6 * (size_t)res * res);
+    for (uint32_t face = 0; face < 6; ++face)
+        for (uint32_t iv = 0; iv < res; ++iv) {
+            uint32_t last = 0;
+            for (uint32_t iu = 0; iu < res; ++iu) {
+                const double u = (iu + 0.5) / res * 2.0 - 1.0, v = (iv + 0.5) / res * 2.0 - 1.0, sgn = (face & 1) ? -1.0 : 1.0;
+                double d[3];
+                if (face < 2) { d[0] = sgn; d[1] = u; d[2] = v; } else if (face < 4) { d[0] = u; d[1] = sgn; d[2] = v; } else { d[0] = u; d[1] = v; d[2] = sgn; }
+                const double l = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+                for (int k = 0; k < 3; ++k) d[k] /= l;
+                // greedy walk over the neighbour lists from the previous cell's answer (a proposal only: a poor one costs a
+                // hop or the plain search on the device, never a wrong answer)
+                auto dist2 = [&](uint32_t j) { const double a = d[0] - pos[j].x, b = d[1] - pos[j].y, c = d[2] - pos[j].z; return a * a + b * b + c * c; };
+                uint32_t best = last; double bd = dist2(best);
+                for (bool moved = true; moved;) {
+                    moved = false;
+                    for (int t = 0; t < 8; ++t) {
+                        const uint16_t j = nbr[8 * (size_t)best + t];
+                        if (j != 0xffffu && dist2(j) < bd) { bd = dist2(j); best = j; moved = true; break; }
+                    }
+                }
+                table[((size_t)face * res + iv) * res + iu] = (uint16_t)best;
+                last = best;
+            }
+        }
+    UAV_CUDA(cudaMalloc(&kd->fast_table, sizeof(uint16_t) * table.size()));
+    UAV_CUDA(cudaMalloc(&kd->fast_pos, sizeof(float4) * (size_t)m));
+    UAV_CUDA(cudaMalloc(&kd->fast_rule, sizeof(uint4) * (size_t)m));
+    UAV_CUDA(cudaMalloc(&kd->fast_nbr, sizeof(uint16_t) * nbr.size()));
+    UAV_CUDA(cudaMemcpy(kd->fast_table, table.data(), sizeof(uint16_t) * table.size(), cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(kd->fast_pos, pos.data(), sizeof(float4) * (size_t)m, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(kd->fast_rule, rule.data(), sizeof(uint4) * (size_t)m, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(kd->fast_nbr, nbr.data(), sizeof(uint16_t) * nbr.size(), cudaMemcpyHostToDevice));
+    kd->fast_m = m; kd->fast_res = res; kd->fast_state = 1;
+    return 0;
+}
+
 }  // namespace uav
 
 using namespace uav;
@@ -165,6 +295,8 @@ int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n
     UAV_CUDA(cudaMalloc(&k->verts, sizeof(float4) * (size_t)n));
     UAV_CUDA(cudaMemcpy(k->nodes, nodes, sizeof(uint4) * (size_t)n, cudaMemcpyHostToDevice));
     if (upload3(verts, n, k->verts)) return 1;
+    k->h_nodes.assign(nodes, nodes + 4 * (size_t)n);
+    k->h_verts.assign(verts, verts + 3 * (size_t)n);
     *out = k;
     return 0;
 }
@@ -173,6 +305,7 @@ int uavmvs_kdtree_destroy(uavmvs_kdtree * k)
 {
     if (!k) return 0;
     cudaFree(k->nodes); cudaFree(k->verts); cudaFree(k->fr_bits);
+    cudaFree(k->fast_table); cudaFree(k->fast_pos); cudaFree(k->fast_rule); cudaFree(k->fast_nbr);
     delete k;
     return 0;
 }

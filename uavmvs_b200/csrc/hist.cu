@@ -289,6 +289,16 @@ k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_
     }
 }
 
+// cacc::nnsearch::find_nn<3> for a batch of queries (libs/cacc/nnsearch.h:67-155); fast.table != null: through the
+// certified lookup of kd.cuh (must return the same indices)
+__global__ void k_kd_find_nn(KdView kd, KdFastView fast, const float * __restrict__ q, uint64_t n, uint32_t * __restrict__ out)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 v = mk(q[3 * i], q[3 * i + 1], q[3 * i + 2]);
+    out[i] = fast.table ? kd_find_nn_fast(fast, kd, v) : kd_find_nn(kd, v);
+}
+
 __global__ void k_fill_positions(const float * __restrict__ pos, uint32_t n, float * __restrict__ views)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -387,6 +397,8 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     cudaStream_t s = (cudaStream_t)stream;
     HistJob hj;
     hj.kd_nodes = kd->nodes; hj.kd_verts = kd->verts; hj.kd_n = kd->num_nodes;
+    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;      // lazily built lookup tables (a cache, like fr_bits)
+    hj.kd_fast = kd_fast_view(kd);
     hj.values = cloud->values; hj.qualities = cloud->qualities;
     hj.with_recon = obs ? 1 : 0; hj.target_recon = target_recon;
     hj.obs = nullptr; hj.num_rows = nullptr; hj.max_rows = 0; hj.stride = 0; hj.recons = nullptr;
@@ -405,6 +417,30 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
     cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s);
     return rc;
+}
+
+int uavmvs_kdtree_find_nn(void * stream, uavmvs_kdtree * kd, const float * queries, uint64_t n, int certified_lookup,
+    uint32_t * out_idx)
+{
+    UAV_REQUIRE(kd && (queries || n == 0) && (out_idx || n == 0), "null argument");
+    if (n == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    KdFastView fv = kd_fast_view(nullptr);
+    if (certified_lookup) {
+        if (kd_fast_ensure(kd)) return 1;
+        fv = kd_fast_view(kd);
+        UAV_REQUIRE(fv.table, "this vertex set has no certified lookup (more than two coincident vertices, or not a tree)");
+    }
+    float * d_q; uint32_t * d_o;
+    UAV_CUDA(cudaMallocAsync(&d_q, sizeof(float) * 3 * n, s));
+    UAV_CUDA(cudaMallocAsync(&d_o, sizeof(uint32_t) * n, s));
+    UAV_CUDA(cudaMemcpyAsync(d_q, queries, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, s));
+    k_kd_find_nn<<<divup(n, 256), 256, 0, s>>>(kd_view(kd), fv, d_q, n, d_o);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaMemcpyAsync(out_idx, d_o, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, s));
+    UAV_CUDA(cudaStreamSynchronize(s));
+    UAV_CUDA(cudaFreeAsync(d_q, s)); UAV_CUDA(cudaFreeAsync(d_o, s));
+    return 0;
 }
 
 int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9], int width, int height,

@@ -1114,7 +1114,7 @@ k_retire_hist(RetireArgs a, HistJob h)
             }
             contrib = func(new_recon, h.target_recon) - func(recon, h.target_recon);
         }
-        const uint32_t bin = kd_find_nn(kd, -v2cn);
+        const uint32_t bin = h.kd_fast.table ? kd_find_nn_fast(h.kd_fast, kd, -v2cn) : kd_find_nn(kd, -v2cn);
         atomicAdd(h.hist + (size_t)view * h.kd_n + bin, contrib);
     }
     if (a.stats) {

@@ -38,6 +38,59 @@ __device__ __forceinline__ uint32_t kd_find_nn(const KdView & kd, V3 q)
     return idx;
 }
 
+// Certified shortcut for kd_find_nn on queries near the unit sphere (the histogram kernels ask for the icosphere
+// vertex nearest to a unit direction, ~25 node visits each).  A cube-map cell proposes a distinct position c; c is
+// the reference's answer when (exact-arithmetic argument, margins three orders of magnitude above the fp32 rounding
+// of the distances, which are a few 1e-8 here):
+//   * d(q,c) + 1e-5 < d(q,u) for every u of c's neighbour list N(c) = all distinct positions closer than D(c) to c,
+//   * d(q,c) < D(c)/2 - 1e-5: any position outside N(c) is then farther than D(c) - d(q,c) > d(q,c) from q.
+// The reference search returns the FIRST vertex of minimal computed distance in its depth-first order.  With the margin
+// above only the (bitwise coincident) duplicates of c attain the minimum; the icosphere stores most positions twice
+// (SURVEY.md Appendix quirk 5).  Two duplicates are either ancestor and descendant in the KD-tree (the ancestor is met
+// first on the way down) or lie on either side of a node A whose split plane passes through them; the walk enters
+// the side `q[dim] - A[dim] < 0 ? left : right` first (nnsearch.h:118-121) and cannot prune the subtree holding the
+// duplicate before reaching it, since every plane between q and c is closer to q than c is and the running bound is
+// still above d(q,c) + 1e-5.  The rule {A, B, dim, coordinate} is precomputed per position (containers.cu).
+// A closer neighbour becomes the new proposal (at most 3 hops); everything else takes the plain search.
+__device__ __forceinline__ uint32_t kd_find_nn_fast(const KdFastView & f, const KdView & kd, V3 q)
+{
+    const float ax = fabsf(q.x), ay = fabsf(q.y), az = fabsf(q.z);
+    uint32_t face; float ma, u, v;
+    if (ax >= ay && ax >= az) { face = q.x < 0.0f ? 1u : 0u; ma = ax; u = q.y; v = q.z; }
+    else if (ay >= az) { face = q.y < 0.0f ? 3u : 2u; ma = ay; u = q.x; v = q.z; }
+    else { face = q.z < 0.0f ? 5u : 4u; ma = az; u = q.x; v = q.y; }
+    if (!(ma > 1e-20f) || !(ma < 1e20f)) return kd_find_nn(kd, q);          // zero, huge or NaN query
+    const float inv = 0.5f * (float)f.res / ma, half = 0.5f * (float)f.res;
+    const int iu = min((int)f.res - 1, max(0, (int)(u * inv + half)));
+    const int iv = min((int)f.res - 1, max(0, (int)(v * inv + half)));
+    uint32_t c = f.table[(face * f.res + (uint32_t)iv) * f.res + (uint32_t)iu];
+    for (int hop = 0; hop < 3; ++hop) {
+        const float4 p = __ldg(f.pos + c);
+        const float d = norm(q - ld3(p));
+        float dn = UAV_INF; uint32_t cn = c;
+        const uint4 nb = __ldg(reinterpret_cast<const uint4 *>(f.nbr) + c);     // 8 x uint16
+        const uint32_t w[4] = { nb.x, nb.y, nb.z, nb.w };
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const uint32_t n = (w[k >> 1] >> ((k & 1) * 16)) & 0xffffu;
+            if (n != 0xffffu) {
+                const float dk = norm(q - ld3(__ldg(f.pos + n)));
+                if (dk < dn) { dn = dk; cn = n; }
+            }
+        }
+        if (d + 1e-5f < dn) {
+            if (!(d < p.w)) break;
+            const uint4 r = __ldg(f.rule + c);
+            if (r.z == 3u) return r.x;
+            const float qd = r.z == 0 ? q.x : (r.z == 1 ? q.y : q.z);
+            return (qd - __uint_as_float(r.w) < 0.0f) ? r.x : r.y;
+        }
+        if (!(dn < d)) break;                      // inside the margin of a bisector (or NaN)
+        c = cn;
+    }
+    return kd_find_nn(kd, q);
+}
+
 static inline KdView kd_view(const uavmvs_kdtree * k) { KdView v; v.nodes = k->nodes; v.verts = k->verts; v.n = k->num_nodes; return v; }
 
 }  // namespace uav
