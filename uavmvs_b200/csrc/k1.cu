@@ -516,7 +516,11 @@ struct RayList {
     uint32_t * rview;     // histogram jobs only: view (candidate position) index of every ray
     uint32_t * tpk;       // packet (block, candidate view) of every ray that has to be traced; NULL: entry points off
     const uint32_t * fr;  // [packets][16] entry points of k_entry: count, wide-node indices
+    // speculative launch (launch_k1): the kernels of a batch are enqueued before the host knows the batch's ray-record
+    // bound; they do nothing when the bound, already on the device, exceeds what the buffers hold
+    const unsigned long long * g_total; unsigned long long g_cap;
 };
+#define K1_SPECULATION_GUARD(rl) do { if ((rl).g_total && *(rl).g_total > (rl).g_cap) return; } while (0)
 
 // Exact cull (kernels.cu:153-167) + ray set-up values (:54-58).  One warp per block, views in
 // order; lanes = points.  A slice is filled in (view, point) order.
@@ -623,6 +627,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
     float max_distance, float cull_distance, int width, int height, RayList rl, unsigned long long * counters)
 {
+    K1_SPECULATION_GUARD(rl);
     __shared__ float4 s_v[K1_WARPS][32], s_n[K1_WARPS][32];
     __shared__ uint32_t s_q[K1_WARPS][64];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -786,6 +791,7 @@ static __device__ __noinline__ bool leaf_box_exact(const float * __restrict__ ra
 __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS)
 k_trace(TraceArgs a)
 {
+    K1_SPECULATION_GUARD(a.rl);
     __shared__ uint32_t s_pend[K1_PEND][K1_WARPS * 32];     // deferred leaves: first << 6 | unverified << 5 | count
     const uint32_t tid = threadIdx.x, lane = tid & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -969,6 +975,7 @@ template <bool POPULATE>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_retire(RetireArgs a)
 {
+    K1_SPECULATION_GUARD(a.rl);
     __shared__ float4 s_nrm[K1_WARPS][32], s_rx[K1_WARPS][32], s_ry[K1_WARPS][32];
     __shared__ uint32_t s_cnt[K1_WARPS][32];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -1063,6 +1070,7 @@ template <bool WITH_RECON>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_retire_hist(RetireArgs a, HistJob h)
 {
+    K1_SPECULATION_GUARD(a.rl);
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t blk = blockIdx.x * K1_WARPS + w;
     if (blk >= a.num_blocks) return;
@@ -1137,6 +1145,7 @@ struct K1Scratch {
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     int grid_trace = 0;
+    cudaEvent_t ev_total = nullptr;
 };
 static thread_local K1Scratch g_k1;
 
@@ -1227,6 +1236,15 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     UAV_CUDA(cudaGetLastError());
 
     // view batches: [v0, v1) such that the upper bound of ray records fits the budget
+    // Speculation: the bound of a batch's ray records is needed on the host only to size the buffers.  When buffers
+    // from an earlier call exist, the whole batch is enqueued at once against their capacity - every kernel that
+    // touches them first checks the bound on the device - and the host waits only for the 8-byte copy of the bound,
+    // which arrives while the cull and the traversal are already running (the stream no longer drains between
+    // k_sum_caps and k_cull_emit: ~0.05 ms per evaluation of config 2).  A bound above the capacity means the
+    // guarded kernels did nothing; the batch is then redone the synchronous way.
+    bool speculate = !getenv("UAVMVS_NO_SPECULATION") && k.rays_cap > 0 && bvh->nested && !bvh->root_is_leaf
+        && !entry_enabled() && !shafts_enabled() && !getenv("UAVMVS_CULL_PACKETS");
+    if (speculate && !k.ev_total) UAV_CUDA(cudaEventCreateWithFlags(&k.ev_total, cudaEventDisableTiming));
     uint32_t v0 = 0, step = num_views;
     while (v0 < num_views) {
         uint32_t v1 = (uint32_t)min((uint64_t)num_views, (uint64_t)v0 + step);
@@ -1234,14 +1252,23 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         k_block_caps<<<divup(nb, 128), 128, 0, s>>>(k.masks, num_views, v0, v1, nb, k.caps);
         k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, s>>>(k.caps, nb, k.total);
         UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-        UAV_CUDA(cudaStreamSynchronize(s));
-        const unsigned long long total = *k.h_total;
-        if (total > ray_budget() && v1 - v0 > 1) {          // too many candidates: halve the batch
-            step = (v1 - v0 + 1) / 2;
-            continue;
+        const bool spec = speculate;
+        speculate = false;                                   // one attempt per call
+        const unsigned long long spec_cap = min((unsigned long long)k.rays_cap, min((unsigned long long)ray_budget(), 1ull << 27));
+        unsigned long long total;
+        if (spec) {
+            UAV_CUDA(cudaEventRecord(k.ev_total, s));
+            total = spec_cap;                                // sizes nothing: the buffers already hold this many records
+        } else {
+            UAV_CUDA(cudaStreamSynchronize(s));
+            total = *k.h_total;
+            if (total > ray_budget() && v1 - v0 > 1) {          // too many candidates: halve the batch
+                step = (v1 - v0 + 1) / 2;
+                continue;
+            }
+            UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
+            if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
         }
-        UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
-        if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
         if (total > 0) {
             if (total > k.rays_cap) {
                 size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap;
@@ -1259,7 +1286,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 ea.fr = k.fr; ea.tau = entry_tau(); ea.counters = k.counters;
                 k_entry<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ea);
             }
-            RayList rl; rl.tpk = entry ? k.tpk : nullptr; rl.fr = k.fr; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
+            RayList rl; rl.g_total = spec ? k.total : nullptr; rl.g_cap = spec_cap; rl.tpk = entry ? k.tpk : nullptr; rl.fr = k.fr; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
             // shafts: whole (block, view) packets proven visible without tracing (nested trees only)
             const uint32_t nchunks = divup(v1 - v0, 32);
             const bool shafts = shafts_enabled() && bvh->nested && !bvh->root_is_leaf;
@@ -1296,15 +1323,19 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 if (hj->with_recon) k_retire_hist<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
                 else k_retire_hist<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
                 UAV_CUDA(cudaGetLastError());
-                v0 = v1;
-                continue;
+            } else {
+                ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
+                ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
+                ra.dirty = obs->dirty;
+                if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
+                else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
+                UAV_CUDA(cudaGetLastError());
             }
-            ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
-            ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
-            ra.dirty = obs->dirty;
-            if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
-            else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
-            UAV_CUDA(cudaGetLastError());
+        }
+        if (spec) {
+            UAV_CUDA(cudaEventSynchronize(k.ev_total));      // the bound only; the batch keeps running
+            if (*k.h_total > spec_cap) continue;             // guarded kernels were no-ops: same batch again, synchronously
+            if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);
         }
         v0 = v1;
     }
