@@ -297,6 +297,7 @@ int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n
     if (upload3(verts, n, k->verts)) return 1;
     k->h_nodes.assign(nodes, nodes + 4 * (size_t)n);
     k->h_verts.assign(verts, verts + 3 * (size_t)n);
+    if (kd_fast_ensure(k)) return 1;          // built here, read-only afterwards: host threads share the handle
     *out = k;
     return 0;
 }
@@ -305,6 +306,7 @@ int uavmvs_kdtree_destroy(uavmvs_kdtree * k)
 {
     if (!k) return 0;
     cudaFree(k->nodes); cudaFree(k->verts); cudaFree(k->fr_bits);
+    for (uint32_t * p : k->fr_old) cudaFree(p);
     cudaFree(k->fast_table); cudaFree(k->fast_pos); cudaFree(k->fast_rule); cudaFree(k->fast_nbr);
     delete k;
     return 0;

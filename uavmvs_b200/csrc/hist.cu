@@ -25,7 +25,7 @@ __device__ __forceinline__ V3 relative_direction(V3 v2cn, V3 n) {
 }
 
 struct HistArgs {
-    BvhView bvh; KdView kd;
+    BvhView bvh; KdView kd; KdFastView kd_fast;
     const float4 * __restrict__ verts; const float4 * __restrict__ normals;
     const float * __restrict__ values; const float * __restrict__ qualities;
     uint32_t n;
@@ -95,7 +95,7 @@ k_populate_spherical_histogram(HistArgs a)
             }
         }
         if (add) {
-            uint32_t bin = kd_find_nn(a.kd, -v2cn);
+            uint32_t bin = a.kd_fast.table ? kd_find_nn_fast(a.kd_fast, a.kd, -v2cn) : kd_find_nn(a.kd, -v2cn);
             atomicAdd(&s_hist[bin], contrib);
         }
     }
@@ -316,6 +316,8 @@ static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos
     UAV_REQUIRE(kd->num_nodes * sizeof(float) <= 48 * 1024, "sphere histogram does not fit shared memory");
     HistArgs a;
     a.bvh = view_of(bvh); a.kd = kd_view(kd);
+    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;
+    a.kd_fast = kd_fast_view(kd);
     a.verts = cloud->vertices; a.normals = cloud->normals; a.values = cloud->values; a.qualities = cloud->qualities;
     a.n = cloud->n;
     a.px = view_pos[0]; a.py = view_pos[1]; a.pz = view_pos[2];
@@ -335,6 +337,38 @@ static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
+
+// Bit matrix of the batched K6 for one (calibration, image size), cached in the KD-tree handle.
+static int frustum_bits(uavmvs_kdtree * kd, const float calib[9], int width, int height, uint32_t image_width,
+    uint32_t image_height, cudaStream_t s, const uint32_t ** out)
+{
+    std::lock_guard<std::mutex> lock(kd->fr_mutex);
+    const uint32_t npix = image_width * image_height, words = (kd->num_nodes + 31) / 32;
+    bool same = kd->fr_bits && kd->fr_w == width && kd->fr_h == height && kd->fr_iw == image_width && kd->fr_ih == image_height
+        && memcmp(kd->fr_calib, calib, 9 * sizeof(float)) == 0;
+    if (!same) {
+        float * d_K;
+        if (kd->fr_bits) kd->fr_old.push_back(kd->fr_bits);
+        kd->fr_bits = nullptr;
+        if (kd->fr_old.size() > 8) {                       // callers alternating calibrations: drain the device, then free
+            UAV_CUDA(cudaDeviceSynchronize());
+            for (uint32_t * p : kd->fr_old) cudaFree(p);
+            kd->fr_old.clear();
+        }
+        UAV_CUDA(cudaMalloc(&kd->fr_bits, sizeof(uint32_t) * (size_t)words * npix));
+        UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
+        UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
+        k_frustum_bits<<<divup(npix, 128), 128, 0, s>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
+        UAV_CUDA(cudaGetLastError());
+        UAV_CUDA(cudaStreamSynchronize(s));                // other streams may use the matrix as soon as the lock drops
+        UAV_CUDA(cudaFree(d_K));
+        memcpy(kd->fr_calib, calib, 9 * sizeof(float)); kd->fr_w = width; kd->fr_h = height;
+        kd->fr_iw = image_width; kd->fr_ih = image_height;
+    }
+    *out = kd->fr_bits;
+    return 0;
+}
+
 
 }  // namespace uav
 
@@ -364,6 +398,22 @@ int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int
     UAV_REQUIRE(sphere_hist->n >= kd->num_nodes, "sphere_hist smaller than the KD-tree");
     UAV_REQUIRE(kd->num_nodes * sizeof(float4) <= 48 * 1024, "sphere does not fit shared memory");
     cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t S = kd->num_nodes, words = (S + 31) / 32, npix = hist->width * hist->height;
+    if (hist->pitch == (uint64_t)hist->width * 4 && words * 32 * sizeof(float) <= 48 * 1024 && !getenv("UAVMVS_K6_REFERENCE_LOOP")) {
+        // contiguous rows (any width that is a multiple of 128, e.g. the apps' 128 x 45): the batched kernel with one
+        // position - same additions in the same order per pixel, the 5760 x 1272 frustum tests replaced by the cached
+        // bit matrix
+        const uint32_t * bits = nullptr;
+        if (frustum_bits(const_cast<uavmvs_kdtree *>(kd), calib, width, height, hist->width, hist->height, s, &bits)) return 1;
+        unsigned long long * d_best;
+        UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long), s));
+        const uint32_t parts = max(1u, npix / EVB_THREADS);
+        k_evaluate_spherical_histogram_batch<<<dim3(1, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(bits, words, npix,
+            sphere_hist->data, S, hist->data, d_best, d_best + 1);
+        UAV_CUDA(cudaGetLastError());
+        UAV_CUDA(cudaFreeAsync(d_best, s));
+        return 0;
+    }
     float * d_K;
     UAV_CUDA(cudaMallocAsync(&d_K, 9 * sizeof(float), s));
     UAV_CUDA(cudaMemcpyAsync(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice, s));
@@ -397,7 +447,7 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     cudaStream_t s = (cudaStream_t)stream;
     HistJob hj;
     hj.kd_nodes = kd->nodes; hj.kd_verts = kd->verts; hj.kd_n = kd->num_nodes;
-    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;      // lazily built lookup tables (a cache, like fr_bits)
+    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;      // built at create; a no-op here
     hj.kd_fast = kd_fast_view(kd);
     hj.values = cloud->values; hj.qualities = cloud->qualities;
     hj.with_recon = obs ? 1 : 0; hj.target_recon = target_recon;
@@ -455,22 +505,8 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
     UAV_REQUIRE(words * 32 * sizeof(float) <= 48 * 1024, "sphere histogram does not fit shared memory");
     if (num_positions == 0) return 0;
     cudaStream_t s = (cudaStream_t)stream;
-    bool same = kd->fr_bits && kd->fr_w == width && kd->fr_h == height && kd->fr_iw == image_width && kd->fr_ih == image_height
-        && memcmp(kd->fr_calib, calib, 9 * sizeof(float)) == 0;
-    if (!same) {
-        float * d_K;
-        UAV_CUDA(cudaStreamSynchronize(s));
-        if (kd->fr_bits) { UAV_CUDA(cudaFree(kd->fr_bits)); kd->fr_bits = nullptr; }
-        UAV_CUDA(cudaMalloc(&kd->fr_bits, sizeof(uint32_t) * (size_t)words * npix));
-        UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
-        UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
-        k_frustum_bits<<<divup(npix, 128), 128, 0, s>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
-        UAV_CUDA(cudaGetLastError());
-        UAV_CUDA(cudaStreamSynchronize(s));
-        UAV_CUDA(cudaFree(d_K));
-        memcpy(kd->fr_calib, calib, 9 * sizeof(float)); kd->fr_w = width; kd->fr_h = height;
-        kd->fr_iw = image_width; kd->fr_ih = image_height;
-    }
+    const uint32_t * bits = nullptr;
+    if (frustum_bits(kd, calib, width, height, image_width, image_height, s, &bits)) return 1;
     // pixel parts: enough CTAs for ~8 per SM when the batch is small; every thread keeps at least one pixel
     uint32_t parts = divup(148u * 8u, num_positions);
     parts = max(1u, min(parts, max(1u, npix / EVB_THREADS)));
@@ -478,7 +514,7 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
     UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long) * (size_t)num_positions, s));
     UAV_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)num_positions, s));
     UAV_CUDA(cudaMemsetAsync(d_best + num_positions, 0, sizeof(unsigned long long) * (size_t)num_positions, s));
-    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(kd->fr_bits, words, npix,
+    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(bits, words, npix,
         sphere_hists->data, S, images ? images->data : nullptr, d_best, d_best + num_positions);
     UAV_CUDA(cudaGetLastError());
     if (h_min || h_argmin || h_max || h_argmax) {
