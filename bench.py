@@ -289,11 +289,9 @@ def run_b200(a, rank, local_rank, world):
 
     def e2e_step():
         # host trajectory -> C ABI (H2D inside) -> evaluation -> D2H of score, per-point recon and counts
-        r = api.evaluate_trajectory(h_views.numpy(), sc.max_distance, sc.target_recon, sc.width, sc.height, bvh,
-                                    cloud, obs, recons, wrecons, stream=stream)
-        recons.download(out=h_recons_np)
-        obs.download(data=False, rows_out=h_rows_np)
-        return r
+        return api.evaluate_trajectory_to_host(h_views.numpy(), sc.max_distance, sc.target_recon, sc.width, sc.height,
+                                               bvh, cloud, obs, recons, wrecons, h_recons=h_recons_np,
+                                               h_num_rows=h_rows_np, stream=stream)
 
     def barrier():
         if world > 1:
@@ -328,6 +326,9 @@ def run_b200(a, rank, local_rank, world):
         e2e_step()
     barrier()
     e2e_ms, _, _ = timed(e2e_step, a.steps)
+    # the host buffers the timed e2e steps filled hold the device results (checked outside the timed region)
+    e2e_ok = bool(np.array_equal(h_recons_np.view(np.uint32), recons.download().view(np.uint32))
+                  and np.array_equal(h_rows_np, obs.download(data=False)[1]))
     barrier()
 
     # max over ranks of the device time; sums of the work
@@ -369,7 +370,9 @@ def run_b200(a, rank, local_rank, world):
             "stage_ms": {"K1": k1_ms, "K2": float(k_ms[1]) / a.steps, "K3_K8": float(k_ms[2]) / a.steps,
                          "K9": float(k_ms[3]) / a.steps},
             "e2e": {"value": rays * a.steps / e2e_sec, "unit": UNIT, "ms_per_step": e2e_ms / a.steps,
-                    "h2d_bytes_per_step": int(views_np.nbytes), "d2h_bytes_per_step": int(8 * n_local + 12 + 32)},
+                    "h2d_bytes_per_step": int(views_np.nbytes), "d2h_bytes_per_step": int(8 * n_local + 12 + 32),
+                    "call": "uavmvs_evaluate_trajectory_to_host (host views in, per-point recon + counts + score out, copies overlapped)",
+                    "host_buffers_match_device": e2e_ok},
             "gpu_launches": 11 * a.steps, "clocks": clocks}
     if rank != 0:
         if world > 1:

@@ -184,6 +184,17 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
     uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4]);
 
+/* The same evaluation followed by the download the app does next (the HOST copy of the per-point arrays,
+ * apps/evaluate_trajectory/evaluate_trajectory.cu:188-194 and :215-240): h_recons[num_points] and h_num_rows[num_points]
+ * (either may be NULL; pinned memory lets the copies overlap) are filled while the evaluation is still running - the
+ * counters beside K2 + K3, the scores in four chunks each copied while the next is computed - and are complete when the
+ * call returns.  Same results as uavmvs_evaluate_trajectory + two downloads. */
+int uavmvs_evaluate_trajectory_to_host(void * stream, const float * views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
+    float out3[3], uint64_t stats[4]);
+
 /* Device time (ms, CUDA events on the call's stream) of the stages of the calling thread's last
  * uavmvs_evaluate_trajectory*: ms[0] = K1 (all views), [1] = K2, [2] = K3+K8, [3] = K9.  The
  * reference only wall-clocks the K1 loop (apps/evaluate_trajectory/evaluate_trajectory.cu:144-171). */

@@ -248,6 +248,14 @@ def test_evaluate_trajectory_fused(api, oracle, tiny_scene, tiny_tree):
         assert np.array_equal(obs.download(data=False)[1], obs_o.num_rows)
         assert _close(recons.download(), r_o)
         assert _close(s / sc.num_points, w_o.astype(np.float64).mean())
+    # the same evaluation with the per-point downloads overlapped (evaluate_trajectory.cu:188-194)
+    r_dev, rows_dev = recons.download(), obs.download(data=False)[1]
+    h_r, h_n = np.full(sc.num_points, -7.0, np.float32), np.full(sc.num_points, 77, np.uint32)
+    s2, mn2, mx2, stats2 = api.evaluate_trajectory_to_host(sc.views28(), sc.max_distance, sc.target_recon, sc.width,
+                                                           sc.height, gbvh, cloud, obs, recons, wrecons, h_r, h_n)
+    assert stats2 == stats and (mn2, mx2) == (mn, mx) and _close(s2, s, 1e-6)
+    assert np.array_equal(h_r.view(np.uint32), r_dev.view(np.uint32)) and np.array_equal(h_n, rows_dev)
+    assert np.array_equal(recons.download().view(np.uint32), r_dev.view(np.uint32))
 
 
 @pytest.mark.parametrize("builder", ["build_lbvh", "build_ploc", "build_sah"])

@@ -389,6 +389,24 @@ def evaluate_trajectory(views, max_distance, target_recon, width, height, bvh_tr
     return float(out[0]), float(out[1]), float(out[2]), st
 
 
+def evaluate_trajectory_to_host(views, max_distance, target_recon, width, height, bvh_tree, cloud, obs_rays,
+                                recons, wrecons, h_recons=None, h_num_rows=None, stream=None, want_stats=True):
+    """evaluate_trajectory + the per-point downloads that follow it in the app (evaluate_trajectory.cu:188-194),
+    overlapped with the evaluation.  h_recons float32[N] / h_num_rows uint32[N]: host arrays (pinned for overlap)."""
+    out = (C.c_float * 3)()
+    stats = (C.c_uint64 * 4)() if want_stats else None
+    views = _f(views, (-1, VIEW_FLOATS))
+    n = cloud.num_points if hasattr(cloud, "num_points") else None
+    for a, dt in ((h_recons, np.float32), (h_num_rows, np.uint32)):
+        assert a is None or (a.dtype == dt and a.flags.c_contiguous and (n is None or a.size == n))
+    _check(_lib.uavmvs_evaluate_trajectory_to_host(
+        _stream_ptr(stream), _p(views), _u32(views.shape[0]), _f32(max_distance), _f32(target_recon),
+        _i32(width), _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr, recons.ptr, wrecons.ptr,
+        _p(h_recons), _p(h_num_rows), out, stats))
+    st = [int(x) for x in stats] if want_stats else None
+    return float(out[0]), float(out[1]), float(out[2]), st
+
+
 def profile_last():
     """Device ms of K1, K2, K3+K8, K9 of this thread's last evaluate_trajectory call."""
     ms = (C.c_float * 4)()

@@ -27,16 +27,17 @@ constexpr int SE_TILE_STRIDE = 33;      // float4 per tile row: padding against 
 template <bool DO_SORT, bool DO_EVAL>
 __global__ void __launch_bounds__(SE_THREADS)
 k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t stride, uint32_t n,
-    float * __restrict__ recons, float target, float * __restrict__ wrecons, Heur h, uint32_t * dirty)
+    float * __restrict__ recons, float target, float * __restrict__ wrecons, Heur h, uint32_t * dirty, uint32_t block0)
 {
+    const uint32_t bx = blockIdx.x + block0;                   // chunked launches (overlapped result copies)
     // incremental form: only blocks in which K1 added or invalidated a row since the last incremental pass
-    if (dirty && dirty[blockIdx.x] == 0u) return;
+    if (dirty && dirty[bx] == 0u) return;
     __shared__ float4 s_tile[32 * SE_TILE_STRIDE];
     __shared__ float4 s_col[SE_THREADS / 32][32];
     __shared__ uint32_t s_rows[32], s_valid[32];
     __shared__ uint16_t s_pairs[496];                      // pair q -> (i << 8 | j), i > j, q = i (i - 1) / 2 + j
     const uint32_t tx = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t pt0 = blockIdx.x * 32;
+    const uint32_t pt0 = bx * 32;
     if (DO_EVAL) {
         for (uint32_t q = threadIdx.x; q < 496; q += SE_THREADS) {
             uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
@@ -127,7 +128,7 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
             }
         }
     }
-    if (dirty && threadIdx.x == 0) dirty[blockIdx.x] = 0u;     // every thread read the flag before the first barrier
+    if (dirty && threadIdx.x == 0) dirty[bx] = 0u;     // every thread read the flag before the first barrier
     if (DO_SORT) {
         __syncthreads();
         for (uint32_t r = w; r < rmax; r += SE_THREADS / 32)
@@ -193,6 +194,8 @@ struct Scratch {   // per-process scratch on the device (views, reduction accumu
     ReduceAcc * h_acc = nullptr; unsigned long long * h_stats = nullptr;   // pinned
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};     // K1 | K2 | K3+K8 | K9 boundaries
     bool ev_valid = false;
+    cudaStream_t copy_stream = nullptr;                                    // result copies of evaluate_trajectory_to_host
+    cudaEvent_t ev_copy[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 static thread_local Scratch g_scratch;
 
@@ -215,21 +218,21 @@ static int ensure_scratch(size_t view_floats)
 }
 
 static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_obs * obs, uavmvs_array * recons,
-    float target, uavmvs_array * wrecons, bool incremental = false)
+    float target, uavmvs_array * wrecons, bool incremental = false, uint32_t block0 = 0, uint32_t nblocks = 0)
 {
     uint32_t * dirty = (incremental && obs) ? obs->dirty : nullptr;
     UAV_REQUIRE(obs, "null handle");
     UAV_REQUIRE(!do_eval || (recons && recons->n == obs->num_cols), "recons size != obs columns");
     UAV_REQUIRE(!wrecons || wrecons->n == obs->num_cols, "wrecons size != obs columns");
-    const unsigned grid = divup(obs->num_cols, 32);
+    const unsigned grid = nblocks ? nblocks : divup(obs->num_cols, 32);
     const uint32_t stride = (uint32_t)(obs->pitch / sizeof(float4));
     float * r = recons ? recons->data : nullptr, * wr = wrecons ? wrecons->data : nullptr;
     if (do_sort && do_eval)
-        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
+        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     else if (do_sort)
-        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
+        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     else
-        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty);
+        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -368,6 +371,68 @@ int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint
             for (int i = 0; i < 4; ++i) stats[i] = g_scratch.h_stats[i];
             stats[2] = (uint64_t)cloud->n * num_views;
         }
+    }
+    return 0;
+}
+
+int uavmvs_evaluate_trajectory_to_host(void * stream, const float * views, uint32_t num_views,
+    float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
+    float out3[3], uint64_t stats[4])
+{
+    UAV_REQUIRE(views || num_views == 0, "null views");
+    UAV_REQUIRE(bvh && cloud && obs && recons && wrecons, "null handle");
+    cudaStream_t s = (cudaStream_t)stream;
+    Scratch & g = g_scratch;
+    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
+    if (!g.copy_stream) {
+        UAV_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+        for (auto & e : g.ev_copy) UAV_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (num_views)
+        UAV_CUDA(cudaMemcpyAsync(g.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views, cudaMemcpyHostToDevice, s));
+    UAV_CUDA(cudaMemsetAsync(obs->num_rows, 0, 4 * (size_t)obs->num_cols, s));
+    if (stats) UAV_CUDA(cudaMemsetAsync(g.stats, 0, 4 * sizeof(unsigned long long), s));
+    g.ev_valid = false;
+    UAV_CUDA(cudaEventRecord(g.ev[0], s));
+    int rc = launch_k1(s, 1, g.views, num_views, max_distance, width, height, bvh, cloud, obs, stats ? g.stats : nullptr);
+    if (rc) return rc;
+    UAV_CUDA(cudaEventRecord(g.ev[1], s));
+    UAV_CUDA(cudaEventRecord(g.ev[2], s));
+    // counters are final after K1 here (nothing was invalidated, so K2 rewrites none: kernels.cu:251-254): their copy
+    // runs beside K2 + K3; recon goes out in four chunks, each copied while the next is computed
+    if (h_num_rows) {
+        UAV_CUDA(cudaEventRecord(g.ev_copy[0], s));
+        UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[0], 0));
+        UAV_CUDA(cudaMemcpyAsync(h_num_rows, obs->num_rows, 4 * (size_t)obs->num_cols, cudaMemcpyDeviceToHost, g.copy_stream));
+    }
+    const uint32_t nblocks = divup(obs->num_cols, 32), chunks = h_recons && nblocks >= 64 ? 4 : 1;
+    for (uint32_t c = 0; c < chunks; ++c) {
+        const uint32_t b0 = (uint32_t)((uint64_t)nblocks * c / chunks), b1 = (uint32_t)((uint64_t)nblocks * (c + 1) / chunks);
+        rc = launch_sort_eval(s, true, true, obs, recons, target_recon, wrecons, false, b0, b1 - b0);
+        if (rc) return rc;
+        if (h_recons) {
+            const size_t p0 = (size_t)b0 * 32, p1 = min((size_t)b1 * 32, (size_t)obs->num_cols);
+            UAV_CUDA(cudaEventRecord(g.ev_copy[1 + c], s));
+            UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[1 + c], 0));
+            UAV_CUDA(cudaMemcpyAsync(h_recons + p0, recons->data + p0, 4 * (p1 - p0), cudaMemcpyDeviceToHost, g.copy_stream));
+        }
+    }
+    UAV_CUDA(cudaEventRecord(g.ev[3], s));
+    if (launch_reduce(s, wrecons)) return 1;
+    UAV_CUDA(cudaEventRecord(g.ev[4], s));
+    g.ev_valid = true;
+    if (stats) UAV_CUDA(cudaMemcpyAsync(g.h_stats, g.stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    if (h_recons || h_num_rows) {                            // the caller's stream owns the host buffers when this returns
+        UAV_CUDA(cudaEventRecord(g.ev_copy[5], g.copy_stream));
+        UAV_CUDA(cudaStreamWaitEvent(s, g.ev_copy[5], 0));
+    }
+    UAV_CUDA(cudaStreamSynchronize(s));
+    if (out3) { out3[0] = (float)g.h_acc->sum; out3[1] = ord2f(g.h_acc->mn); out3[2] = ord2f(g.h_acc->mx); }
+    if (stats) {
+        for (int i = 0; i < 4; ++i) stats[i] = g.h_stats[i];
+        stats[2] = (uint64_t)cloud->n * num_views;
     }
     return 0;
 }
