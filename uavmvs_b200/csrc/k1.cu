@@ -150,17 +150,43 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
     }
 }
 
-// caps[b] = 32 * number of candidate views of block b within [v0, v1)
+// caps[b] = 32 * number of candidate views of block b within [v0, v1).  Warp per super-block (32 blocks = the 32 bits
+// of a mask word): every lane adds its view words into bit-sliced counters (7 planes, carry-save: ~14 logic ops per
+// word count all 32 bits at once), eight loads in flight; the planes are then read out per bit and summed over the
+// lanes with one redux each.  (A thread per block walking the views one dependent load at a time took 0.058 ms on
+// config 2, all of it load latency.)
 __global__ void k_block_caps(const uint32_t * __restrict__ masks, uint32_t num_views, uint32_t v0, uint32_t v1,
     uint32_t num_blocks, uint32_t * __restrict__ caps)
 {
-    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= num_blocks) return;
-    const uint32_t * row = masks + (size_t)(b >> 5) * num_views;     // the same word for the 32 lanes: broadcast
-    const uint32_t bit = b & 31;
+    const uint32_t sb = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (sb >= (num_blocks + 31) / 32) return;                         // warp-uniform
+    const uint32_t * row = masks + (size_t)sb * num_views;
     uint32_t c = 0;
-    for (uint32_t v = v0; v < v1; ++v) c += (__ldg(row + v) >> bit) & 1u;
-    caps[b] = 32u * c;
+    for (uint32_t r0 = v0; r0 < v1; r0 += 32u * 120u) {               // <= 120 words per lane and round: 7 planes hold 127
+        const uint32_t r1 = min(v1, r0 + 32u * 120u);
+        uint32_t p[7] = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        for (uint32_t base = r0; base < r1; base += 32u * 8u) {
+            uint32_t w[8];
+            #pragma unroll
+            for (int j = 0; j < 8; ++j) { const uint32_t v = base + 32u * j + lane; w[j] = v < r1 ? __ldg(row + v) : 0u; }
+            #pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                uint32_t carry = w[j];
+                #pragma unroll
+                for (int k = 0; k < 7; ++k) { const uint32_t t = p[k] & carry; p[k] ^= carry; carry = t; }
+            }
+        }
+        #pragma unroll
+        for (uint32_t bit = 0; bit < 32; ++bit) {
+            uint32_t cnt = 0;
+            #pragma unroll
+            for (int k = 0; k < 7; ++k) cnt |= ((p[k] >> bit) & 1u) << k;
+            const uint32_t sum = __reduce_add_sync(0xffffffffu, cnt);
+            if (lane == bit) c += sum;
+        }
+    }
+    const uint32_t b = sb * 32 + lane;
+    if (b < num_blocks) caps[b] = 32u * c;
 }
 
 __global__ void k_sum_caps(const uint32_t * __restrict__ caps, uint32_t n, unsigned long long * total)
@@ -1249,7 +1275,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     while (v0 < num_views) {
         uint32_t v1 = (uint32_t)min((uint64_t)num_views, (uint64_t)v0 + step);
         UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
-        k_block_caps<<<divup(nb, 128), 128, 0, s>>>(k.masks, num_views, v0, v1, nb, k.caps);
+        k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, s>>>(k.masks, num_views, v0, v1, nb, k.caps);
         k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, s>>>(k.caps, nb, k.total);
         UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
         const bool spec = speculate;
