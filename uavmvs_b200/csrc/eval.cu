@@ -34,6 +34,7 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
     if (dirty && dirty[bx] == 0u) return;
     __shared__ float4 s_tile[32 * SE_TILE_STRIDE];
     __shared__ float4 s_col[SE_THREADS / 32][32];
+    __shared__ __align__(16) float s_key[SE_THREADS / 32][32];
     __shared__ uint32_t s_rows[32], s_valid[32];
     __shared__ uint16_t s_pairs[496];                      // pair q -> (i << 8 | j), i > j, q = i (i - 1) / 2 + j
     const uint32_t tx = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -75,15 +76,22 @@ k_sort_eval(float4 * obs, uint32_t * num_rows_ptr, uint32_t max_rows, uint32_t s
             // reference's bitonic network (it never exchanges equal keys, kernels.cu:241), so a column with a
             // tie among its valid rows runs that network instead.  Invalid rows and padding (-1) sort behind
             // every valid row (cos(theta) >= 0.087) and are never written back.
-            uint32_t rank = 0; bool tie = !(theta == theta);          // a NaN key: leave it to the network
-            for (uint32_t k = 0; k < num_rows; ++k) {
-                const float o = __shfl_sync(0xffffffffu, theta, k);
-                rank += o > theta;
-                tie |= (o == theta) && (k != tx);
+            // The keys go through shared memory, four per load; two valid rows hold equal keys exactly when they get
+            // equal ranks (a larger key counts towards every smaller one), so one match_any finds the ties.
+            __syncwarp();
+            s_key[w][tx] = theta;
+            __syncwarp();
+            uint32_t rank = 0;
+            const float4 * kp = reinterpret_cast<const float4 *>(s_key[w]);
+            for (uint32_t k4 = 0; 4u * k4 < num_rows; ++k4) {
+                const float4 o = kp[k4];
+                rank += (uint32_t)(o.x > theta) + (uint32_t)(o.y > theta) + (uint32_t)(o.z > theta) + (uint32_t)(o.w > theta);
             }
             const bool valid_row = theta >= 0.0f;
             nv = __popc(__ballot_sync(0xffffffffu, valid_row));
-            if (!__any_sync(0xffffffffu, tie && (valid_row || !(theta == theta)))) {
+            const uint32_t peers = __match_any_sync(0xffffffffu, valid_row ? rank : 64u + tx);
+            const bool tie = (valid_row && peers != (1u << tx)) || !(theta == theta);      // a NaN key: leave it to the network
+            if (!__any_sync(0xffffffffu, tie)) {
                 __syncwarp();
                 if (valid_row) { s_tile[rank * SE_TILE_STRIDE + p] = ray; if (DO_EVAL) s_col[w][rank] = ray; }
                 __syncwarp();
