@@ -80,6 +80,13 @@ int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, const float 
  * libs/cacc/kd_tree.cu:15-45.  nodes[4n] = {vid,dim,left,right}, verts[3n]. */
 int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t num_nodes, uavmvs_kdtree ** out);
 int uavmvs_kdtree_destroy(uavmvs_kdtree * kd);
+/* Host-side median-split build over n points (the rule of acc::KDTree<3>, libs/acc/kd_tree.h:92-158, single-threaded
+ * numbering) followed by uavmvs_kdtree_create: for callers that do not link libs/acc. */
+int uavmvs_kdtree_build(const float * verts, uint32_t n, uavmvs_kdtree ** out);
+/* The vertex list of generate_sphere_mesh(radius, subdivisions) (libs/geom/sphere.h:17-115) in its order, coincident
+ * twins included: 1272 vertices / 642 distinct directions at 3 subdivisions -- the bins of sphere_hist
+ * (apps/optimize_trajectory/optimize_trajectory.cu:157-164).  verts == NULL: only *count is written. */
+int uavmvs_sphere_vertices(float radius, uint32_t subdivisions, float * verts, uint32_t capacity, uint32_t * count);
 /* cacc::nnsearch::find_nn<3> (libs/cacc/nnsearch.h:67-155) for n host queries [n][3] -> vertex indices (host).
  * certified_lookup != 0 answers through the cube-map / neighbour-list shortcut the batched histogram path uses
  * (kd.cuh); it must and does return the same indices, duplicates included - the parity tests compare the two. */
@@ -195,10 +202,70 @@ int uavmvs_evaluate_trajectory_to_host(void * stream, const float * views, uint3
     uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
     float out3[3], uint64_t stats[4]);
 
+/* ---- Multi-GPU: the proxy cloud is sharded by points, one process per GPU, mesh / KD-tree / trajectory replicated
+ * (every output of the path is per point).  The only exchange of the evaluation is the trajectory score, which the
+ * reference computes on one GPU with cacc::reduction::sum / min / max (libs/cacc/reduction.h:132-162) and
+ * avg_wrecon = sum / N (apps/optimize_trajectory/optimize_trajectory.cu:529).
+ * A communicator wraps an ncclComm_t.  libnccl.so.2 is resolved with dlopen at the first use (the copy already
+ * loaded into the process, e.g. PyTorch's, else the system's): single-GPU users never need NCCL. */
+typedef struct uavmvs_comm uavmvs_comm;
+#define UAVMVS_COMM_ID_BYTES 128
+/* ncclGetUniqueId on one rank; the caller ships the 128 bytes to the other ranks (MPI, torch.distributed, a file). */
+int uavmvs_comm_unique_id(uint8_t id[UAVMVS_COMM_ID_BYTES]);
+/* ncclCommInitRank on the calling thread's current device (collective over all `world` ranks). */
+int uavmvs_comm_create(const uint8_t id[UAVMVS_COMM_ID_BYTES], int world, int rank, uavmvs_comm ** out);
+/* Wraps an ncclComm_t the application already owns (not destroyed by uavmvs_comm_destroy). */
+int uavmvs_comm_adopt(void * nccl_comm, int world, int rank, uavmvs_comm ** out);
+int uavmvs_comm_info(const uavmvs_comm * comm, int * world, int * rank);
+int uavmvs_comm_destroy(uavmvs_comm * comm);
+
+#define UAVMVS_SCORE_DOUBLES 8
+/* The evaluation of uavmvs_evaluate_trajectory* on this rank's shard of the cloud, followed on the same stream --
+ * no host synchronisation in between -- by ONE collective: an all-gather of a packed 64-byte record per rank
+ * {sum(wrecon) (double), points, rays, observations, pairs after the block cull, min, max, pairs}, folded on the device
+ * in rank order, so every rank returns the same bits:
+ *   score[0] = sum over all shards of wrecon   [1] = number of points   -> avg_wrecon = score[0] / score[1]
+ *   score[2] = min, [3] = max of wrecon        [4] = occlusion rays, [5] = visible observations,
+ *   score[6] = (point, view) pairs surviving the block-level cull, [7] = (point, view) pairs evaluated.
+ * views: HOST [num_views][28] when views_on_device == 0, else a device pointer.  h_recons / h_num_rows: optional HOST
+ * buffers of this rank's shard, filled as by uavmvs_evaluate_trajectory_to_host.  comm == NULL: single GPU (no NCCL).
+ * local_out3 (may be NULL): this shard's {sum, min, max}. */
+int uavmvs_evaluate_trajectory_sharded(void * stream, uavmvs_comm * comm, const float * views, int views_on_device,
+    uint32_t num_views, float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
+    double score[UAVMVS_SCORE_DOUBLES], float local_out3[3]);
+/* SUM all-reduce (ncclAllReduce, in place, on `stream`) of the first `count` floats of a device array: the partial
+ * [B][bins] sphere histograms of the batched K4 / K5 when the cloud is sharded. */
+int uavmvs_allreduce_array(void * stream, uavmvs_comm * comm, uavmvs_array * a, uint64_t count);
+/* All-gather of per-point vectors in shard order: every rank contributes `count` floats (device array `local`) and
+ * receives world * count floats in `all` (device array); shards shorter than `count` are padded by the caller. */
+int uavmvs_allgather_array(void * stream, uavmvs_comm * comm, const uavmvs_array * local, uint64_t count,
+    uavmvs_array * all);
+
+/* A trajectory resident on the device for repeated evaluation ([num_views][28] floats); the device pointer goes to the
+ * *_device / views_on_device entry points.  (The apps keep the cameras on the host and pass one view per launch,
+ * apps/evaluate_trajectory/evaluate_trajectory.cu:154-164.) */
+int uavmvs_views_upload(void * stream, const float * views, uint32_t num_views, float ** d_views);
+int uavmvs_views_free(float * d_views);
+
+/* Kernel launches issued by the evaluation path (K1 pipeline, K2/K3/K8, K9, histogram and closest-point kernels) in this
+ * process since the last reset; diagnostics for bench.py's gpu_launches (no reference counterpart). */
+int uavmvs_launch_count(uint64_t * out, int reset);
+
 /* Device time (ms, CUDA events on the call's stream) of the stages of the calling thread's last
  * uavmvs_evaluate_trajectory*: ms[0] = K1 (all views), [1] = K2, [2] = K3+K8, [3] = K9.  The
  * reference only wall-clocks the K1 loop (apps/evaluate_trajectory/evaluate_trajectory.cu:144-171). */
 int uavmvs_profile_last(float ms[4]);
+/* Per-kernel device time of the K1 pipeline (no reference counterpart).  After uavmvs_profile_k1_enable(1) every K1
+ * launch records CUDA events at its kernel boundaries; uavmvs_profile_k1 returns, for the calling thread's last K1
+ * launch, ms[0] = k_view_masks, [1] = k_block_caps + k_sum_caps + scan, [2] = k_cull_emit, [3] = k_trace,
+ * [4] = k_retire (summed over the view batches). */
+int uavmvs_profile_k1_enable(int on);
+int uavmvs_profile_k1(float ms[5]);
+/* Device time (ms) between the end of K9 and the end of the score collective (pack, all-gather, fold) of the calling
+ * thread's last uavmvs_evaluate_trajectory_sharded. */
+int uavmvs_profile_last_collective(float * ms);
 
 /* Diagnostics of the calling thread's K1 launches since the last reset (no reference counterpart):
  * out[0] = (block, view) packets tested by the visibility-shaft pass, [1] = packets certified

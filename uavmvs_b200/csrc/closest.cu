@@ -117,7 +117,7 @@ extern "C" int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, c
     UAV_CUDA(cudaMallocAsync(&d_found, (size_t)n, s));
     UAV_CUDA(cudaMallocAsync(&d_idx, sizeof(uint32_t) * (size_t)n, s));
     UAV_CUDA(cudaMemcpyAsync(d_pts, points, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, s));
-    k_closest_point<<<divup(n, 128), 128, 0, s>>>(view_of(bvh), d_pts, n, max_dist, d_found, d_idx, d_cp);
+    k_closest_point<<<divup(n, 128), 128, 0, uav::counted(s)>>>(view_of(bvh), d_pts, n, max_dist, d_found, d_idx, d_cp);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaMemcpyAsync(found, d_found, (size_t)n, cudaMemcpyDeviceToHost, s));
     UAV_CUDA(cudaMemcpyAsync(tri_index, d_idx, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, s));

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <atomic>
 
 #include "../../include/uavmvs_b200.h"
 
@@ -33,7 +34,16 @@ int fail(const char * file, int line, const char * what);
 #define UAV_REQUIRE(cond, msg)                                                      \
     do { if (!(cond)) { uav::set_error(__FILE__, __LINE__, #cond, msg); return 2; } } while (0)
 
+#ifndef UAV_STACK
+#define UAV_STACK 96              // binary walks (trace.cuh, closest.cu): one entry per level
+#endif
+constexpr int K1_STACK = 160;     // 4-wide walk of k_trace: <= 3 pushes per wide level (= two binary levels)
+
 static inline unsigned divup(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+// Launch counter of the evaluation path (uavmvs_launch_count): every `<<<..., counted(s)>>>` adds one.
+extern std::atomic<unsigned long long> g_launches;
+static inline cudaStream_t counted(cudaStream_t s, unsigned n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); return s; }
 
 // ---------------------------------------------------------------- device layouts
 // Two-child node, 64 B, one aligned 4 x LDG.128: both child boxes (exact floats, the
@@ -82,6 +92,7 @@ struct uavmvs_bvh {
     float bound_abs[3];   // max |coordinate| of the root box per axis (error band of the fp16 node test)
     uav::Tri64 * ptris;
     uint32_t root_is_leaf, root_first, root_count;
+    uint32_t depth;     // upper bound of the binary depth (2 x levels of the wide collapse), checked against the stacks at upload
     uint32_t nested;    // child boxes inside parent boxes, leaf boxes tight, leaves <= 31 triangles (checked at upload)
     uint32_t max_leaf;
 };
@@ -140,6 +151,8 @@ struct uavmvs_obs {
 };
 
 struct uavmvs_array { uint32_t n; float * data; };
+// ncclComm_t + a device staging buffer for the score all-gather (eval.cu); comm.cu
+struct uavmvs_comm { void * nccl = nullptr; int world = 1, rank = 0, owned = 0; double * gather = nullptr; };
 struct uavmvs_image { uint32_t width, height; uint64_t pitch; float * data; };
 
 namespace uav {
@@ -198,6 +211,8 @@ struct HistJob {
     const float4 * obs; const uint32_t * num_rows; uint32_t max_rows, stride; const float * recons;
     float * hist;
     Heur heur;
+    // order-independent accumulation (k1.cu:k_retire_hist): fixed-point accumulators [views][kd_n] and fx = {scale, bound}
+    unsigned long long * acc; const float * fx;
 };
 
 // K1 pipeline (k1.cu).  d_stats (device, may be null): [0] += occlusion rays, [1] += visible
@@ -206,5 +221,11 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
     uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hist_job = nullptr);
 int k1_counters(unsigned long long out[4], int reset);
+int k1_profile_enable(int on);
+int k1_profile(float ms[5]);
+
+// comm.cu: NCCL collectives on a stream (f64 != 0: doubles, else floats; counts in elements per rank)
+int comm_allgather(cudaStream_t s, uavmvs_comm * c, const void * send, void * recv, size_t count, int f64);
+int comm_allreduce_sum_f32(cudaStream_t s, uavmvs_comm * c, void * buf, size_t count);
 
 }  // namespace uav

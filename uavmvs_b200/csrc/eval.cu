@@ -236,20 +236,20 @@ static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_o
     const uint32_t stride = (uint32_t)(obs->pitch / sizeof(float4));
     float * r = recons ? recons->data : nullptr, * wr = wrecons ? wrecons->data : nullptr;
     if (do_sort && do_eval)
-        k_sort_eval<true, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<true, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     else if (do_sort)
-        k_sort_eval<true, false><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<true, false><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     else
-        k_sort_eval<false, true><<<grid, SE_THREADS, 0, s>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<false, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
 
 static int launch_reduce(cudaStream_t s, const uavmvs_array * a)
 {
-    k_reduce_init<<<1, 1, 0, s>>>(g_scratch.acc);
+    k_reduce_init<<<1, 1, 0, uav::counted(s)>>>(g_scratch.acc);
     unsigned grid = min(divup(a->n, 256 * 8), 148u * 8u);
-    k_reduce<<<grid ? grid : 1, 256, 0, s>>>(a->data, a->n, g_scratch.acc);
+    k_reduce<<<grid ? grid : 1, 256, 0, uav::counted(s)>>>(a->data, a->n, g_scratch.acc);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaMemcpyAsync(g_scratch.h_acc, g_scratch.acc, sizeof(ReduceAcc), cudaMemcpyDeviceToHost, s));
     return 0;
@@ -331,7 +331,7 @@ int uavmvs_reevaluate_observation_rays(void * stream, uavmvs_obs * obs, uavmvs_a
 int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, float target_recon, uavmvs_array * wrecons)
 {
     UAV_REQUIRE(recons && wrecons && recons->n == wrecons->n, "bad arrays");
-    k_calculate_func_recons<<<divup(recons->n, 256), 256, 0, (cudaStream_t)stream>>>(recons->data, recons->n,
+    k_calculate_func_recons<<<divup(recons->n, 256), 256, 0, uav::counted((cudaStream_t)stream)>>>(recons->data, recons->n,
         target_recon, wrecons->data);
     UAV_CUDA(cudaGetLastError());
     return 0;

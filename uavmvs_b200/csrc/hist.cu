@@ -332,8 +332,8 @@ static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos
     a.hist = hist->data; a.heur = current_heur();
     size_t smem = kd->num_nodes * sizeof(float);
     unsigned grid = divup(cloud->n, HIST_THREADS);
-    if (with_recon) k_populate_spherical_histogram<true><<<grid, HIST_THREADS, smem, s>>>(a);
-    else k_populate_spherical_histogram<false><<<grid, HIST_THREADS, smem, s>>>(a);
+    if (with_recon) k_populate_spherical_histogram<true><<<grid, HIST_THREADS, smem, uav::counted(s)>>>(a);
+    else k_populate_spherical_histogram<false><<<grid, HIST_THREADS, smem, uav::counted(s)>>>(a);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -358,7 +358,7 @@ static int frustum_bits(uavmvs_kdtree * kd, const float calib[9], int width, int
         UAV_CUDA(cudaMalloc(&kd->fr_bits, sizeof(uint32_t) * (size_t)words * npix));
         UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
         UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
-        k_frustum_bits<<<divup(npix, 128), 128, 0, s>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
+        k_frustum_bits<<<divup(npix, 128), 128, 0, uav::counted(s)>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
         UAV_CUDA(cudaGetLastError());
         UAV_CUDA(cudaStreamSynchronize(s));                // other streams may use the matrix as soon as the lock drops
         UAV_CUDA(cudaFree(d_K));
@@ -408,7 +408,7 @@ int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int
         unsigned long long * d_best;
         UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long), s));
         const uint32_t parts = max(1u, npix / EVB_THREADS);
-        k_evaluate_spherical_histogram_batch<<<dim3(1, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(bits, words, npix,
+        k_evaluate_spherical_histogram_batch<<<dim3(1, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
             sphere_hist->data, S, hist->data, d_best, d_best + 1);
         UAV_CUDA(cudaGetLastError());
         UAV_CUDA(cudaFreeAsync(d_best, s));
@@ -418,7 +418,7 @@ int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int
     UAV_CUDA(cudaMallocAsync(&d_K, 9 * sizeof(float), s));
     UAV_CUDA(cudaMemcpyAsync(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice, s));
     dim3 grid(divup(hist->width, 128), hist->height);
-    k_evaluate_spherical_histogram<<<grid, 128, kd->num_nodes * sizeof(float4), s>>>(d_K, width, height,
+    k_evaluate_spherical_histogram<<<grid, 128, kd->num_nodes * sizeof(float4), uav::counted(s)>>>(d_K, width, height,
         kd_view(kd), sphere_hist->data, hist->data, hist->width, hist->height, (uint32_t)(hist->pitch / 4));
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaFreeAsync(d_K, s));
@@ -429,7 +429,7 @@ int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const 
     uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud)
 {
     UAV_REQUIRE(bvh && kd && cloud, "null argument");
-    k_estimate_capture_difficulty<<<divup(cloud->n, 64), 64, 0, (cudaStream_t)stream>>>(
+    k_estimate_capture_difficulty<<<divup(cloud->n, 64), 64, 0, uav::counted((cudaStream_t)stream)>>>(
         view_of(bvh), kd_view(kd), mesh_size, max_distance, cloud->vertices, cloud->normals, cloud->n,
         cloud->values, cloud->qualities);
     UAV_CUDA(cudaGetLastError());
@@ -462,7 +462,7 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     UAV_CUDA(cudaMallocAsync(&d_pos, sizeof(float) * 3 * (size_t)num_positions, s));
     UAV_CUDA(cudaMallocAsync(&d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_positions, s));
     UAV_CUDA(cudaMemcpyAsync(d_pos, positions, sizeof(float) * 3 * (size_t)num_positions, cudaMemcpyHostToDevice, s));
-    k_fill_positions<<<divup(num_positions, 256), 256, 0, s>>>(d_pos, num_positions, d_views);
+    k_fill_positions<<<divup(num_positions, 256), 256, 0, uav::counted(s)>>>(d_pos, num_positions, d_views);
     UAV_CUDA(cudaGetLastError());
     int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
     cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s);
@@ -485,7 +485,7 @@ int uavmvs_kdtree_find_nn(void * stream, uavmvs_kdtree * kd, const float * queri
     UAV_CUDA(cudaMallocAsync(&d_q, sizeof(float) * 3 * n, s));
     UAV_CUDA(cudaMallocAsync(&d_o, sizeof(uint32_t) * n, s));
     UAV_CUDA(cudaMemcpyAsync(d_q, queries, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, s));
-    k_kd_find_nn<<<divup(n, 256), 256, 0, s>>>(kd_view(kd), fv, d_q, n, d_o);
+    k_kd_find_nn<<<divup(n, 256), 256, 0, uav::counted(s)>>>(kd_view(kd), fv, d_q, n, d_o);
     UAV_CUDA(cudaGetLastError());
     UAV_CUDA(cudaMemcpyAsync(out_idx, d_o, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, s));
     UAV_CUDA(cudaStreamSynchronize(s));
@@ -514,7 +514,7 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
     UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long) * (size_t)num_positions, s));
     UAV_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)num_positions, s));
     UAV_CUDA(cudaMemsetAsync(d_best + num_positions, 0, sizeof(unsigned long long) * (size_t)num_positions, s));
-    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), s>>>(bits, words, npix,
+    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
         sphere_hists->data, S, images ? images->data : nullptr, d_best, d_best + num_positions);
     UAV_CUDA(cudaGetLastError());
     if (h_min || h_argmin || h_max || h_argmax) {

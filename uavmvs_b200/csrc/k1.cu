@@ -46,7 +46,6 @@ constexpr int K1_SB_PER_WARP = K1_SB_PER_WARP_N;
 constexpr int K1_PEND = 6;        // deferred leaves per lane
 constexpr int K1_REFILL = K1_REFILL_N;   // refill when at least this many lanes are idle
 constexpr int K1_TRI = K1_TRI_N;  // run the triangle phase when this many lanes hold a leaf
-constexpr int K1_STACK = 160;     // <= 3 pushes per two binary levels; LBVH depth <= 96
 constexpr int K1_STEPS = K1_STEPS_N;     // node steps between two rounds of warp-level bookkeeping
 
 // Conservative (group of points, view) test: false only if NO point inside the sphere
@@ -995,7 +994,13 @@ struct RetireArgs {
 };
 
 // Warp per block; the block's rays are walked in (view, point) order, 32 at a time.
-// POPULATE: kernels.cu:171-181 (row = running counter of the point, stored iff row < max_rows).
+// POPULATE: kernels.cu:171-181 (row = running counter of the point, stored iff row < max_rows).  The reference takes
+//   every row with atomicAdd(num_rows, 1), which is what lets its optimiser run K1 for different views from several
+//   host threads on the SAME observation array (optimize_trajectory.cu:470-495).  Here a first pass over the block's
+//   visibility bytes counts the visible rays per point and ONE atomicAdd per point reserves that many rows; the second
+//   pass fills them in view order.  Concurrent launches on one array therefore never hand out a row twice and never
+//   lose an increment -- their rows interleave per (launch, block) instead of per ray, one of the orders the
+//   reference's own concurrent launches can produce.
 // !POPULATE: kernels.cu:183-200 (mark the first stored ray equal within 1e-5).
 template <bool POPULATE>
 __global__ void __launch_bounds__(K1_WARPS * 32)
@@ -1012,6 +1017,7 @@ k_retire(RetireArgs a)
     const bool valid = id < a.n;
     const uint32_t count = a.rl.cnt[blk];
     if (count == 0) return;
+    const uint32_t base = a.rl.off[blk];
     {
         V3 nrm = ld3(a.normals[valid ? id : a.n - 1]);
         V3 rx = normalized(orthogonal(nrm));              // relative_direction(), kernels.cu:63-76
@@ -1019,10 +1025,26 @@ k_retire(RetireArgs a)
         s_nrm[w][lane] = make_float4(nrm.x, nrm.y, nrm.z, 0.0f);
         s_rx[w][lane] = make_float4(rx.x, rx.y, rx.z, 0.0f);
         s_ry[w][lane] = make_float4(ry.x, ry.y, ry.z, 0.0f);
-        s_cnt[w][lane] = valid ? a.num_rows[id] : 0u;
+        s_cnt[w][lane] = POPULATE ? 0u : (valid ? a.num_rows[id] : 0u);
     }
     __syncwarp();
-    const uint32_t base = a.rl.off[blk];
+    if (POPULATE) {
+        // pass 1: visible rays per point of this block (the status bytes stay in L1 / L2 for pass 2)
+        for (uint32_t c0 = 0; c0 < count; c0 += 128) {
+            uint32_t vb4[4];
+            #pragma unroll
+            for (int u = 0; u < 4; ++u) { const uint32_t i = c0 + 32 * u + lane; vb4[u] = i < count ? (uint32_t)__ldg(a.rl.vis + base + i) : 0u; }
+            #pragma unroll
+            for (int u = 0; u < 4; ++u) if ((vb4[u] & 3u) == 2u) atomicAdd(&s_cnt[w][vb4[u] >> 2], 1u);
+        }
+        __syncwarp();
+        const uint32_t mine = s_cnt[w][lane];
+        uint32_t first = 0;
+        if (mine && valid) first = atomicAdd(a.num_rows + id, mine);     // rows [first, first + mine) are this launch's
+        __syncwarp();
+        s_cnt[w][lane] = first;
+        __syncwarp();
+    }
     unsigned long long st_vis = 0;
     bool touched = false;
     // the next 32 records are fetched while the current ones are processed: an iteration is a chain of two
@@ -1082,7 +1104,6 @@ k_retire(RetireArgs a)
             }
         }
     }
-    if (POPULATE && valid) a.num_rows[id] = s_cnt[w][lane];
     if (touched && lane == 0 && a.dirty) a.dirty[blk] = 1u;
     if (a.stats) {
         for (int o = 16; o > 0; o >>= 1) st_vis += __shfl_xor_sync(0xffffffffu, st_vis, o);
@@ -1092,6 +1113,17 @@ k_retire(RetireArgs a)
 
 // Histogram jobs: every visible ray adds its score to hist[view][nearest sphere bin].
 // WITH_RECON = false: K4, kernels.cu:318-335.  true: K5, kernels.cu:366-389.
+//
+// The reference adds every contribution with a float atomicAdd (kernels.cu:335, :389), so its histogram depends on the
+// arrival order in the last bits.  Here the sum is ORDER INDEPENDENT, hence bit-reproducible from run to run: a
+// contribution c with |c| <= bound (a bound known before the launch: the largest quality for K4, 4 (|target| + 1)^2 for
+// K5; fx = {scale, bound}, scale = 2^(36 - e) with bound <= 2^e) is rounded once to the fixed-point integer
+// q = rn(c * scale) -- an absolute error <= bound 2^-37, five orders of magnitude below the float rounding of the sums
+// it replaces -- and integers add associatively.  Rays of one block towards one candidate position mostly fall into the
+// same bin (32 neighbouring points seen from tens of metres away), so the warp first adds the q of equal (position, bin)
+// keys with match_any + redux (q split into two 18-bit halves: redux is a 32-bit instruction) and issues ONE 64-bit
+// atomic per distinct key.  k_hist_finish turns the accumulators back into floats and adds them to the caller's array.
+// Contributions outside the bound (NaN / inf inputs, recons that are not recons) keep the reference's float atomic.
 template <bool WITH_RECON>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_retire_hist(RetireArgs a, HistJob h)
@@ -1104,52 +1136,69 @@ k_retire_hist(RetireArgs a, HistJob h)
     if (count == 0) return;
     const uint32_t base = a.rl.off[blk];
     KdView kd; kd.nodes = h.kd_nodes; kd.verts = h.kd_verts; kd.n = h.kd_n;
+    const float fx_scale = __ldg(h.fx), fx_bound = __ldg(h.fx + 1);
     unsigned long long st_vis = 0;
     for (uint32_t c0 = 0; c0 < count; c0 += 32) {
         const uint32_t i = c0 + lane;
         const uint32_t vb = i < count ? (uint32_t)__ldcs(a.rl.vis + base + i) : 0u;
-        if ((vb & 3u) != 2u) continue;                    // occluded (or past the end)
-        ++st_vis;
-        const float4 d4 = __ldcs(a.rl.dirl + base + i);
-        const uint32_t view = a.rl.rview[base + i];
-        const uint32_t id = blk * 32 + (vb >> 2);
-        const V3 v2cn = ld3(d4), n = ld3(a.normals[id]);
-        const float l = d4.w;
-        const float scale = 1.0f - (l / a.max_distance);
-        const float ctheta = dot(v2cn, n);
+        bool act = (vb & 3u) == 2u;                       // visible (not occluded, not past the end)
+        if (!__any_sync(0xffffffffu, act)) continue;
         float contrib = 0.0f;
-        if (!WITH_RECON) {
-            const float capture_difficulty = fmaxf(h.qualities[id], 0.0f);
-            const float min_theta = fminf(h.values[id], 1.484f);
-            const float scaling = (kPi / 2.0f) / ((kPi / 2.0f) - min_theta);
-            const float theta = acosf(__saturatef(ctheta));
-            const float rel_theta = fmaxf(theta - min_theta, 0.0f) * scaling;
-            contrib = capture_difficulty * cosf(rel_theta) * scale;
-        } else {
-            const uint32_t rows = h.num_rows[id];
-            if (rows >= h.max_rows) continue;             // kernels.cu:373
-            const float recon = h.recons[id];
-            float new_recon = 0.0f;
-            if (rows >= 1) {
-                const V3 rel = relative_direction(v2cn, n);
-                const float m_k = h.heur.m_k, m_x0 = kPi / h.heur.m_x0, t_k = h.heur.t_k, t_x0 = kPi / h.heur.t_x0;
-                float sum = 0.0f;
-                for (uint32_t r = 0; r < rows; ++r) {     // heuristic(), kernels.cu:111-136
-                    const float4 o = h.obs[(size_t)r * h.stride + id];
-                    const float calpha = dot(rel, mk(o.x, o.y, o.z));
-                    const float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
-                    const float sc = fminf(o.w, scale);
-                    const float ct = fminf(o.z, rel.z);
-                    const float matchability = (1.0f - logistic(alpha, m_k, m_x0)) * ct;
-                    const float triangulation = logistic(alpha, t_k, t_x0) * sc;
-                    sum += matchability * triangulation;
+        uint32_t key = 0xffffffffu - lane;                // lanes without a contribution: a key nobody shares
+        if (act) {
+            ++st_vis;
+            const float4 d4 = __ldcs(a.rl.dirl + base + i);
+            const uint32_t view = a.rl.rview[base + i];
+            const uint32_t id = blk * 32 + (vb >> 2);
+            const V3 v2cn = ld3(d4), n = ld3(a.normals[id]);
+            const float l = d4.w;
+            const float scale = 1.0f - (l / a.max_distance);
+            const float ctheta = dot(v2cn, n);
+            if (!WITH_RECON) {
+                const float capture_difficulty = fmaxf(h.qualities[id], 0.0f);
+                const float min_theta = fminf(h.values[id], 1.484f);
+                const float scaling = (kPi / 2.0f) / ((kPi / 2.0f) - min_theta);
+                const float theta = acosf(__saturatef(ctheta));
+                const float rel_theta = fmaxf(theta - min_theta, 0.0f) * scaling;
+                contrib = capture_difficulty * cosf(rel_theta) * scale;
+            } else {
+                const uint32_t rows = h.num_rows[id];
+                if (rows >= h.max_rows) act = false;      // kernels.cu:373
+                else {
+                    const float recon = h.recons[id];
+                    float new_recon = 0.0f;
+                    if (rows >= 1) {
+                        const V3 rel = relative_direction(v2cn, n);
+                        const float m_k = h.heur.m_k, m_x0 = kPi / h.heur.m_x0, t_k = h.heur.t_k, t_x0 = kPi / h.heur.t_x0;
+                        float sum = 0.0f;
+                        for (uint32_t r = 0; r < rows; ++r) {     // heuristic(), kernels.cu:111-136
+                            const float4 o = h.obs[(size_t)r * h.stride + id];
+                            const float calpha = dot(rel, mk(o.x, o.y, o.z));
+                            const float alpha = acosf(fmaxf(-1.0f, fminf(calpha, 1.0f)));
+                            const float sc = fminf(o.w, scale);
+                            const float ct = fminf(o.z, rel.z);
+                            const float matchability = (1.0f - logistic(alpha, m_k, m_x0)) * ct;
+                            const float triangulation = logistic(alpha, t_k, t_x0) * sc;
+                            sum += matchability * triangulation;
+                        }
+                        new_recon = recon + sum;
+                    }
+                    contrib = func(new_recon, h.target_recon) - func(recon, h.target_recon);
                 }
-                new_recon = recon + sum;
             }
-            contrib = func(new_recon, h.target_recon) - func(recon, h.target_recon);
+            if (act) {
+                const uint32_t bin = h.kd_fast.table ? kd_find_nn_fast(h.kd_fast, kd, -v2cn) : kd_find_nn(kd, -v2cn);
+                key = view * h.kd_n + bin;
+            }
         }
-        const uint32_t bin = h.kd_fast.table ? kd_find_nn_fast(h.kd_fast, kd, -v2cn) : kd_find_nn(kd, -v2cn);
-        atomicAdd(h.hist + (size_t)view * h.kd_n + bin, contrib);
+        const bool fin = act && fabsf(contrib) <= fx_bound;                   // NaN: false
+        if (act && !fin) { atomicAdd(h.hist + key, contrib); key = 0xffffffffu - lane; }
+        const long long q = fin ? __float2ll_rn(contrib * fx_scale) : 0ll;    // |q| <= 2^36; c * 2^k is exact
+        const uint32_t peers = __match_any_sync(0xffffffffu, key);
+        const int s_hi = __reduce_add_sync(peers, (int)(q >> 18));
+        const uint32_t s_lo = __reduce_add_sync(peers, (uint32_t)(q & 0x3ffffll));
+        if (fin && lane == (uint32_t)__ffs(peers) - 1u)
+            atomicAdd(h.acc + key, (unsigned long long)((long long)s_hi * 262144ll + (long long)s_lo));
     }
     if (a.stats) {
         for (int o = 16; o > 0; o >>= 1) st_vis += __shfl_xor_sync(0xffffffffu, st_vis, o);
@@ -1172,8 +1221,25 @@ struct K1Scratch {
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     int grid_trace = 0;
     cudaEvent_t ev_total = nullptr;
+    // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
+    std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
+    std::vector<int> ev_kind;                      // what starts at event i: 0 masks, 1 caps + scan, 2 cull, 3 trace, 4 retire, 5 end
 };
 static thread_local K1Scratch g_k1;
+static std::atomic<int> g_k1_profile{0};
+
+static int k1_mark(K1Scratch & k, cudaStream_t s, int kind)
+{
+    if (!g_k1_profile.load(std::memory_order_relaxed)) return 0;
+    if (k.ev_used == k.ev_pool.size()) {
+        cudaEvent_t e;
+        UAV_CUDA(cudaEventCreate(&e));
+        k.ev_pool.push_back(e); k.ev_kind.push_back(0);
+    }
+    k.ev_kind[k.ev_used] = kind;
+    UAV_CUDA(cudaEventRecord(k.ev_pool[k.ev_used++], s));
+    return 0;
+}
 
 template <typename T>
 static int grow(T ** p, size_t * cap, size_t need, cudaStream_t s)
@@ -1252,12 +1318,14 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         k.cub_cap = tmp_need;
     }
 
+    k.ev_used = 0;
+    if (k1_mark(k, s, 0)) return 1;
     dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
     // Histogram jobs test `1 - l / max_distance <= 0` (kernels.cu:310-311): with max_distance <= 0 (the planner's
     // swapped arguments can pass a negative average there, plan_trajectory.cu:270-274) nothing is out of range, so the
     // conservative range culls are switched off and the exact test decides alone.
     const float cull_distance = (hj && !(max_distance > 0.0f)) ? INFINITY : max_distance;
-    k_view_masks<<<mgrid, K1_WARPS * 32, 0, s>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
+    k_view_masks<<<mgrid, K1_WARPS * 32, 0, uav::counted(s)>>>(d_views, num_views, cloud->super_sphere, cloud->num_super,
         cloud->block_sphere, cloud->block_cone, cloud->block_nmax, nb, cull_distance, width, height, k.masks, inside_masks);
     UAV_CUDA(cudaGetLastError());
 
@@ -1274,9 +1342,10 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     uint32_t v0 = 0, step = num_views;
     while (v0 < num_views) {
         uint32_t v1 = (uint32_t)min((uint64_t)num_views, (uint64_t)v0 + step);
+        if (k1_mark(k, s, 1)) return 1;
         UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
-        k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, s>>>(k.masks, num_views, v0, v1, nb, k.caps);
-        k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, s>>>(k.caps, nb, k.total);
+        k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, uav::counted(s)>>>(k.masks, num_views, v0, v1, nb, k.caps);
+        k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, uav::counted(s)>>>(k.caps, nb, k.total);
         UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
         const bool spec = speculate;
         speculate = false;                                   // one attempt per call
@@ -1293,7 +1362,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 continue;
             }
             UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
-            if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
+            if (d_stats) k_add_u64<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
         }
         if (total > 0) {
             if (total > k.rays_cap) {
@@ -1302,7 +1371,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                     || grow(&k.vis, &c2, (size_t)total, s)) return 1;
                 k.rays_cap = (size_t)total;
             }
-            cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, s);
+            cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, uav::counted(s, 2));   // cub: DeviceScanInitKernel + DeviceScanKernel
             if (hj && grow(&k.rview, &k.rview_cap, k.rays_cap, s)) return 1;
             const bool entry = entry_enabled() && bvh->nested && !bvh->root_is_leaf;
             if (entry) {
@@ -1310,7 +1379,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 EntryArgs ea; ea.wide = bvh->wide; ea.lo = cloud->block_lo; ea.hi = cloud->block_hi; ea.num_blocks = nb;
                 ea.views = d_views; ea.num_views = num_views; ea.v0 = v0; ea.v1 = v1; ea.masks = k.masks; ea.off = k.off;
                 ea.fr = k.fr; ea.tau = entry_tau(); ea.counters = k.counters;
-                k_entry<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ea);
+                k_entry<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ea);
             }
             RayList rl; rl.g_total = spec ? k.total : nullptr; rl.g_cap = spec_cap; rl.tpk = entry ? k.tpk : nullptr; rl.fr = k.fr; rl.rview = k.rview; rl.dirl = k.dirl; rl.tdir = k.tdir; rl.torg = k.torg; rl.vis = k.vis; rl.off = k.off; rl.cnt = k.cnt; rl.tcnt = k.tcnt;
             // shafts: whole (block, view) packets proven visible without tracing (nested trees only)
@@ -1324,46 +1393,70 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 sa.views = d_views; sa.num_views = num_views; sa.v0 = v0; sa.v1 = v1; sa.masks = k.masks;
                 sa.cert = k.cert; sa.nchunks = nchunks; sa.counters = k.counters;
                 { const char * e = getenv("UAVMVS_SHAFT_STEPS"); sa.max_steps = e ? (uint32_t)atoi(e) : 1000000u; }
-                k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(sa);
+                k_shaft<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(sa);
             }
             const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
+            if (k1_mark(k, s, 2)) return 1;
             if (queued) rl.tdir = rl.dirl;            // one record per ray: every ray is traced, in list order
-            if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
-            else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
-            else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
-            else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
+            if (k1_mark(k, s, 3)) return 1;
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
             unsigned grid = (unsigned)k.grid_trace;
-            if (bvh->nested) k_trace<<<grid, K1_WARPS * 32, 0, s>>>(ta);
-            else k_trace_exact<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ta, (uint32_t)total);
+            if (bvh->nested) k_trace<<<grid, K1_WARPS * 32, 0, uav::counted(s)>>>(ta);
+            else k_trace_exact<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ta, (uint32_t)total);
+            if (k1_mark(k, s, 4)) return 1;
             RetireArgs ra; ra.verts = cloud->vertices; ra.normals = cloud->normals; ra.n = cloud->n; ra.num_blocks = nb;
             ra.rl = rl; ra.max_distance = max_distance;
             ra.stats = d_stats;
             if (hj) {
                 ra.obs = nullptr; ra.num_rows = nullptr; ra.max_rows = 0; ra.stride = 0; ra.dirty = nullptr;
-                if (hj->with_recon) k_retire_hist<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
-                else k_retire_hist<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra, *hj);
+                if (hj->with_recon) k_retire_hist<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra, *hj);
+                else k_retire_hist<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra, *hj);
                 UAV_CUDA(cudaGetLastError());
             } else {
                 ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
                 ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
                 ra.dirty = obs->dirty;
-                if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
-                else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, s>>>(ra);
+                if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
+                else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
                 UAV_CUDA(cudaGetLastError());
             }
         }
+        if (k1_mark(k, s, 5)) return 1;
         if (spec) {
             UAV_CUDA(cudaEventSynchronize(k.ev_total));      // the bound only; the batch keeps running
             if (*k.h_total > spec_cap) continue;             // guarded kernels were no-ops: same batch again, synchronously
-            if (d_stats) k_add_u64<<<1, 1, 0, s>>>(d_stats + 3, k.total);
+            if (d_stats) k_add_u64<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, k.total);
         }
         v0 = v1;
+    }
+    return 0;
+}
+
+int k1_profile_enable(int on) { g_k1_profile.store(on ? 1 : 0); return 0; }
+
+// ms[0] = k_view_masks, [1] = k_block_caps + k_sum_caps + scan, [2] = k_cull_emit*, [3] = k_trace*, [4] = k_retire*,
+// summed over the view batches of the calling thread's last launch_k1.
+int k1_profile(float ms[5])
+{
+    K1Scratch & k = g_k1;
+    for (int i = 0; i < 5; ++i) ms[i] = 0.0f;
+    UAV_REQUIRE(k.ev_used >= 2, "no profiled K1 launch on this thread (uavmvs_profile_k1_enable)");
+    UAV_CUDA(cudaEventSynchronize(k.ev_pool[k.ev_used - 1]));
+    for (size_t i = 0; i + 1 < k.ev_used; ++i) {
+        const int kind = k.ev_kind[i];
+        if (kind >= 5) continue;                             // "end" of a batch: the gap to the next batch is host time
+        float t = 0.0f;
+        UAV_CUDA(cudaEventElapsedTime(&t, k.ev_pool[i], k.ev_pool[i + 1]));
+        ms[kind] += t;
     }
     return 0;
 }
