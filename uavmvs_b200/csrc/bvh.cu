@@ -259,7 +259,7 @@ int finalize_layout(uavmvs_bvh * b)
         UAV_CUDA(cudaMemset(list_a, 0, 4));                  // the root's wide node is wide[0]
         int mode = 0;     // measured on config 2: two binary levels per wide node 4.95 ms / step, greedy by area 5.01 ms
         if (const char * e = getenv("UAVMVS_COLLAPSE")) mode = atoi(e);
-        uint32_t count = 1, level_base = 0;
+        uint32_t count = 1, level_base = 0, wide_levels = 0;
         while (count) {
             k_wide_expand<<<divup(count, 128), 128>>>(list_a, count, b->nodes, b->aabbs, flag, mode, kids, ninner);
             cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, ninner, off, (int)count);    // count <= n: tmp is large enough
@@ -273,9 +273,17 @@ int finalize_layout(uavmvs_bvh * b)
             UAV_CUDA(cudaGetLastError());
             level_base = next_base; count = last[0] + last[1];
             uint32_t * t = list_a; list_a = list_b; list_b = t;
+            ++wide_levels;
         }
         b->num_wide = level_base;
         cudaFree(list_a); cudaFree(list_b); cudaFree(ninner); cudaFree(off); cudaFree(kids);
+        // Every traversal keeps a fixed local stack (the reference too: 8 + 64 slots, unchecked, libs/cacc/tracing.h:28-33).
+        // A wide level spans at most two binary levels, so the binary depth is <= 2 wide_levels: the binary walks push one
+        // entry per level (UAV_STACK), the 4-wide walk of K1 up to three per wide level (K1_STACK).  Deeper trees are
+        // refused here instead of overflowing there.
+        b->depth = 2 * wide_levels;
+        UAV_REQUIRE(2 * wide_levels <= (uint32_t)UAV_STACK && 3 * wide_levels + 4 <= (uint32_t)K1_STACK,
+            "BVH deeper than the traversal stacks (96 binary levels): rebuild it with uavmvs_bvh_build_sah / _ploc");
     }
     {
         const uint32_t ni = b->num_wide ? b->num_wide : 1;
@@ -558,19 +566,51 @@ int uavmvs_set_device(int device) { UAV_CUDA(cudaSetDevice(device)); return 0; }
 int uavmvs_device_count(int * count) { UAV_CUDA(cudaGetDeviceCount(count)); return 0; }
 int uavmvs_synchronize(void * stream) { UAV_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); return 0; }
 
+// User-supplied topology (the reference's converter trusts acc, libs/cacc/bvh_tree.cu:17-48): every index in range, every
+// node reachable at most once from the root (no cycles, no shared subtrees), triangle ranges inside the array.  Depth is
+// checked by finalize_layout for every tree, GPU-built ones included.
+static int validate_tree_arrays(const uint32_t * nd, uint32_t n, uint32_t t)
+{
+    std::vector<uint32_t> order; order.reserve(n);
+    std::vector<char> seen(n, 0);
+    order.push_back(0); seen[0] = 1;
+    for (size_t h = 0; h < order.size(); ++h) {
+        const uint32_t * q = nd + 4 * (size_t)order[h];
+        const bool inner = q[2] != UAV_NAI && q[3] != UAV_NAI;
+        if (!inner) {
+            UAV_REQUIRE(q[0] < q[1] && q[1] <= t, "leaf triangle range outside the triangle array");
+            continue;
+        }
+        for (int c = 2; c < 4; ++c) {
+            UAV_REQUIRE(q[c] < n, "child index outside the node array");
+            UAV_REQUIRE(!seen[q[c]], "nodes do not form a tree (a node is reachable twice)");
+            seen[q[c]] = 1; order.push_back(q[c]);
+        }
+    }
+    return 0;
+}
+
+static int destroy_on_error(uavmvs_bvh * b, int rc) { if (rc) uavmvs_bvh_destroy(b); return rc; }
+
+static int upload_tree_arrays(uavmvs_bvh * b, const uint32_t * nodes, const float * aabbs, const float * tris, const uint32_t * indices)
+{
+    if (alloc_reference_arrays(b)) return 1;
+    UAV_CUDA(cudaMemcpy(b->nodes, nodes, sizeof(uint4) * (size_t)b->num_nodes, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->aabbs, aabbs, sizeof(float) * 6 * (size_t)b->num_nodes, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->tris, tris, sizeof(float) * 9 * (size_t)b->num_tris, cudaMemcpyHostToDevice));
+    UAV_CUDA(cudaMemcpy(b->indices, indices, sizeof(uint32_t) * (size_t)b->num_tris, cudaMemcpyHostToDevice));
+    return finalize_layout(b);
+}
+
 int uavmvs_bvh_create_from_arrays(const uint32_t * nodes, const float * aabbs, const float * tris,
     const uint32_t * indices, uint32_t num_nodes, uint32_t num_tris, uavmvs_bvh ** out)
 {
     UAV_REQUIRE(nodes && aabbs && tris && indices && out, "null argument");
     UAV_REQUIRE(num_nodes >= 1 && num_tris >= 1, "empty tree");
+    if (int rc = validate_tree_arrays(nodes, num_nodes, num_tris)) return rc;
     uavmvs_bvh * b = new uavmvs_bvh();
     b->num_nodes = num_nodes; b->num_tris = num_tris;
-    if (alloc_reference_arrays(b)) return 1;
-    UAV_CUDA(cudaMemcpy(b->nodes, nodes, sizeof(uint4) * (size_t)num_nodes, cudaMemcpyHostToDevice));
-    UAV_CUDA(cudaMemcpy(b->aabbs, aabbs, sizeof(float) * 6 * (size_t)num_nodes, cudaMemcpyHostToDevice));
-    UAV_CUDA(cudaMemcpy(b->tris, tris, sizeof(float) * 9 * (size_t)num_tris, cudaMemcpyHostToDevice));
-    UAV_CUDA(cudaMemcpy(b->indices, indices, sizeof(uint32_t) * (size_t)num_tris, cudaMemcpyHostToDevice));
-    if (finalize_layout(b)) return 1;
+    if (int rc = destroy_on_error(b, upload_tree_arrays(b, nodes, aabbs, tris, indices))) return rc;
     *out = b;
     return 0;
 }

@@ -2,6 +2,7 @@
 // image, KD-tree.  They mirror the memory layouts of the reference's cacc containers
 // (libs/cacc/point_cloud.h:26-32, vector_array.h:23-50, array.h, image.h, kd_tree.h).
 #include "common.cuh"
+#include "kd.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -169,7 +170,9 @@ int kd_fast_ensure(uavmvs_kdtree * kd)
     if (getenv("UAVMVS_NO_KD_FAST")) return 0;
     const uint32_t n = kd->num_nodes;
     const std::vector<uint32_t> & nd = kd->h_nodes; const std::vector<float> & vt = kd->h_verts;
-    if (n < 2 || n > 60000 || nd.size() != 4 * (size_t)n) return 0;
+    // the neighbour lists below are all-pairs on one host thread: direction sets only (the icosphere has 1272 vertices);
+    // larger trees keep the plain search
+    if (n < 2 || n > 8192 || nd.size() != 4 * (size_t)n) return 0;
     // topology: every node reachable once from the root, vertex ids a permutation
     std::vector<uint32_t> parent(n, UAV_NAI), depth(n, 0), node_of(n, UAV_NAI), order; order.reserve(n);
     std::vector<char> seen(n, 0);
@@ -286,10 +289,32 @@ using namespace uav;
 
 extern "C" {
 
-int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n, uavmvs_kdtree ** out)
+// The device search keeps one stack slot per level with two children (kd.cuh: stack[KD_STACK]; the reference has 6 + 64,
+// libs/cacc/nnsearch.h:28-33, unchecked).  User-supplied topology is validated here instead of overflowing there:
+// indices in range, every node reached at most once from the root, depth within the stack.
+static int kd_validate(const uint32_t * nd, uint32_t n)
 {
-    UAV_REQUIRE(nodes && verts && out && n >= 1, "bad argument");
-    uavmvs_kdtree * k = new uavmvs_kdtree();
+    std::vector<uint32_t> depth(n, 0), order; order.reserve(n);
+    std::vector<char> seen(n, 0);
+    order.push_back(0); seen[0] = 1;
+    for (size_t h = 0; h < order.size(); ++h) {
+        const uint32_t i = order[h];
+        UAV_REQUIRE(nd[4 * (size_t)i] < n, "KD node refers to a vertex outside the array");
+        UAV_REQUIRE(nd[4 * (size_t)i + 1] < 3, "KD node split dimension outside 0..2");
+        for (int c = 2; c < 4; ++c) {
+            const uint32_t ch = nd[4 * (size_t)i + c];
+            if (ch == UAV_NAI) continue;
+            UAV_REQUIRE(ch < n, "KD child index outside the array");
+            UAV_REQUIRE(!seen[ch], "KD nodes do not form a tree (a node is reachable twice)");
+            seen[ch] = 1; depth[ch] = depth[i] + 1; order.push_back(ch);
+            UAV_REQUIRE(depth[ch] < (uint32_t)KD_STACK, "KD-tree deeper than the search stack (40 levels)");
+        }
+    }
+    return 0;
+}
+
+static int kdtree_fill(uavmvs_kdtree * k, const uint32_t * nodes, const float * verts, uint32_t n)
+{
     k->num_nodes = n;
     UAV_CUDA(cudaMalloc(&k->nodes, sizeof(uint4) * (size_t)n));
     UAV_CUDA(cudaMalloc(&k->verts, sizeof(float4) * (size_t)n));
@@ -297,7 +322,15 @@ int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n
     if (upload3(verts, n, k->verts)) return 1;
     k->h_nodes.assign(nodes, nodes + 4 * (size_t)n);
     k->h_verts.assign(verts, verts + 3 * (size_t)n);
-    if (kd_fast_ensure(k)) return 1;          // built here, read-only afterwards: host threads share the handle
+    return kd_fast_ensure(k);                 // built here, read-only afterwards: host threads share the handle
+}
+
+int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n, uavmvs_kdtree ** out)
+{
+    UAV_REQUIRE(nodes && verts && out && n >= 1, "bad argument");
+    if (int rc = kd_validate(nodes, n)) return rc;
+    uavmvs_kdtree * k = new uavmvs_kdtree();
+    if (int rc = kdtree_fill(k, nodes, verts, n)) { uavmvs_kdtree_destroy(k); return rc; }
     *out = k;
     return 0;
 }

@@ -200,7 +200,8 @@ struct Scratch {   // per-process scratch on the device (views, reduction accumu
     ReduceAcc * acc = nullptr;
     unsigned long long * stats = nullptr;
     ReduceAcc * h_acc = nullptr; unsigned long long * h_stats = nullptr;   // pinned
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};     // K1 | K2 | K3+K8 | K9 boundaries
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};     // K1 | K2 | K3+K8 | K9 | score collective boundaries
+    double * score_dev = nullptr, * h_score = nullptr;                     // fold result + one record (single GPU); pinned copy
     bool ev_valid = false;
     cudaStream_t copy_stream = nullptr;                                    // result copies of evaluate_trajectory_to_host
     cudaEvent_t ev_copy[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -215,7 +216,9 @@ static int ensure_scratch(size_t view_floats)
         UAV_CUDA(cudaMalloc(&s.stats, 4 * sizeof(unsigned long long)));
         UAV_CUDA(cudaMallocHost(&s.h_acc, sizeof(ReduceAcc)));
         UAV_CUDA(cudaMallocHost(&s.h_stats, 4 * sizeof(unsigned long long)));
-        for (int i = 0; i < 5; ++i) UAV_CUDA(cudaEventCreate(&s.ev[i]));
+        for (int i = 0; i < 6; ++i) UAV_CUDA(cudaEventCreate(&s.ev[i]));
+        UAV_CUDA(cudaMalloc(&s.score_dev, 16 * sizeof(double)));
+        UAV_CUDA(cudaMallocHost(&s.h_score, 8 * sizeof(double)));
     }
     if (view_floats > s.views_cap) {
         if (s.views) cudaFree(s.views);
@@ -347,40 +350,144 @@ int uavmvs_reduce(void * stream, const uavmvs_array * a, float out3[3])
     return 0;
 }
 
+// ---- the whole evaluation (apps/evaluate_trajectory/evaluate_trajectory.cu:125-202) ------------------------
+// One body for every entry point: clear counters, K1 over all views, K2 + K3 + K8 (optionally in four block ranges whose
+// results are copied to the host while the next range is computed), K9, and -- for the sharded form -- the score record
+// of this shard packed on the device, all-gathered over the ranks and folded in rank order, still on the same stream.
+struct EvalCall {
+    cudaStream_t s; const float * d_views; uint32_t num_views; float max_distance, target_recon; int width, height;
+    const uavmvs_bvh * bvh; const uavmvs_cloud * cloud; uavmvs_obs * obs; uavmvs_array * recons, * wrecons;
+    float * h_recons = nullptr; uint32_t * h_num_rows = nullptr;
+    bool want_stats = false;
+    bool sharded = false; uavmvs_comm * comm = nullptr;
+};
+
+// record = {sum wrecon, points, rays, observations, pairs after the block cull, min, max, pairs}
+__global__ void k_pack_score(const ReduceAcc * acc, const unsigned long long * stats, double points, double pairs, double * rec)
+{
+    rec[0] = acc->sum; rec[1] = points; rec[2] = (double)stats[0]; rec[3] = (double)stats[1]; rec[4] = (double)stats[3];
+    rec[5] = (double)ord2f(acc->mn); rec[6] = (double)ord2f(acc->mx); rec[7] = pairs;
+}
+
+// Fold in rank order (the same additions on every rank: bit-identical results everywhere).
+// out = {sum, points, min, max, rays, observations, pairs after the block cull, pairs}
+__global__ void k_fold_score(const double * recs, int world, double * out)
+{
+    double sum = 0.0, pts = 0.0, rays = 0.0, obs = 0.0, cull = 0.0, pairs = 0.0, mn = INFINITY, mx = -INFINITY;
+    for (int r = 0; r < world; ++r) {
+        const double * q = recs + 8 * r;
+        sum += q[0]; pts += q[1]; rays += q[2]; obs += q[3]; cull += q[4]; pairs += q[7];
+        mn = fmin(mn, q[5]); mx = fmax(mx, q[6]);
+    }
+    out[0] = sum; out[1] = pts; out[2] = mn; out[3] = mx; out[4] = rays; out[5] = obs; out[6] = cull; out[7] = pairs;
+}
+
+static int run_evaluation(const EvalCall & c, float out3[3], uint64_t stats[4], double score[UAVMVS_SCORE_DOUBLES])
+{
+    UAV_REQUIRE(c.bvh && c.cloud && c.obs && c.recons && c.wrecons, "null handle");
+    cudaStream_t s = c.s;
+    Scratch & g = g_scratch;
+    const bool need_stats = c.want_stats || c.sharded;
+    const bool to_host = c.h_recons || c.h_num_rows;
+    if (to_host && !g.copy_stream) {
+        UAV_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+        for (auto & e : g.ev_copy) UAV_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    UAV_CUDA(cudaMemsetAsync(c.obs->num_rows, 0, 4 * (size_t)c.obs->num_cols, s));
+    if (need_stats) UAV_CUDA(cudaMemsetAsync(g.stats, 0, 4 * sizeof(unsigned long long), s));
+    g.ev_valid = false;
+    UAV_CUDA(cudaEventRecord(g.ev[0], s));
+    int rc = launch_k1(s, 1, c.d_views, c.num_views, c.max_distance, c.width, c.height, c.bvh, c.cloud, c.obs,
+        need_stats ? g.stats : nullptr);
+    if (rc) return rc;
+    UAV_CUDA(cudaEventRecord(g.ev[1], s));
+    UAV_CUDA(cudaEventRecord(g.ev[2], s));      // K2 is fused into the next launch
+    // counters are final after K1 here (nothing was invalidated, so K2 rewrites none: kernels.cu:251-254): their copy
+    // runs beside K2 + K3; recon goes out in four chunks, each copied while the next is computed
+    if (c.h_num_rows) {
+        UAV_CUDA(cudaEventRecord(g.ev_copy[0], s));
+        UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[0], 0));
+        UAV_CUDA(cudaMemcpyAsync(c.h_num_rows, c.obs->num_rows, 4 * (size_t)c.obs->num_cols, cudaMemcpyDeviceToHost, g.copy_stream));
+    }
+    const uint32_t nblocks = divup(c.obs->num_cols, 32), chunks = c.h_recons && nblocks >= 64 ? 4 : 1;
+    for (uint32_t k = 0; k < chunks; ++k) {
+        const uint32_t b0 = (uint32_t)((uint64_t)nblocks * k / chunks), b1 = (uint32_t)((uint64_t)nblocks * (k + 1) / chunks);
+        rc = launch_sort_eval(s, true, true, c.obs, c.recons, c.target_recon, c.wrecons, false, b0, b1 - b0);
+        if (rc) return rc;
+        if (c.h_recons) {
+            const size_t p0 = (size_t)b0 * 32, p1 = min((size_t)b1 * 32, (size_t)c.obs->num_cols);
+            UAV_CUDA(cudaEventRecord(g.ev_copy[1 + k], s));
+            UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[1 + k], 0));
+            UAV_CUDA(cudaMemcpyAsync(c.h_recons + p0, c.recons->data + p0, 4 * (p1 - p0), cudaMemcpyDeviceToHost, g.copy_stream));
+        }
+    }
+    UAV_CUDA(cudaEventRecord(g.ev[3], s));
+    if (launch_reduce(s, c.wrecons)) return 1;
+    UAV_CUDA(cudaEventRecord(g.ev[4], s));
+    if (c.sharded) {
+        // the collective follows K9 on the stream: no host synchronisation in between
+        const int world = c.comm ? c.comm->world : 1, rank = c.comm ? c.comm->rank : 0;
+        double * recs = g.score_dev;                        // [8] fold result, then [8 * world] records
+        if (c.comm) {
+            if (!c.comm->gather) UAV_CUDA(cudaMalloc(&c.comm->gather, sizeof(double) * 8 * (size_t)(world + 1)));
+            recs = c.comm->gather;
+        }
+        k_pack_score<<<1, 1, 0, uav::counted(s)>>>(g.acc, g.stats, (double)c.cloud->n, (double)c.cloud->n * (double)c.num_views,
+            recs + 8 + 8 * (size_t)rank);
+        UAV_CUDA(cudaGetLastError());
+        if (c.comm && comm_allgather(s, c.comm, recs + 8 + 8 * (size_t)rank, recs + 8, 8, 1)) return 3;
+        k_fold_score<<<1, 1, 0, uav::counted(s)>>>(recs + 8, world, recs);
+        UAV_CUDA(cudaGetLastError());
+        UAV_CUDA(cudaMemcpyAsync(g.h_score, recs, 8 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    UAV_CUDA(cudaEventRecord(g.ev[5], s));
+    g.ev_valid = true;
+    if (need_stats) UAV_CUDA(cudaMemcpyAsync(g.h_stats, g.stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    if (to_host) {                                           // the caller's stream owns the host buffers when this returns
+        UAV_CUDA(cudaEventRecord(g.ev_copy[5], g.copy_stream));
+        UAV_CUDA(cudaStreamWaitEvent(s, g.ev_copy[5], 0));
+    }
+    if (out3 || stats || score || to_host) {
+        UAV_CUDA(cudaStreamSynchronize(s));
+        if (out3) { out3[0] = (float)g.h_acc->sum; out3[1] = ord2f(g.h_acc->mn); out3[2] = ord2f(g.h_acc->mx); }
+        if (stats) {
+            for (int i = 0; i < 4; ++i) stats[i] = g.h_stats[i];
+            stats[2] = (uint64_t)c.cloud->n * c.num_views;
+        }
+        if (score) for (int i = 0; i < UAVMVS_SCORE_DOUBLES; ++i) score[i] = g.h_score[i];
+    }
+    return 0;
+}
+
+static EvalCall make_call(void * stream, const float * d_views, uint32_t num_views, float max_distance, float target_recon,
+    int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs, uavmvs_array * recons,
+    uavmvs_array * wrecons)
+{
+    EvalCall c; c.s = (cudaStream_t)stream; c.d_views = d_views; c.num_views = num_views; c.max_distance = max_distance;
+    c.target_recon = target_recon; c.width = width; c.height = height; c.bvh = bvh; c.cloud = cloud; c.obs = obs;
+    c.recons = recons; c.wrecons = wrecons;
+    return c;
+}
+
+static int stage_views(cudaStream_t s, const float * views, uint32_t num_views)
+{
+    UAV_REQUIRE(views || num_views == 0, "null views");
+    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
+    if (num_views)
+        UAV_CUDA(cudaMemcpyAsync(g_scratch.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views,
+            cudaMemcpyHostToDevice, s));
+    return 0;
+}
+
 int uavmvs_evaluate_trajectory_device(void * stream, const float * d_views, uint32_t num_views,
     float max_distance, float target_recon, int width, int height,
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
     uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4])
 {
-    UAV_REQUIRE(bvh && cloud && obs && recons && wrecons, "null handle");
-    cudaStream_t s = (cudaStream_t)stream;
     if (ensure_scratch(0)) return 1;
-    UAV_CUDA(cudaMemsetAsync(obs->num_rows, 0, 4 * (size_t)obs->num_cols, s));
-    if (stats) UAV_CUDA(cudaMemsetAsync(g_scratch.stats, 0, 4 * sizeof(unsigned long long), s));
-    g_scratch.ev_valid = false;
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[0], s));
-    int rc = launch_k1(s, 1, d_views, num_views, max_distance, width, height, bvh, cloud, obs,
-        stats ? g_scratch.stats : nullptr);
-    if (rc) return rc;
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[1], s));
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[2], s));      // K2 is fused into the next launch
-    rc = launch_sort_eval(s, true, true, obs, recons, target_recon, wrecons);
-    if (rc) return rc;
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[3], s));
-    if (launch_reduce(s, wrecons)) return 1;
-    UAV_CUDA(cudaEventRecord(g_scratch.ev[4], s));
-    g_scratch.ev_valid = true;
-    if (stats) UAV_CUDA(cudaMemcpyAsync(g_scratch.h_stats, g_scratch.stats, 4 * sizeof(unsigned long long),
-        cudaMemcpyDeviceToHost, s));
-    if (out3 || stats) {
-        UAV_CUDA(cudaStreamSynchronize(s));
-        if (out3) { out3[0] = (float)g_scratch.h_acc->sum; out3[1] = ord2f(g_scratch.h_acc->mn); out3[2] = ord2f(g_scratch.h_acc->mx); }
-        if (stats) {
-            for (int i = 0; i < 4; ++i) stats[i] = g_scratch.h_stats[i];
-            stats[2] = (uint64_t)cloud->n * num_views;
-        }
-    }
-    return 0;
+    EvalCall c = make_call(stream, d_views, num_views, max_distance, target_recon, width, height, bvh, cloud, obs, recons, wrecons);
+    c.want_stats = stats != nullptr;
+    return run_evaluation(c, out3, stats, nullptr);
 }
 
 int uavmvs_evaluate_trajectory_to_host(void * stream, const float * views, uint32_t num_views,
@@ -389,59 +496,46 @@ int uavmvs_evaluate_trajectory_to_host(void * stream, const float * views, uint3
     uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
     float out3[3], uint64_t stats[4])
 {
-    UAV_REQUIRE(views || num_views == 0, "null views");
-    UAV_REQUIRE(bvh && cloud && obs && recons && wrecons, "null handle");
-    cudaStream_t s = (cudaStream_t)stream;
-    Scratch & g = g_scratch;
-    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
-    if (!g.copy_stream) {
-        UAV_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
-        for (auto & e : g.ev_copy) UAV_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    }
-    if (num_views)
-        UAV_CUDA(cudaMemcpyAsync(g.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views, cudaMemcpyHostToDevice, s));
-    UAV_CUDA(cudaMemsetAsync(obs->num_rows, 0, 4 * (size_t)obs->num_cols, s));
-    if (stats) UAV_CUDA(cudaMemsetAsync(g.stats, 0, 4 * sizeof(unsigned long long), s));
-    g.ev_valid = false;
-    UAV_CUDA(cudaEventRecord(g.ev[0], s));
-    int rc = launch_k1(s, 1, g.views, num_views, max_distance, width, height, bvh, cloud, obs, stats ? g.stats : nullptr);
-    if (rc) return rc;
-    UAV_CUDA(cudaEventRecord(g.ev[1], s));
-    UAV_CUDA(cudaEventRecord(g.ev[2], s));
-    // counters are final after K1 here (nothing was invalidated, so K2 rewrites none: kernels.cu:251-254): their copy
-    // runs beside K2 + K3; recon goes out in four chunks, each copied while the next is computed
-    if (h_num_rows) {
-        UAV_CUDA(cudaEventRecord(g.ev_copy[0], s));
-        UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[0], 0));
-        UAV_CUDA(cudaMemcpyAsync(h_num_rows, obs->num_rows, 4 * (size_t)obs->num_cols, cudaMemcpyDeviceToHost, g.copy_stream));
-    }
-    const uint32_t nblocks = divup(obs->num_cols, 32), chunks = h_recons && nblocks >= 64 ? 4 : 1;
-    for (uint32_t c = 0; c < chunks; ++c) {
-        const uint32_t b0 = (uint32_t)((uint64_t)nblocks * c / chunks), b1 = (uint32_t)((uint64_t)nblocks * (c + 1) / chunks);
-        rc = launch_sort_eval(s, true, true, obs, recons, target_recon, wrecons, false, b0, b1 - b0);
-        if (rc) return rc;
-        if (h_recons) {
-            const size_t p0 = (size_t)b0 * 32, p1 = min((size_t)b1 * 32, (size_t)obs->num_cols);
-            UAV_CUDA(cudaEventRecord(g.ev_copy[1 + c], s));
-            UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[1 + c], 0));
-            UAV_CUDA(cudaMemcpyAsync(h_recons + p0, recons->data + p0, 4 * (p1 - p0), cudaMemcpyDeviceToHost, g.copy_stream));
-        }
-    }
-    UAV_CUDA(cudaEventRecord(g.ev[3], s));
-    if (launch_reduce(s, wrecons)) return 1;
-    UAV_CUDA(cudaEventRecord(g.ev[4], s));
-    g.ev_valid = true;
-    if (stats) UAV_CUDA(cudaMemcpyAsync(g.h_stats, g.stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-    if (h_recons || h_num_rows) {                            // the caller's stream owns the host buffers when this returns
-        UAV_CUDA(cudaEventRecord(g.ev_copy[5], g.copy_stream));
-        UAV_CUDA(cudaStreamWaitEvent(s, g.ev_copy[5], 0));
-    }
-    UAV_CUDA(cudaStreamSynchronize(s));
-    if (out3) { out3[0] = (float)g.h_acc->sum; out3[1] = ord2f(g.h_acc->mn); out3[2] = ord2f(g.h_acc->mx); }
-    if (stats) {
-        for (int i = 0; i < 4; ++i) stats[i] = g.h_stats[i];
-        stats[2] = (uint64_t)cloud->n * num_views;
-    }
+    if (int rc = stage_views((cudaStream_t)stream, views, num_views)) return rc;
+    EvalCall c = make_call(stream, g_scratch.views, num_views, max_distance, target_recon, width, height, bvh, cloud, obs, recons, wrecons);
+    c.want_stats = stats != nullptr; c.h_recons = h_recons; c.h_num_rows = h_num_rows;
+    float dummy[3];
+    return run_evaluation(c, out3 ? out3 : dummy, stats, nullptr);      // always synchronises: the host buffers are the result
+}
+
+int uavmvs_evaluate_trajectory_sharded(void * stream, uavmvs_comm * comm, const float * views, int views_on_device,
+    uint32_t num_views, float max_distance, float target_recon, int width, int height,
+    const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
+    uavmvs_array * recons, uavmvs_array * wrecons, float * h_recons, uint32_t * h_num_rows,
+    double score[UAVMVS_SCORE_DOUBLES], float local_out3[3])
+{
+    UAV_REQUIRE(score, "null score");
+    const float * d_views = views;
+    if (!views_on_device) {
+        if (int rc = stage_views((cudaStream_t)stream, views, num_views)) return rc;
+        d_views = g_scratch.views;
+    } else if (ensure_scratch(0)) return 1;
+    EvalCall c = make_call(stream, d_views, num_views, max_distance, target_recon, width, height, bvh, cloud, obs, recons, wrecons);
+    c.sharded = true; c.comm = comm; c.h_recons = h_recons; c.h_num_rows = h_num_rows;
+    return run_evaluation(c, local_out3, nullptr, score);
+}
+
+int uavmvs_views_upload(void * stream, const float * views, uint32_t num_views, float ** d_views)
+{
+    UAV_REQUIRE(views && d_views && num_views > 0, "null argument");
+    float * d = nullptr;
+    const size_t bytes = sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views;
+    UAV_CUDA(cudaMalloc(&d, bytes));
+    cudaError_t e = cudaMemcpyAsync(d, views, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);      // `views` may be pageable / reused
+    if (e != cudaSuccess) { cudaFree(d); UAV_CUDA(e); }
+    *d_views = d;
+    return 0;
+}
+
+int uavmvs_views_free(float * d_views)
+{
+    if (d_views) UAV_CUDA(cudaFree(d_views));
     return 0;
 }
 
@@ -463,17 +557,29 @@ int uavmvs_profile_last(float ms[4])
     return 0;
 }
 
+int uavmvs_profile_k1_enable(int on) { return uav::k1_profile_enable(on); }
+
+int uavmvs_profile_k1(float ms[5])
+{
+    UAV_REQUIRE(ms, "null argument");
+    return uav::k1_profile(ms);
+}
+
+int uavmvs_profile_last_collective(float * ms)
+{
+    UAV_REQUIRE(ms, "null argument");
+    UAV_REQUIRE(g_scratch.ev_valid, "no evaluate_trajectory call recorded on this thread");
+    UAV_CUDA(cudaEventSynchronize(g_scratch.ev[5]));
+    UAV_CUDA(cudaEventElapsedTime(ms, g_scratch.ev[4], g_scratch.ev[5]));
+    return 0;
+}
+
 int uavmvs_evaluate_trajectory(void * stream, const float * views, uint32_t num_views,
     float max_distance, float target_recon, int width, int height,
     const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, uavmvs_obs * obs,
     uavmvs_array * recons, uavmvs_array * wrecons, float out3[3], uint64_t stats[4])
 {
-    UAV_REQUIRE(views || num_views == 0, "null views");
-    cudaStream_t s = (cudaStream_t)stream;
-    if (ensure_scratch((size_t)num_views * UAVMVS_VIEW_FLOATS)) return 1;
-    if (num_views)
-        UAV_CUDA(cudaMemcpyAsync(g_scratch.views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views,
-            cudaMemcpyHostToDevice, s));
+    if (int rc = stage_views((cudaStream_t)stream, views, num_views)) return rc;
     return uavmvs_evaluate_trajectory_device(stream, g_scratch.views, num_views, max_distance, target_recon,
         width, height, bvh, cloud, obs, recons, wrecons, out3, stats);
 }

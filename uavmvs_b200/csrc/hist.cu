@@ -307,6 +307,36 @@ __global__ void k_fill_positions(const float * __restrict__ pos, uint32_t n, flo
     for (int k = 0; k < UAVMVS_VIEW_FLOATS; ++k) v[k] = k < 3 ? pos[3 * (size_t)i + k] : 0.0f;
 }
 
+// ---- fixed-point scale of the batched K4 / K5 (k1.cu:k_retire_hist) -------------------------------------------
+// fx[1] = bound of |contribution|, fx[0] = scale = 2^(36 - e) with bound <= 2^e.  K4: bound = the largest quality of the
+// cloud (score = max(quality, 0) cos(..) scale with both other factors in [0, 1], kernels.cu:318-333); K5: given.
+__global__ void k_fx_init(float * fx, float bound) { fx[0] = 1.0f; fx[1] = bound; }
+__global__ void k_fx_max_quality(const float * __restrict__ q, uint32_t n, float * fx)
+{
+    float m = 0.0f;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float v = q[i];
+        if (v > m && v < UAV_INF) m = v;                  // NaN / inf qualities take the float path of k_retire_hist
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(reinterpret_cast<int *>(fx + 1), __float_as_int(m));   // non-negative floats order like ints
+}
+__global__ void k_fx_scale(float * fx)
+{
+    const float bound = fx[1];
+    int e = 0;
+    if (bound > 0.0f && bound < UAV_INF) { frexpf(bound, &e); }          // bound = m 2^e, m in [0.5, 1)
+    e = max(-60, min(e, 90));
+    fx[0] = ldexpf(1.0f, 36 - e);
+}
+__global__ void k_hist_finish(const unsigned long long * __restrict__ acc, float * __restrict__ hist, size_t n, const float * __restrict__ fx)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long a = (long long)acc[i];
+    if (a != 0) hist[i] += (float)((double)a / (double)fx[0]);
+}
+
 static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos[3], float max_distance,
     float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd,
     const uavmvs_obs * obs, const uavmvs_array * recons, uavmvs_array * hist)
@@ -458,6 +488,23 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
         hj.stride = (uint32_t)(obs->pitch / sizeof(float4)); hj.recons = recons->data;
     }
     hj.hist = sphere_hists->data; hj.heur = current_heur();
+    const size_t cells = (size_t)num_positions * kd->num_nodes;
+    UAV_REQUIRE(cells < 0xffffff00ull, "positions x bins does not fit the 32-bit accumulator key");
+    UAV_REQUIRE(cloud->n < (1u << 26), "more than 2^26 points per call (fixed-point head room)");
+    unsigned long long * d_acc = nullptr; float * d_fx = nullptr;
+    UAV_CUDA(cudaMallocAsync(&d_acc, sizeof(unsigned long long) * cells, s));
+    UAV_CUDA(cudaMallocAsync(&d_fx, 2 * sizeof(float), s));
+    UAV_CUDA(cudaMemsetAsync(d_acc, 0, sizeof(unsigned long long) * cells, s));
+    if (obs) {
+        const float t1 = fabsf(target_recon) + 1.0f;
+        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 4.0f * t1 * t1);
+    } else {
+        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 0.0f);
+        k_fx_max_quality<<<min(divup(cloud->n, 256 * 8), 1024u), 256, 0, uav::counted(s)>>>(cloud->qualities, cloud->n, d_fx);
+    }
+    k_fx_scale<<<1, 1, 0, uav::counted(s)>>>(d_fx);
+    UAV_CUDA(cudaGetLastError());
+    hj.acc = d_acc; hj.fx = d_fx;
     float * d_pos = nullptr, * d_views = nullptr;
     UAV_CUDA(cudaMallocAsync(&d_pos, sizeof(float) * 3 * (size_t)num_positions, s));
     UAV_CUDA(cudaMallocAsync(&d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_positions, s));
@@ -465,7 +512,11 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     k_fill_positions<<<divup(num_positions, 256), 256, 0, uav::counted(s)>>>(d_pos, num_positions, d_views);
     UAV_CUDA(cudaGetLastError());
     int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
-    cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s);
+    if (!rc) {
+        k_hist_finish<<<divup(cells, 256), 256, 0, uav::counted(s)>>>(d_acc, sphere_hists->data, cells, d_fx);
+        if (cudaGetLastError() != cudaSuccess) rc = 1;
+    }
+    cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s); cudaFreeAsync(d_acc, s); cudaFreeAsync(d_fx, s);
     return rc;
 }
 

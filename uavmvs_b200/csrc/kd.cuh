@@ -5,6 +5,8 @@
 
 namespace uav {
 
+constexpr int KD_STACK = 40;     // checked against the tree's depth at upload (containers.cu: kd_validate)
+
 struct KdView { const uint4 * __restrict__ nodes; const float4 * __restrict__ verts; uint32_t n; };
 
 // libs/cacc/nnsearch.h:67-155: depth-first nearest neighbour, strict '<' (first found wins)
@@ -12,7 +14,7 @@ __device__ __forceinline__ uint32_t kd_find_nn(const KdView & kd, V3 q)
 {
     uint32_t idx = UAV_NAI; float max_dist = UAV_INF;
     uint32_t node_idx = 0; bool down = true;
-    uint32_t stack[40]; int sp = 0;
+    uint32_t stack[KD_STACK]; int sp = 0;
     while (true) {
         uint4 node = __ldg(kd.nodes + node_idx);          // vid, dim, left, right
         float4 v4 = __ldg(kd.verts + node.x);
