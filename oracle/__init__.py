@@ -70,6 +70,8 @@ def lib():
     build()
     L = C.CDLL(os.path.join(_HERE, "liboracle.so"))
     u32, u64, i32, f32 = C.c_uint32, C.c_uint64, C.c_int, C.c_float
+    L.orc_set_threads.restype = i32
+    L.orc_set_threads.argtypes = [i32]
     L.orc_bvh_build.restype = _vp
     L.orc_bvh_build.argtypes = [_f32p, u32, _u32p, u32, i32]
     L.orc_bvh_from_arrays.restype = _vp
@@ -111,6 +113,11 @@ def lib():
     L.orc_sample_proxy_cloud.argtypes = [_f32p, _u32p, u32, f32, _opt(_f32p), _opt(_f32p), u32]
     _LIB = L
     return L
+
+
+def set_threads(n=0):
+    """Sets the OpenMP team size of the oracle's loops (0: keep) and returns the team size a parallel region gets."""
+    return int(lib().orc_set_threads(int(n)))
 
 
 def ref():

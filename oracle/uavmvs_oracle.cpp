@@ -23,6 +23,7 @@
  * Every function cites the reference file:line (relative to /root/reference)
  * it restates.
  */
+#include <omp.h>
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
@@ -664,6 +665,20 @@ inline V3 ld3(float const * p, std::size_t i) { return V3{p[3 * i], p[3 * i + 1]
 }  // namespace
 
 extern "C" {
+
+/* OpenMP team size of every parallel loop below.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers, which
+ * would silently turn the CPU baseline into a single-thread run: bench.py sets the team explicitly and reports what it got. */
+int orc_set_threads(int n)
+{
+    if (n > 0) omp_set_num_threads(n);
+    int got = 1;
+    #pragma omp parallel
+    {
+        #pragma omp single
+        got = omp_get_num_threads();
+    }
+    return got;
+}
 
 /* ---- trees ---- */
 void * orc_bvh_build(float const * verts, u32 num_verts, u32 const * faces, u32 num_faces, int threads)

@@ -193,6 +193,16 @@ class KDTree(_Handle):
         return obj
 
 
+    @classmethod
+    def build(cls, verts):
+        """Median-split build on the host (acc::KDTree<3>'s rule) + upload, for callers without libs/acc."""
+        verts = _f(verts, (-1, 3))
+        h = _vp()
+        _check(_lib.uavmvs_kdtree_build(_p(verts), _u32(verts.shape[0]), C.byref(h)))
+        obj = cls(h)
+        obj.num_verts = verts.shape[0]
+        return obj
+
     def find_nn(self, queries, certified_lookup=False, stream=None):
         """cacc::nnsearch::find_nn<3> for a batch of queries [n,3] -> vertex indices."""
         q = _f(queries).reshape(-1, 3)
@@ -357,16 +367,125 @@ def reduce(array, stream=None):
 
 
 class DeviceViews:
-    """A trajectory resident on the device ([V,28] floats) for repeated evaluation."""
+    """A trajectory resident on the device ([V,28] floats) for repeated evaluation (uavmvs_views_upload)."""
 
-    def __init__(self, views):
-        import torch  # device memory plumbing only
-        self.num_views = int(np.asarray(views).reshape(-1, VIEW_FLOATS).shape[0])
-        self.tensor = torch.from_numpy(_f(views, (-1, VIEW_FLOATS)).copy()).cuda()
+    def __init__(self, views, stream=None):
+        v = _f(views, (-1, VIEW_FLOATS))
+        self.num_views = int(v.shape[0])
+        d = C.POINTER(C.c_float)()
+        _check(_lib.uavmvs_views_upload(_stream_ptr(stream), _p(v), _u32(self.num_views), C.byref(d)))
+        self._d = d
 
     @property
     def ptr(self):
-        return _vp(self.tensor.data_ptr())
+        return C.cast(self._d, _vp)
+
+    def free(self):
+        if getattr(self, "_d", None):
+            _lib.uavmvs_views_free(self._d)
+            self._d = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Comm(_Handle):
+    """One rank of the point-sharded evaluation: an ncclComm_t behind the C ABI (include/uavmvs_b200.h)."""
+    _destroy = "uavmvs_comm_destroy"
+    ID_BYTES = 128
+
+    @staticmethod
+    def unique_id():
+        """ncclGetUniqueId: call on one rank, ship the 128 bytes to the others."""
+        buf = (C.c_uint8 * Comm.ID_BYTES)()
+        _check(_lib.uavmvs_comm_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def create(cls, unique_id, world, rank):
+        """ncclCommInitRank on the current device (collective)."""
+        buf = (C.c_uint8 * cls.ID_BYTES).from_buffer_copy(unique_id)
+        h = _vp()
+        _check(_lib.uavmvs_comm_create(buf, _i32(world), _i32(rank), C.byref(h)))
+        obj = cls(h)
+        obj.world, obj.rank = world, rank
+        return obj
+
+    @classmethod
+    def from_torch_distributed(cls, group=None):
+        """Bootstrap over an initialised torch.distributed group (plumbing only: rank 0's id is broadcast)."""
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=group)
+        return cls.create(box[0], world, rank)
+
+
+SCORE_KEYS = ("sum", "points", "min", "max", "rays", "observations", "pairs_after_block_cull", "pairs")
+
+
+def evaluate_trajectory_sharded(comm, views, max_distance, target_recon, width, height, bvh_tree, cloud, obs_rays,
+                                recons, wrecons, h_recons=None, h_num_rows=None, stream=None):
+    """uavmvs_evaluate_trajectory_sharded: this rank's shard + ONE collective for the trajectory score.
+    `comm` may be None (single GPU).  Returns (score dict over all shards, (local sum, min, max))."""
+    score, loc = (C.c_double * 8)(), (C.c_float * 3)()
+    on_dev = isinstance(views, DeviceViews)
+    if on_dev:
+        vptr, nv = views.ptr, views.num_views
+    else:
+        views = _f(views, (-1, VIEW_FLOATS))
+        vptr, nv = _p(views), views.shape[0]
+    for a, dt in ((h_recons, np.float32), (h_num_rows, np.uint32)):
+        assert a is None or (a.dtype == dt and a.flags.c_contiguous)
+    _check(_lib.uavmvs_evaluate_trajectory_sharded(
+        _stream_ptr(stream), None if comm is None else comm.ptr, vptr, _i32(1 if on_dev else 0), _u32(nv),
+        _f32(max_distance), _f32(target_recon), _i32(width), _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr,
+        recons.ptr, wrecons.ptr, _p(h_recons), _p(h_num_rows), score, loc))
+    out = dict(zip(SCORE_KEYS, (float(x) for x in score)))
+    for k in ("points", "rays", "observations", "pairs_after_block_cull", "pairs"):
+        out[k] = int(round(out[k]))
+    out["score"] = out["sum"] / max(out["points"], 1)       # avg_wrecon, optimize_trajectory.cu:529
+    return out, (float(loc[0]), float(loc[1]), float(loc[2]))
+
+
+def allreduce_array(comm, array, count=None, stream=None):
+    """SUM all-reduce of the first `count` floats of a device Array (partial sphere histograms of a sharded cloud)."""
+    _check(_lib.uavmvs_allreduce_array(_stream_ptr(stream), None if comm is None else comm.ptr, array.ptr,
+                                       _u64(array.n if count is None else count)))
+
+
+def allgather_array(comm, local, count, out, stream=None):
+    """All-gather `count` floats per rank (shard order) into the device Array `out`."""
+    _check(_lib.uavmvs_allgather_array(_stream_ptr(stream), None if comm is None else comm.ptr, local.ptr,
+                                       _u64(count), out.ptr))
+
+
+def launch_count(reset=True):
+    """Kernel launches issued by the evaluation path in this process since the last reset."""
+    n = _u64(0)
+    _check(_lib.uavmvs_launch_count(C.byref(n), _i32(1 if reset else 0)))
+    return n.value
+
+
+def profile_k1_enable(on=True):
+    _check(_lib.uavmvs_profile_k1_enable(_i32(1 if on else 0)))
+
+
+def profile_k1():
+    """Device ms of k_view_masks, caps + scan, k_cull_emit, k_trace, k_retire of this thread's last K1 launch."""
+    ms = (C.c_float * 5)()
+    _check(_lib.uavmvs_profile_k1(ms))
+    return [float(x) for x in ms]
+
+
+def profile_last_collective():
+    """Device ms of the score collective (pack, all-gather, fold) of this thread's last sharded evaluation."""
+    ms = _f32(0)
+    _check(_lib.uavmvs_profile_last_collective(C.byref(ms)))
+    return ms.value
 
 
 def evaluate_trajectory(views, max_distance, target_recon, width, height, bvh_tree, cloud, obs_rays,
@@ -475,6 +594,15 @@ def estimate_capture_difficulty(max_distance, bvh_tree, mesh_size, kd_tree, clou
     """libs/eval/kernels.h:81-84"""
     _check(_lib.uavmvs_estimate_capture_difficulty(_stream_ptr(stream), _f32(max_distance), bvh_tree.ptr,
                                                    _u32(mesh_size), kd_tree.ptr, cloud.ptr))
+
+
+def sphere_vertices(radius=1.0, subdivisions=3):
+    """generate_sphere_mesh(radius, subdivisions)'s vertex list (libs/geom/sphere.h:17-115): [1272, 3] at 3 subdivisions."""
+    n = _u32(0)
+    _check(_lib.uavmvs_sphere_vertices(_f32(radius), _u32(subdivisions), None, _u32(0), C.byref(n)))
+    out = np.empty((n.value, 3), np.float32)
+    _check(_lib.uavmvs_sphere_vertices(_f32(radius), _u32(subdivisions), _p(out), _u32(n.value), C.byref(n)))
+    return out
 
 
 def sample_proxy_cloud(verts, faces, samples_per_unit_area):

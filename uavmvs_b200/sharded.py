@@ -5,9 +5,10 @@ replicated read-only data (BVH, KD-tree, trajectory), so the proxy cloud is cut 
 contiguous Z-order ranges, one per rank, and there is no collective on the data path
 (SURVEY.md 8e).  The only exchanges are
 
-  * the trajectory score: one all-reduce of {sum wrecon, #points, rays, observations,
-    pairs} (SUM) and one each of min / max -- what cacc::reduction::sum/min/max
-    (libs/cacc/reduction.h:132-162) produce on one GPU in the reference;
+  * the trajectory score: ONE all-gather of an 8-double record per rank {sum wrecon, #points, rays,
+    observations, pairs, min, max}, folded in rank order -- what cacc::reduction::sum/min/max
+    (libs/cacc/reduction.h:132-162) produce on one GPU in the reference.  In the product this is
+    uavmvs_evaluate_trajectory_sharded (C ABI, ncclAllGather on the evaluation's stream);
   * on request the full per-point vector (recon, counts): an all-gather of the shards;
   * for the histogram kernels one SUM all-reduce of the [B, S] partial histograms.
 
@@ -36,28 +37,39 @@ def _device_for(group=None):
     return torch.device("cpu")
 
 
+def fold_records(recs):
+    """Fold of the per-rank score records {sum, points, rays, observations, pairs after the block cull, min, max,
+    pairs} in rank order -- the host mirror of k_fold_score (csrc/eval.cu)."""
+    tot = pts = rays = obs = cull = pairs = 0.0
+    mn, mx = float("inf"), float("-inf")
+    for q in recs:
+        tot += q[0]; pts += q[1]; rays += q[2]; obs += q[3]; cull += q[4]; pairs += q[7]
+        mn, mx = min(mn, q[5]), max(mx, q[6])
+    pts = int(round(pts))
+    return {"sum": tot, "min": mn, "max": mx, "points": pts, "score": tot / max(pts, 1),
+            "stats": [int(round(rays)), int(round(obs)), int(round(pairs)), int(round(cull))]}
+
+
 def combine_scores(local_sum, local_min, local_max, local_points, stats=None, group=None):
-    """All-reduce the per-shard reduction of wrecon into the trajectory-level result.
+    """Per-shard reduction of wrecon -> trajectory-level result with ONE collective: an all-gather of the 8-double
+    record of every rank, folded in rank order (what uavmvs_evaluate_trajectory_sharded does on the device with
+    ncclAllGather; this torch.distributed form serves host-side callers and the gloo tests).
 
     Returns dict(sum, min, max, points, score, stats) with score = sum / points
     (apps/optimize_trajectory/optimize_trajectory.cu:529).  Without an initialised
     process group this is the single-GPU identity."""
     import torch
     stats = list(stats) if stats is not None else [0, 0, 0, 0]
+    rec = [float(local_sum), float(local_points), float(stats[0]), float(stats[1]), float(stats[3]),
+           float(local_min), float(local_max), float(stats[2])]
     dist = _dist()
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
-        tot, mn, mx, st, pts = float(local_sum), float(local_min), float(local_max), stats, int(local_points)
-    else:
-        dev = _device_for(group)
-        s = torch.tensor([float(local_sum), float(local_points)] + [float(x) for x in stats],
-                         dtype=torch.float64, device=dev)
-        m = torch.tensor([float(local_min), -float(local_max)], dtype=torch.float64, device=dev)
-        dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(m, op=dist.ReduceOp.MIN, group=group)
-        s, m = s.cpu().tolist(), m.cpu().tolist()
-        tot, pts, st = s[0], int(round(s[1])), [int(round(x)) for x in s[2:]]
-        mn, mx = m[0], -m[1]
-    return {"sum": tot, "min": mn, "max": mx, "points": pts, "score": tot / max(pts, 1), "stats": st}
+        return fold_records([rec])
+    dev = _device_for(group)
+    mine = torch.tensor(rec, dtype=torch.float64, device=dev)
+    every = torch.empty(dist.get_world_size(group) * 8, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(every, mine, group=group)
+    return fold_records(every.cpu().reshape(-1, 8).tolist())
 
 
 def gather_point_vector(local, n_total, group=None):
@@ -112,7 +124,16 @@ class ShardedEvaluator:
         return self.api.evaluate_trajectory(views, max_distance, target_recon, width, height, self.bvh, self.cloud,
                                             self.obs, self.recons, self.wrecons, stream=stream)
 
-    def evaluate(self, views, max_distance, target_recon, width, height, stream=None, group=None):
+    def evaluate(self, views, max_distance, target_recon, width, height, stream=None, comm=None, group=None):
+        """Shard evaluation + the score collective.  With `comm` (api.Comm, or None on one GPU) the whole thing is
+        one C-ABI call (uavmvs_evaluate_trajectory_sharded, ncclAllGather on the stream); with a torch.distributed
+        `group` and no comm the collective goes through torch.distributed instead."""
+        if group is None:
+            res, _ = self.api.evaluate_trajectory_sharded(comm, views, max_distance, target_recon, width, height,
+                                                          self.bvh, self.cloud, self.obs, self.recons, self.wrecons,
+                                                          stream=stream)
+            res["stats"] = [res["rays"], res["observations"], res["pairs"], res["pairs_after_block_cull"]]
+            return res
         s, mn, mx, st = self.evaluate_local(views, max_distance, target_recon, width, height, stream)
         return combine_scores(s, mn, mx, self.n_local, st, group)
 
