@@ -42,6 +42,15 @@ def _hist_close(h_gpu, h_ref, bins, contrib, S):
     return np.all(np.abs(h_gpu.astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12)
 
 
+def _k5_close(h_gpu, h_ref, bins, deltas, S):
+    """K5's delta = func(new) - func(old) can cancel, so every contribution is gated at
+    |a - b| <= 1e-5 max(|a|, |b|) + 1e-6; a bin is the sum of its contributions, hence of their gates."""
+    tol = np.zeros(S, np.float64)
+    ok = bins != 0xFFFFFFFF
+    np.add.at(tol, bins[ok], 1e-5 * np.abs(deltas[ok].astype(np.float64)) + 1e-6)
+    return np.all(np.abs(h_gpu.astype(np.float64) - h_ref) <= tol + 1e-12)
+
+
 POSITIONS = [(32.0, 32.0, 45.0), (10.0, 50.0, 30.0), (60.0, 5.0, 70.0), (32.0, 32.0, 400.0)]
 
 
@@ -88,11 +97,8 @@ def test_populate_spherical_histogram_k5_and_image_k6(api, oracle, setup):
         api.populate_spherical_histogram(pos, sc.max_distance, s["gbvh"], s["cloud"], s["gkd"], hist,
                                          target_recon=sc.target_recon, obs_rays=obs, recons=recons)
         h_gpu = hist.download()
-        # deltas are differences of squares: 1e-5 of their operands' magnitude (func(new), func(old) <= 16)
-        mag = np.zeros(S, np.float64)
         ok = bins != 0xFFFFFFFF
-        np.add.at(mag, bins[ok], 16.0)
-        assert np.all(np.abs(h_gpu.astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12)
+        assert _k5_close(h_gpu, h_ref, bins, deltas, S)
         assert ok.sum() > 100 and (h_ref < 0).any()
         # K6 on the GPU histogram vs the oracle on the same histogram
         img = api.Image.create(128, 45)
@@ -193,10 +199,7 @@ def test_batched_k5_optimizer_inner_loop(api, oracle, setup):
     for b in range(B):
         h_ref, bins, deltas = oracle.populate_spherical_histogram_recon(
             s["obvh"], s["okd"], cand[b], sc.max_distance, sc.target_recon, sc.points, sc.normals, obs_o, r_g, S)
-        mag = np.zeros(S, np.float64)
-        ok = bins != 0xFFFFFFFF
-        np.add.at(mag, bins[ok], 16.0)
-        assert np.all(np.abs(h_b[b].astype(np.float64) - h_ref) <= 1e-5 * mag + 1e-12), b
+        assert _k5_close(h_b[b], h_ref, bins, deltas, S), b
     vmin, imin, vmax, imax = api.evaluate_spherical_histogram_batch(sc.calib[0], sc.width, sc.height, s["gkd"], hists, B)
     for b in (0, 9, B - 1):
         i_ref = oracle.evaluate_spherical_histogram(sc.calib[0], sc.width, sc.height, s["sv"], h_b[b])
