@@ -130,3 +130,45 @@ def test_point_sharding_world2_gloo(tmp_path, oracle, tiny_scene, tiny_tree):
     assert abs(float(r["score"]) - float(w.astype(np.float64).mean())) < 1e-9
     assert float(r["mn"]) == float(w.min()) and float(r["mx"]) == float(w.max())
     assert np.all(r["h"] == 3.0)
+
+
+def test_user_trees_are_validated_before_upload():
+    """uavmvs_bvh_create_from_arrays / uavmvs_kdtree_create check user topology on the host (indices in range, a tree)
+    and fail with a status code and a message -- before touching the device, so this runs without a GPU."""
+    from uavmvs_b200 import api
+    NAI = 0xFFFFFFFF
+    aabbs = np.zeros((3, 6), np.float32)
+    tris = np.zeros((2, 9), np.float32)
+    idx = np.arange(2, dtype=np.uint32)
+    good = np.array([[0, 2, 1, 2], [0, 1, NAI, NAI], [1, 2, NAI, NAI]], np.uint32)
+    for bad, what in ((np.array([[0, 2, 1, 7], [0, 1, NAI, NAI], [1, 2, NAI, NAI]], np.uint32), "child index"),
+                      (np.array([[0, 2, 1, 1], [0, 1, NAI, NAI], [1, 2, NAI, NAI]], np.uint32), "reachable twice"),
+                      (np.array([[0, 2, 1, 0], [0, 1, NAI, NAI], [1, 2, NAI, NAI]], np.uint32), "reachable twice"),
+                      (np.array([[0, 2, 1, 2], [0, 5, NAI, NAI], [1, 2, NAI, NAI]], np.uint32), "triangle range")):
+        with pytest.raises(api.UavmvsError, match=what):
+            api.BVHTree.create(bad, aabbs, tris, idx)
+    verts = np.zeros((3, 3), np.float32)
+    for bad, what in ((np.array([[0, 0, 1, 2], [1, 1, NAI, NAI], [9, 2, NAI, NAI]], np.uint32), "vertex outside"),
+                      (np.array([[0, 3, 1, 2], [1, 1, NAI, NAI], [2, 2, NAI, NAI]], np.uint32), "dimension"),
+                      (np.array([[0, 0, 1, 5], [1, 1, NAI, NAI], [2, 2, NAI, NAI]], np.uint32), "child index"),
+                      (np.array([[0, 0, 1, 1], [1, 1, NAI, NAI], [2, 2, NAI, NAI]], np.uint32), "reachable twice")):
+        with pytest.raises(api.UavmvsError, match=what):
+            api.KDTree.create(bad, verts)
+    # a chain deeper than the device search stack
+    n = 64
+    chain = np.array([[i, i % 3, i + 1 if i + 1 < n else NAI, NAI] for i in range(n)], np.uint32)
+    with pytest.raises(api.UavmvsError, match="deeper than the search stack"):
+        api.KDTree.create(chain, np.zeros((n, 3), np.float32))
+    assert good.shape == (3, 4)
+
+
+def test_sphere_vertices_equal_the_oracle(oracle):
+    """uavmvs_sphere_vertices (host code of the product) against the oracle's restatement of libs/geom/sphere.h."""
+    from uavmvs_b200 import api
+    for sub, count in ((0, 12), (1, 72), (2, 312), (3, 1272)):
+        v = api.sphere_vertices(1.0, sub)
+        assert v.shape == (count, 3)
+        assert np.array_equal(v.view(np.uint32), oracle.sphere_vertices(1.0, sub).view(np.uint32))
+    v = api.sphere_vertices(1.0, 3)
+    assert np.unique(v, axis=0).shape[0] == 642                     # SURVEY.md appendix quirk 5: 630 coincident twins
+    assert np.array_equal(api.sphere_vertices(2.5, 2).view(np.uint32), oracle.sphere_vertices(2.5, 2).view(np.uint32))

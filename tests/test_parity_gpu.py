@@ -531,3 +531,74 @@ def test_config1_bundled_mesh_full_evaluation(api, oracle, tmp_path):
     assert strict.mean() > 0.9995
     w_o = oracle.calculate_func_recons(r_o, sc.target_recon).astype(np.float64)
     assert abs(s_sum / len(pts) - w_o.mean()) <= 1e-5 * w_o.mean() + 1e-9
+
+
+def test_concurrent_populate_on_one_observation_array(api, oracle):
+    """The reference's optimiser calls update_observation_rays(true, ...) for different views from several host threads /
+    streams on the SAME obs_rays (optimize_trajectory.cu:470-495); rows are taken with atomicAdd there.  Two host threads,
+    two streams, the two halves of a dense trajectory (views that share points and 32-point blocks): counters equal the
+    serial result, and so does the multiset of rows of every column that never overflowed."""
+    import threading
+    import torch
+    from uavmvs_b200 import scenes
+    sc = scenes.dense()
+    bvh = api.BVHTree.build_sah(sc.verts, sc.faces)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    views = sc.views28()
+    serial = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, views, sc.max_distance, sc.width, sc.height, bvh, cloud, serial)
+    d_s, r_s = serial.download()
+    for attempt in range(4):
+        obs = api.VectorArray.create(sc.num_points, 32)
+        obs.null()
+        api.synchronize()
+        errors = []
+
+        def work(part):
+            try:
+                api.set_device(0)
+                st = torch.cuda.Stream()
+                for k in range(0, part.shape[0], 8):         # several launches per thread: more interleavings
+                    api.update_observation_rays_batch(True, part[k:k + 8], sc.max_distance, sc.width, sc.height, bvh, cloud,
+                                                      obs, stream=st)
+                api.synchronize(st)
+            except Exception as e:                           # noqa: BLE001
+                errors.append(e)
+        th = [threading.Thread(target=work, args=(views[0::2],)), threading.Thread(target=work, args=(views[1::2],))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        assert not errors, errors
+        d_c, r_c = obs.download()
+        assert np.array_equal(r_c, r_s)                      # no lost increment, no row handed out twice
+        ok = r_s <= 32
+        m = (np.arange(32)[:, None] < np.minimum(r_s, 32)[None, :]) & ok[None, :]
+
+        def keys(d):
+            a = np.where(m[:, :, None], d, 0).view(np.uint32).astype(np.uint64)
+            return np.sort(a[:, :, 0] * 7 + a[:, :, 1] * 13 + a[:, :, 2] * 31 + a[:, :, 3], axis=0)
+        assert np.array_equal(keys(d_c), keys(d_s))
+
+
+def test_tree_deeper_than_the_stacks_is_refused(api):
+    """A chain-shaped tree of 240 levels (valid indices, nested boxes) must come back as an error from the upload, not
+    overflow the traversal stacks (the reference has the same unchecked stacks, libs/cacc/tracing.h:28-33)."""
+    NAI = 0xFFFFFFFF
+    depth = 240
+    tris = np.zeros((depth + 1, 9), np.float32)
+    for t in range(depth + 1):
+        tris[t] = [t, 0, 0, t + 0.5, 0, 0, t, 0.5, 0]
+    nodes, aabbs = [], []
+    # node 2k: inner {leaf 2k+1, inner 2k+2}; the last inner node holds two leaves
+    for k in range(depth):
+        last = k == depth - 1
+        nodes.append([k, depth + 1, 2 * k + 1, 2 * k + 2])
+        aabbs.append([k, 0, 0, depth + 0.5, 0.5, 0])
+        nodes.append([k, k + 1, NAI, NAI])
+        aabbs.append([k, 0, 0, k + 0.5, 0.5, 0])
+        if last:
+            nodes.append([k + 1, k + 2, NAI, NAI])
+            aabbs.append([k + 1, 0, 0, k + 1.5, 0.5, 0])
+    with pytest.raises(api.UavmvsError, match="deeper than the traversal stacks"):
+        api.BVHTree.create(np.array(nodes, np.uint32), np.array(aabbs, np.float32), tris, np.arange(depth + 1, dtype=np.uint32))
