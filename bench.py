@@ -386,12 +386,19 @@ def parity_check(orc, api, sc, bvh, cloud, pts, nrm, nviews=24):
     counts_equal = bool(np.array_equal(rows, o.num_rows))
     rows_equal = counts_equal and bool(np.array_equal(o.data.view(np.uint32)[mask], data.view(np.uint32)[mask]))
     r_o = probe["recons"]
-    rel = np.abs(r_g.astype(np.float64) - r_o) / np.maximum(np.maximum(np.abs(r_g), np.abs(r_o)), 1e-30)
+    diff = np.abs(r_g.astype(np.float64) - r_o)
+    mag = np.maximum(np.abs(r_g), np.abs(r_o)).astype(np.float64)
+    big = mag > 1e-3                                      # recon of a well-conditioned point (see the gate below)
+    gate = 1e-5 * mag + 1e-6                              # SURVEY.md 7E, per element
     res = {"views": int(len(vidx)), "points": int(n), "rays_gpu": int(stats[0]), "rays_oracle": int(probe["rays"]),
            "rays_equal": int(stats[0]) == int(probe["rays"]), "counts_equal": counts_equal, "rows_equal": rows_equal,
-           "recon_max_rel": float(rel.max()), "tolerance": 1e-5,
+           "recon_gate": "|a - b| <= 1e-5 max(|a|, |b|) + 1e-6 per point (SURVEY.md 7E: 1 - logistic cancels for the wide-parallax "
+                         "pairs of a point seen by two or three views, so recon ~ 1e-6 carries an absolute error)",
+           "recon_gate_violations": int((diff > gate).sum()),
+           "recon_max_rel_above_1e-3": float((diff[big] / mag[big]).max()) if big.any() else 0.0,
+           "recon_max_abs": float(diff.max()),
            "tree": "the timed run's own tree, exported through uavmvs_bvh_export"}
-    res["ok"] = bool(res["rays_equal"] and counts_equal and rows_equal and res["recon_max_rel"] <= 1e-5)
+    res["ok"] = bool(res["rays_equal"] and counts_equal and rows_equal and res["recon_gate_violations"] == 0)
     probe.pop("obs"); probe.pop("recons")
     return res, probe, (nodes.nbytes + aabbs.nbytes + tris.nbytes)
 

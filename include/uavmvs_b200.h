@@ -163,7 +163,9 @@ int uavmvs_evaluate_observation_rays(void * stream, const uavmvs_obs * obs, uavm
  * evaluate_observation_rays and calculate_func_recons over ALL points every iteration).  Every observation array keeps
  * one flag per 32 columns, set by update_observation_rays (either direction) when a column of the block received or
  * lost a row, and by clear / upload / mark_dirty for all blocks; this call runs the three kernels on the flagged blocks
- * only and clears the flags.  Result identical to the three full launches PROVIDED `recons` (and `wrecons`, may be NULL)
+ * only and clears the flags.  Result identical to the three full launches -- except that rows holding EQUAL sort keys may
+ * come out in another order within their column: the reference's network is not idempotent on ties (kernels.cu:241), and
+ * the full launches re-sort unchanged columns too -- PROVIDED `recons` (and `wrecons`, may be NULL)
  * are the arrays, and target_recon the value, of the previous call for this observation array (the first call after
  * create / clear / upload evaluates everything). */
 int uavmvs_reevaluate_observation_rays(void * stream, uavmvs_obs * obs, uavmvs_array * recons, float target_recon,

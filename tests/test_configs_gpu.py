@@ -112,7 +112,18 @@ def test_config3_optimizer_candidates_at_config_size(c2, oracle):
     d_g, rows_g = loop.obs.download()
     assert np.array_equal(rows_g, obs_o.num_rows)                                        # counts after the removal: exact
     m = np.arange(32)[:, None] < np.minimum(rows_g, 32)[None, :]
-    assert np.array_equal(d_g.view(np.uint32)[m], obs_o.data.view(np.uint32)[m])         # rows after K2: exact
+    # rows after K2: the sorted keys are exact; the rows themselves are exact except among EQUAL keys -- the reference's
+    # network is not idempotent on ties (kernels.cu:241 never exchanges equal keys, so a second K2 over an unchanged
+    # column may permute its tied rows) and the oracle, like the reference app, re-sorts every column while the
+    # incremental re-evaluation only visits the 32-point blocks K1 touched
+    assert np.array_equal(d_g[:, :, 2].view(np.uint32)[m], obs_o.data[:, :, 2].view(np.uint32)[m])
+    differ = (d_g.view(np.uint32) != obs_o.data.view(np.uint32)).any(axis=2) & m
+    assert differ.mean() < 1e-4
+
+    def colkeys(d):
+        a = np.where(m[:, :, None], d, 0).view(np.uint32).astype(np.uint64)
+        return np.sort(a[:, :, 0] * 7 + a[:, :, 1] * 13 + a[:, :, 2] * 31 + a[:, :, 3], axis=0)
+    assert np.array_equal(colkeys(d_g), colkeys(obs_o.data))                            # same multiset of rows per column
     r_g = loop.recons.download()
     r_o = oracle.evaluate_observation_rays(obs_o)
     assert np.all(np.abs(r_g.astype(np.float64) - r_o) <= 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o)) + 1e-6)
