@@ -145,12 +145,17 @@ __global__ void k_build_wide80(const Node128 * __restrict__ wide, uint32_t n, No
     __half h[24];
     for (int k = 0; k < 4; ++k)
         for (int a = 0; a < 3; ++a) {
+#if K1_PRMT
+            const int lo = 2 * (3 * k + a), hi = lo + 1;                          // word (min, max) per child and axis
+#else
+            const int lo = 6 * k + a, hi = 6 * k + 3 + a;
+#endif
             if (occ[k]) {
-                h[6 * k + a] = __float2half_rd(__fsub_rd(q[6 * k + a], c[a]));
-                h[6 * k + 3 + a] = __float2half_ru(__fsub_ru(q[6 * k + 3 + a], c[a]));
+                h[lo] = __float2half_rd(__fsub_rd(q[6 * k + a], c[a]));
+                h[hi] = __float2half_ru(__fsub_ru(q[6 * k + 3 + a], c[a]));
             } else {
-                h[6 * k + a] = __ushort_as_half((unsigned short)0x7c00);      // +inf: no segment reaches it
-                h[6 * k + 3 + a] = __ushort_as_half((unsigned short)0x7c00);
+                h[lo] = __ushort_as_half((unsigned short)0x7c00);      // +inf: no segment reaches it
+                h[hi] = __ushort_as_half((unsigned short)0x7c00);
             }
         }
     Node80 o;

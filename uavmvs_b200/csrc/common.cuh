@@ -70,7 +70,12 @@ struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
 // box is re-checked against its exact box once one of its triangles is accepted (see k_trace).
 //   c = {cx, cy, cz, unused};  h[0..2] = 24 halves: child k -> mn.x mn.y mn.z mx.x mx.y mx.z at 6k..6k+5
 //   cnt as in Node128;  empty slot: all offsets +inf
+//   K1_PRMT layout: the 24 halves are 12 words (min, max), word 3k + a = child k, axis a, so that one PRMT orders a
+//   word (near, far) for the ray's direction sign (k1.cu:k_trace)
 struct __align__(16) Node80 { float4 c; uint4 h[3]; uint4 cnt; };
+#ifndef K1_PRMT
+#define K1_PRMT 0
+#endif
 // Pre-reduced triangle, 64 B: a, ab, ac, unit normal (N/|N|), d00, d01, d11, denom.
 // All derived values are computed with the reference's operation order, so using them
 // gives bit-identical operands (libs/acc/primitives.h:214-248, :134-153).

@@ -535,6 +535,10 @@ struct RayList {
     uint8_t * vis;        // every ray: (point's index within its block) << 2 | status: 1 occluded, 2 visible
     float4 * tdir;        // rays that have to be traced (not certified by k_shaft): direction, w = l
     float4 * torg;        // ... origin (the point), w = bits of (ray index << 5 | point's index within its block)
+    float4 * trd;         // ... traversal constants set up by the cull kernel on full warps: fl(1 / dir), w = error band em
+                          //     (ray_fma_setup80), or w < 0: the ray takes the reference walk (axis-parallel direction,
+                          //     single-leaf tree).  NULL: k_trace sets them up itself (packet modes)
+    float bx, by, bz; uint32_t root_is_leaf;      // scene bounds of the error band, single-leaf tree flag
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
     uint32_t * tcnt;      // [num_blocks] rays of the slice that have to be traced
@@ -710,6 +714,16 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             __stcs(rl.dirl + idx, make_float4(v2cn.x, v2cn.y, v2cn.z, l));      // rl.tdir aliases rl.dirl (nothing certified)
             if (HIST) rl.rview[idx] = k;
             __stcs(rl.torg + idx, make_float4(v.x, v.y, v.z, __uint_as_float(idx << 5 | pt)));
+            if (rl.trd) {
+                // k_trace's per-ray set-up (three IEEE reciprocals, the error band), done here where every lane holds a ray
+                RayT rt; rt.ox = v.x; rt.oy = v.y; rt.oz = v.z; rt.tmax = l;
+                rt.rdx = 1.0f / v2cn.x; rt.rdy = 1.0f / v2cn.y; rt.rdz = 1.0f / v2cn.z;
+                ray_fma_setup80(rt, rl.bx, rl.by, rl.bz);
+                const float mn = fminf(fminf(fabsf(v2cn.x), fabsf(v2cn.y)), fabsf(v2cn.z));
+                const float mx = fmaxf(fmaxf(fabsf(v2cn.x), fabsf(v2cn.y)), fabsf(v2cn.z));
+                const bool fast = mn > 1e-4f && mx < 2.0f && !rl.root_is_leaf && rt.em >= 0.0f;   // below: em would be uselessly wide
+                __stcs(rl.trd + idx, make_float4(rt.rdx, rt.rdy, rt.rdz, fast ? rt.em : -1.0f));
+            }
         }
         count += __popc(m);
         __syncwarp();
@@ -769,6 +783,7 @@ struct TraceArgs {
     RayList rl;
     uint32_t num_blocks;
     uint32_t * work;              // next block slice to hand out
+    int refill, tri, steps;       // K1_REFILL / K1_TRI / K1_STEPS (env overrides for sweeps)
 };
 
 __device__ __forceinline__ void prefetch_l2(const void * p)
@@ -828,11 +843,14 @@ k_trace(TraceArgs a)
     RayT rt; rt.ox = rt.oy = rt.oz = rt.rdx = rt.rdy = rt.rdz = rt.tmin = rt.tmax = 0.0f;
     rt.nox = rt.noy = rt.noz = rt.em = 0.0f;
     V3 rd = mk(0.f, 0.f, 0.f);
+#if K1_PRMT
+    uint32_t selx = 0x3210u, sely = 0x3210u, selz = 0x3210u;     // PRMT selectors: (min, max) -> (near, far) per axis
+#endif
     uint32_t serviced_idle = 0;
 
     for (;;) {
         uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
-        if (idle != serviced_idle && __popc(idle) >= K1_REFILL) {
+        if (idle != serviced_idle && __popc(idle) >= a.refill) {
             // ---------------- refill idle lanes from the ray list ----------------
             const uint32_t need = __popc(idle), rank = __popc(idle & lt_mask);
             uint32_t given = 0; bool mine = false;
@@ -866,11 +884,25 @@ k_trace(TraceArgs a)
                 rd = ld3(d4);
                 rt.ox = o.x; rt.oy = o.y; rt.oz = o.z;
                 rt.tmin = d4.w * 0.001f; rt.tmax = d4.w;                 // kernels.cu:54-58
-                const float mn = fminf(fminf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
-                const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
-                if (mn > 1e-4f && mx < 2.0f && !a.bvh.root_is_leaf) {     // below: em would be uselessly wide
-                    rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
-                    ray_fma_setup80(rt, a.bvh.bx, a.bvh.by, a.bvh.bz);
+                bool fast;
+                if (a.rl.trd) {                                           // constants set up by k_cull_emit_q
+                    const float4 t4 = __ldcs(a.rl.trd + slot);
+                    rt.rdx = t4.x; rt.rdy = t4.y; rt.rdz = t4.z; rt.em = t4.w;
+                    rt.nox = -(rt.ox * rt.rdx); rt.noy = -(rt.oy * rt.rdy); rt.noz = -(rt.oz * rt.rdz);
+                    fast = t4.w >= 0.0f;
+                } else {
+                    const float mn = fminf(fminf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
+                    const float mx = fmaxf(fmaxf(fabsf(rd.x), fabsf(rd.y)), fabsf(rd.z));
+                    fast = mn > 1e-4f && mx < 2.0f && !a.bvh.root_is_leaf;     // below: em would be uselessly wide
+                    if (fast) {
+                        rt.rdx = 1.0f / rd.x; rt.rdy = 1.0f / rd.y; rt.rdz = 1.0f / rd.z;
+                        ray_fma_setup80(rt, a.bvh.bx, a.bvh.by, a.bvh.bz);
+                    }
+                }
+                if (fast) {
+#if K1_PRMT
+                    selx = rt.rdx < 0.0f ? 0x1032u : 0x3210u; sely = rt.rdy < 0.0f ? 0x1032u : 0x3210u; selz = rt.rdz < 0.0f ? 0x1032u : 0x3210u;
+#endif
                     has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
                     if (a.rl.tpk) {                                      // start from the packet's entry points
                         const uint32_t * rec = a.rl.fr + ((size_t)__ldg(a.rl.tpk + slot) << 4);
@@ -894,13 +926,34 @@ k_trace(TraceArgs a)
 
         // ---------------- K1_STEPS traversal steps (4-wide nodes) ----------------
         #pragma unroll 1
-        for (int step = 0; step < K1_STEPS; ++step) {
+        for (int step = 0; step < a.steps; ++step) {
             if (traversing && npend <= K1_PEND - 4) {
                 const Node80 * np = a.bvh.wide80 + cur;
                 const float4 c4 = __ldg(&np->c);
                 const uint4 ha = __ldg(&np->h[0]), hb = __ldg(&np->h[1]), hc = __ldg(&np->h[2]);
                 const uint4 cnt = __ldg(&np->cnt);
                 const float crx = __fmaf_rn(c4.x, rt.rdx, rt.nox), cry = __fmaf_rn(c4.y, rt.rdy, rt.noy), crz = __fmaf_rn(c4.z, rt.rdz, rt.noz);
+#if K1_PRMT
+                // Node80 holds one word (min, max) per child and axis; one PRMT per word orders it (near, far) for this ray's
+                // direction signs, so the near planes only feed the max chain and the far planes the min chain (no min/max
+                // pairs).  The error band is folded into the far side: far constants and the ray's tmax are raised by em,
+                // and "tmax~ + em < tmin~" (= g < -em) proves the rejection.
+                const float cfx = crx + rt.em, cfy = cry + rt.em, cfz = crz + rt.em, tmaxe = rt.tmax + rt.em;
+                #define UAV_SLAB(wx, wy, wz, hit) { \
+                    const uint32_t ux = __byte_perm((wx), 0u, selx), uy = __byte_perm((wy), 0u, sely), uz = __byte_perm((wz), 0u, selz); \
+                    const float2 fx = __half22float2(*reinterpret_cast<const __half2 *>(&ux)); \
+                    const float2 fy = __half22float2(*reinterpret_cast<const __half2 *>(&uy)); \
+                    const float2 fz = __half22float2(*reinterpret_cast<const __half2 *>(&uz)); \
+                    const float tn = fmaxf(fmaxf(__fmaf_rn(fx.x, rt.rdx, crx), __fmaf_rn(fy.x, rt.rdy, cry)), fmaxf(__fmaf_rn(fz.x, rt.rdz, crz), rt.tmin)); \
+                    const float tf = fminf(fminf(__fmaf_rn(fx.y, rt.rdx, cfx), __fmaf_rn(fy.y, rt.rdy, cfy)), fminf(__fmaf_rn(fz.y, rt.rdz, cfz), tmaxe)); \
+                    hit = !(tf < tn); }
+                bool h0, h1, h2, h3;
+                UAV_SLAB(ha.x, ha.y, ha.z, h0)
+                UAV_SLAB(ha.w, hb.x, hb.y, h1)
+                UAV_SLAB(hb.z, hb.w, hc.x, h2)
+                UAV_SLAB(hc.y, hc.z, hc.w, h3)
+                #undef UAV_SLAB
+#else
                 #define UAV_H2(w) __half22float2(*reinterpret_cast<const __half2 *>(&(w)))
                 const float2 p0 = UAV_H2(ha.x), p1 = UAV_H2(ha.y), p2 = UAV_H2(ha.z), p3 = UAV_H2(ha.w);
                 const float2 p4 = UAV_H2(hb.x), p5 = UAV_H2(hb.y), p6 = UAV_H2(hb.z), p7 = UAV_H2(hb.w);
@@ -914,6 +967,7 @@ k_trace(TraceArgs a)
                 // visit unless surely missed; leaf children are deferred (any-hit is order independent)
                 // with the "box not verified" flag when the filtered test cannot prove the hit
                 const bool h0 = !(g0 < -m0), h1 = !(g1 < -m1), h2 = !(g2 < -m2), h3 = !(g3 < -m3);
+#endif
                 const bool f0 = h0 && (int)cnt.x >= 0, f1 = h1 && (int)cnt.y >= 0, f2 = h2 && (int)cnt.z >= 0, f3 = h3 && (int)cnt.w >= 0;
                 const bool i0 = h0 && (int)cnt.x < 0, i1 = h1 && (int)cnt.y < 0, i2 = h2 && (int)cnt.z < 0, i3 = h3 && (int)cnt.w < 0;
                 const uint4 ref = make_uint4(cnt.x & 0x7fffffffu, cnt.y & 0x7fffffffu, cnt.z & 0x7fffffffu, cnt.w & 0x7fffffffu);
@@ -942,7 +996,7 @@ k_trace(TraceArgs a)
             if (pmask) {
                 const uint32_t tmask = __ballot_sync(0xffffffffu, traversing);
                 const uint32_t full = __ballot_sync(0xffffffffu, npend > K1_PEND - 4);
-                if (__popc(pmask) >= K1_TRI || full || !tmask) {
+                if (__popc(pmask) >= a.tri || full || !tmask) {
                     if (npend > 0) {
                         Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
                         for (uint32_t p = 0; p < npend && !hit; ++p) {
@@ -1211,7 +1265,7 @@ struct K1Scratch {
     uint32_t * masks = nullptr; size_t masks_cap = 0;
     uint32_t * caps = nullptr, * off = nullptr, * cnt = nullptr; size_t blocks_cap = 0;
     void * cub_tmp = nullptr; size_t cub_cap = 0;
-    float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr, * trd = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
     uint32_t * tcnt = nullptr;
     uint32_t * rview = nullptr; size_t rview_cap = 0;
     uint32_t * tpk = nullptr; size_t tpk_cap = 0;
@@ -1220,6 +1274,7 @@ struct K1Scratch {
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     int grid_trace = 0;
+    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS;
     cudaEvent_t ev_total = nullptr;
     // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -1301,6 +1356,10 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         int occ = occ_a < occ_b ? occ_a : occ_b;
         { const char * e = getenv("UAVMVS_TRACE_CTAS"); if (e && atoi(e) > 0 && atoi(e) < occ) occ = atoi(e); }   // dev: leave room for co-running kernels
         k.grid_trace = sms * (occ > 0 ? occ : 1);
+        // dev sweeps: thresholds of the traversal kernel's bookkeeping
+        if (const char * e = getenv("UAVMVS_K1_REFILL")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_refill = atoi(e);
+        if (const char * e = getenv("UAVMVS_K1_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_tri = atoi(e);
+        if (const char * e = getenv("UAVMVS_K1_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) k.tune_steps = atoi(e);
     }
     if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
     uint32_t * inside_masks = k.masks + (size_t)cloud->num_super * num_views;
@@ -1366,9 +1425,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         }
         if (total > 0) {
             if (total > k.rays_cap) {
-                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap;
+                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap, c4 = k.rays_cap;
                 if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.tdir, &c1, (size_t)total, s) || grow(&k.torg, &c3, (size_t)total, s)
-                    || grow(&k.vis, &c2, (size_t)total, s)) return 1;
+                    || grow(&k.vis, &c2, (size_t)total, s) || grow(&k.trd, &c4, (size_t)total, s)) return 1;
                 k.rays_cap = (size_t)total;
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, uav::counted(s, 2));   // cub: DeviceScanInitKernel + DeviceScanKernel
@@ -1398,6 +1457,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
             if (k1_mark(k, s, 2)) return 1;
             if (queued) rl.tdir = rl.dirl;            // one record per ray: every ray is traced, in list order
+            rl.trd = (queued && !getenv("UAVMVS_TRACE_SETUP")) ? k.trd : nullptr;
+            rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
             if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
             else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
@@ -1409,6 +1470,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             if (k1_mark(k, s, 3)) return 1;
             UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
+            ta.refill = k.tune_refill; ta.tri = k.tune_tri; ta.steps = k.tune_steps;
             unsigned grid = (unsigned)k.grid_trace;
             if (bvh->nested) k_trace<<<grid, K1_WARPS * 32, 0, uav::counted(s)>>>(ta);
             else k_trace_exact<<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ta, (uint32_t)total);
