@@ -170,4 +170,5 @@ def test_config5_city_tree_counts_and_rows_bit_exact(oracle):
     assert np.array_equal(data.view(np.uint32)[m], obs_o.data.view(np.uint32)[m])
     r_o = oracle.evaluate_observation_rays(obs_o)
     r_g = rc.download()
-    assert np.all(np.abs(r_g.astype(np.float64) - r_o) <= 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o)))
+    # 64 of 10 000 views: most points hold two or three observations, where 1 - logistic cancels (SURVEY.md 7E gate)
+    assert np.all(np.abs(r_g.astype(np.float64) - r_o) <= 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o)) + 1e-6)

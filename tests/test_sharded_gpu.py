@@ -47,7 +47,7 @@ def test_sharded_entry_world1_nccl(tiny_scene):
             assert score["observations"] == ref["stats"][1] and score["pairs"] == sc.num_points * sc.num_views
             assert score["pairs_after_block_cull"] == ref["stats"][3]
             assert np.float32(score["sum"]) == np.float32(ref["sum"]) and score["min"] == ref["min"] and score["max"] == ref["max"]
-            assert abs(score["sum"] - ref["wsum64"]) <= 1e-9 * abs(ref["wsum64"])      # the record carries K9's double sum
+            assert abs(score["sum"] - ref["wsum64"]) <= 1e-6 * abs(ref["wsum64"])      # K9: float partial sums, double across blocks
             assert loc[0] == ref["sum"]
             assert np.array_equal(h_rc.view(np.uint32), ref["recons"].view(np.uint32)) and np.array_equal(h_rows, ref["rows"])
     assert api.profile_last_collective() >= 0.0
@@ -127,5 +127,5 @@ def test_sharded_entry_world2_nccl(tmp_path, tiny_scene):
     got = dict(zip(api.SCORE_KEYS, r0["rec"]))
     assert int(got["points"]) == sc.num_points and int(got["rays"]) == want["stats"][0] and int(got["observations"]) == want["stats"][1]
     assert got["min"] == want["min"] and got["max"] == want["max"]
-    assert abs(got["sum"] - want["sum"]) <= 1e-9 * abs(want["sum"])
+    assert abs(got["sum"] - want["sum"]) <= 1e-6 * abs(want["sum"])
     assert np.array_equal(r0["full"].view(np.uint32), full.view(np.uint32))

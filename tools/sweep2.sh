@@ -28,7 +28,7 @@ run "default r16" $D UAVMVS_K1_REFILL=16
 run "default r12" $D UAVMVS_K1_REFILL=12
 run "default r8" $D UAVMVS_K1_REFILL=8
 run "default r4" $D UAVMVS_K1_REFILL=4
-run "trace-setup r20" $D UAVMVS_TRACE_SETUP=1
+run "cull-setup r20" $D UAVMVS_CULL_SETUP=1
 run "default r12 tri8" $D UAVMVS_K1_REFILL=12 UAVMVS_K1_TRI=8
 run "default r12 steps4" $D UAVMVS_K1_REFILL=12 UAVMVS_K1_STEPS=4
 run "default r12 steps8" $D UAVMVS_K1_REFILL=12 UAVMVS_K1_STEPS=8

@@ -197,6 +197,19 @@ __global__ void k_check_tree(const uint4 * __restrict__ nodes, const float * __r
     if (!ok) atomicAdd(out, 1u);
 }
 
+// Exact leaf boxes addressed by the leaf's first triangle (k_trace re-checks a deferred leaf against its own box once one
+// of its triangles is accepted; the pending entry only carries first / count).
+__global__ void k_leaf_boxes(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n, float4 * __restrict__ out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 nd = nodes[i];
+    if (nd.z != UAV_NAI && nd.w != UAV_NAI) return;
+    const float * p = aabbs + 6 * (size_t)i;
+    out[2 * (size_t)nd.x] = make_float4(p[0], p[1], p[2], p[3]);
+    out[2 * (size_t)nd.x + 1] = make_float4(p[4], p[5], 0.0f, 0.0f);
+}
+
 // Per-triangle constants with the reference's operation order (libs/acc/primitives.h:
 // 217-225 normal, :139-145 Gram terms).  Degenerate triangles (|N| < eps, rejected at
 // :222) get a zero normal, which the |cosine| < eps test rejects.
@@ -301,6 +314,11 @@ int finalize_layout(uavmvs_bvh * b)
             float m = fmaxf(fabsf(root[a]), fabsf(root[3 + a]));
             b->bound_abs[a] = (m == m && m < 1e30f) ? m : 1e30f;
         }
+    }
+    if (b->nested) {
+        UAV_CUDA(cudaMalloc(&b->leafbox, sizeof(float4) * 2 * (size_t)t));
+        UAV_CUDA(cudaMemset(b->leafbox, 0, sizeof(float4) * 2 * (size_t)t));
+        k_leaf_boxes<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, n, b->leafbox);
     }
     k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
     UAV_CUDA(cudaGetLastError());
@@ -745,7 +763,7 @@ int uavmvs_bvh_destroy(uavmvs_bvh * b)
 {
     if (!b) return 0;
     cudaFree(b->nodes); cudaFree(b->aabbs); cudaFree(b->tris); cudaFree(b->indices);
-    cudaFree(b->inner); cudaFree(b->wide); cudaFree(b->wide80); cudaFree(b->ptris);
+    cudaFree(b->inner); cudaFree(b->wide); cudaFree(b->wide80); cudaFree(b->ptris); cudaFree(b->leafbox);
     delete b;
     return 0;
 }

@@ -74,7 +74,7 @@ struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
 //   word (near, far) for the ray's direction sign (k1.cu:k_trace)
 struct __align__(16) Node80 { float4 c; uint4 h[3]; uint4 cnt; };
 #ifndef K1_PRMT
-#define K1_PRMT 0
+#define K1_PRMT 1       // measured on config 2 (profiles/r02_b_sweep.txt): k_trace 2.62 -> 2.54 ms at 7 CTAs per SM
 #endif
 // Pre-reduced triangle, 64 B: a, ab, ac, unit normal (N/|N|), d00, d01, d11, denom.
 // All derived values are computed with the reference's operation order, so using them
@@ -96,6 +96,8 @@ struct uavmvs_bvh {
     uav::Node80 * wide80;
     float bound_abs[3];   // max |coordinate| of the root box per axis (error band of the fp16 node test)
     uav::Tri64 * ptris;
+    float4 * leafbox;     // nested trees: the stored (exact) box of the leaf whose first triangle is t at [2t], [2t + 1]:
+                          // {min.xyz, max.x}, {max.y, max.z, 0, 0}; the re-check of k_trace's deferred leaves
     uint32_t root_is_leaf, root_first, root_count;
     uint32_t depth;     // upper bound of the binary depth (2 x levels of the wide collapse), checked against the stacks at upload
     uint32_t nested;    // child boxes inside parent boxes, leaf boxes tight, leaves <= 31 triangles (checked at upload)

@@ -539,6 +539,7 @@ struct RayList {
                           //     (ray_fma_setup80), or w < 0: the ray takes the reference walk (axis-parallel direction,
                           //     single-leaf tree).  NULL: k_trace sets them up itself (packet modes)
     float bx, by, bz; uint32_t root_is_leaf;      // scene bounds of the error band, single-leaf tree flag
+    uint32_t debug;       // UAVMVS_K1_DEBUG: k_cull_emit_q counts candidates / queued / rejected pairs into counters[4..7]
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
     uint32_t * tcnt;      // [num_blocks] rays of the slice that have to be traced
@@ -675,6 +676,8 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const float md2 = cull_distance * cull_distance * 1.00001f;
     const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
     uint32_t count = 0, qn = 0;
+    const bool dbg = counters && rl.debug;                // UAVMVS_K1_DEBUG: where the candidate pairs go
+    uint32_t n_cand = 0, n_queued = 0, n_rej_exact = 0, n_rej_image = 0;
 
     // exact cull + emit of the first min(qn, 32) queued pairs
     auto flush = [&]() {
@@ -694,6 +697,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             pass = lane < take && !(scale <= 0.0f) && !(ctheta < 0.087f);
         } else {
             pass = lane < take && !(ctheta < 0.087f) && !(l >= max_distance);
+            if (dbg && lane < take) { ++n_queued; if (!pass) ++n_rej_exact; }
             const bool need = pass && !((e >> 5) & 1u);               // block not surely inside this view's image
             if (__any_sync(0xffffffffu, need)) {
                 if (need) {
@@ -705,6 +709,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
                         vw[4 * i] = t.x; vw[4 * i + 1] = t.y; vw[4 * i + 2] = t.z; vw[4 * i + 3] = t.w;
                     }
                     pass = in_image(vw, v, width, height);
+                    if (dbg && !pass) ++n_rej_image;
                 }
             }
         }
@@ -762,6 +767,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             const float c = dn * rsqrtf(l2);
             const bool reject = (c < bf_lim) || (l2 > md2);
             const bool maybe = valid && !reject;
+            if (dbg && valid) ++n_cand;
             const uint32_t m = __ballot_sync(0xffffffffu, maybe);
             if (maybe) s_q[w][qn + __popc(m & lt_mask)] = (k << 6) | (((iword >> kb) & 1u) << 5) | lane;
             qn += __popc(m);
@@ -774,6 +780,16 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
         if (counters && count) atomicAdd(counters + 3, (unsigned long long)count);
+    }
+    if (dbg) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_cand += __shfl_xor_sync(0xffffffffu, n_cand, o); n_queued += __shfl_xor_sync(0xffffffffu, n_queued, o);
+            n_rej_exact += __shfl_xor_sync(0xffffffffu, n_rej_exact, o); n_rej_image += __shfl_xor_sync(0xffffffffu, n_rej_image, o);
+        }
+        if (lane == 0) {
+            atomicAdd(counters + 4, (unsigned long long)n_cand); atomicAdd(counters + 5, (unsigned long long)n_queued);
+            atomicAdd(counters + 6, (unsigned long long)n_rej_exact); atomicAdd(counters + 7, (unsigned long long)n_rej_image);
+        }
     }
 }
 
@@ -799,24 +815,20 @@ __device__ __forceinline__ void prefetch_l2(const void * p)
 #define K1_RAY_PREFETCH 0      // measured: no change (3.80-3.85 ms either way)
 #endif
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 8
+#define K1_MIN_BLOCKS 7        // measured (r02_b): the PRMT node test needs 70 registers; 8 CTAs (64) spill and gain nothing
 #endif
 
-// Exact leaf box (the tight bound of the leaf's triangles, verified at upload to equal the
-// reference's stored box) tested with the reference's own slab arithmetic.
-static __device__ __noinline__ bool leaf_box_exact(const float * __restrict__ raw_tris, uint32_t first, uint32_t count,
-    float ox, float oy, float oz, float dx, float dy, float dz, float tmin, float tmax)
+// The leaf's own box (the reference's stored box; for nested trees verified at upload to be the tight bound of the leaf's
+// triangles) tested with the reference's decision: slab_bool() proves accept / reject from t~ = (b - o) fl(1 / d) when the
+// margin allows (nearly always) and runs the reference's own divisions otherwise.
+static __device__ __noinline__ bool leaf_box_exact(const float4 * __restrict__ leafbox, uint32_t first,
+    float ox, float oy, float oz, float dx, float dy, float dz, float rdx, float rdy, float rdz, float tmin, float tmax)
 {
-    float mn[3] = {UAV_INF, UAV_INF, UAV_INF}, mx[3] = {-UAV_INF, -UAV_INF, -UAV_INF};
-    for (uint32_t t = first; t < first + count; ++t)
-        for (int v = 0; v < 3; ++v)
-            for (int k = 0; k < 3; ++k) {
-                float x = __ldg(raw_tris + 9 * (size_t)t + 3 * v + k);
-                mn[k] = fminf(mn[k], x); mx[k] = fmaxf(mx[k], x);
-            }
-    Ray r; r.o = mk(ox, oy, oz); r.d = mk(dx, dy, dz); r.tmin = tmin; r.tmax = tmax;
+    const float4 b0 = __ldg(leafbox + 2 * (size_t)first), b1 = __ldg(leafbox + 2 * (size_t)first + 1);
+    RayQ q; q.r.o = mk(ox, oy, oz); q.r.d = mk(dx, dy, dz); q.r.tmin = tmin; q.r.tmax = tmax;
+    q.rd = mk(rdx, rdy, rdz); q.fast = true;             // callers only hold rays with 1e-4 < |d_k| < 2
     float t;
-    return slab(r, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2], t);
+    return slab_bool(q, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, t);
 }
 
 // Occlusion rays against the 4-wide BVH of a tree whose boxes are nested (every child box
@@ -1005,7 +1017,7 @@ k_trace(TraceArgs a)
                             float t; bool h = false;
                             for (uint32_t i = 0; i < count; ++i) h |= hit_tri(ray, a.bvh.tris + first + i, t);
                             if (h && (r & 32u))      // rare: the leaf's box still has to pass the exact test
-                                h = leaf_box_exact(a.bvh.raw_tris, first, count, rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.tmin, rt.tmax);
+                                h = leaf_box_exact(a.bvh.leafbox, first, rt.ox, rt.oy, rt.oz, rd.x, rd.y, rd.z, rt.rdx, rt.rdy, rt.rdz, rt.tmin, rt.tmax);
                             hit = h;
                         }
                         npend = 0;
@@ -1265,7 +1277,7 @@ struct K1Scratch {
     uint32_t * masks = nullptr; size_t masks_cap = 0;
     uint32_t * caps = nullptr, * off = nullptr, * cnt = nullptr; size_t blocks_cap = 0;
     void * cub_tmp = nullptr; size_t cub_cap = 0;
-    float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr, * trd = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0;
+    float4 * dirl = nullptr, * tdir = nullptr, * torg = nullptr, * trd = nullptr; uint8_t * vis = nullptr; size_t rays_cap = 0, trd_cap = 0;
     uint32_t * tcnt = nullptr;
     uint32_t * rview = nullptr; size_t rview_cap = 0;
     uint32_t * tpk = nullptr; size_t tpk_cap = 0;
@@ -1425,9 +1437,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         }
         if (total > 0) {
             if (total > k.rays_cap) {
-                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap, c4 = k.rays_cap;
+                size_t c0 = k.rays_cap, c1 = k.rays_cap, c2 = k.rays_cap, c3 = k.rays_cap;
                 if (grow(&k.dirl, &c0, (size_t)total, s) || grow(&k.tdir, &c1, (size_t)total, s) || grow(&k.torg, &c3, (size_t)total, s)
-                    || grow(&k.vis, &c2, (size_t)total, s) || grow(&k.trd, &c4, (size_t)total, s)) return 1;
+                    || grow(&k.vis, &c2, (size_t)total, s)) return 1;
                 k.rays_cap = (size_t)total;
             }
             cub::DeviceScan::ExclusiveSum(k.cub_tmp, tmp_need, k.caps, k.off, (int)nb, uav::counted(s, 2));   // cub: DeviceScanInitKernel + DeviceScanKernel
@@ -1457,7 +1469,12 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             const bool queued = !shafts && !entry && !getenv("UAVMVS_CULL_PACKETS");
             if (k1_mark(k, s, 2)) return 1;
             if (queued) rl.tdir = rl.dirl;            // one record per ray: every ray is traced, in list order
-            rl.trd = (queued && !getenv("UAVMVS_TRACE_SETUP")) ? k.trd : nullptr;
+            // measured on config 2 (profiles/r02_b_sweep.txt): the set-up in the cull kernel costs it 0.05 ms and gains k_trace
+            // nothing (the refill is not where its issue slots go), so it stays opt-in
+            const bool cull_setup = queued && getenv("UAVMVS_CULL_SETUP");
+            if (cull_setup && grow(&k.trd, &k.trd_cap, k.rays_cap, s)) return 1;
+            rl.trd = cull_setup ? k.trd : nullptr;
+            rl.debug = getenv("UAVMVS_K1_DEBUG") ? 1u : 0u;
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
             if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
@@ -1529,6 +1546,12 @@ int k1_counters(unsigned long long out[4], int reset)
     for (int i = 0; i < 4; ++i) out[i] = 0;
     if (!k.counters) return 0;
     UAV_CUDA(cudaMemcpy(out, k.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (getenv("UAVMVS_K1_DEBUG")) {
+        unsigned long long d[8];
+        UAV_CUDA(cudaMemcpy(d, k.counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[k1] cull: candidate pairs %llu, queued for the exact cull %llu, rejected there by back-face / range %llu, by the image test %llu, rays %llu\n",
+            d[4], d[5], d[6], d[7], d[3]);
+    }
     if (getenv("UAVMVS_SHAFT_DEBUG")) {
         unsigned long long d[8];
         UAV_CUDA(cudaMemcpy(d, k.counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));

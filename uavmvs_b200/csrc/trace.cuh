@@ -22,13 +22,14 @@ struct BvhView {
     const Tri64 * __restrict__ tris;
     const float * __restrict__ raw_tris;     // 9 floats per triangle, leaf order (reference layout)
     const uint32_t * __restrict__ indices;
+    const float4 * __restrict__ leafbox;     // see uavmvs_bvh::leafbox (null for trees that are not nested)
     uint32_t root_is_leaf, root_first, root_count;
 };
 
 __host__ inline BvhView view_of(const uavmvs_bvh * b) {
     BvhView v;
     v.inner = b->inner; v.wide = b->wide; v.wide80 = b->wide80;
-    v.bx = b->bound_abs[0]; v.by = b->bound_abs[1]; v.bz = b->bound_abs[2]; v.tris = b->ptris; v.raw_tris = b->tris; v.indices = b->indices;
+    v.bx = b->bound_abs[0]; v.by = b->bound_abs[1]; v.bz = b->bound_abs[2]; v.tris = b->ptris; v.raw_tris = b->tris; v.indices = b->indices; v.leafbox = b->leafbox;
     v.root_is_leaf = b->root_is_leaf; v.root_first = b->root_first; v.root_count = b->root_count;
     return v;
 }
