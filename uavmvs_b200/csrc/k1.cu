@@ -650,7 +650,7 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
 // pairs (lane = pair, not point).  The queue is filled in (view, point) order and drained in order, so
 // the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
 // passes keep using k_cull_emit.
-template <bool HIST>
+template <bool HIST, bool DBG>
 __global__ void __launch_bounds__(K1_WARPS * 32)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
@@ -676,7 +676,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const float md2 = cull_distance * cull_distance * 1.00001f;
     const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
     uint32_t count = 0, qn = 0;
-    const bool dbg = counters && rl.debug;                // UAVMVS_K1_DEBUG: where the candidate pairs go
+    const bool dbg = DBG && counters;                     // UAVMVS_K1_DEBUG: where the candidate pairs go
     uint32_t n_cand = 0, n_queued = 0, n_rej_exact = 0, n_rej_image = 0;
 
     // exact cull + emit of the first min(qn, 32) queued pairs
@@ -1476,9 +1476,11 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             rl.trd = cull_setup ? k.trd : nullptr;
             rl.debug = getenv("UAVMVS_K1_DEBUG") ? 1u : 0u;
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
-            if (queued && hj) k_cull_emit_q<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            if (queued && rl.debug && !hj) k_cull_emit_q<false, true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
-            else if (queued) k_cull_emit_q<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+            else if (queued && hj) k_cull_emit_q<true, false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
+                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
+            else if (queued) k_cull_emit_q<false, false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
             else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
