@@ -10,7 +10,7 @@ want = ['gpu__time_duration.sum', 'smsp__inst_executed.sum', 'smsp__thread_inst_
         'smsp__issue_active.avg.pct_of_peak_sustained_active', 'sm__warps_active.avg.pct_of_peak_sustained_active',
         'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed', 'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active',
-        'dram__bytes_read.sum', 'dram__bytes_write.sum', 'lts__t_bytes.sum', 'l1tex__t_bytes.sum', 'launch__registers_per_thread', 'l1tex__t_sector_hit_rate.pct',
+        'dram__bytes_read.sum', 'dram__bytes_write.sum', 'lts__t_sectors.sum', 'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'launch__registers_per_thread', 'l1tex__t_sector_hit_rate.pct',
         'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
         'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']
 kn = hdr.index('Kernel Name')
@@ -41,7 +41,8 @@ with open(f"{pr}/{tag}_step_kernels.txt", "w") as f:
                       "l1_data_pipe_wavefronts_pct": val('l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed'),
                       "dram_throughput_pct": val('gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'),
                       "warp_instructions": val('smsp__inst_executed.sum'),
-                      "l2_bytes": val('lts__t_bytes.sum') * {'Mbyte': 1e6, 'Kbyte': 1e3, 'Gbyte': 1e9, 'byte': 1}.get(units[hdr.index('lts__t_bytes.sum')], 1),
+                      "l2_bytes": (val('lts__t_sectors.sum') * 32.0) if 'lts__t_sectors.sum' in hdr else None,
+                      "l2_throughput_pct": val('lts__throughput.avg.pct_of_peak_sustained_elapsed') if 'lts__throughput.avg.pct_of_peak_sustained_elapsed' in hdr else None,
                       "registers": val('launch__registers_per_thread'),
                       "active_threads_per_instruction": val('smsp__thread_inst_executed_per_inst_executed.ratio')}
 k1 = [k for k in traffic if any(x in k for x in ('view_masks', 'block_caps', 'sum_caps', 'add_u64', 'cull_emit', 'k_trace', 'k_retire'))]
