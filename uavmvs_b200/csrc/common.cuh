@@ -127,6 +127,7 @@ struct uavmvs_kdtree {
 
 struct uavmvs_cloud {
     uint32_t n;
+    float bound_abs[3];   // max |coordinate| of the points per axis (error bound of the fast image-reject proof, k1.cu)
     float4 * vertices, * normals;
     float * values, * qualities;
     // per 32-point block: bounding sphere (xyz, r) for the conservative view cull

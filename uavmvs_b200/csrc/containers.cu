@@ -366,6 +366,11 @@ int uavmvs_cloud_create(const float * vertices, const float * normals, const flo
     UAV_CUDA(cudaMalloc(&c->super_sphere, sizeof(float4) * (size_t)c->num_super));
     if (upload3(vertices, n, c->vertices)) return 1;
     if (upload3(normals, n, c->normals)) return 1;
+    for (int a = 0; a < 3; ++a) c->bound_abs[a] = 0.0f;
+    for (size_t i = 0; i < 3 * (size_t)n; ++i) {
+        const float m = fabsf(vertices[i]);
+        if (!(m <= c->bound_abs[i % 3])) c->bound_abs[i % 3] = m;     // NaN sticks: the proof then never fires
+    }
     if (values) UAV_CUDA(cudaMemcpy(c->values, values, 4 * (size_t)n, cudaMemcpyHostToDevice));
     else k_fill<<<divup(n, 256), 256>>>(c->values, n, 0.0f);        /* libs/util/cio.h:45 */
     if (qualities) UAV_CUDA(cudaMemcpy(c->qualities, qualities, 4 * (size_t)n, cudaMemcpyHostToDevice));

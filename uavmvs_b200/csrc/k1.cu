@@ -539,6 +539,7 @@ struct RayList {
                           //     (ray_fma_setup80), or w < 0: the ray takes the reference walk (axis-parallel direction,
                           //     single-leaf tree).  NULL: k_trace sets them up itself (packet modes)
     float bx, by, bz; uint32_t root_is_leaf;      // scene bounds of the error band, single-leaf tree flag
+    const float * vproj;  // k_view_proj rows + margins per view, or NULL (histogram jobs: no image test)
     uint32_t debug;       // UAVMVS_K1_DEBUG: k_cull_emit_q counts candidates / queued / rejected pairs into counters[4..7]
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
@@ -641,6 +642,32 @@ k_cull_emit(const float4 * __restrict__ verts, const float4 * __restrict__ norma
     }
 }
 
+// Per view: M = calib * w2c[0..2] (3 x 4, so that p = M [v, 1] is the reference's calib * (w2c * v), kernels.cu:21-27,
+// :165-167, in ONE step) and a margin per row: both the reference's two-stage unfused evaluation and the fused
+// evaluation with the rounded M differ from the real number p_i by less than 7.8e-7 A_i (13 roundings of 2^-24) and
+// 3e-7 A_i (5 roundings) respectively, A_i = sum_jk |K_ij| |W_jk| |v_k| + sum_j |K_ij| |W_j3|; with |v_k| <= B_k (the cloud's bounds) A_i is a per-view constant and
+// d_i = 2e-6 A_i bounds |p_i(reference) - P_i(fast)|.  vproj[v][16] = M (12), d0, d1, d2, 0.
+__global__ void k_view_proj(const float * __restrict__ views, uint32_t num_views, float bx, float by, float bz, float * __restrict__ vproj)
+{
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= num_views) return;
+    const float * W = views + (size_t)v * UAVMVS_VIEW_FLOATS + 3, * K = W + 16;
+    const double B[4] = {(double)bx, (double)by, (double)bz, 1.0};
+    float * o = vproj + 16 * (size_t)v;
+    for (int i = 0; i < 3; ++i) {
+        double A = 0.0;
+        for (int j = 0; j < 4; ++j) {
+            double m = 0.0, ma = 0.0;
+            for (int k = 0; k < 3; ++k) { m += (double)K[3 * i + k] * (double)W[4 * k + j]; ma += fabs((double)K[3 * i + k] * (double)W[4 * k + j]); }
+            o[4 * i + j] = (float)m;
+            A += ma * B[j];
+        }
+        const double d = 2e-6 * A;
+        o[12 + i] = (d == d && d < 1e30) ? (float)(d * 1.0000002) : __int_as_float(0x7f800000);   // NaN / inf: no proof
+    }
+    o[15] = 0.0f;
+}
+
 // Same result as k_cull_emit, fewer instructions: the exact cull costs ~400 instructions per 32 pairs
 // (IEEE sqrt, 8 IEEE divisions, unfused multiply-adds) and only ~40 % of the candidate pairs survive it,
 // most of the others failing the back-face test.  Phase 1 therefore proves rejections with a dozen
@@ -674,6 +701,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t mbit = blk & 31;
     const uint32_t base = rl.off[blk];
     const float md2 = cull_distance * cull_distance * 1.00001f;
+    const float wph = ((float)width + 0.5f) * 1.000001f, hph = ((float)height + 0.5f) * 1.000001f;
     const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
     uint32_t count = 0, qn = 0;
     const bool dbg = DBG && counters;                     // UAVMVS_K1_DEBUG: where the candidate pairs go
@@ -765,7 +793,23 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             const float l2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
             const float dn = __fmaf_rn(dz, nrm.z, __fmaf_rn(dy, nrm.y, dx * nrm.x));
             const float c = dn * rsqrtf(l2);
-            const bool reject = (c < bf_lim) || (l2 > md2);
+            bool reject = (c < bf_lim) || (l2 > md2);
+            if (!HIST && rl.vproj && !((iword >> kb) & 1u)) {
+                // fast proof that the reference's image test (kernels.cu:165-167) rejects the pair: the point lies in front
+                // of the camera (p2 surely positive) and projects outside the image by more than the margins allow
+                const float4 m0 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k));
+                const float4 m1 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 1);
+                const float4 m2 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 2);
+                const float4 dm = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 3);
+                const float P0 = __fmaf_rn(m0.z, v.z, __fmaf_rn(m0.y, v.y, __fmaf_rn(m0.x, v.x, m0.w)));
+                const float P1 = __fmaf_rn(m1.z, v.z, __fmaf_rn(m1.y, v.y, __fmaf_rn(m1.x, v.x, m1.w)));
+                const float P2 = __fmaf_rn(m2.z, v.z, __fmaf_rn(m2.y, v.y, __fmaf_rn(m2.x, v.x, m2.w)));
+                const float lo2 = P2 - dm.z, hi2 = P2 + dm.z;                    // p2 of the reference lies in [lo2, hi2]
+                // x = fl(p0 / p2) - 0.5 < 0  <=  p0 < 0.4999995 p2 ;  x >= width  <=  p0 > (width + 0.5)(1 + 1e-6) p2   (p2 > 0)
+                const bool out_x = (P0 + dm.x < 0.4999995f * lo2) || (P0 - dm.x > wph * hi2);
+                const bool out_y = (P1 + dm.y < 0.4999995f * lo2) || (P1 - dm.y > hph * hi2);
+                reject = reject || (lo2 > 0.0f && (out_x || out_y));            // NaN anywhere: no proof
+            }
             const bool maybe = valid && !reject;
             if (dbg && valid) ++n_cand;
             const uint32_t m = __ballot_sync(0xffffffffu, maybe);
@@ -1285,6 +1329,7 @@ struct K1Scratch {
     uint32_t * cert = nullptr; size_t cert_cap = 0;
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
+    float * vproj = nullptr; size_t vproj_cap = 0;
     int grid_trace = 0;
     int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS;
     cudaEvent_t ev_total = nullptr;
@@ -1391,6 +1436,12 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 
     k.ev_used = 0;
     if (k1_mark(k, s, 0)) return 1;
+    const bool img_proof = !hj && !getenv("UAVMVS_NO_IMAGE_PROOF");
+    if (img_proof) {
+        if (grow(&k.vproj, &k.vproj_cap, 16 * (size_t)num_views, s)) return 1;
+        k_view_proj<<<divup(num_views, 128), 128, 0, uav::counted(s)>>>(d_views, num_views, cloud->bound_abs[0], cloud->bound_abs[1],
+            cloud->bound_abs[2], k.vproj);
+    }
     dim3 mgrid(divup(num_views, 32), divup(cloud->num_super, K1_WARPS * K1_SB_PER_WARP));
     // Histogram jobs test `1 - l / max_distance <= 0` (kernels.cu:310-311): with max_distance <= 0 (the planner's
     // swapped arguments can pass a negative average there, plan_trajectory.cu:270-274) nothing is out of range, so the
@@ -1475,6 +1526,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             if (cull_setup && grow(&k.trd, &k.trd_cap, k.rays_cap, s)) return 1;
             rl.trd = cull_setup ? k.trd : nullptr;
             rl.debug = getenv("UAVMVS_K1_DEBUG") ? 1u : 0u;
+            rl.vproj = img_proof ? k.vproj : nullptr;
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
             if (queued && rl.debug && !hj) k_cull_emit_q<false, true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
