@@ -1436,7 +1436,10 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 
     k.ev_used = 0;
     if (k1_mark(k, s, 0)) return 1;
-    const bool img_proof = !hj && !getenv("UAVMVS_NO_IMAGE_PROOF");
+    // Opt-in (UAVMVS_IMAGE_PROOF=1).  Measured on config 2 (profiles/r02_d_image_proof.txt): 16.1 M of the 39.0 M pairs queued
+    // for the exact cull fail only the image test, and the proof removes them -- but it lengthens the latency-bound
+    // per-view loop of phase 1 (four uniform loads + a 9-FMA chain per candidate): k_cull_emit_q 0.79 -> 1.08 ms.
+    const bool img_proof = !hj && getenv("UAVMVS_IMAGE_PROOF");
     if (img_proof) {
         if (grow(&k.vproj, &k.vproj_cap, 16 * (size_t)num_views, s)) return 1;
         k_view_proj<<<divup(num_views, 128), 128, 0, uav::counted(s)>>>(d_views, num_views, cloud->bound_abs[0], cloud->bound_abs[1],
