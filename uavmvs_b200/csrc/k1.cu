@@ -197,6 +197,21 @@ __global__ void k_sum_caps(const uint32_t * __restrict__ caps, uint32_t n, unsig
 }
 
 __global__ void k_add_u64(unsigned long long * dst, const unsigned long long * src) { *dst += *src; }
+__global__ void k_add_val(unsigned long long * dst, unsigned long long val) { *dst += val; }
+
+// vcaps[v] = 32 x number of candidate blocks of view v = the ray-record bound of that view alone; the bound of a batch
+// [v0, v1) is the sum of its views' (what k_block_caps + k_sum_caps give per batch).  One pass over the mask matrix lets
+// the host cut a long trajectory into batches that fit the ray budget with ONE synchronisation instead of one per
+// (tentative) batch.  grid = (views / 128, super-blocks / 64); coalesced along the view index.
+__global__ void k_view_caps(const uint32_t * __restrict__ masks, uint32_t num_views, uint32_t num_super, uint32_t * __restrict__ vcaps)
+{
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= num_views) return;
+    const uint32_t sb0 = blockIdx.y * 64u, sb1 = min(num_super, sb0 + 64u);
+    uint32_t c = 0;
+    for (uint32_t sb = sb0; sb < sb1; ++sb) c += __popc(__ldg(masks + (size_t)sb * num_views + v));
+    if (c) atomicAdd(vcaps + v, 32u * c);
+}
 
 // ---- visibility shafts ----------------------------------------------------------------------
 // A (block, view) packet is CERTIFIED when no ray from any point of the block to the camera can be
@@ -1330,6 +1345,8 @@ struct K1Scratch {
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     float * vproj = nullptr; size_t vproj_cap = 0;
+    uint32_t * vcaps = nullptr, * h_vcaps = nullptr; size_t vcaps_cap = 0, h_vcaps_cap = 0;   // per-view bounds (batch planning)
+    uint32_t plan_views = 0, plan_blocks = 0;      // the last call with this shape needed a plan: plan at once
     int grid_trace = 0;
     int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS;
     cudaEvent_t ev_total = nullptr;
@@ -1464,30 +1481,57 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     bool speculate = !getenv("UAVMVS_NO_SPECULATION") && k.rays_cap > 0 && bvh->nested && !bvh->root_is_leaf
         && !entry_enabled() && !shafts_enabled() && !getenv("UAVMVS_CULL_PACKETS");
     if (speculate && !k.ev_total) UAV_CUDA(cudaEventCreateWithFlags(&k.ev_total, cudaEventDisableTiming));
-    uint32_t v0 = 0, step = num_views;
+    // A trajectory whose bound exceeds the budget is cut into batches of consecutive views from the per-view bounds
+    // (k_view_caps): one synchronisation for the whole call, every batch then enqueued without waiting for the device.
+    bool planned = false;
+    auto make_plan = [&]() -> int {
+        if (grow(&k.vcaps, &k.vcaps_cap, (size_t)num_views, s)) return 1;
+        if (num_views > k.h_vcaps_cap) {
+            if (k.h_vcaps) cudaFreeHost(k.h_vcaps);
+            UAV_CUDA(cudaMallocHost(&k.h_vcaps, sizeof(uint32_t) * (size_t)num_views));
+            k.h_vcaps_cap = num_views;
+        }
+        UAV_CUDA(cudaMemsetAsync(k.vcaps, 0, sizeof(uint32_t) * (size_t)num_views, s));
+        k_view_caps<<<dim3(divup(num_views, 128), divup(cloud->num_super, 64)), 128, 0, uav::counted(s)>>>(k.masks, num_views, cloud->num_super, k.vcaps);
+        UAV_CUDA(cudaMemcpyAsync(k.h_vcaps, k.vcaps, sizeof(uint32_t) * (size_t)num_views, cudaMemcpyDeviceToHost, s));
+        UAV_CUDA(cudaStreamSynchronize(s));
+        planned = true; k.plan_views = num_views; k.plan_blocks = nb;
+        return 0;
+    };
+    if (num_views > 1 && k.plan_views == num_views && k.plan_blocks == nb) { speculate = false; if (make_plan()) return 1; }
+    uint32_t v0 = 0;
     while (v0 < num_views) {
-        uint32_t v1 = (uint32_t)min((uint64_t)num_views, (uint64_t)v0 + step);
+        uint32_t v1 = num_views;
+        unsigned long long total = 0;
+        if (planned) {
+            v1 = v0;
+            while (v1 < num_views && (v1 == v0 || total + k.h_vcaps[v1] <= ray_budget())) total += k.h_vcaps[v1++];
+            UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
+        }
         if (k1_mark(k, s, 1)) return 1;
-        UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
         k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, uav::counted(s)>>>(k.masks, num_views, v0, v1, nb, k.caps);
-        k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, uav::counted(s)>>>(k.caps, nb, k.total);
-        UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-        const bool spec = speculate;
+        const bool spec = speculate && !planned;
         speculate = false;                                   // one attempt per call
         const unsigned long long spec_cap = min((unsigned long long)k.rays_cap, min((unsigned long long)ray_budget(), 1ull << 27));
-        unsigned long long total;
-        if (spec) {
-            UAV_CUDA(cudaEventRecord(k.ev_total, s));
-            total = spec_cap;                                // sizes nothing: the buffers already hold this many records
+        if (planned) {
+            if (d_stats && total) k_add_val<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, total);   // pairs surviving the block-level cull
         } else {
-            UAV_CUDA(cudaStreamSynchronize(s));
-            total = *k.h_total;
-            if (total > ray_budget() && v1 - v0 > 1) {          // too many candidates: halve the batch
-                step = (v1 - v0 + 1) / 2;
-                continue;
+            UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
+            k_sum_caps<<<min(divup(nb, 256), 1024u), 256, 0, uav::counted(s)>>>(k.caps, nb, k.total);
+            UAV_CUDA(cudaMemcpyAsync(k.h_total, k.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+            if (spec) {
+                UAV_CUDA(cudaEventRecord(k.ev_total, s));
+                total = spec_cap;                            // sizes nothing: the buffers already hold this many records
+            } else {
+                UAV_CUDA(cudaStreamSynchronize(s));
+                total = *k.h_total;
+                if (total > ray_budget() && v1 - v0 > 1) {   // too many candidates for one batch: plan the batches
+                    if (make_plan()) return 1;
+                    continue;
+                }
+                UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
+                if (d_stats) k_add_u64<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
             }
-            UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
-            if (d_stats) k_add_u64<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, k.total);   // pairs surviving the block-level cull
         }
         if (total > 0) {
             if (total > k.rays_cap) {
@@ -1569,7 +1613,10 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         if (k1_mark(k, s, 5)) return 1;
         if (spec) {
             UAV_CUDA(cudaEventSynchronize(k.ev_total));      // the bound only; the batch keeps running
-            if (*k.h_total > spec_cap) continue;             // guarded kernels were no-ops: same batch again, synchronously
+            if (*k.h_total > spec_cap) {                     // guarded kernels were no-ops: same views again, sized properly
+                if (*k.h_total > ray_budget() && num_views > 1 && make_plan()) return 1;
+                continue;
+            }
             if (d_stats) k_add_u64<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, k.total);
         }
         v0 = v1;
