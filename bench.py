@@ -462,6 +462,7 @@ def evaluation_block(a, torch, dist, api, comm, rank, world, stream, flush, step
     sampler = ClockSampler(visible_gpu_index(int(os.environ.get("LOCAL_RANK", "0"))))
     barrier()
     api.launch_count(reset=True)
+    api.k1_counters(reset=True)
     sampler.start()
     ms, last = timer.run(resident_step, steps, after)
     barrier()
@@ -480,9 +481,12 @@ def evaluation_block(a, torch, dist, api, comm, rank, world, stream, flush, step
         barrier()
     api.profile_k1_enable(False)
     bits = {"hw_slowdown": 1, "hw_thermal_slowdown": 2, "sw_thermal_slowdown": 4, "sw_power_cap": 8}
+    rays_local = api.k1_counters(reset=True)[3] / max(steps, 1)
     per_rank = gather_rank_stats(torch, dist, world, [ms / steps, float(k_ms[0]) / steps, float(k1_ms[3]) / steps,
                                                       float(n_local), clocks["sm_mhz"] or 0.0,
-                                                      float(sum(bits[r] for r in clocks["reasons"]))])
+                                                      float(sum(bits[r] for r in clocks["reasons"])),
+                                                      float(k1_ms[0]) / steps, float(k1_ms[1]) / steps, float(k1_ms[2]) / steps,
+                                                      float(k1_ms[4]) / steps, float(k_ms[2]) / steps, float(rays_local)])
     if world > 1:
         t = torch.tensor([ms, e2e_ms or 0.0], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -495,7 +499,7 @@ def evaluation_block(a, torch, dist, api, comm, rank, world, stream, flush, step
         clocks = dict(clocks, sm_mhz=min(mhz), sm_mhz_per_rank=mhz, reasons=sorted(r for r, b in bits.items() if mask & b))
     return dict(sc=sc, pts=pts, nrm=nrm, bvh=bvh, cloud=cloud, n_local=n_local, V=V, build_s=build_s, ms=ms, steps=steps,
                 e2e_ms=e2e_ms, e2e_ok=e2e_ok, score=score, k_ms=k_ms / steps, k1_ms=k1_ms / steps, coll_ms=coll_ms[0] / steps,
-                clocks=clocks, launches=launches, per_rank=[r[:5] for r in per_rank], views_bytes=int(views_np.nbytes))
+                clocks=clocks, launches=launches, per_rank=[r[:5] + r[6:] for r in per_rank], views_bytes=int(views_np.nbytes))
 
 
 def roofline(blk, probe, tree_bytes, hbm_peak, peak_src, sms=148):
@@ -609,7 +613,8 @@ def extras_config34(a, torch, api, stream, blk, line):
 
 
 def per_rank_table(blk):
-    return {"columns": ["ms_per_step", "K1_ms", "k_trace_ms", "points", "sm_mhz"],
+    return {"columns": ["ms_per_step", "K1_ms", "k_trace_ms", "points", "sm_mhz", "k_view_masks_ms", "caps_scan_ms", "k_cull_emit_q_ms",
+                        "k_retire_ms", "K3_K8_ms", "rays"],
             "rows": [[round(float(x), 4) for x in r] for r in blk["per_rank"]]}
 
 
