@@ -701,14 +701,16 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
 {
     K1_SPECULATION_GUARD(rl);
     __shared__ float4 s_v[K1_WARPS][32], s_n[K1_WARPS][32];
-    __shared__ uint32_t s_q[K1_WARPS][64];
+    __shared__ uint32_t s_q[K1_WARPS][64], s_vq[K1_WARPS][64];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t blk = blockIdx.x * K1_WARPS + w;
     if (blk >= num_blocks) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t id = blk * 32 + lane;
     const bool valid = id < n;
-    const float4 v4 = verts[valid ? id : n - 1], n4 = normals[valid ? id : n - 1];
+    const float4 v4 = verts[valid ? id : n - 1];
+    float4 n4 = normals[valid ? id : n - 1];
+    n4.w = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));   // phase 1's back-face limit of this point
     s_v[w][lane] = v4; s_n[w][lane] = n4;
     __syncwarp();
     const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
@@ -717,7 +719,6 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t base = rl.off[blk];
     const float md2 = cull_distance * cull_distance * 1.00001f;
     const float wph = ((float)width + 0.5f) * 1.000001f, hph = ((float)height + 0.5f) * 1.000001f;
-    const float bf_lim = 0.087f - 1e-5f * (1.0f + fabsf(n4.x) + fabsf(n4.y) + fabsf(n4.z));
     uint32_t count = 0, qn = 0;
     const bool dbg = DBG && counters;                     // UAVMVS_K1_DEBUG: where the candidate pairs go
     uint32_t n_cand = 0, n_queued = 0, n_rej_exact = 0, n_rej_image = 0;
@@ -783,7 +784,73 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         __syncwarp();
     };
 
-    const V3 v = ld3(v4), nrm = ld3(n4);
+    // Phase 1, transposed: candidate views of the block are collected 32 at a time (lane = view, its position -- and, with
+    // the image proof, its projection rows -- in registers), and the 32 points are looped over from shared memory: 32
+    // independent iterations of a dozen instructions instead of one latency-bound iteration per candidate view (a block
+    // whose bounding sphere is huge -- a jump of the Z-order curve -- is a candidate for thousands of views; walked one view
+    // at a time such a block alone set the duration of the kernel: 0.5 us per view, 5 ms for the 9978 views of one block of
+    // a config-5 shard).  Lane p keeps the word "views of this group that may see point p"; the pairs are then queued in
+    // (view, point) order exactly as before.
+    const uint32_t nvalid = min(32u, n - blk * 32u);                       // points of this block
+    uint32_t vqn = 0;
+    auto process_views = [&](uint32_t take) {
+        const uint32_t ve = s_vq[w][lane < take ? lane : 0];               // view index | block surely inside its image << 31
+        const uint32_t k = ve & 0x7fffffffu;
+        const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
+        const float px = __ldg(view), py = __ldg(view + 1), pz = __ldg(view + 2);
+        const bool proof = !HIST && rl.vproj != nullptr && !(ve >> 31);
+        float4 m0 = make_float4(0.f, 0.f, 0.f, 0.f), m1 = m0, m2 = m0, dm = m0;
+        if (!HIST && rl.vproj) {
+            const float4 * vp = reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k);
+            m0 = __ldg(vp); m1 = __ldg(vp + 1); m2 = __ldg(vp + 2); dm = __ldg(vp + 3);
+        }
+        uint32_t mybits = 0;
+        #pragma unroll 4
+        for (uint32_t p = 0; p < nvalid; ++p) {
+            const float4 V = s_v[w][p], N = s_n[w][p];                     // broadcast; N.w = back-face limit of the point
+            // fast-math proof of rejection (any doubt, any NaN -> queued for the exact test)
+            const float dx = px - V.x, dy = py - V.y, dz = pz - V.z;
+            const float l2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+            const float dn = __fmaf_rn(dz, N.z, __fmaf_rn(dy, N.y, dx * N.x));
+            const float c = dn * rsqrtf(l2);
+            bool reject = (c < N.w) || (l2 > md2);
+            if (!HIST && rl.vproj) {
+                // fast proof that the reference's image test (kernels.cu:165-167) rejects the pair: the point lies in front
+                // of the camera (p2 surely positive) and projects outside the image by more than the margins allow
+                const float P0 = __fmaf_rn(m0.z, V.z, __fmaf_rn(m0.y, V.y, __fmaf_rn(m0.x, V.x, m0.w)));
+                const float P1 = __fmaf_rn(m1.z, V.z, __fmaf_rn(m1.y, V.y, __fmaf_rn(m1.x, V.x, m1.w)));
+                const float P2 = __fmaf_rn(m2.z, V.z, __fmaf_rn(m2.y, V.y, __fmaf_rn(m2.x, V.x, m2.w)));
+                const float lo2 = P2 - dm.z, hi2 = P2 + dm.z;              // p2 of the reference lies in [lo2, hi2]
+                // x = fl(p0 / p2) - 0.5 < 0  <=  p0 < 0.4999995 p2 ;  x >= width  <=  p0 > (width + 0.5)(1 + 1e-6) p2   (p2 > 0)
+                const bool out_x = (P0 + dm.x < 0.4999995f * lo2) || (P0 - dm.x > wph * hi2);
+                const bool out_y = (P1 + dm.y < 0.4999995f * lo2) || (P1 - dm.y > hph * hi2);
+                reject = reject || (proof && lo2 > 0.0f && (out_x || out_y));   // NaN anywhere: no proof
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, lane < take && !reject);
+            if (lane == p) mybits = m;
+        }
+        if (dbg && lane == 0) n_cand += take * nvalid;
+        // queue the surviving pairs in (view, point) order
+        uint32_t anyv = __reduce_or_sync(0xffffffffu, mybits);
+        while (anyv) {
+            const uint32_t j = __ffs(anyv) - 1; anyv &= anyv - 1;
+            const uint32_t vj = s_vq[w][j];
+            const bool has = (mybits >> j) & 1u;
+            const uint32_t m = __ballot_sync(0xffffffffu, has);
+            if (has) s_q[w][qn + __popc(m & lt_mask)] = ((vj & 0x7fffffffu) << 6) | ((vj >> 31) << 5) | lane;
+            qn += __popc(m);
+            __syncwarp();
+            if (qn >= 32u) flush();
+        }
+        // keep the views that did not fit
+        __syncwarp();
+        const uint32_t rest = vqn - take;
+        const uint32_t carry = lane < rest ? s_vq[w][32 + lane] : 0u;
+        __syncwarp();
+        if (lane < rest) s_vq[w][lane] = carry;
+        vqn = rest;
+        __syncwarp();
+    };
     for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
       uint32_t mw4[4], iw4[4];
       #pragma unroll
@@ -796,45 +863,16 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
       for (int u = 0; u < 4; ++u) {
         const uint32_t c0 = g0 + 32 * u;
         if (c0 >= v1) break;
-        uint32_t word = __ballot_sync(0xffffffffu, (mw4[u] >> mbit) & 1u);
-        const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
-        while (word) {
-            const uint32_t kb = __ffs(word) - 1;
-            const uint32_t k = c0 + kb; word &= word - 1;
-            const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
-            const float px = __ldg(view), py = __ldg(view + 1), pz = __ldg(view + 2);
-            // phase 1: fast-math proof of rejection (any doubt, any NaN -> queued for the exact test)
-            const float dx = px - v.x, dy = py - v.y, dz = pz - v.z;
-            const float l2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-            const float dn = __fmaf_rn(dz, nrm.z, __fmaf_rn(dy, nrm.y, dx * nrm.x));
-            const float c = dn * rsqrtf(l2);
-            bool reject = (c < bf_lim) || (l2 > md2);
-            if (!HIST && rl.vproj && !((iword >> kb) & 1u)) {
-                // fast proof that the reference's image test (kernels.cu:165-167) rejects the pair: the point lies in front
-                // of the camera (p2 surely positive) and projects outside the image by more than the margins allow
-                const float4 m0 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k));
-                const float4 m1 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 1);
-                const float4 m2 = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 2);
-                const float4 dm = __ldg(reinterpret_cast<const float4 *>(rl.vproj + 16 * (size_t)k) + 3);
-                const float P0 = __fmaf_rn(m0.z, v.z, __fmaf_rn(m0.y, v.y, __fmaf_rn(m0.x, v.x, m0.w)));
-                const float P1 = __fmaf_rn(m1.z, v.z, __fmaf_rn(m1.y, v.y, __fmaf_rn(m1.x, v.x, m1.w)));
-                const float P2 = __fmaf_rn(m2.z, v.z, __fmaf_rn(m2.y, v.y, __fmaf_rn(m2.x, v.x, m2.w)));
-                const float lo2 = P2 - dm.z, hi2 = P2 + dm.z;                    // p2 of the reference lies in [lo2, hi2]
-                // x = fl(p0 / p2) - 0.5 < 0  <=  p0 < 0.4999995 p2 ;  x >= width  <=  p0 > (width + 0.5)(1 + 1e-6) p2   (p2 > 0)
-                const bool out_x = (P0 + dm.x < 0.4999995f * lo2) || (P0 - dm.x > wph * hi2);
-                const bool out_y = (P1 + dm.y < 0.4999995f * lo2) || (P1 - dm.y > hph * hi2);
-                reject = reject || (lo2 > 0.0f && (out_x || out_y));            // NaN anywhere: no proof
-            }
-            const bool maybe = valid && !reject;
-            if (dbg && valid) ++n_cand;
-            const uint32_t m = __ballot_sync(0xffffffffu, maybe);
-            if (maybe) s_q[w][qn + __popc(m & lt_mask)] = (k << 6) | (((iword >> kb) & 1u) << 5) | lane;
-            qn += __popc(m);
-            __syncwarp();
-            if (qn >= 32u) flush();
-        }
+        const bool cand = (mw4[u] >> mbit) & 1u;
+        const uint32_t word = __ballot_sync(0xffffffffu, cand);
+        if (!word) continue;
+        if (cand) s_vq[w][vqn + __popc(word & lt_mask)] = (c0 + lane) | (((iw4[u] >> mbit) & 1u) << 31);
+        vqn += __popc(word);
+        __syncwarp();
+        if (vqn >= 32u) process_views(32u);
       }
     }
+    if (vqn) process_views(vqn);
     while (qn) flush();
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
