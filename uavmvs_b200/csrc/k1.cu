@@ -555,6 +555,7 @@ struct RayList {
                           //     single-leaf tree).  NULL: k_trace sets them up itself (packet modes)
     float bx, by, bz; uint32_t root_is_leaf;      // scene bounds of the error band, single-leaf tree flag
     const float * vproj;  // k_view_proj rows + margins per view, or NULL (histogram jobs: no image test)
+    uint32_t reverse;     // dev: k_cull_emit_q walks the blocks from the last to the first
     uint32_t debug;       // UAVMVS_K1_DEBUG: k_cull_emit_q counts candidates / queued / rejected pairs into counters[4..7]
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
@@ -692,18 +693,18 @@ __global__ void k_view_proj(const float * __restrict__ views, uint32_t num_views
 // pairs (lane = pair, not point).  The queue is filled in (view, point) order and drained in order, so
 // the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
 // passes keep using k_cull_emit.
-template <bool HIST, bool DBG>
-__global__ void __launch_bounds__(K1_WARPS * 32)
+template <bool HIST, bool DBG, int CW>
+__global__ void __launch_bounds__(CW * 32)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
     const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
     float max_distance, float cull_distance, int width, int height, RayList rl, unsigned long long * counters)
 {
     K1_SPECULATION_GUARD(rl);
-    __shared__ float4 s_v[K1_WARPS][32], s_n[K1_WARPS][32];
-    __shared__ uint32_t s_q[K1_WARPS][64], s_vq[K1_WARPS][64];
+    __shared__ float4 s_v[CW][32], s_n[CW][32];
+    __shared__ uint32_t s_q[CW][64], s_vq[CW][64];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    const uint32_t blk = rl.reverse ? num_blocks - 1u - (blockIdx.x * CW + w) : blockIdx.x * CW + w;
     if (blk >= num_blocks) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t id = blk * 32 + lane;
@@ -1386,7 +1387,7 @@ struct K1Scratch {
     uint32_t * vcaps = nullptr, * h_vcaps = nullptr; size_t vcaps_cap = 0, h_vcaps_cap = 0;   // per-view bounds (batch planning)
     uint32_t plan_views = 0, plan_blocks = 0;      // the last call with this shape needed a plan: plan at once
     int grid_trace = 0;
-    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS;
+    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 4;
     cudaEvent_t ev_total = nullptr;
     // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -1471,6 +1472,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         // dev sweeps: thresholds of the traversal kernel's bookkeeping
         if (const char * e = getenv("UAVMVS_K1_REFILL")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_refill = atoi(e);
         if (const char * e = getenv("UAVMVS_K1_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_tri = atoi(e);
+        if (const char * e = getenv("UAVMVS_CULL_WARPS")) if (atoi(e) == 1 || atoi(e) == 2 || atoi(e) == 4) k.tune_cull_warps = atoi(e);
         if (const char * e = getenv("UAVMVS_K1_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) k.tune_steps = atoi(e);
     }
     if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
@@ -1611,14 +1613,20 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             if (cull_setup && grow(&k.trd, &k.trd_cap, k.rays_cap, s)) return 1;
             rl.trd = cull_setup ? k.trd : nullptr;
             rl.debug = getenv("UAVMVS_K1_DEBUG") ? 1u : 0u;
+            rl.reverse = getenv("UAVMVS_CULL_REVERSE") ? 1u : 0u;
             rl.vproj = img_proof ? k.vproj : nullptr;
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
-            if (queued && rl.debug && !hj) k_cull_emit_q<false, true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
-            else if (queued && hj) k_cull_emit_q<true, false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
-            else if (queued) k_cull_emit_q<false, false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
-                d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters);
+            if (queued) {
+                // CTA size of the cull kernel: a CTA holds its SM slot until its slowest warp (= 32-point block) is done, and
+                // the work per block varies by orders of magnitude, so small CTAs pack better (UAVMVS_CULL_WARPS: 1, 2 or 4)
+                const int cw = k.tune_cull_warps;
+                #define UAV_CULL(H, D, W) k_cull_emit_q<H, D, W><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
+                    cloud->n, nb, d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters)
+                if (rl.debug && !hj) UAV_CULL(false, true, 4);
+                else if (hj) { if (cw == 1) UAV_CULL(true, false, 1); else if (cw == 2) UAV_CULL(true, false, 2); else UAV_CULL(true, false, 4); }
+                else { if (cw == 1) UAV_CULL(false, false, 1); else if (cw == 2) UAV_CULL(false, false, 2); else UAV_CULL(false, false, 4); }
+                #undef UAV_CULL
+            }
             else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
