@@ -18,6 +18,7 @@
 // The ray list is why lanes never wait for each other's rays (rays binned by camera: the
 // rays of one block towards one view are adjacent) and why the traversal kernel is small.
 #include <cub/cub.cuh>
+#include <algorithm>
 
 #include "common.cuh"
 #include "trace.cuh"
@@ -556,6 +557,9 @@ struct RayList {
     float bx, by, bz; uint32_t root_is_leaf;      // scene bounds of the error band, single-leaf tree flag
     const float * vproj;  // k_view_proj rows + margins per view, or NULL (histogram jobs: no image test)
     uint32_t reverse;     // dev: k_cull_emit_q walks the blocks from the last to the first
+    const uint32_t * caps;   // [num_blocks] 32 x candidate views of the block in this batch (k_block_caps)
+    uint32_t transpose_at;   // k_cull_emit_q: candidate views from which a block takes the transposed phase 1
+    uint32_t * dbg_blocks;   // UAVMVS_K1_DEBUG: per block {cycles, rays, candidate views} of k_cull_emit_q
     uint32_t debug;       // UAVMVS_K1_DEBUG: k_cull_emit_q counts candidates / queued / rejected pairs into counters[4..7]
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
     uint32_t * cnt;       // [num_blocks] rays in the slice
@@ -694,7 +698,7 @@ __global__ void k_view_proj(const float * __restrict__ views, uint32_t num_views
 // the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
 // passes keep using k_cull_emit.
 template <bool HIST, bool DBG, int CW>
-__global__ void __launch_bounds__(CW * 32)
+__global__ void __launch_bounds__(CW * 32, 32 / CW)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
     const uint32_t * __restrict__ masks, const uint32_t * __restrict__ inside_masks,
@@ -722,6 +726,8 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const float wph = ((float)width + 0.5f) * 1.000001f, hph = ((float)height + 0.5f) * 1.000001f;
     uint32_t count = 0, qn = 0;
     const bool dbg = DBG && counters;                     // UAVMVS_K1_DEBUG: where the candidate pairs go
+    const long long dbg_t0 = DBG ? clock64() : 0ll;
+    uint32_t dbg_views = 0;
     uint32_t n_cand = 0, n_queued = 0, n_rej_exact = 0, n_rej_image = 0;
 
     // exact cull + emit of the first min(qn, 32) queued pairs
@@ -831,6 +837,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             if (lane == p) mybits = m;
         }
         if (dbg && lane == 0) n_cand += take * nvalid;
+        if (DBG) dbg_views += take;
         // queue the surviving pairs in (view, point) order
         uint32_t anyv = __reduce_or_sync(0xffffffffu, mybits);
         while (anyv) {
@@ -852,6 +859,11 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         vqn = rest;
         __syncwarp();
     };
+    // Blocks with few candidate views keep the direct form (lane = point, one candidate view per iteration: fewer
+    // instructions when most views of a group queue something anyway); rl.transpose_at = candidate views from which a
+    // block takes the transposed form (k_block_caps knows the count before this kernel runs).
+    const bool transposed = (rl.caps[blk] >> 5) >= rl.transpose_at || (!HIST && rl.vproj != nullptr);
+    const V3 pv = ld3(v4); const float bf_lim = n4.w;
     for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
       uint32_t mw4[4], iw4[4];
       #pragma unroll
@@ -865,12 +877,34 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         const uint32_t c0 = g0 + 32 * u;
         if (c0 >= v1) break;
         const bool cand = (mw4[u] >> mbit) & 1u;
-        const uint32_t word = __ballot_sync(0xffffffffu, cand);
+        uint32_t word = __ballot_sync(0xffffffffu, cand);
         if (!word) continue;
-        if (cand) s_vq[w][vqn + __popc(word & lt_mask)] = (c0 + lane) | (((iw4[u] >> mbit) & 1u) << 31);
-        vqn += __popc(word);
-        __syncwarp();
-        if (vqn >= 32u) process_views(32u);
+        if (transposed) {
+            if (cand) s_vq[w][vqn + __popc(word & lt_mask)] = (c0 + lane) | (((iw4[u] >> mbit) & 1u) << 31);
+            vqn += __popc(word);
+            __syncwarp();
+            if (vqn >= 32u) process_views(32u);
+            continue;
+        }
+        const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
+        while (word) {
+            const uint32_t kb = __ffs(word) - 1;
+            const uint32_t k = c0 + kb; word &= word - 1;
+            const float * view = views + UAVMVS_VIEW_FLOATS * (size_t)k;
+            const float px = __ldg(view), py = __ldg(view + 1), pz = __ldg(view + 2);
+            // fast-math proof of rejection (any doubt, any NaN -> queued for the exact test)
+            const float dx = px - pv.x, dy = py - pv.y, dz = pz - pv.z;
+            const float l2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+            const float dn = __fmaf_rn(dz, n4.z, __fmaf_rn(dy, n4.y, dx * n4.x));
+            const float c = dn * rsqrtf(l2);
+            const bool maybe = valid && !((c < bf_lim) || (l2 > md2));
+            if (DBG) { if (dbg && valid) ++n_cand; ++dbg_views; }
+            const uint32_t m = __ballot_sync(0xffffffffu, maybe);
+            if (maybe) s_q[w][qn + __popc(m & lt_mask)] = (k << 6) | (((iword >> kb) & 1u) << 5) | lane;
+            qn += __popc(m);
+            __syncwarp();
+            if (qn >= 32u) flush();
+        }
       }
     }
     if (vqn) process_views(vqn);
@@ -878,6 +912,9 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
         if (counters && count) atomicAdd(counters + 3, (unsigned long long)count);
+    }
+    if (DBG && rl.dbg_blocks && lane == 0) {
+        rl.dbg_blocks[3 * (size_t)blk] = (uint32_t)(clock64() - dbg_t0); rl.dbg_blocks[3 * (size_t)blk + 1] = count; rl.dbg_blocks[3 * (size_t)blk + 2] = dbg_views;
     }
     if (dbg) {
         for (int o = 16; o > 0; o >>= 1) {
@@ -1384,10 +1421,11 @@ struct K1Scratch {
     uint32_t * work = nullptr; unsigned long long * total = nullptr, * h_total = nullptr;
     unsigned long long * counters = nullptr;      // diagnostics: shaft packets tested / certified, rays certified / traced
     float * vproj = nullptr; size_t vproj_cap = 0;
+    uint32_t * dbg_blocks = nullptr; size_t dbg_blocks_cap = 0;
     uint32_t * vcaps = nullptr, * h_vcaps = nullptr; size_t vcaps_cap = 0, h_vcaps_cap = 0;   // per-view bounds (batch planning)
     uint32_t plan_views = 0, plan_blocks = 0;      // the last call with this shape needed a plan: plan at once
     int grid_trace = 0;
-    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 4;
+    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 4, tune_transpose_at = 256;
     cudaEvent_t ev_total = nullptr;
     // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -1473,6 +1511,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         if (const char * e = getenv("UAVMVS_K1_REFILL")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_refill = atoi(e);
         if (const char * e = getenv("UAVMVS_K1_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_tri = atoi(e);
         if (const char * e = getenv("UAVMVS_CULL_WARPS")) if (atoi(e) == 1 || atoi(e) == 2 || atoi(e) == 4) k.tune_cull_warps = atoi(e);
+        if (const char * e = getenv("UAVMVS_CULL_TRANSPOSE_AT")) k.tune_transpose_at = atoi(e) >= 0 ? atoi(e) : 256;
         if (const char * e = getenv("UAVMVS_K1_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) k.tune_steps = atoi(e);
     }
     if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
@@ -1614,6 +1653,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             rl.trd = cull_setup ? k.trd : nullptr;
             rl.debug = getenv("UAVMVS_K1_DEBUG") ? 1u : 0u;
             rl.reverse = getenv("UAVMVS_CULL_REVERSE") ? 1u : 0u;
+            rl.caps = k.caps; rl.transpose_at = k.tune_transpose_at;
+            rl.dbg_blocks = nullptr;
+            if (rl.debug) { if (grow(&k.dbg_blocks, &k.dbg_blocks_cap, 3 * (size_t)nb, s)) return 1; rl.dbg_blocks = k.dbg_blocks; }
             rl.vproj = img_proof ? k.vproj : nullptr;
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
             if (queued) {
@@ -1699,6 +1741,18 @@ int k1_counters(unsigned long long out[4], int reset)
     if (getenv("UAVMVS_K1_DEBUG")) {
         unsigned long long d[8];
         UAV_CUDA(cudaMemcpy(d, k.counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        if (k.dbg_blocks && k.dbg_blocks_cap) {
+            const size_t nbk = k.dbg_blocks_cap / 3;
+            std::vector<uint32_t> h(3 * nbk);
+            UAV_CUDA(cudaMemcpy(h.data(), k.dbg_blocks, sizeof(uint32_t) * h.size(), cudaMemcpyDeviceToHost));
+            std::vector<uint32_t> order(nbk);
+            for (size_t i = 0; i < nbk; ++i) order[i] = (uint32_t)i;
+            std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return h[3 * a] > h[3 * b]; });
+            double sum = 0.0; for (size_t i = 0; i < nbk; ++i) sum += h[3 * i];
+            fprintf(stderr, "[k1] cull per block: %zu blocks, mean %.0f cycles, median %u, p99 %u; slowest:", nbk, sum / nbk, h[3 * order[nbk / 2]], h[3 * order[nbk / 100]]);
+            for (int i = 0; i < 6 && i < (int)nbk; ++i) fprintf(stderr, " [blk %u: %u cycles, %u rays, %u views]", order[i], h[3 * order[i]], h[3 * order[i] + 1], h[3 * order[i] + 2]);
+            fprintf(stderr, "\n");
+        }
         fprintf(stderr, "[k1] cull: candidate pairs %llu, queued for the exact cull %llu, rejected there by back-face / range %llu, by the image test %llu, rays %llu\n",
             d[4], d[5], d[6], d[7], d[3]);
     }
