@@ -697,7 +697,7 @@ __global__ void k_view_proj(const float * __restrict__ views, uint32_t num_views
 // pairs (lane = pair, not point).  The queue is filled in (view, point) order and drained in order, so
 // the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
 // passes keep using k_cull_emit.
-template <bool HIST, bool DBG, int CW>
+template <bool HIST, bool DBG, int CW, bool TR>
 __global__ void __launch_bounds__(CW * 32, 32 / CW)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
@@ -710,6 +710,8 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t blk = rl.reverse ? num_blocks - 1u - (blockIdx.x * CW + w) : blockIdx.x * CW + w;
     if (blk >= num_blocks) return;
+    // two launches share the blocks: TR = false takes those with few candidate views, TR = true the heavy ones
+    if ((((rl.caps[blk] >> 5) >= rl.transpose_at) || (!HIST && rl.vproj != nullptr)) != TR) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t id = blk * 32 + lane;
     const bool valid = id < n;
@@ -862,7 +864,6 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     // Blocks with few candidate views keep the direct form (lane = point, one candidate view per iteration: fewer
     // instructions when most views of a group queue something anyway); rl.transpose_at = candidate views from which a
     // block takes the transposed form (k_block_caps knows the count before this kernel runs).
-    const bool transposed = (rl.caps[blk] >> 5) >= rl.transpose_at || (!HIST && rl.vproj != nullptr);
     const V3 pv = ld3(v4); const float bf_lim = n4.w;
     for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
       uint32_t mw4[4], iw4[4];
@@ -879,13 +880,14 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         const bool cand = (mw4[u] >> mbit) & 1u;
         uint32_t word = __ballot_sync(0xffffffffu, cand);
         if (!word) continue;
-        if (transposed) {
+        if constexpr (TR) {
             if (cand) s_vq[w][vqn + __popc(word & lt_mask)] = (c0 + lane) | (((iw4[u] >> mbit) & 1u) << 31);
             vqn += __popc(word);
             __syncwarp();
             if (vqn >= 32u) process_views(32u);
             continue;
         }
+        if constexpr (!TR) {
         const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
         while (word) {
             const uint32_t kb = __ffs(word) - 1;
@@ -905,9 +907,10 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             __syncwarp();
             if (qn >= 32u) flush();
         }
+        }
       }
     }
-    if (vqn) process_views(vqn);
+    if constexpr (TR) { if (vqn) process_views(vqn); }
     while (qn) flush();
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
@@ -1662,12 +1665,15 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 // CTA size of the cull kernel: a CTA holds its SM slot until its slowest warp (= 32-point block) is done, and
                 // the work per block varies by orders of magnitude, so small CTAs pack better (UAVMVS_CULL_WARPS: 1, 2 or 4)
                 const int cw = k.tune_cull_warps;
-                #define UAV_CULL(H, D, W) k_cull_emit_q<H, D, W><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
+                const bool only_tr = !hj && rl.vproj != nullptr;          // the image proof lives in the transposed form
+                #define UAV_CULL1(H, D, W, T) k_cull_emit_q<H, D, W, T><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
                     cloud->n, nb, d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters)
+                #define UAV_CULL(H, D, W) do { if (!only_tr) UAV_CULL1(H, D, W, false); if (only_tr || rl.transpose_at < 0x7fffffffu) UAV_CULL1(H, D, W, true); } while (0)
                 if (rl.debug && !hj) UAV_CULL(false, true, 4);
                 else if (hj) { if (cw == 1) UAV_CULL(true, false, 1); else if (cw == 2) UAV_CULL(true, false, 2); else UAV_CULL(true, false, 4); }
                 else { if (cw == 1) UAV_CULL(false, false, 1); else if (cw == 2) UAV_CULL(false, false, 2); else UAV_CULL(false, false, 4); }
                 #undef UAV_CULL
+                #undef UAV_CULL1
             }
             else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
