@@ -697,7 +697,7 @@ __global__ void k_view_proj(const float * __restrict__ views, uint32_t num_views
 // pairs (lane = pair, not point).  The queue is filled in (view, point) order and drained in order, so
 // the slice comes out in exactly the order k_cull_emit writes.  No packets: the opt-in shaft / entry-point
 // passes keep using k_cull_emit.
-template <bool HIST, bool DBG, int CW, bool TR>
+template <bool HIST, bool DBG, int CW>
 __global__ void __launch_bounds__(CW * 32, 32 / CW)
 k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ normals, uint32_t n, uint32_t num_blocks,
     const float * __restrict__ views, uint32_t num_views, uint32_t v0, uint32_t v1,
@@ -710,8 +710,6 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t blk = rl.reverse ? num_blocks - 1u - (blockIdx.x * CW + w) : blockIdx.x * CW + w;
     if (blk >= num_blocks) return;
-    // two launches share the blocks: TR = false takes those with few candidate views, TR = true the heavy ones
-    if ((((rl.caps[blk] >> 5) >= rl.transpose_at) || (!HIST && rl.vproj != nullptr)) != TR) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t id = blk * 32 + lane;
     const bool valid = id < n;
@@ -864,6 +862,7 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     // Blocks with few candidate views keep the direct form (lane = point, one candidate view per iteration: fewer
     // instructions when most views of a group queue something anyway); rl.transpose_at = candidate views from which a
     // block takes the transposed form (k_block_caps knows the count before this kernel runs).
+    const bool transposed = (rl.caps[blk] >> 5) >= rl.transpose_at || (!HIST && rl.vproj != nullptr);
     const V3 pv = ld3(v4); const float bf_lim = n4.w;
     for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
       uint32_t mw4[4], iw4[4];
@@ -880,14 +879,13 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
         const bool cand = (mw4[u] >> mbit) & 1u;
         uint32_t word = __ballot_sync(0xffffffffu, cand);
         if (!word) continue;
-        if constexpr (TR) {
+        if (transposed) {
             if (cand) s_vq[w][vqn + __popc(word & lt_mask)] = (c0 + lane) | (((iw4[u] >> mbit) & 1u) << 31);
             vqn += __popc(word);
             __syncwarp();
             if (vqn >= 32u) process_views(32u);
             continue;
         }
-        if constexpr (!TR) {
         const uint32_t iword = __ballot_sync(0xffffffffu, (iw4[u] >> mbit) & 1u);   // whole block surely inside the image
         while (word) {
             const uint32_t kb = __ffs(word) - 1;
@@ -907,10 +905,9 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
             __syncwarp();
             if (qn >= 32u) flush();
         }
-        }
       }
     }
-    if constexpr (TR) { if (vqn) process_views(vqn); }
+    if (vqn) process_views(vqn);
     while (qn) flush();
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
@@ -1428,7 +1425,7 @@ struct K1Scratch {
     uint32_t * vcaps = nullptr, * h_vcaps = nullptr; size_t vcaps_cap = 0, h_vcaps_cap = 0;   // per-view bounds (batch planning)
     uint32_t plan_views = 0, plan_blocks = 0;      // the last call with this shape needed a plan: plan at once
     int grid_trace = 0;
-    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 4, tune_transpose_at = 256;
+    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 1, tune_transpose_at = 512;
     cudaEvent_t ev_total = nullptr;
     // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -1663,17 +1660,17 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             rl.bx = bvh->bound_abs[0]; rl.by = bvh->bound_abs[1]; rl.bz = bvh->bound_abs[2]; rl.root_is_leaf = bvh->root_is_leaf;
             if (queued) {
                 // CTA size of the cull kernel: a CTA holds its SM slot until its slowest warp (= 32-point block) is done, and
-                // the work per block varies by orders of magnitude, so small CTAs pack better (UAVMVS_CULL_WARPS: 1, 2 or 4)
+                // the work per block varies by orders of magnitude, so small CTAs pack better (UAVMVS_CULL_WARPS: 1, 2 or 4).
+                // Measured on config 2 (profiles/r02_k_sweep.txt): 4 warps 0.71 ms, 1 warp 0.68; transposed phase 1 from 512
+                // candidate views 0.65, from 128 1.00, never 0.83 (the slowest block then sets the duration of the kernel);
+                // the two forms as separate kernels 0.72 - 0.86 (r02_l: the heavy blocks' kernel is one long tail)
                 const int cw = k.tune_cull_warps;
-                const bool only_tr = !hj && rl.vproj != nullptr;          // the image proof lives in the transposed form
-                #define UAV_CULL1(H, D, W, T) k_cull_emit_q<H, D, W, T><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
+                #define UAV_CULL(H, D, W) k_cull_emit_q<H, D, W><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
                     cloud->n, nb, d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters)
-                #define UAV_CULL(H, D, W) do { if (!only_tr) UAV_CULL1(H, D, W, false); if (only_tr || rl.transpose_at < 0x7fffffffu) UAV_CULL1(H, D, W, true); } while (0)
                 if (rl.debug && !hj) UAV_CULL(false, true, 4);
                 else if (hj) { if (cw == 1) UAV_CULL(true, false, 1); else if (cw == 2) UAV_CULL(true, false, 2); else UAV_CULL(true, false, 4); }
                 else { if (cw == 1) UAV_CULL(false, false, 1); else if (cw == 2) UAV_CULL(false, false, 2); else UAV_CULL(false, false, 4); }
                 #undef UAV_CULL
-                #undef UAV_CULL1
             }
             else if (hj) k_cull_emit<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
