@@ -137,6 +137,10 @@ int uavmvs_image_destroy(uavmvs_image * img);
 /* ---- configure_heuristic, libs/eval/kernels.h:93, kernels.cu:93-103.
  * Process-global like the reference's __constant__ symbols; defaults 8, 4, 32, 16. */
 int uavmvs_configure_heuristic(float m_k, float m_x0, float t_k, float t_x0);
+/* The same constants bound to ONE observation array: every kernel that evaluates the heuristic on it (K3, K5, the fused
+ * evaluations) then uses these instead of the process-wide ones, so host threads working on different arrays -- or one
+ * thread alternating between them -- do not share state (SURVEY.md 8b "per-call or per-context, not global"). */
+int uavmvs_obs_configure_heuristic(uavmvs_obs * obs, float m_k, float m_x0, float t_k, float t_x0);
 
 /* ---- K1 update_observation_rays, libs/eval/kernels.h:26-35, kernels.cu:138-202.
  * One view, all points; same arguments as the kernel plus the stream. */

@@ -602,3 +602,30 @@ def test_tree_deeper_than_the_stacks_is_refused(api):
             aabbs.append([k + 1, 0, 0, k + 1.5, 0.5, 0])
     with pytest.raises(api.UavmvsError, match="deeper than the traversal stacks"):
         api.BVHTree.create(np.array(nodes, np.uint32), np.array(aabbs, np.float32), tris, np.arange(depth + 1, dtype=np.uint32))
+
+
+def test_heuristic_constants_per_observation_array(api, oracle, tiny_scene, tiny_tree):
+    """uavmvs_obs_configure_heuristic: two observation arrays evaluated with different constants in one process
+    (per context, not global); each equals the oracle run with its own constants."""
+    sc = tiny_scene
+    obvh, arrays = tiny_tree
+    gbvh = _gpu_tree(api, arrays)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs_o = oracle.ObsRays(sc.num_points, 32)
+    oracle.update_observation_rays(obvh, True, sc.views28(), sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    heurs = [(8.0, 4.0, 32.0, 16.0), (4.0, 3.0, 16.0, 12.0)]
+    arrays_g = []
+    for h in heurs:
+        obs = api.VectorArray.create(sc.num_points, 32)
+        obs.configure_heuristic(*h)
+        arrays_g.append(obs)
+    recons = [api.Array.create(sc.num_points) for _ in heurs]
+    wrecons = [api.Array.create(sc.num_points) for _ in heurs]
+    for obs, rc, wr in zip(arrays_g, recons, wrecons):      # interleaved use of the two contexts
+        api.evaluate_trajectory(sc.views28(), sc.max_distance, sc.target_recon, sc.width, sc.height, gbvh, cloud, obs, rc, wr)
+    got = [rc.download() for rc in recons]
+    for h, r_g in zip(heurs, got):
+        r_o = oracle.evaluate_observation_rays(obs_o, heur=h)
+        assert np.all(np.abs(r_g.astype(np.float64) - r_o) <= 1e-5 * np.maximum(np.abs(r_g), np.abs(r_o)) + 1e-6)
+    assert not np.allclose(got[0], got[1])

@@ -251,6 +251,10 @@ class VectorArray(_Handle):
         obj.num_cols, obj.max_rows = num_cols, max_rows
         return obj
 
+    def configure_heuristic(self, m_k=8.0, m_x0=4.0, t_k=32.0, t_x0=16.0):
+        """Heuristic constants of this observation array only (the process-wide ones stay as they are)."""
+        _check(_lib.uavmvs_obs_configure_heuristic(self.ptr, _f32(m_k), _f32(m_x0), _f32(t_k), _f32(t_x0)))
+
     def null(self, stream=None):
         _check(_lib.uavmvs_obs_clear(_stream_ptr(stream), self.ptr))
 

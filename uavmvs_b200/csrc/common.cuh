@@ -156,6 +156,9 @@ struct uavmvs_obs {
     float4 * data;
     uint32_t * num_rows;
     uint32_t * dirty;        // one word per 32 columns: a column of the block changed since the last incremental evaluation
+    // heuristic constants of THIS observation array (uavmvs_obs_configure_heuristic); has_heur == 0: the process-wide
+    // ones of uavmvs_configure_heuristic at the time of the call, the reference's convention
+    float heur[4]; int has_heur;
 };
 
 struct uavmvs_array { uint32_t n; float * data; };
@@ -200,6 +203,7 @@ struct Ray { V3 o, d; float tmin, tmax; };
 // passed to kernels by value
 struct Heur { float m_k, m_x0, t_k, t_x0; };
 Heur current_heur();
+Heur heur_of(const uavmvs_obs * obs);     // the array's own constants, else the process-wide ones
 
 // Batched spherical-histogram job run through the K1 ray-list pipeline (k1.cu): the "views" are bare
 // candidate positions (no frustum), visible rays are binned into hist[view][bin] instead of becoming

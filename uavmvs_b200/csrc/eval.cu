@@ -9,6 +9,11 @@ namespace uav {
 
 static Heur g_heur = {8.0f, 4.0f, 32.0f, 16.0f};   // m_k, m_x0, t_k, t_x0 (kernels.cu:93-96)
 Heur current_heur() { return g_heur; }
+Heur heur_of(const uavmvs_obs * obs)
+{
+    if (obs && obs->has_heur) { Heur h = {obs->heur[0], obs->heur[1], obs->heur[2], obs->heur[3]}; return h; }
+    return g_heur;
+}
 
 // ---- K2 + K3 (+K8): process_observation_rays, kernels.cu:204-264, evaluate_observation_rays,
 // :266-291 (heuristic :111-136), calculate_func_recons :496-510 -------------------------------
@@ -239,11 +244,11 @@ static int launch_sort_eval(cudaStream_t s, bool do_sort, bool do_eval, uavmvs_o
     const uint32_t stride = (uint32_t)(obs->pitch / sizeof(float4));
     float * r = recons ? recons->data : nullptr, * wr = wrecons ? wrecons->data : nullptr;
     if (do_sort && do_eval)
-        k_sort_eval<true, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<true, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, heur_of(obs), dirty, block0);
     else if (do_sort)
-        k_sort_eval<true, false><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<true, false><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, heur_of(obs), dirty, block0);
     else
-        k_sort_eval<false, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, g_heur, dirty, block0);
+        k_sort_eval<false, true><<<grid, SE_THREADS, 0, uav::counted(s)>>>(obs->data, obs->num_rows, obs->max_rows, stride, obs->num_cols, r, target, wr, heur_of(obs), dirty, block0);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
@@ -267,6 +272,13 @@ extern "C" {
 int uavmvs_configure_heuristic(float m_k, float m_x0, float t_k, float t_x0)
 {
     g_heur.m_k = m_k; g_heur.m_x0 = m_x0; g_heur.t_k = t_k; g_heur.t_x0 = t_x0;
+    return 0;
+}
+
+int uavmvs_obs_configure_heuristic(uavmvs_obs * obs, float m_k, float m_x0, float t_k, float t_x0)
+{
+    UAV_REQUIRE(obs, "null obs");
+    obs->heur[0] = m_k; obs->heur[1] = m_x0; obs->heur[2] = t_k; obs->heur[3] = t_x0; obs->has_heur = 1;
     return 0;
 }
 

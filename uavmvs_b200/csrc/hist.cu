@@ -359,7 +359,7 @@ static int launch_populate(cudaStream_t s, bool with_recon, const float view_pos
         a.obs = obs->data; a.num_rows = obs->num_rows; a.max_rows = obs->max_rows;
         a.stride = (uint32_t)(obs->pitch / sizeof(float4)); a.recons = recons->data;
     }
-    a.hist = hist->data; a.heur = current_heur();
+    a.hist = hist->data; a.heur = heur_of(obs);
     size_t smem = kd->num_nodes * sizeof(float);
     unsigned grid = divup(cloud->n, HIST_THREADS);
     if (with_recon) k_populate_spherical_histogram<true><<<grid, HIST_THREADS, smem, uav::counted(s)>>>(a);
@@ -487,7 +487,7 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
         hj.obs = obs->data; hj.num_rows = obs->num_rows; hj.max_rows = obs->max_rows;
         hj.stride = (uint32_t)(obs->pitch / sizeof(float4)); hj.recons = recons->data;
     }
-    hj.hist = sphere_hists->data; hj.heur = current_heur();
+    hj.hist = sphere_hists->data; hj.heur = heur_of(obs);
     const size_t cells = (size_t)num_positions * kd->num_nodes;
     UAV_REQUIRE(cells < 0xffffff00ull, "positions x bins does not fit the 32-bit accumulator key");
     UAV_REQUIRE(cloud->n < (1u << 26), "more than 2^26 points per call (fixed-point head room)");
