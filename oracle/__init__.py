@@ -43,6 +43,11 @@ def build(force=False):
     if os.path.isdir("/root/reference/libs/acc") and (force or not os.path.exists(ref_so)
                                                       or os.path.getmtime(ref_so) < os.path.getmtime(shim)):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    geom_so = os.path.join(_HERE, "_ref", "libref_geom.so")
+    geom_shim = os.path.join(_HERE, "ref_shim", "ref_geom.cpp")
+    if os.path.isdir("/root/reference/libs/geom") and (force or not os.path.exists(geom_so)
+                                                        or os.path.getmtime(geom_so) < os.path.getmtime(geom_shim)):
+        subprocess.check_call(["make", "-C", _HERE, "refgeom"], stdout=subprocess.DEVNULL)
     cu_so = os.path.join(_HERE, "_ref", "libref_cuda_fast.so")
     cu_shim = os.path.join(_HERE, "ref_shim", "ref_cuda.cu")
     if os.path.isdir("/root/reference/libs/eval") and (force or not os.path.exists(cu_so)
@@ -113,6 +118,30 @@ def lib():
     L.orc_sample_proxy_cloud.argtypes = [_f32p, _u32p, u32, f32, _opt(_f32p), _opt(_f32p), u32]
     _LIB = L
     return L
+
+
+_REFGEOM = None
+
+
+def refgeom():
+    """The reference's own libs/geom + libs/util writers (None when oracle/_ref/libref_geom.so was not built)."""
+    global _REFGEOM
+    if _REFGEOM is not None:
+        return _REFGEOM or None
+    path = os.path.join(_HERE, "_ref", "libref_geom.so")
+    if not os.path.exists(path):
+        _REFGEOM = False
+        return None
+    R = C.CDLL(path)
+    u32, i32, f32 = C.c_uint32, C.c_int, C.c_float
+    R.ref_sphere_vertices.restype = u32
+    R.ref_sphere_vertices.argtypes = [f32, u32, _opt(_f32p), u32]
+    R.ref_save_numpy_f32.argtypes = [C.c_char_p, _f32p, u32, u32]
+    R.ref_save_numpy_i32.argtypes = [C.c_char_p, np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS"), u32, u32]
+    R.ref_save_volume.argtypes = [C.c_char_p, u32, u32, u32, _f32p, _f32p, u32, _u32p, i32, i32, i32, _f32p]
+    R.ref_load_volume.argtypes = [C.c_char_p, _u32p, _f32p, _f32p, C.POINTER(u32), _u32p, u32, _f32p, C.c_uint64]
+    _REFGEOM = R
+    return R
 
 
 def set_threads(n=0):

@@ -27,6 +27,7 @@ public:
     Vector() {}
     explicit Vector(T const & fill) { for (int i = 0; i < N; ++i) v[i] = fill; }
     Vector(T const & x, T const & y, T const & z) { static_assert(N == 3, ""); v[0] = x; v[1] = y; v[2] = z; }
+    Vector(T const & x, T const & y) { static_assert(N == 2, ""); v[0] = x; v[1] = y; }
     explicit Vector(T const * ptr) { for (int i = 0; i < N; ++i) v[i] = ptr[i]; }
 
     T & operator[](int i) { return v[i]; }
@@ -60,7 +61,22 @@ public:
     Vector & operator-=(Vector const & o) { for (int i = 0; i < N; ++i) v[i] -= o.v[i]; return *this; }
     Vector & operator*=(T const & s) { for (int i = 0; i < N; ++i) v[i] *= s; return *this; }
     Vector & operator/=(T const & s) { for (int i = 0; i < N; ++i) v[i] /= s; return *this; }
+
+    /* used by libs/geom (sphere.h, volume.h): MVE's normalized() = *this / norm(), component-wise products / quotients,
+     * converting constructor */
+    Vector normalized() const { return *this / norm(); }
+    Vector cw_mult(Vector const & o) const { Vector r; for (int i = 0; i < N; ++i) r.v[i] = v[i] * o.v[i]; return r; }
+    Vector cw_div(Vector const & o) const { Vector r; for (int i = 0; i < N; ++i) r.v[i] = v[i] / o.v[i]; return r; }
+    template <typename O> explicit Vector(Vector<O, N> const & o) { for (int i = 0; i < N; ++i) v[i] = T(o[i]); }
 };
+
+/* MVE prints a vector as its components separated by single spaces (math/vector.h, operator<<) */
+template <typename T, int N, typename Stream>
+inline Stream & operator<<(Stream & os, Vector<T, N> const & a) {
+    for (int i = 0; i < N - 1; ++i) os << a.v[i] << " ";
+    os << a.v[N - 1];
+    return os;
+}
 
 template <typename T, int N>
 inline Vector<T, N> operator*(T const & s, Vector<T, N> const & a) {
@@ -69,7 +85,9 @@ inline Vector<T, N> operator*(T const & s, Vector<T, N> const & a) {
     return r;
 }
 
+typedef Vector<float, 2> Vec2f;
 typedef Vector<float, 3> Vec3f;
+typedef Vector<float, 4> Vec4f;
 typedef Vector<unsigned int, 3> Vec3ui;
 
 }  // namespace math

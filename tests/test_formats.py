@@ -1,5 +1,6 @@
 """File formats either side of the path (uavmvs_b200/formats.py): round trips, the header arithmetic of
 libs/util/numpy_io.h, the bundled reference mesh, and a file-driven evaluation equal to the array-driven one."""
+import ctypes as C
 import os
 
 import numpy as np
@@ -94,3 +95,61 @@ def test_bundled_sphere_fixture_is_the_reference_mesh():
     if os.path.exists(REF_PLY):                                       # build container only
         d = F.load_ply(REF_PLY)
         assert np.array_equal(d["vertices"], g["vertices"]) and np.array_equal(d["faces"], g["faces"])
+
+
+def _geom_inputs():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_geom", os.path.join(os.path.dirname(__file__), "golden", "make_golden_geom.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.inputs()
+
+
+def test_writers_equal_the_reference_bytes(tmp_path):
+    """.npy (libs/util/numpy_io.h:59-102) and VOL (libs/geom/volume_io.h:22-47) files byte for byte against what the
+    reference's own writers produced (tests/golden/ref_geom.npz, made by oracle/_ref/libref_geom.so), and live against
+    that library when it is present."""
+    from uavmvs_b200 import formats
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_geom.npz"))
+    f3, i1, (w, h, d, vmin, vmax, idx, imgs) = _geom_inputs()
+    p = str(tmp_path / "a.npy")
+    formats.save_numpy_file(p, f3[0], f3[1], f3[2])
+    assert open(p, "rb").read() == g["npy_f32x3"].tobytes()
+    assert np.array_equal(np.load(p), f3)                              # and numpy reads the reference's layout
+    formats.save_numpy_file(p, i1[0])
+    assert open(p, "rb").read() == g["npy_i32x1"].tobytes()
+    pv = str(tmp_path / "a.vol")
+    formats.save_volume(pv, w, h, d, vmin, vmax, {int(i): imgs[k] for k, i in enumerate(idx)})
+    assert open(pv, "rb").read() == g["vol"].tobytes()
+    W, H, D, mn, mx, images = formats.load_volume(pv)
+    assert (W, H, D) == (w, h, d) and sorted(images) == [int(i) for i in idx]
+    assert all(np.array_equal(images[int(i)], imgs[k]) for k, i in enumerate(idx))
+    import oracle
+    R = oracle.refgeom()
+    if R is not None:                                                  # live: the reference's loader reads OUR file
+        dims, rmn, rmx = np.zeros(3, np.uint32), np.zeros(3, np.float32), np.zeros(3, np.float32)
+        n = C.c_uint32(0)
+        ridx, rdata = np.zeros(8, np.uint32), np.zeros(imgs.size, np.float32)
+        assert R.ref_load_volume(pv.encode(), dims, rmn, rmx, C.byref(n), ridx, 8, rdata, rdata.size) == 0
+        assert list(dims) == [w, h, d] and n.value == len(idx) and np.array_equal(ridx[:n.value], idx)
+        assert np.array_equal(rdata, imgs.reshape(-1))
+        assert np.allclose(rmn, vmin, rtol=1e-5) and np.allclose(rmx, vmax, rtol=1e-5)   # six significant digits survive the text header
+
+
+def test_sphere_vertices_equal_the_reference():
+    """The 1272-vertex direction set: product (uavmvs_sphere_vertices) == oracle restatement == the reference's own
+    generate_sphere_mesh(1.0f, 3u) (golden fixture; live when oracle/_ref/libref_geom.so is present)."""
+    import oracle
+    from uavmvs_b200 import api
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_geom.npz"))
+    ref = g["sphere"]
+    assert ref.shape == (1272, 3) and np.unique(ref, axis=0).shape[0] == 642
+    assert np.array_equal(oracle.sphere_vertices(1.0, 3).view(np.uint32), ref.view(np.uint32))
+    assert np.array_equal(api.sphere_vertices(1.0, 3).view(np.uint32), ref.view(np.uint32))
+    R = oracle.refgeom()
+    if R is not None:
+        live = np.zeros((2048, 3), np.float32)
+        n = R.ref_sphere_vertices(1.0, 3, live, 2048)
+        assert n in (0, 1272)                                          # 0: generate_sphere_mesh only works once per process
+        if n:
+            assert np.array_equal(live[:n].view(np.uint32), ref.view(np.uint32))

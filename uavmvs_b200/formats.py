@@ -237,7 +237,8 @@ def save_volume(path, width, height, depth, minimum, maximum, images):
     """libs/geom/volume_io.h:22-46.  images: dict linear index -> float32 array [h, w] or [h, w, c]."""
     with open(path, "wb") as f:
         f.write(b"VOL 0.1\n%d %d %d \n" % (width, height, depth))
-        f.write((" ".join(repr(float(x)) for x in minimum) + " " + " ".join(repr(float(x)) for x in maximum)).encode())
+        # `out << float` in the C++ default format (precision 6, %g); MVE prints a vector as "x y z" (volume_io.h:34)
+        f.write((" ".join("%g" % float(np.float32(x)) for x in minimum) + " " + " ".join("%g" % float(np.float32(x)) for x in maximum)).encode())
         for i in sorted(images):
             img = np.asarray(images[i], np.float32)
             if img.ndim == 2:
