@@ -21,7 +21,8 @@
  * print "file:line (call): message" and exit (libs/cacc/defines.h:20-29).
  *
  * Host-side inputs are plain arrays (the acc tree's nodes/aabbs/tris/indices, exactly what
- * cacc::BVHTree<HOST>::convert produces, libs/cacc/bvh_tree.cu:17-48); no MVE types appear.
+ * cacc::BVHTree<HOST>::convert produces, libs/cacc/bvh_tree.cu:17-48) or, when "acc/bvh_tree.h" / "acc/kd_tree.h" were
+ * included first, the acc trees themselves through the reference's own create<...>(tree) calls.
  * Plain C++11, no CUDA headers needed by the caller.
  */
 #ifndef UAVMVS_B200_CACC_HPP
@@ -41,6 +42,57 @@
             std::exit(EXIT_FAILURE);                                                        \
         }                                                                                   \
     } while (0)
+
+/* ---- construction from the reference's own host trees ------------------------------------------------------------
+ * When the application has included the reference's libs/acc headers BEFORE this one ("acc/bvh_tree.h",
+ * "acc/kd_tree.h"), the original factory calls keep working unchanged:
+ *     cacc::BVHTree<cacc::DEVICE>::create<uint, math::Vec3f>(bvh_tree)      (libs/cacc/bvh_tree.h:190-194)
+ *     cacc::KDTree<3, cacc::DEVICE>::create<uint>(kd_tree)                  (libs/cacc/kd_tree.h:150-154)
+ * acc declares `template <class C> static C convert(tree)` and leaves the definition to the consumer; the reference
+ * specialises it in libs/cacc/bvh_tree.cu:17-48 and libs/cacc/kd_tree.cu:15-36 for <unsigned int, math::Vec3f>.  The two
+ * specialisations below do the same job for a plain-array target, so no .cu file of the reference has to be linked. */
+#if defined(ACC_BVHTREE_HEADER) || defined(ACC_KDTREE_HEADER)
+namespace uavmvs_b200 {
+struct HostTree { std::vector<uint32_t> nodes, indices; std::vector<float> aabbs, tris; };
+struct HostKd { std::vector<uint32_t> nodes; std::vector<float> verts; };
+}
+#endif
+#ifdef ACC_BVHTREE_HEADER
+ACC_NAMESPACE_BEGIN
+template <> template <> inline uavmvs_b200::HostTree
+BVHTree<unsigned int, math::Vec3f>::convert<uavmvs_b200::HostTree>(BVHTree<unsigned int, math::Vec3f> const & tree) {
+    uavmvs_b200::HostTree h;
+    const std::size_t n = tree.num_nodes, t = tree.tris.size();
+    h.nodes.resize(4 * n); h.aabbs.resize(6 * n); h.tris.resize(9 * t); h.indices.resize(t);
+    for (std::size_t i = 0; i < n; ++i) {
+        Node const & nd = tree.nodes[i];
+        h.nodes[4 * i] = nd.first; h.nodes[4 * i + 1] = nd.last; h.nodes[4 * i + 2] = nd.left; h.nodes[4 * i + 3] = nd.right;
+        for (int k = 0; k < 3; ++k) { h.aabbs[6 * i + k] = nd.aabb.min[k]; h.aabbs[6 * i + 3 + k] = nd.aabb.max[k]; }
+    }
+    for (std::size_t i = 0; i < t; ++i) {
+        h.indices[i] = tree.indices[i];
+        for (int k = 0; k < 3; ++k) { h.tris[9 * i + k] = tree.tris[i].a[k]; h.tris[9 * i + 3 + k] = tree.tris[i].b[k]; h.tris[9 * i + 6 + k] = tree.tris[i].c[k]; }
+    }
+    return h;
+}
+ACC_NAMESPACE_END
+#endif
+#ifdef ACC_KDTREE_HEADER
+ACC_NAMESPACE_BEGIN
+template <> template <> inline uavmvs_b200::HostKd
+KDTree<3u, unsigned int>::convert<uavmvs_b200::HostKd>(KDTree<3u, unsigned int> const & tree) {
+    uavmvs_b200::HostKd h;
+    const std::size_t n = tree.num_nodes;
+    h.nodes.resize(4 * n); h.verts.resize(3 * n);
+    for (std::size_t i = 0; i < n; ++i) {
+        h.nodes[4 * i] = tree.nodes[i].vertex_id; h.nodes[4 * i + 1] = tree.nodes[i].d;
+        h.nodes[4 * i + 2] = tree.nodes[i].left; h.nodes[4 * i + 3] = tree.nodes[i].right;
+        for (int k = 0; k < 3; ++k) h.verts[3 * i + k] = tree.vertices[i][k];
+    }
+    return h;
+}
+ACC_NAMESPACE_END
+#endif
 
 namespace cacc {
 
@@ -74,6 +126,15 @@ public:
         UAVMVS_CHECK(uavmvs_bvh_build_sah(verts, num_verts, faces, num_faces, &p->h));
         return p;
     }
+#ifdef ACC_BVHTREE_HEADER
+    /* cacc::BVHTree<DEVICE>::create<IdxType, Vec3fType>(acc_tree), libs/cacc/bvh_tree.h:190-194 + bvh_tree.cu:54-57 */
+    template <typename IdxType, typename Vec3fType>
+    static Ptr create(typename acc::BVHTree<IdxType, Vec3fType>::ConstPtr tree) {
+        uavmvs_b200::HostTree t = acc::BVHTree<IdxType, Vec3fType>::template convert<uavmvs_b200::HostTree>(*tree);
+        return create(t.nodes.data(), t.aabbs.data(), t.tris.data(), t.indices.data(), (uint32_t)(t.nodes.size() / 4),
+            (uint32_t)t.indices.size());
+    }
+#endif
     Accessor accessor() const { Accessor a = {h}; return a; }
     ~BVHTree() { uavmvs_bvh_destroy(h); }
 private:
@@ -91,6 +152,14 @@ public:
         UAVMVS_CHECK(uavmvs_kdtree_create(nodes, verts, num_nodes, &p->h));
         return p;
     }
+#ifdef ACC_KDTREE_HEADER
+    /* cacc::KDTree<3, DEVICE>::create<IdxType>(acc_kd_tree), libs/cacc/kd_tree.h:150-154 + kd_tree.cu:42-45 */
+    template <typename IdxType>
+    static Ptr create(typename acc::KDTree<3u, IdxType>::ConstPtr tree) {
+        uavmvs_b200::HostKd t = acc::KDTree<3u, IdxType>::template convert<uavmvs_b200::HostKd>(*tree);
+        return create(t.nodes.data(), t.verts.data(), (uint32_t)(t.nodes.size() / 4));
+    }
+#endif
     Accessor accessor() const { Accessor a = {h}; return a; }
     ~KDTree() { uavmvs_kdtree_destroy(h); }
 private:

@@ -48,6 +48,13 @@ def build(force=False):
     if os.path.isdir("/root/reference/libs/geom") and (force or not os.path.exists(geom_so)
                                                         or os.path.getmtime(geom_so) < os.path.getmtime(geom_shim)):
         subprocess.check_call(["make", "-C", _HERE, "refgeom"], stdout=subprocess.DEVNULL)
+    demo = os.path.join(_HERE, "_ref", "acc_tree_facade")
+    demo_src = os.path.join(_HERE, "..", "tests", "cpp", "acc_tree_facade.cpp")
+    facade = os.path.join(_HERE, "..", "include", "uavmvs_b200", "cacc.hpp")
+    product = os.path.join(_HERE, "..", "uavmvs_b200", "libuavmvs_b200.so")
+    if os.path.isdir("/root/reference/libs/acc") and os.path.exists(product) and os.path.exists(demo_src) and (
+            force or not os.path.exists(demo) or os.path.getmtime(demo) < max(os.path.getmtime(demo_src), os.path.getmtime(facade))):
+        subprocess.check_call(["make", "-C", _HERE, "accdemo"], stdout=subprocess.DEVNULL)
     cu_so = os.path.join(_HERE, "_ref", "libref_cuda_fast.so")
     cu_shim = os.path.join(_HERE, "ref_shim", "ref_cuda.cu")
     if os.path.isdir("/root/reference/libs/eval") and (force or not os.path.exists(cu_so)

@@ -93,3 +93,25 @@ def test_facade_optimizer_inner_loop(tmp_path, oracle, tiny_scene, tiny_tree):
         scale = 16.0 * max(int((bins != 0xFFFFFFFF).sum()), 1)
         assert abs(best[c, 0] - float(img.min())) <= 1e-5 * scale + 1e-9
         assert 0 <= int(best[c, 1]) < 128 * 45
+
+
+ACC_DEMO = os.path.join(ROOT, "oracle", "_ref", "acc_tree_facade")
+
+
+def test_facade_accepts_the_reference_acc_trees_compile(oracle):
+    """cacc::BVHTree<DEVICE>::create<uint, math::Vec3f>(acc_tree) and cacc::KDTree<3, DEVICE>::create<uint>(acc_kd)
+    (libs/cacc/bvh_tree.h:190-194, kd_tree.h:150-154) through the facade: tests/cpp/acc_tree_facade.cpp includes the
+    reference's own acc headers and compiles -Wall -Werror where the reference is present (oracle.build())."""
+    if not os.path.isdir("/root/reference/libs/acc"):
+        pytest.skip("the reference checkout is not on this machine")
+    assert os.path.exists(ACC_DEMO)
+
+
+@pytest.mark.gpu
+def test_facade_accepts_the_reference_acc_trees_run():
+    """The prebuilt demo (it travels in oracle/_ref/): acc-built trees uploaded through the original create<...>() calls;
+    20 000 closest-hit rays and nearest-neighbour queries on the device equal acc's own CPU answers bit for bit."""
+    if not os.path.exists(ACC_DEMO):
+        pytest.skip("oracle/_ref/acc_tree_facade was not built (no reference checkout at build time)")
+    out = subprocess.run([ACC_DEMO], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout + out.stderr
