@@ -118,11 +118,10 @@ struct uavmvs_kdtree {
     float4 * fast_pos = nullptr;        // [m] xyz, w = half the certified radius
     uint4 * fast_rule = nullptr;        // [m] {vertex id A, vertex id B, dim (3 = always A), coordinate bits}
     uint16_t * fast_nbr = nullptr;      // [m][8] neighbouring distinct positions, 0xffff = none
-    // (host threads sharing the handle: looked up / rebuilt under fr_mutex; a replaced matrix stays allocated until
-    // destroy or until 8 have piled up, since kernels of other threads may still read it)
-    std::mutex fr_mutex; std::vector<uint32_t *> fr_old;
-    uint32_t * fr_bits = nullptr;   // [words][pixels], words = ceil(num_nodes / 32)
-    float fr_calib[9] = {0}; int fr_w = 0, fr_h = 0; uint32_t fr_iw = 0, fr_ih = 0;
+    // (host threads sharing the handle: looked up / added under fr_mutex; one entry per (calib, width, height, image
+    // size), every entry stays allocated until destroy since kernels of other threads may be reading it)
+    struct FrustumBits { float calib[9]; int w, h; uint32_t iw, ih; uint32_t * bits; };   // bits: [words][pixels]
+    std::mutex fr_mutex; std::vector<FrustumBits> fr_cache;
 };
 
 struct uavmvs_cloud {

@@ -338,8 +338,8 @@ int uavmvs_kdtree_create(const uint32_t * nodes, const float * verts, uint32_t n
 int uavmvs_kdtree_destroy(uavmvs_kdtree * k)
 {
     if (!k) return 0;
-    cudaFree(k->nodes); cudaFree(k->verts); cudaFree(k->fr_bits);
-    for (uint32_t * p : k->fr_old) cudaFree(p);
+    cudaFree(k->nodes); cudaFree(k->verts);
+    for (const uavmvs_kdtree::FrustumBits & e : k->fr_cache) cudaFree(e.bits);
     cudaFree(k->fast_table); cudaFree(k->fast_pos); cudaFree(k->fast_rule); cudaFree(k->fast_nbr);
     delete k;
     return 0;

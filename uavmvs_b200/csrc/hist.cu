@@ -374,28 +374,24 @@ static int frustum_bits(uavmvs_kdtree * kd, const float calib[9], int width, int
 {
     std::lock_guard<std::mutex> lock(kd->fr_mutex);
     const uint32_t npix = image_width * image_height, words = (kd->num_nodes + 31) / 32;
-    bool same = kd->fr_bits && kd->fr_w == width && kd->fr_h == height && kd->fr_iw == image_width && kd->fr_ih == image_height
-        && memcmp(kd->fr_calib, calib, 9 * sizeof(float)) == 0;
-    if (!same) {
-        float * d_K;
-        if (kd->fr_bits) kd->fr_old.push_back(kd->fr_bits);
-        kd->fr_bits = nullptr;
-        if (kd->fr_old.size() > 8) {                       // callers alternating calibrations: drain the device, then free
-            UAV_CUDA(cudaDeviceSynchronize());
-            for (uint32_t * p : kd->fr_old) cudaFree(p);
-            kd->fr_old.clear();
+    for (const uavmvs_kdtree::FrustumBits & e : kd->fr_cache)
+        if (e.w == width && e.h == height && e.iw == image_width && e.ih == image_height && memcmp(e.calib, calib, 9 * sizeof(float)) == 0) {
+            *out = e.bits;
+            return 0;
         }
-        UAV_CUDA(cudaMalloc(&kd->fr_bits, sizeof(uint32_t) * (size_t)words * npix));
-        UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
-        UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
-        k_frustum_bits<<<divup(npix, 128), 128, 0, uav::counted(s)>>>(d_K, width, height, kd_view(kd), image_width, image_height, kd->fr_bits);
-        UAV_CUDA(cudaGetLastError());
-        UAV_CUDA(cudaStreamSynchronize(s));                // other streams may use the matrix as soon as the lock drops
-        UAV_CUDA(cudaFree(d_K));
-        memcpy(kd->fr_calib, calib, 9 * sizeof(float)); kd->fr_w = width; kd->fr_h = height;
-        kd->fr_iw = image_width; kd->fr_ih = image_height;
-    }
-    *out = kd->fr_bits;
+    UAV_REQUIRE(kd->fr_cache.size() < 256, "more than 256 distinct (calibration, image size) combinations on one KD-tree handle");
+    uavmvs_kdtree::FrustumBits e;
+    memcpy(e.calib, calib, 9 * sizeof(float)); e.w = width; e.h = height; e.iw = image_width; e.ih = image_height; e.bits = nullptr;
+    float * d_K = nullptr;
+    UAV_CUDA(cudaMalloc(&e.bits, sizeof(uint32_t) * (size_t)words * npix));
+    UAV_CUDA(cudaMalloc(&d_K, 9 * sizeof(float)));
+    UAV_CUDA(cudaMemcpy(d_K, calib, 9 * sizeof(float), cudaMemcpyHostToDevice));
+    k_frustum_bits<<<divup(npix, 128), 128, 0, uav::counted(s)>>>(d_K, width, height, kd_view(kd), image_width, image_height, e.bits);
+    UAV_CUDA(cudaGetLastError());
+    UAV_CUDA(cudaStreamSynchronize(s));                    // other streams may use the matrix as soon as the lock drops
+    UAV_CUDA(cudaFree(d_K));
+    kd->fr_cache.push_back(e);
+    *out = e.bits;
     return 0;
 }
 
