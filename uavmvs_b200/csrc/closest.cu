@@ -102,6 +102,16 @@ k_closest_point(BvhView bvh, const float * __restrict__ points, uint32_t n, floa
 
 using namespace uav;
 
+int uav::launch_closest_point(cudaStream_t s, const uavmvs_bvh * bvh, const float * d_points, uint32_t n, float max_dist,
+    uint8_t * d_found, uint32_t * d_tri_index, float * d_closest)
+{
+    UAV_REQUIRE(bvh && d_points && d_found && d_tri_index && d_closest, "null argument");
+    if (n == 0) return 0;
+    k_closest_point<<<divup(n, 128), 128, 0, uav::counted(s)>>>(view_of(bvh), d_points, n, max_dist, d_found, d_tri_index, d_closest);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int uavmvs_bvh_closest_point(void * stream, const uavmvs_bvh * bvh, const float * points, uint64_t num_points,
     float max_dist, uint8_t * found, uint32_t * tri_index, float * closest)
 {

@@ -224,6 +224,10 @@ struct HistJob {
     Heur heur;
     // order-independent accumulation (k1.cu:k_retire_hist): fixed-point accumulators [views][kd_n] and fx = {scale, bound}
     unsigned long long * acc; const float * fx;
+    // 1: size the ray buffers for the worst case (every block a candidate of every position) instead of reading the
+    // bound back from the device -- no host synchronisation at all; used by the device-resident optimiser step (nm.cu),
+    // whose batches are a few dozen positions
+    int no_readback;
 };
 
 // K1 pipeline (k1.cu).  d_stats (device, may be null): [0] += occlusion rays, [1] += visible
@@ -234,6 +238,19 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
 int k1_counters(unsigned long long out[4], int reset);
 int k1_profile_enable(int on);
 int k1_profile(float ms[5]);
+
+// closest.cu: acc::BVHTree::closest_point for n DEVICE queries [n][3] -> device found / leaf-order triangle index / point
+int launch_closest_point(cudaStream_t s, const uavmvs_bvh * bvh, const float * d_points, uint32_t n, float max_dist,
+    uint8_t * d_found, uint32_t * d_tri_index, float * d_closest);
+// hist.cu: batched K4 / K5 for DEVICE positions [n][3]; batched K6 leaving the packed extrema on the device
+int populate_hist_batch_device(cudaStream_t s, const float * d_positions, uint32_t num_positions, float max_distance,
+    float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd, const uavmvs_obs * obs,
+    const uavmvs_array * recons, float * d_sphere_hists, int no_readback);
+// d_best: [2 * num_positions] packed keys (min keys, then max keys; see k_evaluate_spherical_histogram_batch), initialised
+// here; d_weights: NULL or one factor per position applied to every pixel before the comparison
+int evaluate_hist_batch_device(cudaStream_t s, const float calib[9], int width, int height, uavmvs_kdtree * kd,
+    const float * d_sphere_hists, uint32_t num_positions, uint32_t image_width, uint32_t image_height, float * d_images,
+    const float * d_weights, unsigned long long * d_best);
 
 // comm.cu: NCCL collectives on a stream (f64 != 0: doubles, else floats; counts in elements per rank)
 int comm_allgather(cudaStream_t s, uavmvs_comm * c, const void * send, void * recv, size_t count, int f64);

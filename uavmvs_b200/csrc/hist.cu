@@ -248,7 +248,7 @@ __device__ __forceinline__ uint32_t f2ord(float f) { uint32_t u = __float_as_uin
 __global__ void __launch_bounds__(EVB_THREADS)
 k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_t words, uint32_t npix,
     const float * __restrict__ sphere_hists, uint32_t S, float * __restrict__ images,
-    unsigned long long * __restrict__ best_min, unsigned long long * __restrict__ best_max)
+    unsigned long long * __restrict__ best_min, unsigned long long * __restrict__ best_max, const float * __restrict__ weights)
 {
     extern __shared__ float s_h[];
     __shared__ float s_v[2][EVB_THREADS / 32]; __shared__ uint32_t s_i[2][EVB_THREADS / 32];
@@ -258,6 +258,7 @@ k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_
     for (uint32_t i = threadIdx.x; i < words * 32; i += EVB_THREADS) s_h[i] = i < S ? sphere_hists[(size_t)b * S + i] : 0.0f;
     __syncthreads();
     float vmin = UAV_INF, vmax = -UAV_INF; uint32_t imin = UAV_NAI, imax = UAV_NAI;
+    const float wgt = weights ? __ldg(weights + b) : 1.0f;
     for (uint32_t pix = p0 + threadIdx.x; pix < p1; pix += EVB_THREADS) {
         float sum = 0.0f;
         for (uint32_t wd = 0; wd < words; ++wd) {
@@ -265,6 +266,7 @@ k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_
             while (m) { const uint32_t k = __ffs(m) - 1; m &= m - 1; sum += s_h[wd * 32 + k]; }
         }
         if (images) images[(size_t)b * npix + pix] = sum;
+        if (weights) sum = wgt * sum;                        // the optimiser's `w * data` (optimize_trajectory.cu:417)
         if (sum < vmin) { vmin = sum; imin = pix; }          // pixels ascend per thread: first occurrence
         if (sum > vmax) { vmax = sum; imax = pix; }
     }
@@ -396,6 +398,76 @@ static int frustum_bits(uavmvs_kdtree * kd, const float calib[9], int width, int
 }
 
 
+int populate_hist_batch_device(cudaStream_t s, const float * d_pos, uint32_t num_positions, float max_distance,
+    float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud, const uavmvs_kdtree * kd, const uavmvs_obs * obs,
+    const uavmvs_array * recons, float * d_sphere_hists, int no_readback)
+{
+    UAV_REQUIRE(d_pos && bvh && cloud && kd && d_sphere_hists, "null argument");
+    UAV_REQUIRE((obs == nullptr) == (recons == nullptr), "obs and recons go together (both NULL: K4, both set: K5)");
+    if (num_positions == 0) return 0;
+    HistJob hj;
+    hj.kd_nodes = kd->nodes; hj.kd_verts = kd->verts; hj.kd_n = kd->num_nodes;
+    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;      // built at create; a no-op here
+    hj.kd_fast = kd_fast_view(kd);
+    hj.values = cloud->values; hj.qualities = cloud->qualities;
+    hj.with_recon = obs ? 1 : 0; hj.target_recon = target_recon;
+    hj.obs = nullptr; hj.num_rows = nullptr; hj.max_rows = 0; hj.stride = 0; hj.recons = nullptr;
+    if (obs) {
+        UAV_REQUIRE(obs->num_cols == cloud->n && recons->n == cloud->n, "size mismatch");
+        hj.obs = obs->data; hj.num_rows = obs->num_rows; hj.max_rows = obs->max_rows;
+        hj.stride = (uint32_t)(obs->pitch / sizeof(float4)); hj.recons = recons->data;
+    }
+    hj.hist = d_sphere_hists; hj.heur = heur_of(obs); hj.no_readback = no_readback;
+    const size_t cells = (size_t)num_positions * kd->num_nodes;
+    UAV_REQUIRE(cells < 0xffffff00ull, "positions x bins does not fit the 32-bit accumulator key");
+    UAV_REQUIRE(cloud->n < (1u << 26), "more than 2^26 points per call (fixed-point head room)");
+    unsigned long long * d_acc = nullptr; float * d_fx = nullptr, * d_views = nullptr;
+    UAV_CUDA(cudaMallocAsync(&d_acc, sizeof(unsigned long long) * cells, s));
+    UAV_CUDA(cudaMallocAsync(&d_fx, 2 * sizeof(float), s));
+    UAV_CUDA(cudaMallocAsync(&d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_positions, s));
+    UAV_CUDA(cudaMemsetAsync(d_acc, 0, sizeof(unsigned long long) * cells, s));
+    if (obs) {
+        const float t1 = fabsf(target_recon) + 1.0f;
+        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 4.0f * t1 * t1);
+    } else {
+        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 0.0f);
+        k_fx_max_quality<<<min(divup(cloud->n, 256 * 8), 1024u), 256, 0, uav::counted(s)>>>(cloud->qualities, cloud->n, d_fx);
+    }
+    k_fx_scale<<<1, 1, 0, uav::counted(s)>>>(d_fx);
+    hj.acc = d_acc; hj.fx = d_fx;
+    k_fill_positions<<<divup(num_positions, 256), 256, 0, uav::counted(s)>>>(d_pos, num_positions, d_views);
+    UAV_CUDA(cudaGetLastError());
+    int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
+    if (!rc) {
+        k_hist_finish<<<divup(cells, 256), 256, 0, uav::counted(s)>>>(d_acc, d_sphere_hists, cells, d_fx);
+        if (cudaGetLastError() != cudaSuccess) rc = 1;
+    }
+    cudaFreeAsync(d_views, s); cudaFreeAsync(d_acc, s); cudaFreeAsync(d_fx, s);
+    return rc;
+}
+
+int evaluate_hist_batch_device(cudaStream_t s, const float calib[9], int width, int height, uavmvs_kdtree * kd,
+    const float * d_sphere_hists, uint32_t num_positions, uint32_t image_width, uint32_t image_height, float * d_images,
+    const float * d_weights, unsigned long long * d_best)
+{
+    UAV_REQUIRE(calib && kd && d_sphere_hists && d_best, "null argument");
+    UAV_REQUIRE(image_width >= 1 && image_height >= 1, "empty image");
+    const uint32_t npix = image_width * image_height, S = kd->num_nodes, words = (S + 31) / 32;
+    UAV_REQUIRE(words * 32 * sizeof(float) <= 48 * 1024, "sphere histogram does not fit shared memory");
+    if (num_positions == 0) return 0;
+    const uint32_t * bits = nullptr;
+    if (frustum_bits(kd, calib, width, height, image_width, image_height, s, &bits)) return 1;
+    // pixel parts: enough CTAs for ~8 per SM when the batch is small; every thread keeps at least one pixel
+    uint32_t parts = divup(148u * 8u, num_positions);
+    parts = max(1u, min(parts, max(1u, npix / EVB_THREADS)));
+    UAV_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)num_positions, s));
+    UAV_CUDA(cudaMemsetAsync(d_best + num_positions, 0, sizeof(unsigned long long) * (size_t)num_positions, s));
+    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
+        d_sphere_hists, S, d_images, d_best, d_best + num_positions, d_weights);
+    UAV_CUDA(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace uav
 
 using namespace uav;
@@ -435,7 +507,7 @@ int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int
         UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long), s));
         const uint32_t parts = max(1u, npix / EVB_THREADS);
         k_evaluate_spherical_histogram_batch<<<dim3(1, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
-            sphere_hist->data, S, hist->data, d_best, d_best + 1);
+            sphere_hist->data, S, hist->data, d_best, d_best + 1, nullptr);
         UAV_CUDA(cudaGetLastError());
         UAV_CUDA(cudaFreeAsync(d_best, s));
         return 0;
@@ -466,53 +538,16 @@ int uavmvs_populate_spherical_histogram_batch(void * stream, const float * posit
     float max_distance, float target_recon, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
     const uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons, uavmvs_array * sphere_hists)
 {
-    UAV_REQUIRE(positions && bvh && cloud && kd && sphere_hists, "null argument");
-    UAV_REQUIRE((obs == nullptr) == (recons == nullptr), "obs and recons go together (both NULL: K4, both set: K5)");
+    UAV_REQUIRE(positions && kd && sphere_hists, "null argument");
     UAV_REQUIRE((uint64_t)sphere_hists->n >= (uint64_t)num_positions * kd->num_nodes, "sphere_hists smaller than [positions][bins]");
     if (num_positions == 0) return 0;
     cudaStream_t s = (cudaStream_t)stream;
-    HistJob hj;
-    hj.kd_nodes = kd->nodes; hj.kd_verts = kd->verts; hj.kd_n = kd->num_nodes;
-    if (kd_fast_ensure(const_cast<uavmvs_kdtree *>(kd))) return 1;      // built at create; a no-op here
-    hj.kd_fast = kd_fast_view(kd);
-    hj.values = cloud->values; hj.qualities = cloud->qualities;
-    hj.with_recon = obs ? 1 : 0; hj.target_recon = target_recon;
-    hj.obs = nullptr; hj.num_rows = nullptr; hj.max_rows = 0; hj.stride = 0; hj.recons = nullptr;
-    if (obs) {
-        UAV_REQUIRE(obs->num_cols == cloud->n && recons->n == cloud->n, "size mismatch");
-        hj.obs = obs->data; hj.num_rows = obs->num_rows; hj.max_rows = obs->max_rows;
-        hj.stride = (uint32_t)(obs->pitch / sizeof(float4)); hj.recons = recons->data;
-    }
-    hj.hist = sphere_hists->data; hj.heur = heur_of(obs);
-    const size_t cells = (size_t)num_positions * kd->num_nodes;
-    UAV_REQUIRE(cells < 0xffffff00ull, "positions x bins does not fit the 32-bit accumulator key");
-    UAV_REQUIRE(cloud->n < (1u << 26), "more than 2^26 points per call (fixed-point head room)");
-    unsigned long long * d_acc = nullptr; float * d_fx = nullptr;
-    UAV_CUDA(cudaMallocAsync(&d_acc, sizeof(unsigned long long) * cells, s));
-    UAV_CUDA(cudaMallocAsync(&d_fx, 2 * sizeof(float), s));
-    UAV_CUDA(cudaMemsetAsync(d_acc, 0, sizeof(unsigned long long) * cells, s));
-    if (obs) {
-        const float t1 = fabsf(target_recon) + 1.0f;
-        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 4.0f * t1 * t1);
-    } else {
-        k_fx_init<<<1, 1, 0, uav::counted(s)>>>(d_fx, 0.0f);
-        k_fx_max_quality<<<min(divup(cloud->n, 256 * 8), 1024u), 256, 0, uav::counted(s)>>>(cloud->qualities, cloud->n, d_fx);
-    }
-    k_fx_scale<<<1, 1, 0, uav::counted(s)>>>(d_fx);
-    UAV_CUDA(cudaGetLastError());
-    hj.acc = d_acc; hj.fx = d_fx;
-    float * d_pos = nullptr, * d_views = nullptr;
+    float * d_pos = nullptr;
     UAV_CUDA(cudaMallocAsync(&d_pos, sizeof(float) * 3 * (size_t)num_positions, s));
-    UAV_CUDA(cudaMallocAsync(&d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_positions, s));
     UAV_CUDA(cudaMemcpyAsync(d_pos, positions, sizeof(float) * 3 * (size_t)num_positions, cudaMemcpyHostToDevice, s));
-    k_fill_positions<<<divup(num_positions, 256), 256, 0, uav::counted(s)>>>(d_pos, num_positions, d_views);
-    UAV_CUDA(cudaGetLastError());
-    int rc = launch_k1(s, 1, d_views, num_positions, max_distance, 0, 0, bvh, cloud, nullptr, nullptr, &hj);
-    if (!rc) {
-        k_hist_finish<<<divup(cells, 256), 256, 0, uav::counted(s)>>>(d_acc, sphere_hists->data, cells, d_fx);
-        if (cudaGetLastError() != cudaSuccess) rc = 1;
-    }
-    cudaFreeAsync(d_pos, s); cudaFreeAsync(d_views, s); cudaFreeAsync(d_acc, s); cudaFreeAsync(d_fx, s);
+    const int rc = populate_hist_batch_device(s, d_pos, num_positions, max_distance, target_recon, bvh, cloud, kd, obs, recons,
+        sphere_hists->data, 0);
+    cudaFreeAsync(d_pos, s);
     return rc;
 }
 
@@ -545,25 +580,15 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
     uint32_t image_height, uavmvs_array * images, float * h_min, uint32_t * h_argmin, float * h_max, uint32_t * h_argmax)
 {
     UAV_REQUIRE(calib && kd && sphere_hists, "null argument");
-    UAV_REQUIRE(image_width >= 1 && image_height >= 1, "empty image");
     UAV_REQUIRE((uint64_t)sphere_hists->n >= (uint64_t)num_positions * kd->num_nodes, "sphere_hists smaller than [positions][bins]");
-    const uint32_t npix = image_width * image_height, S = kd->num_nodes, words = (S + 31) / 32;
+    const uint32_t npix = image_width * image_height;
     UAV_REQUIRE(!images || (uint64_t)images->n >= (uint64_t)num_positions * npix, "images smaller than [positions][h][w]");
-    UAV_REQUIRE(words * 32 * sizeof(float) <= 48 * 1024, "sphere histogram does not fit shared memory");
     if (num_positions == 0) return 0;
     cudaStream_t s = (cudaStream_t)stream;
-    const uint32_t * bits = nullptr;
-    if (frustum_bits(kd, calib, width, height, image_width, image_height, s, &bits)) return 1;
-    // pixel parts: enough CTAs for ~8 per SM when the batch is small; every thread keeps at least one pixel
-    uint32_t parts = divup(148u * 8u, num_positions);
-    parts = max(1u, min(parts, max(1u, npix / EVB_THREADS)));
     unsigned long long * d_best;                      // [min keys | max keys]
     UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long) * (size_t)num_positions, s));
-    UAV_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)num_positions, s));
-    UAV_CUDA(cudaMemsetAsync(d_best + num_positions, 0, sizeof(unsigned long long) * (size_t)num_positions, s));
-    k_evaluate_spherical_histogram_batch<<<dim3(num_positions, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
-        sphere_hists->data, S, images ? images->data : nullptr, d_best, d_best + num_positions);
-    UAV_CUDA(cudaGetLastError());
+    if (int rc = evaluate_hist_batch_device(s, calib, width, height, kd, sphere_hists->data, num_positions, image_width, image_height,
+            images ? images->data : nullptr, nullptr, d_best)) { cudaFreeAsync(d_best, s); return rc; }
     if (h_min || h_argmin || h_max || h_argmax) {
         std::vector<unsigned long long> hb(2 * (size_t)num_positions);
         UAV_CUDA(cudaMemcpyAsync(hb.data(), d_best, sizeof(unsigned long long) * hb.size(), cudaMemcpyDeviceToHost, s));

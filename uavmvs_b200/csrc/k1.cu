@@ -1577,11 +1577,16 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         planned = true; k.plan_views = num_views; k.plan_blocks = nb;
         return 0;
     };
-    if (num_views > 1 && k.plan_views == num_views && k.plan_blocks == nb) { speculate = false; if (make_plan()) return 1; }
+    // histogram jobs of the device-resident optimiser: buffers for the worst case, nothing read back
+    const unsigned long long worst = 32ull * nb * num_views;
+    const bool no_readback = hj && hj->no_readback && worst <= min((unsigned long long)ray_budget(), 1ull << 27);
+    if (no_readback) speculate = false;
+    else if (num_views > 1 && k.plan_views == num_views && k.plan_blocks == nb) { speculate = false; if (make_plan()) return 1; }
     uint32_t v0 = 0;
     while (v0 < num_views) {
         uint32_t v1 = num_views;
         unsigned long long total = 0;
+        if (no_readback) total = worst;
         if (planned) {
             v1 = v0;
             while (v1 < num_views && (v1 == v0 || total + k.h_vcaps[v1] <= ray_budget())) total += k.h_vcaps[v1++];
@@ -1592,7 +1597,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         const bool spec = speculate && !planned;
         speculate = false;                                   // one attempt per call
         const unsigned long long spec_cap = min((unsigned long long)k.rays_cap, min((unsigned long long)ray_budget(), 1ull << 27));
-        if (planned) {
+        if (no_readback) {
+        } else if (planned) {
             if (d_stats && total) k_add_val<<<1, 1, 0, uav::counted(s)>>>(d_stats + 3, total);   // pairs surviving the block-level cull
         } else {
             UAV_CUDA(cudaMemsetAsync(k.total, 0, sizeof(unsigned long long), s));
