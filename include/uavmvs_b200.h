@@ -310,6 +310,26 @@ int uavmvs_evaluate_spherical_histogram_batch(void * stream, const float calib[9
     uavmvs_kdtree * kd, const uavmvs_array * sphere_hists, uint32_t num_positions, uint32_t image_width,
     uint32_t image_height, uavmvs_array * images, float * h_min, uint32_t * h_argmin, float * h_max, uint32_t * h_argmax);
 
+/* ---- One Nelder-Mead step of the optimiser for a batch of views, on the device: libs/opti/nelder_mead.h:29-121 driven by
+ * the objective of apps/optimize_trajectory/optimize_trajectory.cu:366-438 (altitude test, airspace test through
+ * acc::BVHTree::closest_point within min_distance, K5, K6, first arg-min of w * image).  The reference runs this per view
+ * on a host thread with a D2H copy and a host arg-min per evaluation; here the views advance in lock-step -- three batched
+ * evaluations (4 vertices, reflected point, expansion / contraction candidate) with the decisions taken by device kernels
+ * in between -- and nothing is copied to the host inside a step.
+ * A handle keeps the simplices ([num_views][4][3] floats, Simplex<3>::verts) and the results of the last step:
+ * ret_vid / ret_value = nelder_mead()'s return pair, vmin / vtheta / vphi = the closure's best orientation (:430-434).
+ * `active`: HOST indices of the views that take the step (mutually independent ones, :286-310).  airspace = the tree
+ * closest_point runs on (the apps use the proxy mesh itself).  num_bins = vertices of the KD-tree (1272). */
+typedef struct uavmvs_nm uavmvs_nm;
+int uavmvs_nm_create(uint32_t num_views, uint32_t num_bins, uavmvs_nm ** out);
+int uavmvs_nm_upload(uavmvs_nm * nm, const float * simplices);
+int uavmvs_nm_download(void * stream, const uavmvs_nm * nm, float * simplices, uint32_t * ret_vid, float * ret_value,
+    float * vmin, float * vtheta, float * vphi);
+int uavmvs_nm_step(void * stream, uavmvs_nm * nm, const uint32_t * active, uint32_t num_active, float min_distance,
+    float max_distance, float target_recon, const float calib[9], int width, int height, const uavmvs_bvh * bvh,
+    const uavmvs_bvh * airspace, const uavmvs_cloud * cloud, uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons);
+int uavmvs_nm_destroy(uavmvs_nm * nm);
+
 /* ---- K7 estimate_capture_difficulty, kernels.h:81-84, kernels.cu:448-494 */
 int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const uavmvs_bvh * bvh,
     uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud);

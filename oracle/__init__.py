@@ -128,6 +128,19 @@ def lib():
 
 
 _REFGEOM = None
+REF_OBJECTIVE = C.CFUNCTYPE(C.c_float, C.POINTER(C.c_float), C.c_void_p)
+
+
+def ref_nelder_mead_step(simplex, objective):
+    """libs/opti/nelder_mead.h:29-121 (the reference's own code, oracle/_ref/libref_geom.so) on one Simplex<3>;
+    objective(pos[3]) -> float.  Returns (new simplex [4,3], vertex id, value)."""
+    R = refgeom()
+    s = np.ascontiguousarray(simplex, np.float32).reshape(12).copy()
+    cb = REF_OBJECTIVE(lambda p, _u: float(objective(np.array([p[0], p[1], p[2]], np.float32))))
+    vid, val = C.c_uint32(0), C.c_float(0)
+    R.ref_nelder_mead_step(s, cb, None, C.byref(vid), C.byref(val))
+    return s.reshape(4, 3), int(vid.value), float(val.value)
+
 
 
 def refgeom():
@@ -147,6 +160,8 @@ def refgeom():
     R.ref_save_numpy_i32.argtypes = [C.c_char_p, np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS"), u32, u32]
     R.ref_save_volume.argtypes = [C.c_char_p, u32, u32, u32, _f32p, _f32p, u32, _u32p, i32, i32, i32, _f32p]
     R.ref_load_volume.argtypes = [C.c_char_p, _u32p, _f32p, _f32p, C.POINTER(u32), _u32p, u32, _f32p, C.c_uint64]
+    if hasattr(R, "ref_nelder_mead_step"):
+        R.ref_nelder_mead_step.argtypes = [_f32p, REF_OBJECTIVE, _vp, C.POINTER(u32), C.POINTER(f32)]
     _REFGEOM = R
     return R
 

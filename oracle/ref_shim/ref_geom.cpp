@@ -1,6 +1,6 @@
 /*
  * TEST INFRASTRUCTURE (oracle/_ref/libref_geom.so): the reference's own libs/geom/sphere.h, libs/util/numpy_io.h and
- * libs/geom/volume_io.h, included from where they lie under $(REFERENCE)/libs and compiled unmodified against the MVE
+ * libs/geom/volume_io.h and libs/opti/nelder_mead.h, included from where they lie under $(REFERENCE)/libs and compiled unmodified against the MVE
  * stand-ins of this directory.  Pins the 1272-vertex direction set of the spherical histogram and the bytes of the
  * .npy / VOL writers (uavmvs_b200/formats.py, uavmvs_sphere_vertices).  Nothing in the product loads this.
  */
@@ -15,6 +15,7 @@
 #include "geom/sphere.h"
 #include "util/numpy_io.h"
 #include "geom/volume_io.h"
+#include "opti/nelder_mead.h"
 
 extern "C" {
 
@@ -96,6 +97,20 @@ int ref_load_volume(const char * filename, uint32_t dims[3], float mn[3], float 
         *n = count;
         return 0;
     } catch (...) { return 1; }
+}
+
+/* One step of the reference's simplex-downhill (libs/opti/nelder_mead.h:29-121) on a Simplex<3> given as 12 floats;
+ * the objective is a C callback (the tests evaluate it with the oracle's K5 / K6). */
+typedef float (*ref_objective_t)(const float * pos, void * user);
+int ref_nelder_mead_step(float * simplex12, ref_objective_t f, void * user, uint32_t * vid, float * value)
+{
+    Simplex<3> sx;
+    for (int i = 0; i < 4; ++i) sx.verts[i] = math::Vec3f(simplex12[3 * i], simplex12[3 * i + 1], simplex12[3 * i + 2]);
+    std::function<float(math::Vector<float, 3>)> func = [&](math::Vector<float, 3> p) -> float { return f(*p, user); };
+    std::pair<std::size_t, float> r = nelder_mead<3>(&sx, func);
+    for (int i = 0; i < 4; ++i) for (int k = 0; k < 3; ++k) simplex12[3 * i + k] = sx.verts[i][k];
+    *vid = (uint32_t)r.first; *value = r.second;
+    return 0;
 }
 
 }  // extern "C"

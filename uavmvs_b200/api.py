@@ -594,6 +594,40 @@ def evaluate_spherical_histogram_batch(calib, width, height, kd_tree, sphere_his
     return (vmin, imin, vmax, imax) if want_best else None
 
 
+class NelderMead(_Handle):
+    """Simplices of the optimiser's views on the device and one lock-step simplex-downhill step for a batch of them
+    (uavmvs_nm_*: libs/opti/nelder_mead.h:29-121 with the objective of optimize_trajectory.cu:366-438)."""
+    _destroy = "uavmvs_nm_destroy"
+
+    @classmethod
+    def create(cls, num_views, num_bins):
+        h = _vp()
+        _check(_lib.uavmvs_nm_create(_u32(num_views), _u32(num_bins), C.byref(h)))
+        obj = cls(h)
+        obj.num_views = num_views
+        return obj
+
+    def upload(self, simplices):
+        s = _f(simplices, (self.num_views, 4, 3))
+        _check(_lib.uavmvs_nm_upload(self.ptr, _p(s)))
+
+    def step(self, active, min_distance, max_distance, target_recon, calib, width, height, bvh_tree, cloud, kd_tree, obs_rays,
+             recons, airspace=None, stream=None):
+        a = _u(active)
+        _check(_lib.uavmvs_nm_step(_stream_ptr(stream), self.ptr, _p(a), _u32(a.shape[0]), _f32(min_distance), _f32(max_distance),
+                                   _f32(target_recon), _p(_f(calib, 9)), _i32(width), _i32(height), bvh_tree.ptr,
+                                   (airspace or bvh_tree).ptr, cloud.ptr, kd_tree.ptr, obs_rays.ptr, recons.ptr))
+
+    def download(self, stream=None):
+        """-> dict(simplices [V,4,3], vid [V], value [V], vmin [V], vtheta [V], vphi [V]) (synchronises)."""
+        n = self.num_views
+        sx = np.empty((n, 4, 3), np.float32)
+        vid = np.empty(n, np.uint32)
+        val, vmin, vth, vph = (np.empty(n, np.float32) for _ in range(4))
+        _check(_lib.uavmvs_nm_download(_stream_ptr(stream), self.ptr, _p(sx), _p(vid), _p(val), _p(vmin), _p(vth), _p(vph)))
+        return dict(simplices=sx, vid=vid, value=val, vmin=vmin, vtheta=vth, vphi=vph)
+
+
 def estimate_capture_difficulty(max_distance, bvh_tree, mesh_size, kd_tree, cloud, stream=None):
     """libs/eval/kernels.h:81-84"""
     _check(_lib.uavmvs_estimate_capture_difficulty(_stream_ptr(stream), _f32(max_distance), bvh_tree.ptr,
