@@ -13,6 +13,7 @@ def _objective(oracle, ctx, track):
     def f(pos):
         pos = np.asarray(pos, np.float32)
         if pos[2] < md:
+            ctx["early"] += 1
             return float(md - pos[2])
         w = np.float32(1.0)
         found, tri, cp = ctx["obvh"].closest_point(pos[None, :], float(md))
@@ -22,7 +23,9 @@ def _objective(oracle, ctx, track):
             cpp = (pos - cp[0]).astype(np.float32)
             dist = np.float32(np.sqrt(np.float32(cpp[0] * cpp[0]) + np.float32(cpp[1] * cpp[1]) + np.float32(cpp[2] * cpp[2])))
             if float(np.dot(normal.astype(np.float64), cpp.astype(np.float64))) < 0.0:
+                ctx["early"] += 1
                 return float(dist)
+            ctx["weighted"] += 1
             w = np.float32(1.0) - (md - dist) / md
         h, _, _ = oracle.populate_spherical_histogram_recon(ctx["obvh"], ctx["okd"], pos, sc.max_distance, sc.target_recon,
                                                             sc.points, sc.normals, ctx["obs_o"], ctx["recons"], ctx["S"])
@@ -62,7 +65,7 @@ def test_nelder_mead_step_equals_the_reference(oracle):
     obs_o = oracle.ObsRays(sc.num_points, 32)
     oracle.update_observation_rays(obvh, True, views, sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
     oracle.process_observation_rays(obs_o)
-    ctx = dict(sc=sc, obvh=obvh, okd=okd, sv=sv, S=S, obs_o=obs_o, recons=recons.download(), tris=arrays.tris, min_distance=4.0)
+    ctx = dict(sc=sc, obvh=obvh, okd=okd, sv=sv, S=S, obs_o=obs_o, recons=recons.download(), tris=arrays.tris, min_distance=4.0, early=0, weighted=0)
     # simplices: a tetrahedron around every 20th view, one lowered below the altitude limit, one pushed into a building
     sel = list(range(0, sc.num_views, 20))[:8]
     V = len(sel)
@@ -90,4 +93,5 @@ def test_nelder_mead_step_equals_the_reference(oracle):
             if track["vmin"] < -1e-3:                    # the orientation of a clear minimum
                 assert abs(float(got["vtheta"][v]) - track["vtheta"]) < 1e-6 and abs(float(got["vphi"][v]) - track["vphi"]) < 1e-6, (step, v)
             cur[v] = new
-    assert (got["value"] < 0).any() and (got["value"] > 0).any()         # histogram values and constraint returns both occur
+    # the constraint branches of the objective were exercised (early returns, airspace weights) beside plain histogram values
+    assert ctx["early"] > 0 and ctx["weighted"] > 0 and (got["value"] < 0).any()
