@@ -113,5 +113,6 @@ def test_facade_accepts_the_reference_acc_trees_run():
     20 000 closest-hit rays and nearest-neighbour queries on the device equal acc's own CPU answers bit for bit."""
     if not os.path.exists(ACC_DEMO):
         pytest.skip("oracle/_ref/acc_tree_facade was not built (no reference checkout at build time)")
-    out = subprocess.run([ACC_DEMO], capture_output=True, text=True)
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "uavmvs_b200") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    out = subprocess.run([ACC_DEMO], capture_output=True, text=True, env=env)
     assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout + out.stderr
