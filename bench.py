@@ -78,7 +78,8 @@ def parse():
 def config_dict(a, world):
     """The same dict in both arms (the driver compares them)."""
     what = {2: "full evaluation K1+K2+K3+K8+K9 + score collective",
-            3: "optimiser inner loop (remove 16 views, K2+K3+K8, 112 candidates K5+K6+arg-min, re-add, K2+K3+K8+K9)",
+            3: "optimiser iteration (remove 16 views, K2+K3+K8, one Nelder-Mead step per view on the device = 96 objective "
+               "evaluations K5+K6+arg-min, re-add, K2+K3+K8+K9)",
             4: "guidance volume %d^3 grid, batched K4+K6+arg-min/max" % a.grid,
             5: "full evaluation K1+K2+K3+K8+K9 + score collective, points sharded over the GPUs"}[a.config]
     per = "%d proxy points per GPU x %d GPU" % (a.points, world) if a.scaling == "weak" else \
@@ -584,6 +585,35 @@ def extras_config34(a, torch, api, stream, blk, line):
                       "what": "optimize_trajectory.cu:283-549 on the resident config-2 state, median of %d iterations; candidate "
                               "positions are random trial points around the removed views" % len(times)}
     del loop
+    # ---- config 3 with the simplex-downhill step itself on the device (uavmvs_nm_step): the full optimiser iteration
+    loop = apps.OptimizerLoop(scn, bvh, blk["cloud"], kd, S, nelder_mead=True, min_distance=2.5)
+    loop.populate(stream)
+    loop.relax_independence()
+    times, stage = [], []
+    order = ["remove", "reeval", "nm", "readd", "end"]
+    for it in range(8):
+        marks = {}
+
+        def mark(name, marks=marks):
+            e = ev(); e.record(stream); marks[name] = e
+        api.k1_counters()
+        r = loop.iteration_nm(stream, mark)
+        torch.cuda.synchronize()
+        ms = [marks[order[i]].elapsed_time(marks[order[i + 1]]) for i in range(4)]
+        if it >= 2:
+            times.append(marks["remove"].elapsed_time(marks["end"]))
+            stage.append(ms + [api.k1_counters()[3], r["views"]])
+    st = np.median(np.array(stage), axis=0)
+    out["config3_nm_ms_per_iteration"] = float(np.median(times))
+    out["config3_nm"] = {"iterations_timed": len(times), "views_per_iteration": int(st[5]), "rays_per_iteration": int(st[4]),
+                         "objective_evaluations_per_view": 6, "score": r["score"],
+                         "stage_ms": dict(zip(("remove_K1", "K2_K3_K8_changed_blocks", "nelder_mead_step_on_device", "readd_K1_K2_K3_K8_K9_and_D2H"),
+                                              (float(x) for x in st[:4]))),
+                         "what": "the same iteration with libs/opti/nelder_mead.h's step for the 16 selected views on the device "
+                                 "(uavmvs_nm_step: 4 + 1 + 1 objective evaluations per view = altitude / closest_point airspace test, K5, "
+                                 "K6, arg-min, in three batches, decisions by device kernels); H2D: the selected views; no D2H until "
+                                 "the score and the 16 moved poses at the end of the iteration"}
+    del loop
     # ---- config 4: a fixed 64 k-position sample of the 128^3 volume
     rng = np.random.default_rng(4)
     cloud4 = api.PointCloud.create(pts, nrm, rng.uniform(0.0, 1.2, len(pts)).astype(np.float32),
@@ -778,11 +808,11 @@ def run_b200_config34(a, torch, api, stream, flush, rank, world):
     sampler = ClockSampler(visible_gpu_index(int(os.environ.get("LOCAL_RANK", "0"))))
     if a.config == 3:
         cloud = api.PointCloud.create(pts, nrm)
-        loop = apps.OptimizerLoop(sc, bvh, cloud, kd, S)
+        loop = apps.OptimizerLoop(sc, bvh, cloud, kd, S, nelder_mead=True, min_distance=2.5)
         loop.populate(stream)
         loop.relax_independence()
         for _ in range(a.warmup):
-            loop.iteration(stream)
+            loop.iteration_nm(stream)
         torch.cuda.synchronize()
         api.launch_count(reset=True); api.k1_counters()
         sampler.start()
@@ -791,7 +821,7 @@ def run_b200_config34(a, torch, api, stream, flush, rank, world):
             flush.fill_(1)
             e0, e1 = ev(), ev()
             e0.record(stream)
-            r = loop.iteration(stream)
+            r = loop.iteration_nm(stream)
             e1.record(stream); e1.synchronize()
             ms += e0.elapsed_time(e1)
         rays = api.k1_counters()[3]

@@ -253,6 +253,9 @@ int uavmvs_allgather_array(void * stream, uavmvs_comm * comm, const uavmvs_array
  * *_device / views_on_device entry points.  (The apps keep the cameras on the host and pass one view per launch,
  * apps/evaluate_trajectory/evaluate_trajectory.cu:154-164.) */
 int uavmvs_views_upload(void * stream, const float * views, uint32_t num_views, float ** d_views);
+/* Overwrites the first num_views views of a device array (stream-ordered; `views` must stay valid until the copy ran). */
+int uavmvs_views_update(void * stream, float * d_views, const float * views, uint32_t num_views);
+int uavmvs_views_download(void * stream, const float * d_views, uint32_t num_views, float * views);
 int uavmvs_views_free(float * d_views);
 
 /* Kernel launches issued by the evaluation path (K1 pipeline, K2/K3/K8, K9, histogram and closest-point kernels) in this
@@ -328,6 +331,12 @@ int uavmvs_nm_download(void * stream, const uavmvs_nm * nm, float * simplices, u
 int uavmvs_nm_step(void * stream, uavmvs_nm * nm, const uint32_t * active, uint32_t num_active, float min_distance,
     float max_distance, float target_recon, const float calib[9], int width, int height, const uavmvs_bvh * bvh,
     const uavmvs_bvh * airspace, const uavmvs_cloud * cloud, uavmvs_kdtree * kd, const uavmvs_obs * obs, const uavmvs_array * recons);
+/* The poses the views of the last uavmvs_nm_step take (optimize_trajectory.cu:441-467): position = the returned simplex
+ * vertex, orientation = utp::rotation_from_spherical(vtheta, vphi) (libs/utp/trajectory.cpp:14-39), w2c = [rot | -rot pos];
+ * views whose step returned a value >= 0 keep their pose (their re-initialisation, :446-461, stays with the application).
+ * d_views: DEVICE [num_views][28] in the order of that step's `active`, updated in place -- ready for the re-adding
+ * uavmvs_update_observation_rays_batch_device, so the optimiser's iteration needs no copy to the host in its middle. */
+int uavmvs_nm_apply_views(void * stream, const uavmvs_nm * nm, float * d_views, uint32_t num_views);
 int uavmvs_nm_destroy(uavmvs_nm * nm);
 
 /* ---- K7 estimate_capture_difficulty, kernels.h:81-84, kernels.cu:448-494 */

@@ -335,6 +335,11 @@ def update_observation_rays_batch(populate, views, max_distance, width, height, 
                                   stream=None):
     """The launch loop of apps/evaluate_trajectory/evaluate_trajectory.cu:154-164 as one call;
     views [V,28] = pos, w2c, calib (host)."""
+    if isinstance(views, DeviceViews):
+        _check(_lib.uavmvs_update_observation_rays_batch_device(_stream_ptr(stream), _i32(1 if populate else 0), views.ptr,
+                                                                _u32(views.num_views), _f32(max_distance), _i32(width),
+                                                                _i32(height), bvh_tree.ptr, cloud.ptr, obs_rays.ptr))
+        return
     views = _f(views, (-1, VIEW_FLOATS))
     _check(_lib.uavmvs_update_observation_rays_batch(_stream_ptr(stream), _i32(1 if populate else 0), _p(views),
                                                      _u32(views.shape[0]), _f32(max_distance), _i32(width),
@@ -383,6 +388,18 @@ class DeviceViews:
     @property
     def ptr(self):
         return C.cast(self._d, _vp)
+
+    def update(self, views, stream=None):
+        """Overwrites the views (same count) -- a stream-ordered H2D copy, no allocation."""
+        v = _f(views, (-1, VIEW_FLOATS))
+        assert v.shape[0] == self.num_views
+        self._host = v                                      # keep the source alive until the copy ran
+        _check(_lib.uavmvs_views_update(_stream_ptr(stream), self._d, _p(v), _u32(self.num_views)))
+
+    def download(self, stream=None):
+        out = np.empty((self.num_views, VIEW_FLOATS), np.float32)
+        _check(_lib.uavmvs_views_download(_stream_ptr(stream), self._d, _u32(self.num_views), _p(out)))
+        return out
 
     def free(self):
         if getattr(self, "_d", None):
@@ -617,6 +634,10 @@ class NelderMead(_Handle):
         _check(_lib.uavmvs_nm_step(_stream_ptr(stream), self.ptr, _p(a), _u32(a.shape[0]), _f32(min_distance), _f32(max_distance),
                                    _f32(target_recon), _p(_f(calib, 9)), _i32(width), _i32(height), bvh_tree.ptr,
                                    (airspace or bvh_tree).ptr, cloud.ptr, kd_tree.ptr, obs_rays.ptr, recons.ptr))
+
+    def apply_views(self, device_views, stream=None):
+        """Writes the poses of the last step's views into a DeviceViews holding them (in the step's order)."""
+        _check(_lib.uavmvs_nm_apply_views(_stream_ptr(stream), self.ptr, device_views._d, _u32(device_views.num_views)))
 
     def download(self, stream=None):
         """-> dict(simplices [V,4,3], vid [V], value [V], vmin [V], vtheta [V], vphi [V]) (synchronises)."""

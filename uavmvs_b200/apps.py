@@ -85,11 +85,43 @@ class GuidanceVolume:
         return {"min": vmin, "argmin": imin, "max": vmax, "argmax": imax, "crc32": "%08x" % crc}
 
 
+def rotation_from_spherical(theta, phi):
+    """utp::rotation_from_spherical (libs/utp/trajectory.cpp:14-39), float32, rows rx, ry, rz."""
+    f = np.float32
+    ct, st, cp, sp = f(np.cos(f(theta))), f(np.sin(f(theta))), f(np.cos(f(phi))), f(np.sin(f(phi)))
+    rz = np.array([st * cp, st * sp, ct], f)
+    rz = rz / f(np.sqrt(f(rz @ rz)))
+    up = np.array([0, 0, -1], f)
+    if not abs(float(up @ rz)) < 0.99:
+        up = np.array([cp, sp, 0], f)
+    rx = np.cross(up, rz).astype(f)
+    rx = rx / f(np.sqrt(f(rx @ rx)))
+    ry = np.cross(rz, rx).astype(f)
+    ry = ry / f(np.sqrt(f(ry @ ry)))
+    return np.stack([rx, ry, rz]).astype(f)
+
+
+def initial_simplices(positions, scale, rng):
+    """optimize_trajectory.cu:123-138, :210-226: a regular tetrahedron of the given scale around every view position,
+    rotated by a random (theta, phi).  -> [V, 4, 3] float32."""
+    t = np.float32(1.0 / np.sqrt(2.0))
+    tet = np.array([[1, 0, -t], [-1, 0, -t], [0, 1, t], [0, -1, t]], np.float32)
+    out = np.empty((len(positions), 4, 3), np.float32)
+    for i, p in enumerate(np.asarray(positions, np.float32)):
+        rot = rotation_from_spherical(rng.uniform(0.0, np.pi), 2.0 * rng.uniform(0.0, np.pi))
+        out[i] = p[None, :] + (tet * np.float32(scale)) @ rot.T
+    return out
+
+
 class OptimizerLoop:
-    """The state optimize_trajectory keeps on the device: observation rays of the whole trajectory, recons, wrecons."""
+    """The state optimize_trajectory keeps on the device: observation rays of the whole trajectory, recons, wrecons --
+    and, with nelder_mead=True, the simplices: an iteration then is remove -> K2/K3 -> one lock-step simplex-downhill
+    step of the selected views on the device (uavmvs_nm_step: 6 batched objective evaluations' worth of K5 + K6, the
+    decisions of libs/opti/nelder_mead.h in between) -> poses written on the device -> re-add -> K2/K3/K8/K9, with no copy
+    to the host between its kernels; the score and the moved poses come back once, at its end."""
 
     def __init__(self, scene, bvh, cloud, kd, num_bins, views=None, candidates_per_view=7, want_views=16, seed=7,
-                 full_eval=False):
+                 full_eval=False, nelder_mead=False, min_distance=2.5):
         self.sc, self.bvh, self.cloud, self.kd, self.S = scene, bvh, cloud, kd, num_bins
         self.views = scene.views28().copy() if views is None else views.copy()
         self.V, self.N = self.views.shape[0], scene.num_points
@@ -100,6 +132,12 @@ class OptimizerLoop:
         self.iters_left = np.full(self.V, 100.0)
         self.hists = api.Array.create(want_views * candidates_per_view * num_bins)
         self.independence = 1.0
+        self.min_distance = float(min_distance)
+        self.nm, self._d_sel = None, None
+        if nelder_mead:
+            self.nm = api.NelderMead.create(self.V, num_bins)
+            # scale = 0.5 * (min_distance / 10) in the app (:213); trial positions a few metres apart exercise the kernels more
+            self.nm.upload(initial_simplices(self.views[:, :3], 0.5 * self.min_distance, self.gen))
 
     def reeval(self, stream=None):
         sc = self.sc
@@ -140,6 +178,32 @@ class OptimizerLoop:
             self.independence *= 0.5
             sel = self.select()
         return len(sel)
+
+    def iteration_nm(self, stream=None, mark=_noop):
+        """One optimiser iteration (:283-549) with the simplex-downhill step on the device."""
+        sc, views = self.sc, self.views
+        sel = self.select()
+        if self._d_sel is None or self._d_sel.num_views != len(sel):
+            self._d_sel = api.DeviceViews(views[sel], stream=stream)
+        else:
+            self._d_sel.update(views[sel], stream=stream)                      # H2D: the selected views
+        d_sel = self._d_sel
+        mark("remove")
+        api.update_observation_rays_batch(False, d_sel, sc.max_distance, sc.width, sc.height, self.bvh, self.cloud, self.obs, stream=stream)
+        mark("reeval")
+        self.reeval(stream)
+        mark("nm")
+        self.nm.step(np.asarray(sel, np.uint32), self.min_distance, sc.max_distance, sc.target_recon, sc.calib[0], sc.width, sc.height,
+                     self.bvh, self.cloud, self.kd, self.obs, self.recons, stream=stream)
+        self.nm.apply_views(d_sel, stream=stream)
+        mark("readd")
+        api.update_observation_rays_batch(True, d_sel, sc.max_distance, sc.width, sc.height, self.bvh, self.cloud, self.obs, stream=stream)
+        self.reeval(stream)
+        score = api.reduce(self.wrecons, stream=stream)[0] / self.N         # D2H: the score ...
+        views[sel] = d_sel.download(stream)                                  # ... and the moved poses, once per iteration
+        mark("end")
+        self.iters_left[sel] -= 1
+        return {"views": len(sel), "candidates": 6 * len(sel), "score": score, "selected": sel}
 
     def iteration(self, stream=None, mark=_noop):
         """One optimiser iteration (:283-549) with random trial positions standing in for the simplex vertices

@@ -545,6 +545,21 @@ int uavmvs_views_upload(void * stream, const float * views, uint32_t num_views, 
     return 0;
 }
 
+int uavmvs_views_update(void * stream, float * d_views, const float * views, uint32_t num_views)
+{
+    UAV_REQUIRE(views && d_views, "null argument");
+    UAV_CUDA(cudaMemcpyAsync(d_views, views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return 0;
+}
+
+int uavmvs_views_download(void * stream, const float * d_views, uint32_t num_views, float * views)
+{
+    UAV_REQUIRE(views && d_views, "null argument");
+    UAV_CUDA(cudaMemcpyAsync(views, d_views, sizeof(float) * UAVMVS_VIEW_FLOATS * (size_t)num_views, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    UAV_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+
 int uavmvs_views_free(float * d_views)
 {
     if (d_views) UAV_CUDA(cudaFree(d_views));

@@ -188,11 +188,38 @@ __global__ void k_nm_finish(NmState * __restrict__ states, const uint32_t * __re
     st.ret_vid = vid; st.ret_value = val;
 }
 
+// The pose an optimised view takes after the step (optimize_trajectory.cu:441-467): position = the returned simplex vertex,
+// orientation = utp::rotation_from_spherical(vtheta, vphi) (libs/utp/trajectory.cpp:14-39), w2c = [rot | -rot pos].
+// Views whose step returned a non-negative value ("does not contribute", :446) are left as they are: their
+// re-initialisation (:447-461) is the application's business.  views: [n][28] in the order of `active`, updated in place.
+__global__ void k_nm_apply_views(const NmState * __restrict__ states, const uint32_t * __restrict__ active, uint32_t n, float * __restrict__ views)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const NmState & st = states[active[i]];
+    if (!(st.ret_value < 0.0f)) return;
+    const V3 pos = mk(st.verts[st.ret_vid][0], st.verts[st.ret_vid][1], st.verts[st.ret_vid][2]);
+    const float ct = cosf(st.vtheta), sn = sinf(st.vtheta), cp = cosf(st.vphi), sp = sinf(st.vphi);
+    const V3 rz = normalized(mk(sn * cp, sn * sp, ct));
+    V3 up = mk(0.0f, 0.0f, -1.0f);
+    if (!(fabsf(dot(up, rz)) < 0.99f)) up = mk(cp, sp, 0.0f);
+    const V3 rx = normalized(cross(up, rz));
+    const V3 ry = normalized(cross(rz, rx));
+    float * v = views + (size_t)i * UAVMVS_VIEW_FLOATS;
+    v[0] = pos.x; v[1] = pos.y; v[2] = pos.z;
+    const V3 rows[3] = {rx, ry, rz};
+    for (int r = 0; r < 3; ++r) {
+        v[3 + 4 * r] = rows[r].x; v[3 + 4 * r + 1] = rows[r].y; v[3 + 4 * r + 2] = rows[r].z;
+        v[3 + 4 * r + 3] = -dot(rows[r], pos);                                      // trans = -rot * pos
+    }
+    v[15] = 0.0f; v[16] = 0.0f; v[17] = 0.0f; v[18] = 1.0f;
+}
+
 }  // namespace uav
 
 // ---- host side --------------------------------------------------------------------------------------------------
 struct uavmvs_nm {
-    uint32_t n = 0, bins = 0;
+    uint32_t n = 0, bins = 0, last_active = 0;
     uav::NmState * states = nullptr;
     uint32_t * active = nullptr;
     // scratch for up to 4 n positions
@@ -316,6 +343,17 @@ int uavmvs_nm_step(void * stream, uavmvs_nm * h, const uint32_t * active, uint32
     UAV_CUDA(cudaGetLastError());
     if (int rc = nm_evaluate(c, n)) return rc;                                                  // expansion / contraction candidates
     k_nm_finish<<<divup(n, 128), 128, 0, counted(s)>>>(h->states, h->active, n, h->value, h->theta, h->phi, h->from_hist);
+    UAV_CUDA(cudaGetLastError());
+    h->last_active = n;
+    return 0;
+}
+
+int uavmvs_nm_apply_views(void * stream, const uavmvs_nm * h, float * d_views, uint32_t num_views)
+{
+    UAV_REQUIRE(h && d_views, "null argument");
+    UAV_REQUIRE(num_views == h->last_active, "the view array must hold the views of the last uavmvs_nm_step, in its order");
+    if (num_views == 0) return 0;
+    k_nm_apply_views<<<divup(num_views, 128), 128, 0, counted((cudaStream_t)stream)>>>(h->states, h->active, num_views, d_views);
     UAV_CUDA(cudaGetLastError());
     return 0;
 }
