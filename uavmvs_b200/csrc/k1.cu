@@ -155,8 +155,16 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
 // word count all 32 bits at once), eight loads in flight; the planes are then read out per bit and summed over the
 // lanes with one redux each.  (A thread per block walking the views one dependent load at a time took 0.058 ms on
 // config 2, all of it load latency.)
+// Blocks with >= early_at candidate views are also appended to the early list (EarlyList below): the cull kernel starts
+// them first and cuts the largest into pieces.
+#define K1_EARLY_MAX 512u      // listed blocks per batch (the rest keeps its place in the grid)
+#define K1_EARLY_PIECES 8u     // CTAs per listed block
+// uint32 words of the list: [0] k_trace's work counter, [1] listed blocks, [2, 2 + MAX) pieces done per block -- zeroed per
+// batch -- then block ids [MAX], slice base [MAX x PIECES] and ray count [MAX x PIECES] per piece
+#define K1_EARLY_ZEROED (2u + K1_EARLY_MAX)
+#define K1_EARLY_WORDS (2u + 2u * K1_EARLY_MAX + 2u * K1_EARLY_MAX * K1_EARLY_PIECES)
 __global__ void k_block_caps(const uint32_t * __restrict__ masks, uint32_t num_views, uint32_t v0, uint32_t v1,
-    uint32_t num_blocks, uint32_t * __restrict__ caps)
+    uint32_t num_blocks, uint32_t * __restrict__ caps, uint32_t early_at, uint32_t * __restrict__ early)
 {
     const uint32_t sb = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (sb >= (num_blocks + 31) / 32) return;                         // warp-uniform
@@ -186,7 +194,13 @@ __global__ void k_block_caps(const uint32_t * __restrict__ masks, uint32_t num_v
         }
     }
     const uint32_t b = sb * 32 + lane;
-    if (b < num_blocks) caps[b] = 32u * c;
+    if (b < num_blocks) {
+        caps[b] = 32u * c;
+        if (early && c >= early_at) {
+            const uint32_t slot = atomicAdd(early + 1, 1u);
+            if (slot < K1_EARLY_MAX) early[K1_EARLY_ZEROED + slot] = b;
+        }
+    }
 }
 
 __global__ void k_sum_caps(const uint32_t * __restrict__ caps, uint32_t n, unsigned long long * total)
@@ -559,6 +573,8 @@ struct RayList {
     uint32_t reverse;     // dev: k_cull_emit_q walks the blocks from the last to the first
     const uint32_t * caps;   // [num_blocks] 32 x candidate views of the block in this batch (k_block_caps)
     uint32_t transpose_at;   // k_cull_emit_q: candidate views from which a block takes the transposed phase 1
+    uint32_t * early;        // K1_EARLY_WORDS words (k_block_caps), or NULL: blocks the cull kernel starts first
+    uint32_t early_at, split_at;   // candidate views from which a block is listed / views per piece of a listed block
     uint32_t * dbg_blocks;   // UAVMVS_K1_DEBUG: per block {cycles, rays, candidate views} of k_cull_emit_q
     uint32_t debug;       // UAVMVS_K1_DEBUG: k_cull_emit_q counts candidates / queued / rejected pairs into counters[4..7]
     const uint32_t * off; // [num_blocks] first entry of each block's slice (both lists)
@@ -708,9 +724,41 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     __shared__ float4 s_v[CW][32], s_n[CW][32];
     __shared__ uint32_t s_q[CW][64], s_vq[CW][64];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t blk = rl.reverse ? num_blocks - 1u - (blockIdx.x * CW + w) : blockIdx.x * CW + w;
-    if (blk >= num_blocks) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
+    // Early list (CW == 1): the first K1_EARLY_MAX x K1_EARLY_PIECES CTAs of the grid belong to the listed blocks, so the
+    // blocks with the most candidate views start at once instead of wherever their index puts them, and a block with
+    // thousands of candidate views (a jump of the Z-order curve: on a config-5 shard ONE such block ran for 0.8 ms of a
+    // 0.88 ms kernel) is cut into pieces by view range.  A piece writes at the slice position its candidate views give
+    // it; the last piece to finish moves the pieces together, in view order, so the slice is what one warp would have
+    // written.
+    uint32_t blk = rl.reverse ? num_blocks - 1u - (blockIdx.x * CW + w) : blockIdx.x * CW + w;
+    uint32_t piece = 0, npieces = 1, eslot = 0;
+    if (CW == 1 && rl.early) {
+        const uint32_t EG = K1_EARLY_MAX * K1_EARLY_PIECES;
+        const uint32_t en = min(rl.early[1], K1_EARLY_MAX);
+        if (blockIdx.x < EG) {
+            eslot = blockIdx.x / K1_EARLY_PIECES; piece = blockIdx.x % K1_EARLY_PIECES;
+            if (eslot >= en) return;
+            blk = rl.early[K1_EARLY_ZEROED + eslot];
+            npieces = min(K1_EARLY_PIECES, 1u + (rl.caps[blk] >> 5) / rl.split_at);
+            if (piece >= npieces) return;
+        } else {
+            blk = rl.reverse ? num_blocks - 1u - (blockIdx.x - EG) : blockIdx.x - EG;
+            if (blk >= num_blocks) return;
+            if ((rl.caps[blk] >> 5) >= rl.early_at) {              // listed?  then its CTAs are at the front of the grid
+                bool found = false;
+                for (uint32_t i = lane; i < en; i += 32) found = found || rl.early[K1_EARLY_ZEROED + i] == blk;
+                if (__any_sync(0xffffffffu, found)) return;
+            }
+        }
+    }
+    if (blk >= num_blocks) return;
+    // this CTA's views: all of the batch, or the piece's share (multiples of 128 views: the loop below reads 4 x 32)
+    uint32_t lv0 = v0, lv1 = v1;
+    if (npieces > 1) {
+        const uint32_t per = ((v1 - v0 + npieces - 1) / npieces + 127u) / 128u * 128u;
+        lv0 = min(v1, v0 + piece * per); lv1 = min(v1, lv0 + per);
+    }
     const uint32_t id = blk * 32 + lane;
     const bool valid = id < n;
     const float4 v4 = verts[valid ? id : n - 1];
@@ -721,7 +769,12 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     const uint32_t * mrow = masks + (size_t)(blk >> 5) * num_views;
     const uint32_t * irow = inside_masks + (size_t)(blk >> 5) * num_views;
     const uint32_t mbit = blk & 31;
-    const uint32_t base = rl.off[blk];
+    uint32_t base = rl.off[blk];
+    if (piece) {                                          // skip the records of the candidate views before this piece
+        uint32_t c = 0;
+        for (uint32_t vi = v0 + lane; vi < lv0; vi += 32) c += (__ldg(mrow + vi) >> mbit) & 1u;
+        base += 32u * __reduce_add_sync(0xffffffffu, c);
+    }
     const float md2 = cull_distance * cull_distance * 1.00001f;
     const float wph = ((float)width + 0.5f) * 1.000001f, hph = ((float)height + 0.5f) * 1.000001f;
     uint32_t count = 0, qn = 0;
@@ -864,18 +917,18 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     // block takes the transposed form (k_block_caps knows the count before this kernel runs).
     const bool transposed = (rl.caps[blk] >> 5) >= rl.transpose_at || (!HIST && rl.vproj != nullptr);
     const V3 pv = ld3(v4); const float bf_lim = n4.w;
-    for (uint32_t g0 = v0; g0 < v1; g0 += 128) {
+    for (uint32_t g0 = lv0; g0 < lv1; g0 += 128) {
       uint32_t mw4[4], iw4[4];
       #pragma unroll
       for (int u = 0; u < 4; ++u) {
           const uint32_t vi = g0 + 32 * u + lane;
-          mw4[u] = vi < v1 ? __ldg(mrow + vi) : 0u;
-          iw4[u] = (!HIST && vi < v1) ? __ldg(irow + vi) : 0u;
+          mw4[u] = vi < lv1 ? __ldg(mrow + vi) : 0u;
+          iw4[u] = (!HIST && vi < lv1) ? __ldg(irow + vi) : 0u;
       }
       #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint32_t c0 = g0 + 32 * u;
-        if (c0 >= v1) break;
+        if (c0 >= lv1) break;
         const bool cand = (mw4[u] >> mbit) & 1u;
         uint32_t word = __ballot_sync(0xffffffffu, cand);
         if (!word) continue;
@@ -909,6 +962,35 @@ k_cull_emit_q(const float4 * __restrict__ verts, const float4 * __restrict__ nor
     }
     if (vqn) process_views(vqn);
     while (qn) flush();
+    if (npieces > 1) {
+        uint32_t * pb = rl.early + K1_EARLY_ZEROED + K1_EARLY_MAX + eslot * K1_EARLY_PIECES, * pc = pb + K1_EARLY_MAX * K1_EARLY_PIECES;
+        __threadfence();                                   // this piece's records before its count
+        __syncwarp();
+        uint32_t old = 0;
+        if (lane == 0) { pb[piece] = base; pc[piece] = count; __threadfence(); old = atomicAdd(rl.early + 2 + eslot, 1u); }
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old != npieces - 1) return;
+        __threadfence();
+        uint32_t total = 0;
+        const uint32_t b0 = rl.off[blk];
+        for (uint32_t p = 0; p < npieces; ++p) {
+            const uint32_t src = *(volatile uint32_t *)(pb + p), cn = *(volatile uint32_t *)(pc + p), dst = b0 + total;
+            if (src != dst) for (uint32_t i = 0; i < cn; i += 32) {       // dst < src: a step never overwrites what a later one reads
+                const bool in = i + lane < cn;
+                float4 d = make_float4(0.f, 0.f, 0.f, 0.f), o = d, t = d;
+                if (in) { d = __ldcg(rl.dirl + src + i + lane); o = __ldcg(rl.torg + src + i + lane); if (rl.trd) t = __ldcg(rl.trd + src + i + lane); }
+                __syncwarp();
+                if (in) {
+                    const uint32_t idx = dst + i + lane;
+                    o.w = __uint_as_float(idx << 5 | (__float_as_uint(o.w) & 31u));
+                    __stcs(rl.dirl + idx, d); __stcs(rl.torg + idx, o); if (rl.trd) __stcs(rl.trd + idx, t);
+                }
+                __syncwarp();
+            }
+            total += cn;
+        }
+        count = total;
+    }
     if (lane == 0) {
         rl.cnt[blk] = count; rl.tcnt[blk] = count;
         if (counters && count) atomicAdd(counters + 3, (unsigned long long)count);
@@ -1425,7 +1507,7 @@ struct K1Scratch {
     uint32_t * vcaps = nullptr, * h_vcaps = nullptr; size_t vcaps_cap = 0, h_vcaps_cap = 0;   // per-view bounds (batch planning)
     uint32_t plan_views = 0, plan_blocks = 0;      // the last call with this shape needed a plan: plan at once
     int grid_trace = 0;
-    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 1, tune_transpose_at = 512;
+    int tune_refill = K1_REFILL, tune_tri = K1_TRI, tune_steps = K1_STEPS, tune_cull_warps = 1, tune_transpose_at = 512, tune_early_at = 256, tune_split_at = 1024;
     cudaEvent_t ev_total = nullptr;
     // per-kernel timing of the last launch_k1 (uavmvs_profile_k1): events at the kernel boundaries of every view batch
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -1494,7 +1576,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     K1Scratch & k = g_k1;
     const uint32_t nb = cloud->num_blocks;
     if (!k.work) {
-        UAV_CUDA(cudaMalloc(&k.work, sizeof(uint32_t)));
+        UAV_CUDA(cudaMalloc(&k.work, sizeof(uint32_t) * K1_EARLY_WORDS));   // word 0: k_trace's counter, then the early list
         UAV_CUDA(cudaMalloc(&k.total, sizeof(unsigned long long)));
         UAV_CUDA(cudaMalloc(&k.counters, 8 * sizeof(unsigned long long)));
         UAV_CUDA(cudaMemset(k.counters, 0, 8 * sizeof(unsigned long long)));
@@ -1512,6 +1594,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         if (const char * e = getenv("UAVMVS_K1_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_tri = atoi(e);
         if (const char * e = getenv("UAVMVS_CULL_WARPS")) if (atoi(e) == 1 || atoi(e) == 2 || atoi(e) == 4) k.tune_cull_warps = atoi(e);
         if (const char * e = getenv("UAVMVS_CULL_TRANSPOSE_AT")) k.tune_transpose_at = atoi(e) >= 0 ? atoi(e) : 256;
+        if (const char * e = getenv("UAVMVS_CULL_EARLY_AT")) k.tune_early_at = atoi(e);        // 0: no early list
+        if (const char * e = getenv("UAVMVS_CULL_SPLIT_AT")) k.tune_split_at = atoi(e) > 0 ? atoi(e) : 1024;
         if (const char * e = getenv("UAVMVS_K1_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) k.tune_steps = atoi(e);
     }
     if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
@@ -1593,7 +1677,11 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             UAV_REQUIRE(total <= (1ull << 27), "a single view yields more than 2^27 candidate pairs");
         }
         if (k1_mark(k, s, 1)) return 1;
-        k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, uav::counted(s)>>>(k.masks, num_views, v0, v1, nb, k.caps);
+        // early list of the cull kernel (CW == 1, evaluation jobs): zeroed together with k_trace's work counter
+        const bool early = !hj && k.tune_cull_warps == 1 && k.tune_early_at > 0;
+        UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t) * K1_EARLY_ZEROED, s));
+        k_block_caps<<<divup((size_t)cloud->num_super * 32, 128), 128, 0, uav::counted(s)>>>(k.masks, num_views, v0, v1, nb, k.caps,
+            (uint32_t)k.tune_early_at, early ? k.work : nullptr);
         const bool spec = speculate && !planned;
         speculate = false;                                   // one attempt per call
         const unsigned long long spec_cap = min((unsigned long long)k.rays_cap, min((unsigned long long)ray_budget(), 1ull << 27));
@@ -1673,9 +1761,12 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 // candidate views 0.65, from 128 1.00, never 0.83 (the slowest block then sets the duration of the kernel);
                 // the two forms as separate kernels 0.72 - 0.86 (r02_l: the heavy blocks' kernel is one long tail)
                 const int cw = k.tune_cull_warps;
-                #define UAV_CULL(H, D, W) k_cull_emit_q<H, D, W><<<divup(nb, W), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
+                rl.early = (early && !(rl.debug && cw != 1)) ? k.work : nullptr;
+                rl.early_at = (uint32_t)k.tune_early_at; rl.split_at = (uint32_t)k.tune_split_at;
+                const uint32_t eg = rl.early ? K1_EARLY_MAX * K1_EARLY_PIECES : 0u;
+                #define UAV_CULL(H, D, W) k_cull_emit_q<H, D, W><<<divup(nb, W) + (W == 1 ? eg : 0u), W * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, \
                     cloud->n, nb, d_views, num_views, v0, v1, k.masks, inside_masks, max_distance, cull_distance, width, height, rl, k.counters)
-                if (rl.debug && !hj) UAV_CULL(false, true, 4);
+                if (rl.debug && !hj) { if (cw == 1) UAV_CULL(false, true, 1); else UAV_CULL(false, true, 4); }
                 else if (hj) { if (cw == 1) UAV_CULL(true, false, 1); else if (cw == 2) UAV_CULL(true, false, 2); else UAV_CULL(true, false, 4); }
                 else { if (cw == 1) UAV_CULL(false, false, 1); else if (cw == 2) UAV_CULL(false, false, 2); else UAV_CULL(false, false, 4); }
                 #undef UAV_CULL
@@ -1685,7 +1776,6 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
             else k_cull_emit<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(cloud->vertices, cloud->normals, cloud->n, nb,
                 d_views, num_views, v0, v1, k.masks, inside_masks, shafts ? k.cert : nullptr, nchunks, max_distance, width, height, rl, k.counters);
             if (k1_mark(k, s, 3)) return 1;
-            UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
             TraceArgs ta; ta.bvh = view_of(bvh); ta.verts = cloud->vertices; ta.rl = rl; ta.num_blocks = nb; ta.work = k.work;
             ta.refill = k.tune_refill; ta.tri = k.tune_tri; ta.steps = k.tune_steps;
             unsigned grid = (unsigned)k.grid_trace;
