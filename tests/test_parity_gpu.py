@@ -403,6 +403,36 @@ def test_axis_parallel_rays_and_flat_boxes(api, oracle):
     assert np.array_equal(rows, obs_o.num_rows)
 
 
+@pytest.mark.parametrize("early_at,split_at", [("1", "16"), ("8", "64"), ("0", "1024")])
+def test_cull_early_list_and_view_range_pieces_are_bit_exact(api, oracle, early_at, split_at, monkeypatch):
+    """k_cull_emit_q starts the blocks with many candidate views first and cuts the largest into up to 8 view-range pieces
+    whose records the last piece moves together.  With the thresholds lowered every block of a small scene with 700 views
+    takes that path (pieces of 128 views, some of them empty); rows, counters and order must not change."""
+    from uavmvs_b200 import scenes
+    sc = scenes.urban(num_tris=8000, num_points=8192 + 17, num_views=700, extent=64.0, seed=6)
+    monkeypatch.setenv("UAVMVS_CULL_EARLY_AT", early_at)
+    monkeypatch.setenv("UAVMVS_CULL_SPLIT_AT", split_at)
+    gbvh = api.BVHTree.build_sah(sc.verts, sc.faces)
+    nodes, aabbs, tris, indices = gbvh.export()
+    obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    obs_o, state, _ = _run_oracle_eval(oracle, obvh, sc)
+    cloud = api.PointCloud.create(sc.points, sc.normals)
+    obs = api.VectorArray.create(sc.num_points, 32)
+    api.update_observation_rays_batch(True, sc.views28(), sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    data, rows = obs.download()
+    assert rows.max() > 32
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+    # removal goes through the same kernel
+    api.update_observation_rays_batch(False, sc.views28()[100:400], sc.max_distance, sc.width, sc.height, gbvh, cloud, obs)
+    oracle.update_observation_rays(obvh, False, sc.views28()[100:400], sc.max_distance, sc.width, sc.height, sc.points, sc.normals, obs_o)
+    oracle.process_observation_rays(obs_o)
+    api.process_observation_rays(obs)
+    data, rows = obs.download()
+    assert np.array_equal(rows, obs_o.num_rows)
+    assert _valid_rows_equal(obs_o.data, data, rows, 32)
+
+
 @pytest.mark.parametrize("tau", ["4", "32"])
 def test_packet_entry_points_opt_in_is_bit_exact(api, oracle, tau, monkeypatch):
     """UAVMVS_ENTRY=1: rays start from their packet's frontier of wide nodes (k_entry) instead of the root."""

@@ -1594,10 +1594,11 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         if (const char * e = getenv("UAVMVS_K1_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) k.tune_tri = atoi(e);
         if (const char * e = getenv("UAVMVS_CULL_WARPS")) if (atoi(e) == 1 || atoi(e) == 2 || atoi(e) == 4) k.tune_cull_warps = atoi(e);
         if (const char * e = getenv("UAVMVS_CULL_TRANSPOSE_AT")) k.tune_transpose_at = atoi(e) >= 0 ? atoi(e) : 256;
-        if (const char * e = getenv("UAVMVS_CULL_EARLY_AT")) k.tune_early_at = atoi(e);        // 0: no early list
-        if (const char * e = getenv("UAVMVS_CULL_SPLIT_AT")) k.tune_split_at = atoi(e) > 0 ? atoi(e) : 1024;
         if (const char * e = getenv("UAVMVS_K1_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) k.tune_steps = atoi(e);
     }
+    // read per call (tests lower them to push small scenes through the piece path)
+    { const char * e = getenv("UAVMVS_CULL_EARLY_AT"); k.tune_early_at = e ? atoi(e) : 256; }                     // 0: no early list
+    { const char * e = getenv("UAVMVS_CULL_SPLIT_AT"); k.tune_split_at = (e && atoi(e) > 0) ? atoi(e) : 1024; }
     if (grow(&k.masks, &k.masks_cap, 2 * (size_t)cloud->num_super * num_views, s)) return 1;   // candidate bits, then "surely inside the image" bits
     uint32_t * inside_masks = k.masks + (size_t)cloud->num_super * num_views;
     if (nb + 1 > k.blocks_cap) {
@@ -1760,6 +1761,9 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 // Measured on config 2 (profiles/r02_k_sweep.txt): 4 warps 0.71 ms, 1 warp 0.68; transposed phase 1 from 512
                 // candidate views 0.65, from 128 1.00, never 0.83 (the slowest block then sets the duration of the kernel);
                 // the two forms as separate kernels 0.72 - 0.86 (r02_l: the heavy blocks' kernel is one long tail)
+                // r02_q: phase 2 as two queued stages (exact image test first, then back-face / range + emit on the 59 % that
+                // survive it): 0.616 -> 0.653 ms, the second queue costs more than the arithmetic it saves; early list from
+                // 128 candidate views instead of 256: 0.685
                 const int cw = k.tune_cull_warps;
                 rl.early = (early && !(rl.debug && cw != 1)) ? k.work : nullptr;
                 rl.early_at = (uint32_t)k.tune_early_at; rl.split_at = (uint32_t)k.tune_split_at;
