@@ -182,6 +182,18 @@ int uavmvs_calculate_func_recons(void * stream, const uavmvs_array * recons, flo
 /* ---- K9 cacc::reduction::{sum,min,max}, libs/cacc/reduction.h:132-162.
  * out3 = {sum, min, max} (HOST); synchronises the stream. */
 int uavmvs_reduce(void * stream, const uavmvs_array * a, float out3[3]);
+/* ---- K9 without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same {sum, min, max} as uavmvs_reduce, written to out3->data[0..2] -- a DEVICE array of >= 3 floats the caller created
+ * beforehand (uavmvs_array_create) -- asynchronously on `stream` (no synchronisation, no host copy).  The call performs
+ * no cudaMalloc / cudaFree / cudaMallocHost and calls no allocating routine: its scratch (one partial per 2048 elements)
+ * is a static __device__ array of the library, 128 KB on every GPU that loads it, held until the process exits.
+ * Limits: 1 <= a->n <= UAVMVS_REDUCE_NOALLOC_MAX_N, larger inputs are rejected (return 2, message in uavmvs_last_error).
+ * The additions have a fixed order: repeated calls on the same data give the same bits (sum within 1e-6 relative of
+ * uavmvs_reduce, whose atomics fix no order; min / max identical).  ALL calls on one device share the scratch array:
+ * calls that overlap on the GPU (different streams or host threads) race; calls on one stream are ordered by it. */
+#define UAVMVS_REDUCE_NOALLOC_MAX_N (1u << 24)
+int uavmvs_reduce_noalloc(void * stream, const uavmvs_array * a, uavmvs_array * out3);
 
 /* ---- Whole evaluation as apps/evaluate_trajectory/evaluate_trajectory.cu:125-202 runs it:
  * clear obs, K1 over all views, K2, K3, K8, K9.  views are HOST memory (copied inside).

@@ -375,6 +375,16 @@ def reduce(array, stream=None):
     return float(out[0]), float(out[1]), float(out[2])
 
 
+REDUCE_NOALLOC_MAX_N = 1 << 24      # UAVMVS_REDUCE_NOALLOC_MAX_N
+
+
+def reduce_noalloc(array, out3, stream=None):
+    """uavmvs_reduce_noalloc: K9 into `out3` (an Array of >= 3 floats created beforehand) without any allocation or
+    synchronisation; no counterpart in the reference.  Read the result with out3.download()[:3] after the stream is done.
+    Calls on one device share a static scratch array: do not overlap them."""
+    _check(_lib.uavmvs_reduce_noalloc(_stream_ptr(stream), array.ptr, out3.ptr))
+
+
 class DeviceViews:
     """A trajectory resident on the device ([V,28] floats) for repeated evaluation (uavmvs_views_upload)."""
 
