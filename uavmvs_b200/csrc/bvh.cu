@@ -125,6 +125,24 @@ __global__ void k_wide_emit(uint32_t count, const uint4 * __restrict__ kids_in, 
     wide[level_base + i] = o;
 }
 
+// Directed fp32 -> bf16 (bits): the largest bf16 <= x / the smallest bf16 >= x.  Truncating the low 16 bits rounds towards
+// zero; one unit is added to the magnitude when bits were dropped and the direction points away from zero (a carry into
+// the exponent, up to infinity, is still on the right side).  NaN stays NaN.
+__device__ __forceinline__ unsigned short f2bf_rd(float x)
+{
+    const uint32_t u = __float_as_uint(x);
+    uint32_t t = u >> 16;
+    if ((u & 0xffffu) && (u >> 31)) t += 1u;
+    return (unsigned short)t;
+}
+__device__ __forceinline__ unsigned short f2bf_ru(float x)
+{
+    const uint32_t u = __float_as_uint(x);
+    uint32_t t = u >> 16;
+    if ((u & 0xffffu) && !(u >> 31)) t += 1u;
+    return (unsigned short)t;
+}
+
 // Node80 from Node128: centre of the union of the occupied children, outward-rounded fp16 offsets.
 __global__ void k_build_wide80(const Node128 * __restrict__ wide, uint32_t n, Node80 * __restrict__ out)
 {
@@ -150,6 +168,15 @@ __global__ void k_build_wide80(const Node128 * __restrict__ wide, uint32_t n, No
 #else
             const int lo = 6 * k + a, hi = 6 * k + 3 + a;
 #endif
+#if K1_PRMT && K1_BF16
+            if (occ[k]) {
+                h[lo] = __ushort_as_half(f2bf_rd(__fsub_rd(q[6 * k + a], c[a])));      // bf16 bits in the 16-bit slots
+                h[hi] = __ushort_as_half(f2bf_ru(__fsub_ru(q[6 * k + 3 + a], c[a])));
+            } else {
+                h[lo] = __ushort_as_half((unsigned short)0x7f80);      // +inf: no segment reaches it
+                h[hi] = __ushort_as_half((unsigned short)0x7f80);
+            }
+#else
             if (occ[k]) {
                 h[lo] = __float2half_rd(__fsub_rd(q[6 * k + a], c[a]));
                 h[hi] = __float2half_ru(__fsub_ru(q[6 * k + 3 + a], c[a]));
@@ -157,6 +184,7 @@ __global__ void k_build_wide80(const Node128 * __restrict__ wide, uint32_t n, No
                 h[lo] = __ushort_as_half((unsigned short)0x7c00);      // +inf: no segment reaches it
                 h[hi] = __ushort_as_half((unsigned short)0x7c00);
             }
+#endif
         }
     Node80 o;
     o.c = make_float4(c[0], c[1], c[2], 0.0f);

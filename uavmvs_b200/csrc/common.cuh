@@ -73,6 +73,15 @@ struct __align__(128) Node128 { float4 q[6]; uint4 ref; uint4 cnt; };
 //   K1_PRMT layout: the 24 halves are 12 words (min, max), word 3k + a = child k, axis a, so that one PRMT orders a
 //   word (near, far) for the ray's direction sign (k1.cu:k_trace)
 struct __align__(16) Node80 { float4 c; uint4 h[3]; uint4 cnt; };
+// K1_BF16 (with K1_PRMT): the offsets are stored as bf16 instead of fp16.  A bf16 is the upper half of an fp32, so ONE PRMT
+// both picks the near (or far) half of a (min, max) word for the ray's direction sign and places it in the upper half of
+// a zero word = the decoded fp32 plane offset: 2 instructions per word instead of 3 (PRMT + two HADD2.F32).  8 mantissa
+// bits instead of 11: the outward-rounded boxes are up to 2^-8 of the offset larger, still conservative.
+// Measured on config 2 (profiles/r02_x_bf16_nodes.txt): node step 156 -> 145 instructions, parity suite bit-exact, but
+// k_trace 2.448 -> 2.577 ms: the looser boxes cost more node visits than the decode saves.  Off by default.
+#ifndef K1_BF16
+#define K1_BF16 0
+#endif
 #ifndef K1_PRMT
 #define K1_PRMT 1       // measured on config 2 (profiles/r02_b_sweep.txt): k_trace 2.62 -> 2.54 ms at 7 CTAs per SM
 #endif

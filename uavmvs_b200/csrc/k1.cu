@@ -1073,7 +1073,13 @@ k_trace(TraceArgs a)
     rt.nox = rt.noy = rt.noz = rt.em = 0.0f;
     V3 rd = mk(0.f, 0.f, 0.f);
 #if K1_PRMT
+#if K1_BF16
+    // PRMT selectors of the NEAR plane per axis: bytes {0, 0, lo, hi} of the min half (0x1044) or of the max half (0x3244) of a
+    // (min, max) word = that bf16 offset as an fp32; the far plane's selector is the other one (^ 0x2200)
+    uint32_t selx = 0x1044u, sely = 0x1044u, selz = 0x1044u;
+#else
     uint32_t selx = 0x3210u, sely = 0x3210u, selz = 0x3210u;     // PRMT selectors: (min, max) -> (near, far) per axis
+#endif
 #endif
     uint32_t serviced_idle = 0;
 
@@ -1130,7 +1136,11 @@ k_trace(TraceArgs a)
                 }
                 if (fast) {
 #if K1_PRMT
+#if K1_BF16
+                    selx = rt.rdx < 0.0f ? 0x3244u : 0x1044u; sely = rt.rdy < 0.0f ? 0x3244u : 0x1044u; selz = rt.rdz < 0.0f ? 0x3244u : 0x1044u;
+#else
                     selx = rt.rdx < 0.0f ? 0x1032u : 0x3210u; sely = rt.rdy < 0.0f ? 0x1032u : 0x3210u; selz = rt.rdz < 0.0f ? 0x1032u : 0x3210u;
+#endif
 #endif
                     has_ray = true; hit = false; sp = 0; npend = 0; traversing = true; cur = 0;
                     if (a.rl.tpk) {                                      // start from the packet's entry points
@@ -1168,6 +1178,16 @@ k_trace(TraceArgs a)
                 // pairs).  The error band is folded into the far side: far constants and the ray's tmax are raised by em,
                 // and "tmax~ + em < tmin~" (= g < -em) proves the rejection.
                 const float cfx = crx + rt.em, cfy = cry + rt.em, cfz = crz + rt.em, tmaxe = rt.tmax + rt.em;
+#if K1_BF16
+                const uint32_t fsx = selx ^ 0x2200u, fsy = sely ^ 0x2200u, fsz = selz ^ 0x2200u;
+                #define UAV_SLAB(wx, wy, wz, hit) { \
+                    const float nx = __uint_as_float(__byte_perm((wx), 0u, selx)), fx = __uint_as_float(__byte_perm((wx), 0u, fsx)); \
+                    const float ny = __uint_as_float(__byte_perm((wy), 0u, sely)), fy = __uint_as_float(__byte_perm((wy), 0u, fsy)); \
+                    const float nz = __uint_as_float(__byte_perm((wz), 0u, selz)), fz = __uint_as_float(__byte_perm((wz), 0u, fsz)); \
+                    const float tn = fmaxf(fmaxf(__fmaf_rn(nx, rt.rdx, crx), __fmaf_rn(ny, rt.rdy, cry)), fmaxf(__fmaf_rn(nz, rt.rdz, crz), rt.tmin)); \
+                    const float tf = fminf(fminf(__fmaf_rn(fx, rt.rdx, cfx), __fmaf_rn(fy, rt.rdy, cfy)), fminf(__fmaf_rn(fz, rt.rdz, cfz), tmaxe)); \
+                    hit = !(tf < tn); }
+#else
                 #define UAV_SLAB(wx, wy, wz, hit) { \
                     const uint32_t ux = __byte_perm((wx), 0u, selx), uy = __byte_perm((wy), 0u, sely), uz = __byte_perm((wz), 0u, selz); \
                     const float2 fx = __half22float2(*reinterpret_cast<const __half2 *>(&ux)); \
@@ -1176,6 +1196,7 @@ k_trace(TraceArgs a)
                     const float tn = fmaxf(fmaxf(__fmaf_rn(fx.x, rt.rdx, crx), __fmaf_rn(fy.x, rt.rdy, cry)), fmaxf(__fmaf_rn(fz.x, rt.rdz, crz), rt.tmin)); \
                     const float tf = fminf(fminf(__fmaf_rn(fx.y, rt.rdx, cfx), __fmaf_rn(fy.y, rt.rdy, cfy)), fminf(__fmaf_rn(fz.y, rt.rdz, cfz), tmaxe)); \
                     hit = !(tf < tn); }
+#endif
                 bool h0, h1, h2, h3;
                 UAV_SLAB(ha.x, ha.y, ha.z, h0)
                 UAV_SLAB(ha.w, hb.x, hb.y, h1)
