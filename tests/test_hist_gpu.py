@@ -127,6 +127,63 @@ def test_estimate_capture_difficulty_k7(api, oracle, setup):
     assert q_o.max() > 0 and v_o.min() < 1.5
 
 
+def test_k7_wide_walk_equals_reference_walk_with_ties_and_airspace(api, oracle, monkeypatch):
+    """K7 on the 4-wide tree (k7.cu) against the reference-order closest-hit walk (UAVMVS_K7_EXACT=1) and the oracle, on a
+    tree built to need the fallback: the "airspace" (faces >= mesh_size) holds exact duplicates of every 5th mesh face
+    (closest hits of the two classes at the SAME t: the visiting order decides) and a two-triangle sheet above the block
+    whose diagonal is hit twice within the +-1e-3 barycentric slack; the points sit on axis-aligned faces, so a sixth of
+    the icosphere directions have a zero component (axes dropped in the node test)."""
+    from uavmvs_b200 import scenes
+    sc = scenes.tiny()
+    nv = sc.verts.shape[0]
+    dup = sc.faces[::5]
+    z = float(sc.verts[:, 2].max()) + 7.0
+    lo, hi = sc.verts[:, :2].min(0) - 3.0, sc.verts[:, :2].max(0) + 3.0
+    sheet_v = np.array([[lo[0], lo[1], z], [hi[0], lo[1], z], [hi[0], hi[1], z], [lo[0], hi[1], z]], np.float32)
+    sheet_f = np.array([[nv, nv + 1, nv + 2], [nv, nv + 2, nv + 3]], sc.faces.dtype)
+    verts = np.ascontiguousarray(np.concatenate([sc.verts, sheet_v]).astype(np.float32))
+    faces = np.ascontiguousarray(np.concatenate([sc.faces, dup, sheet_f]).astype(sc.faces.dtype))
+    mesh_size = sc.faces.shape[0]
+    gbvh = api.BVHTree.build_sah(verts, faces)
+    nodes, aabbs, tris, indices = gbvh.export()
+    obvh = oracle.BVH.from_arrays(oracle.TreeArrays(nodes, aabbs, tris, indices))
+    sv = api.sphere_vertices(1.0, 3)
+    kn, kv = oracle.KD.build(sv).export()
+    gkd = api.KDTree.create(kn, kv)
+    n = 1536 + 7                                             # a ragged last block
+    pts, nrm = np.ascontiguousarray(sc.points[:n]), np.ascontiguousarray(sc.normals[:n])
+    out = {}
+    for mode in ("wide", "exact", "wide_small_batches"):
+        if mode == "exact":
+            monkeypatch.setenv("UAVMVS_K7_EXACT", "1")
+        else:
+            monkeypatch.delenv("UAVMVS_K7_EXACT", raising=False)
+        if mode == "wide_small_batches":
+            monkeypatch.setenv("UAVMVS_K7_BATCH", "512")   # several launches, the last one ragged
+        cloud = api.PointCloud.create(pts, nrm)
+        api.estimate_capture_difficulty(sc.max_distance, gbvh, mesh_size, gkd, cloud)
+        out[mode] = cloud.download_attributes()
+    for mode in ("wide", "wide_small_batches"):
+        assert np.array_equal(out[mode][0].view(np.uint32), out["exact"][0].view(np.uint32)), mode    # values: same bits
+        assert np.array_equal(out[mode][1].view(np.uint32), out["exact"][1].view(np.uint32)), mode    # qualities: same bits
+    v_o, q_o = oracle.estimate_capture_difficulty(obvh, sc.max_distance, mesh_size, sv, pts, nrm)
+    assert np.allclose(out["wide"][0], v_o, rtol=1e-5, atol=1e-6) and np.allclose(out["wide"][1], q_o, rtol=1e-5, atol=1e-6)
+    assert q_o.max() > 0
+    # with mesh_size beyond every face the predicate is plain any-hit: the two walks agree there too
+    monkeypatch.delenv("UAVMVS_K7_BATCH", raising=False)
+    res = []
+    for exact in (False, True):
+        if exact:
+            monkeypatch.setenv("UAVMVS_K7_EXACT", "1")
+        else:
+            monkeypatch.delenv("UAVMVS_K7_EXACT", raising=False)
+        cloud = api.PointCloud.create(pts, nrm)
+        api.estimate_capture_difficulty(sc.max_distance, gbvh, faces.shape[0], gkd, cloud)
+        res.append(cloud.download_attributes())
+    assert np.array_equal(res[0][0].view(np.uint32), res[1][0].view(np.uint32))
+    assert np.array_equal(res[0][1].view(np.uint32), res[1][1].view(np.uint32))
+
+
 def test_batched_k4_k6_equal_single_calls(api, oracle, setup):
     """uavmvs_populate_spherical_histogram_batch / _evaluate_spherical_histogram_batch (config 4: one call per
     batch of candidate voxels) against the per-position entry points and the oracle."""

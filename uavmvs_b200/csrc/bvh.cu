@@ -227,7 +227,9 @@ __global__ void k_check_tree(const uint4 * __restrict__ nodes, const float * __r
 
 // Exact leaf boxes addressed by the leaf's first triangle (k_trace re-checks a deferred leaf against its own box once one
 // of its triangles is accepted; the pending entry only carries first / count).
-__global__ void k_leaf_boxes(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n, float4 * __restrict__ out)
+// max_diag: largest box diagonal over the leaves, as float bits (positive floats order like their bits); k7.cu's margin
+__global__ void k_leaf_boxes(const uint4 * __restrict__ nodes, const float * __restrict__ aabbs, uint32_t n, float4 * __restrict__ out,
+    uint32_t * __restrict__ max_diag)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -236,6 +238,9 @@ __global__ void k_leaf_boxes(const uint4 * __restrict__ nodes, const float * __r
     const float * p = aabbs + 6 * (size_t)i;
     out[2 * (size_t)nd.x] = make_float4(p[0], p[1], p[2], p[3]);
     out[2 * (size_t)nd.x + 1] = make_float4(p[4], p[5], 0.0f, 0.0f);
+    const float dx = p[3] - p[0], dy = p[4] - p[1], dz = p[5] - p[2];
+    const float dg = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (dg == dg) atomicMax(max_diag, __float_as_uint(fmaxf(dg, 0.0f)));
 }
 
 // Per-triangle constants with the reference's operation order (libs/acc/primitives.h:
@@ -346,7 +351,13 @@ int finalize_layout(uavmvs_bvh * b)
     if (b->nested) {
         UAV_CUDA(cudaMalloc(&b->leafbox, sizeof(float4) * 2 * (size_t)t));
         UAV_CUDA(cudaMemset(b->leafbox, 0, sizeof(float4) * 2 * (size_t)t));
-        k_leaf_boxes<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, n, b->leafbox);
+        uint32_t * d_diag = nullptr, h_diag = 0;
+        UAV_CUDA(cudaMalloc(&d_diag, sizeof(uint32_t)));
+        UAV_CUDA(cudaMemset(d_diag, 0, sizeof(uint32_t)));
+        k_leaf_boxes<<<divup(n, 256), 256>>>(b->nodes, b->aabbs, n, b->leafbox, d_diag);
+        UAV_CUDA(cudaMemcpy(&h_diag, d_diag, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        cudaFree(d_diag);
+        memcpy(&b->max_leaf_diag, &h_diag, sizeof(float));
     }
     k_build_tris<<<divup(t, 256), 256>>>(b->tris, t, b->ptris);
     UAV_CUDA(cudaGetLastError());

@@ -111,6 +111,7 @@ struct uavmvs_bvh {
     uint32_t depth;     // upper bound of the binary depth (2 x levels of the wide collapse), checked against the stacks at upload
     uint32_t nested;    // child boxes inside parent boxes, leaf boxes tight, leaves <= 31 triangles (checked at upload)
     uint32_t max_leaf;
+    float max_leaf_diag = 0.0f;   // nested trees: largest leaf-box diagonal (k7.cu: how far behind a hit its leaf's box can begin)
 };
 
 struct uavmvs_kdtree {
@@ -244,6 +245,9 @@ struct HistJob {
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
     uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hist_job = nullptr);
+// k7.cu: K7 on the 4-wide tree (nested trees); 1 / 0 and the launch
+int k7_wide_available(const uavmvs_bvh * bvh);
+int k7_wide(cudaStream_t s, float max_distance, const uavmvs_bvh * bvh, uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud);
 int k1_counters(unsigned long long out[4], int reset);
 int k1_profile_enable(int on);
 int k1_profile(float ms[5]);

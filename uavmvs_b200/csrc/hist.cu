@@ -527,6 +527,9 @@ int uavmvs_estimate_capture_difficulty(void * stream, float max_distance, const 
     uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud)
 {
     UAV_REQUIRE(bvh && kd && cloud, "null argument");
+    // nested trees: the wide walk of k7.cu (same results; UAVMVS_K7_EXACT=1 keeps the reference walk for every ray)
+    if (uav::k7_wide_available(bvh) && !getenv("UAVMVS_K7_EXACT"))
+        return uav::k7_wide((cudaStream_t)stream, max_distance, bvh, mesh_size, kd, cloud);
     k_estimate_capture_difficulty<<<divup(cloud->n, 64), 64, 0, uav::counted((cudaStream_t)stream)>>>(
         view_of(bvh), kd_view(kd), mesh_size, max_distance, cloud->vertices, cloud->normals, cloud->n,
         cloud->values, cloud->qualities);
