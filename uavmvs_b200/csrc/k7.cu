@@ -43,8 +43,19 @@ constexpr int K7_WARPS = 4;
 constexpr int K7_PEND = 6;            // deferred leaves per lane
 constexpr int K7_REFILL = 20;         // refill when this many lanes are idle (k_trace's measured optimum)
 constexpr int K7_TRI = 12;            // triangle phase when this many lanes hold a leaf
-constexpr int K7_STEPS = 6;           // node steps between two rounds of bookkeeping
-constexpr uint32_t K7_UNITS_PER_GRAB = 8;   // (block, direction) units per atomic
+constexpr int K7_STEPS = 12;          // node steps between two rounds of bookkeeping (tools/sweep_k7.sh: 6 -> 40.8 ms per 2^18 points, 12 -> 39.0, 24 -> 39.1;
+                                      // refill 4 / 8 / 12 / 20 / 24 -> 43.4 / 42.2 / 41.6 / 40.8 / 39.0 with 16 steps)
+constexpr uint32_t K7_UNITS_PER_GRAB = 8;   // (block, direction) units per atomic = blocks per group
+// Unit order: groups of 8 consecutive 32-point blocks; within a group direction-major, so that one grab is ONE direction over
+// 8 neighbouring blocks: the rays a warp holds are parallel and start next to each other (Z-ordered cloud), like the rays of
+// one block towards one camera in K1.  (Block-major order, a warp walking one block through consecutive icosphere indices,
+// mixes unrelated directions in a warp.)
+__device__ __forceinline__ void k7_unit(uint32_t u, uint32_t S, uint32_t & b, uint32_t & i)
+{
+    const uint32_t per = K7_UNITS_PER_GRAB * S, g = u / per, r = u - g * per;
+    i = r / K7_UNITS_PER_GRAB;
+    b = g * K7_UNITS_PER_GRAB + (r - i * K7_UNITS_PER_GRAB);
+}
 
 struct K7Args {
     BvhView bvh;
@@ -57,6 +68,7 @@ struct K7Args {
     float margin;                     // M above: 1.02 x the largest leaf-box diagonal of the tree + 1e-3
     uint8_t * status;                 // [kd.n][np] : 0 not cast, 1 mesh, 2 free, 3 reference walk needed
     uint32_t * work;                  // unit counter
+    int refill, steps, tri;           // K7_REFILL / K7_STEPS / K7_TRI (UAVMVS_K7_REFILL / _STEPS / _TRI for sweeps)
 };
 
 // the leaf's stored box against the reference's slab test at [tmin, tmax]; `fast` = the filtered form may be used
@@ -77,7 +89,7 @@ k_k7_trace(K7Args a)
     const uint32_t tid = threadIdx.x, lane = tid & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t S = a.kd.n;
-    const uint32_t total_units = ((a.np + 31) / 32) * S;    // unit = (32-point block, direction), block-major
+    const uint32_t total_units = (((a.np + 31) / 32 + K7_UNITS_PER_GRAB - 1) / K7_UNITS_PER_GRAB) * K7_UNITS_PER_GRAB * S;   // blocks beyond the last hold no points
     const float l = a.max_distance;
     uint32_t stack[K1_STACK];
     RayT rt; V3 rd = mk(0.f, 0.f, 1.f), rq = rd;
@@ -93,7 +105,7 @@ k_k7_trace(K7Args a)
 
     for (;;) {
         const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
-        if (idle != serviced_idle && __popc(idle) >= K7_REFILL) {
+        if (idle != serviced_idle && __popc(idle) >= a.refill) {
             // ---------------- refill idle lanes: the next cast (point, direction) pairs in unit order ----------------
             const uint32_t need = __popc(idle), rank = __popc(idle & lt_mask);
             uint32_t given = 0, my_unit = 0, my_p = 0; bool mine = false;
@@ -107,7 +119,7 @@ k_k7_trace(K7Args a)
                         unit = g; unit_end = min(g + K7_UNITS_PER_GRAB, total_units);
                     }
                     cu = unit++;
-                    const uint32_t b = cu / S, i = cu - b * S;
+                    uint32_t b, i; k7_unit(cu, S, b, i);
                     const uint32_t pl = b * 32 + lane;                   // lane = point of the block
                     bool cast = false;
                     if (pl < a.np) {                                     // kernels.cu:468-470
@@ -124,7 +136,8 @@ k_k7_trace(K7Args a)
                 given += take;
             }
             if (mine) {
-                const uint32_t b = my_unit / S, i = my_unit - b * S, pl = b * 32 + my_p;
+                uint32_t b, i; k7_unit(my_unit, S, b, i);
+                const uint32_t pl = b * 32 + my_p;
                 out_idx = i * a.np + pl;
                 const V3 o = ld3(a.verts[a.p0 + pl]);
                 rd = normalized(ld3(__ldg(a.kd.verts + i)));
@@ -159,7 +172,7 @@ k_k7_trace(K7Args a)
 
         // ---------------- node steps: k_trace's conservative test on the Node80 tree, original interval throughout ----------------
         #pragma unroll 1
-        for (int step = 0; step < K7_STEPS; ++step) {
+        for (int step = 0; step < a.steps; ++step) {
             if (traversing && npend <= K7_PEND - 4) {
                 const Node80 * np = a.bvh.wide80 + cur;
                 const float4 c4 = __ldg(&np->c);
@@ -207,7 +220,7 @@ k_k7_trace(K7Args a)
             if (pmask) {
                 const uint32_t tmask = __ballot_sync(0xffffffffu, traversing);
                 const uint32_t full = __ballot_sync(0xffffffffu, npend > K7_PEND - 4);
-                if (__popc(pmask) >= K7_TRI || full || !tmask) {
+                if (__popc(pmask) >= a.tri || full || !tmask) {
                     if (npend > 0) {
                         Ray ray; ray.o = mk(rt.ox, rt.oy, rt.oz); ray.d = rd; ray.tmin = rt.tmin; ray.tmax = rt.tmax;
                         for (uint32_t p = 0; p < npend; ++p) {
@@ -322,7 +335,7 @@ int k7_wide(cudaStream_t s, float max_distance, const uavmvs_bvh * bvh, uint32_t
     // points per launch: one status byte per (direction, point); 2^18 points x 1272 directions = 333 MB
     uint32_t batch = 1u << 18;
     { const char * e = getenv("UAVMVS_K7_BATCH"); if (e && atoi(e) >= 32) batch = ((uint32_t)atoi(e) + 31u) / 32u * 32u; }
-    while ((unsigned long long)batch * S >= (1ull << 32)) batch /= 2;      // out_idx and the unit counter are 32-bit
+    while ((unsigned long long)(batch + 32ull * K7_UNITS_PER_GRAB) * S >= (1ull << 32)) batch /= 2;      // out_idx and the unit counter are 32-bit
     const size_t need = (size_t)std::min(batch, (n + 31u) / 32u * 32u) * S;
     if (need > k.status_cap) {
         if (k.status) UAV_CUDA(cudaFree(k.status));
@@ -335,6 +348,10 @@ int k7_wide(cudaStream_t s, float max_distance, const uavmvs_bvh * bvh, uint32_t
         a.p0 = p0; a.np = std::min(batch, n - p0); a.mesh_size = mesh_size; a.max_distance = max_distance;
         a.margin = 1.02f * bvh->max_leaf_diag + 1e-3f;
         a.status = k.status; a.work = k.work;
+        a.refill = K7_REFILL; a.steps = K7_STEPS; a.tri = K7_TRI;
+        if (const char * e = getenv("UAVMVS_K7_REFILL")) if (atoi(e) >= 1 && atoi(e) <= 32) a.refill = atoi(e);
+        if (const char * e = getenv("UAVMVS_K7_STEPS")) if (atoi(e) >= 1 && atoi(e) <= 64) a.steps = atoi(e);
+        if (const char * e = getenv("UAVMVS_K7_TRI")) if (atoi(e) >= 1 && atoi(e) <= 32) a.tri = atoi(e);
         UAV_CUDA(cudaMemsetAsync(k.status, 0, (size_t)a.np * S, s));
         UAV_CUDA(cudaMemsetAsync(k.work, 0, sizeof(uint32_t), s));
         k_k7_trace<<<k.grid, K7_WARPS * 32, 0, uav::counted(s)>>>(a);
