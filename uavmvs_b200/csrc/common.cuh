@@ -244,7 +244,15 @@ struct HistJob {
 // observations, [3] += (point, view) pairs that survive the block-level cull.
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
-    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hist_job = nullptr);
+    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hist_job = nullptr, const struct K1AfterRetire * after = nullptr);
+// Optional continuation of a populate launch (eval.cu: K2 + K3 + K8 of a block range while the next range retires).  On the
+// LAST view batch k_retire runs in `chunks` block ranges on the caller's stream; after each range `fn(ctx, side, block0,
+// nblocks)` enqueues its work on `side`, which waits for that range; the caller's stream waits for `side` before
+// launch_k1 returns.  ev: chunks + 1 events (no timing).
+struct K1AfterRetire {
+    uint32_t chunks; cudaStream_t side; cudaEvent_t * ev;
+    int (*fn)(void * ctx, cudaStream_t side, uint32_t block0, uint32_t nblocks); void * ctx;
+};
 // k7.cu: K7 on the 4-wide tree (nested trees); 1 / 0 and the launch
 int k7_wide_available(const uavmvs_bvh * bvh);
 int k7_wide(cudaStream_t s, float max_distance, const uavmvs_bvh * bvh, uint32_t mesh_size, const uavmvs_kdtree * kd, uavmvs_cloud * cloud);

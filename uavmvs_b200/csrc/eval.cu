@@ -209,6 +209,7 @@ struct Scratch {   // per-process scratch on the device (views, reduction accumu
     double * score_dev = nullptr, * h_score = nullptr;                     // fold result + one record (single GPU); pinned copy
     bool ev_valid = false;
     cudaStream_t copy_stream = nullptr;                                    // result copies of evaluate_trajectory_to_host
+    cudaStream_t side_stream = nullptr; cudaEvent_t ev_side[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // K2 + K3 + K8 beside k_retire (UAVMVS_OVERLAP_K3)
     cudaEvent_t ev_copy[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 static thread_local Scratch g_scratch;
@@ -394,6 +395,24 @@ __global__ void k_fold_score(const double * recs, int world, double * out)
     out[0] = sum; out[1] = pts; out[2] = mn; out[3] = mx; out[4] = rays; out[5] = obs; out[6] = cull; out[7] = pairs;
 }
 
+// K2 + K3 + K8 of a block range as soon as that range has retired (K1AfterRetire), and the range's recon copy behind it
+struct AfterCtx { const EvalCall * c; uint32_t k; };
+static int run_evaluation_after_retire(void * ctx, cudaStream_t side, uint32_t b0, uint32_t nbk)
+{
+    AfterCtx * a = static_cast<AfterCtx *>(ctx);
+    const EvalCall & c = *a->c;
+    Scratch & g = g_scratch;
+    if (int rc = launch_sort_eval(side, true, true, c.obs, c.recons, c.target_recon, c.wrecons, false, b0, nbk)) return rc;
+    if (c.h_recons && a->k < 4) {
+        const size_t p0 = (size_t)b0 * 32, p1 = min((size_t)(b0 + nbk) * 32, (size_t)c.obs->num_cols);
+        UAV_CUDA(cudaEventRecord(g.ev_copy[1 + a->k], side));
+        UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[1 + a->k], 0));
+        UAV_CUDA(cudaMemcpyAsync(c.h_recons + p0, c.recons->data + p0, 4 * (p1 - p0), cudaMemcpyDeviceToHost, g.copy_stream));
+    }
+    ++a->k;
+    return 0;
+}
+
 static int run_evaluation(const EvalCall & c, float out3[3], uint64_t stats[4], double score[UAVMVS_SCORE_DOUBLES])
 {
     UAV_REQUIRE(c.bvh && c.cloud && c.obs && c.recons && c.wrecons, "null handle");
@@ -409,8 +428,21 @@ static int run_evaluation(const EvalCall & c, float out3[3], uint64_t stats[4], 
     if (need_stats) UAV_CUDA(cudaMemsetAsync(g.stats, 0, 4 * sizeof(unsigned long long), s));
     g.ev_valid = false;
     UAV_CUDA(cudaEventRecord(g.ev[0], s));
+    // Opt-in, measured slower (profiles/r02_aa_overlap_k3.txt): k_retire in four block ranges with K2 + K3 + K8 of each finished
+    // range on a side stream.  retire + K3 0.887 ms back to back, 0.957 ms overlapped (step 4.226 -> 4.305 ms): k_sort_eval
+    // already fills the issue slots, and four launches of each cost more than the overlap returns.
+    const bool overlap = getenv("UAVMVS_OVERLAP_K3") != nullptr;
+    AfterCtx actx{&c, 0};
+    K1AfterRetire after{4, nullptr, g.ev_side, run_evaluation_after_retire, &actx};
+    if (overlap) {
+        if (!g.side_stream) {
+            UAV_CUDA(cudaStreamCreateWithFlags(&g.side_stream, cudaStreamNonBlocking));
+            for (auto & e : g.ev_side) UAV_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        }
+        after.side = g.side_stream;
+    }
     int rc = launch_k1(s, 1, c.d_views, c.num_views, c.max_distance, c.width, c.height, c.bvh, c.cloud, c.obs,
-        need_stats ? g.stats : nullptr);
+        need_stats ? g.stats : nullptr, nullptr, overlap ? &after : nullptr);
     if (rc) return rc;
     UAV_CUDA(cudaEventRecord(g.ev[1], s));
     UAV_CUDA(cudaEventRecord(g.ev[2], s));      // K2 is fused into the next launch
@@ -421,7 +453,7 @@ static int run_evaluation(const EvalCall & c, float out3[3], uint64_t stats[4], 
         UAV_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_copy[0], 0));
         UAV_CUDA(cudaMemcpyAsync(c.h_num_rows, c.obs->num_rows, 4 * (size_t)c.obs->num_cols, cudaMemcpyDeviceToHost, g.copy_stream));
     }
-    const uint32_t nblocks = divup(c.obs->num_cols, 32), chunks = c.h_recons && nblocks >= 64 ? 4 : 1;
+    const uint32_t nblocks = divup(c.obs->num_cols, 32), chunks = overlap ? 0 : (c.h_recons && nblocks >= 64 ? 4 : 1);
     for (uint32_t k = 0; k < chunks; ++k) {
         const uint32_t b0 = (uint32_t)((uint64_t)nblocks * k / chunks), b1 = (uint32_t)((uint64_t)nblocks * (k + 1) / chunks);
         rc = launch_sort_eval(s, true, true, c.obs, c.recons, c.target_recon, c.wrecons, false, b0, b1 - b0);

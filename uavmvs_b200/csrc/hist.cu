@@ -270,6 +270,7 @@ k_evaluate_spherical_histogram_batch(const uint32_t * __restrict__ bits, uint32_
         if (sum < vmin) { vmin = sum; imin = pix; }          // pixels ascend per thread: first occurrence
         if (sum > vmax) { vmax = sum; imax = pix; }
     }
+    if (!best_min) return;                                   // images only (single-position entry point): uniform over the CTA
     // lexicographic (value, index) reduction keeps the first occurrence
     for (int o = 16; o > 0; o >>= 1) {
         float ov = __shfl_xor_sync(0xffffffffu, vmin, o); uint32_t oi = __shfl_xor_sync(0xffffffffu, imin, o);
@@ -503,13 +504,10 @@ int uavmvs_evaluate_spherical_histogram(void * stream, const float calib[9], int
         // bit matrix
         const uint32_t * bits = nullptr;
         if (frustum_bits(const_cast<uavmvs_kdtree *>(kd), calib, width, height, hist->width, hist->height, s, &bits)) return 1;
-        unsigned long long * d_best;
-        UAV_CUDA(cudaMallocAsync(&d_best, 2 * sizeof(unsigned long long), s));
         const uint32_t parts = max(1u, npix / EVB_THREADS);
         k_evaluate_spherical_histogram_batch<<<dim3(1, parts), EVB_THREADS, words * 32 * sizeof(float), uav::counted(s)>>>(bits, words, npix,
-            sphere_hist->data, S, hist->data, d_best, d_best + 1, nullptr);
+            sphere_hist->data, S, hist->data, nullptr, nullptr, nullptr);   // the image only: no extrema, nothing to allocate
         UAV_CUDA(cudaGetLastError());
-        UAV_CUDA(cudaFreeAsync(d_best, s));
         return 0;
     }
     float * d_K;

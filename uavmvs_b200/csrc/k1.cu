@@ -1290,6 +1290,7 @@ __global__ void k_trace_exact(TraceArgs a, uint32_t total)
 struct RetireArgs {
     const float4 * __restrict__ verts; const float4 * __restrict__ normals;
     uint32_t n, num_blocks;
+    uint32_t block0 = 0;             // k_retire: first block of this launch (num_blocks = end of its range)
     RayList rl;
     float max_distance;
     float4 * obs; uint32_t * num_rows; uint32_t max_rows; uint32_t stride;   // stride in float4
@@ -1314,7 +1315,7 @@ k_retire(RetireArgs a)
     __shared__ float4 s_nrm[K1_WARPS][32], s_rx[K1_WARPS][32], s_ry[K1_WARPS][32];
     __shared__ uint32_t s_cnt[K1_WARPS][32];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t blk = blockIdx.x * K1_WARPS + w;
+    const uint32_t blk = a.block0 + blockIdx.x * K1_WARPS + w;
     if (blk >= a.num_blocks) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t id = blk * 32 + lane;
@@ -1587,13 +1588,13 @@ static size_t ray_budget()
 
 int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_views,
     float max_distance, int width, int height, const uavmvs_bvh * bvh, const uavmvs_cloud * cloud,
-    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hj)
+    uavmvs_obs * obs, unsigned long long * d_stats, const HistJob * hj, const K1AfterRetire * after)
 {
     UAV_REQUIRE(bvh && cloud && (obs || hj), "null handle");
     UAV_REQUIRE(hj || obs->num_cols == cloud->n, "obs_rays columns != cloud vertices");
     if (hj) { width = 0; height = 0; }                   // bare positions: no image test anywhere
     UAV_REQUIRE(bvh->num_tris < (1u << 25), "more than 2^25 triangles");
-    if (num_views == 0) return 0;
+    if (num_views == 0) return (populate && after) ? after->fn(after->ctx, s, 0, cloud->num_blocks) : 0;
     K1Scratch & k = g_k1;
     const uint32_t nb = cloud->num_blocks;
     if (!k.work) {
@@ -1688,6 +1689,7 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
     const bool no_readback = hj && hj->no_readback && worst <= min((unsigned long long)ray_budget(), 1ull << 27);
     if (no_readback) speculate = false;
     else if (num_views > 1 && k.plan_views == num_views && k.plan_blocks == nb) { speculate = false; if (make_plan()) return 1; }
+    bool after_done = false;
     uint32_t v0 = 0;
     while (v0 < num_views) {
         uint32_t v1 = num_views;
@@ -1819,9 +1821,31 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
                 ra.obs = obs->data; ra.num_rows = obs->num_rows; ra.max_rows = obs->max_rows;
                 ra.stride = (uint32_t)(obs->pitch / sizeof(float4));
                 ra.dirty = obs->dirty;
-                if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
-                else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
-                UAV_CUDA(cudaGetLastError());
+                if (populate && after && after->chunks > 1 && v1 == num_views && nb >= 64 * after->chunks) {
+                    // last batch: every column is complete once its block has retired -> hand the ranges on one by one
+                    for (uint32_t c = 0; c < after->chunks; ++c) {
+                        const uint32_t b0 = (uint32_t)((uint64_t)nb * c / after->chunks), b1 = (uint32_t)((uint64_t)nb * (c + 1) / after->chunks);
+                        ra.block0 = b0; ra.num_blocks = b1;
+                        k_retire<true><<<divup(b1 - b0, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
+                        UAV_CUDA(cudaGetLastError());
+                        UAV_CUDA(cudaEventRecord(after->ev[c], s));
+                        UAV_CUDA(cudaStreamWaitEvent(after->side, after->ev[c], 0));
+                        if (int rc = after->fn(after->ctx, after->side, b0, b1 - b0)) return rc;
+                    }
+                    after_done = true;
+                    UAV_CUDA(cudaEventRecord(after->ev[after->chunks], after->side));
+                    UAV_CUDA(cudaStreamWaitEvent(s, after->ev[after->chunks], 0));
+                } else {
+                    if (populate && after && v1 == num_views) {          // too small to split: the continuation follows on the same stream
+                        k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
+                        UAV_CUDA(cudaGetLastError());
+                        if (int rc = after->fn(after->ctx, s, 0, nb)) return rc;
+                        after_done = true;
+                    }
+                    else if (populate) k_retire<true><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
+                    else k_retire<false><<<divup(nb, K1_WARPS), K1_WARPS * 32, 0, uav::counted(s)>>>(ra);
+                    UAV_CUDA(cudaGetLastError());
+                }
             }
         }
         if (k1_mark(k, s, 5)) return 1;
@@ -1835,6 +1859,8 @@ int launch_k1(cudaStream_t s, int populate, const float * d_views, uint32_t num_
         }
         v0 = v1;
     }
+    // the continuation runs exactly when the columns are final, also when the last batch held no candidate pair
+    if (populate && after && !after_done) { if (int rc = after->fn(after->ctx, s, 0, nb)) return rc; }
     return 0;
 }
 
