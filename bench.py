@@ -623,20 +623,31 @@ def extras_config34(a, torch, api, stream, blk, line):
     vol_w = apps.GuidanceVolume(scn, bvh, cloud4, kd, S, grid=a.grid, batch=8192)
     vol_w.subsample(8192)
     vol_w.run(stream)                                   # warm-up (bit matrix, first buffers)
-    r1 = vol.run(stream)                                # untimed: the ray buffers grow to the largest batch of THIS sample
-    torch.cuda.synchronize()                            # (the library reallocates them inside a call when a batch needs more)
+    # two identical runs under the clock sampler: the first lets the ray buffers grow to the largest batch of THIS sample (the
+    # library reallocates them inside a call when a batch needs more), the second is the reported one.  This block keeps
+    # k_trace busy for ~1 s, unlike the 4 ms steps above: sustained clocks and throttle reasons are part of the record
+    torch.cuda.synchronize()
+    sampler4 = ClockSampler(visible_gpu_index(int(os.environ.get("LOCAL_RANK", "0"))))
+    sampler4.start()
+    f0, f1 = ev(), ev()
+    f0.record(stream)
+    r1 = vol.run(stream)
+    f1.record(stream)
+    torch.cuda.synchronize()
     api.k1_counters()
     e0, e1 = ev(), ev()
     e0.record(stream)
-    r2 = vol.run(stream)                                # timed: the same sample again, steady state
+    r2 = vol.run(stream)
     e1.record(stream)
     torch.cuda.synchronize()
+    clocks4 = sampler4.stop()
     rays4 = api.k1_counters()[3]
     ms4 = e0.elapsed_time(e1)
     out["config4_us_per_position"] = 1e3 * ms4 / npos
     out["config4"] = {"positions": npos, "of_free_space_positions": vol.free_total, "grid": a.grid, "ms": ms4, "rays": int(rays4),
                       "rays_per_s": rays4 / (ms4 / 1e3), "crc32_min_argmin_max_argmax": r1["crc32"],
                       "reproducible": r1["crc32"] == r2["crc32"], "positions_with_signal": int((r1["max"] > 0).sum()),
+                      "ms_first_run": f0.elapsed_time(f1), "clocks": clocks4,
                       "what": "generate_guidance_volume.cu:128-275, evenly strided sample of the free-space voxels of the 128^3 grid "
                               "x all points (values U[0,1.2], qualities U[0,1], seed 4), batches of 8192, wall of the event pair "
                               "(includes the per-batch result copies); second of two identical runs, so that no buffer grows "
