@@ -652,6 +652,40 @@ def extras_config34(a, torch, api, stream, blk, line):
                               "x all points (values U[0,1.2], qualities U[0,1], seed 4), batches of 8192, wall of the event pair "
                               "(includes the per-batch result copies); second of two identical runs, so that no buffer grows "
                               "inside the timed region"}
+    del vol, vol_w, cloud4
+    # ---- K7 estimate_capture_difficulty on a 2^18-point sample of the cloud: wide-node walk, and the
+    # reference-order walk of every ray (UAVMVS_K7_EXACT=1) as the checker and the comparison
+    m7 = min(len(pts), 1 << 18)
+    p7, n7 = np.ascontiguousarray(pts[:m7]), np.ascontiguousarray(nrm[:m7])
+    dirs = sv / np.linalg.norm(sv, axis=1, keepdims=True)
+    rays7 = int(sum(int(((n7[i:i + 65536] @ dirs.T) >= 0.087).sum()) for i in range(0, m7, 65536)))
+    res7, ms7 = {}, {}
+    for mode in ("wide", "exact"):
+        if mode == "exact":
+            os.environ["UAVMVS_K7_EXACT"] = "1"
+        c7 = api.PointCloud.create(p7, n7)
+        best = None
+        for _ in range(3):
+            e0, e1 = ev(), ev()
+            e0.record(stream)
+            api.estimate_capture_difficulty(sc.max_distance, bvh, sc.num_tris, kd, c7, stream=stream)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            best = e0.elapsed_time(e1) if best is None else min(best, e0.elapsed_time(e1))
+        ms7[mode] = best
+        res7[mode] = c7.download_attributes()
+        os.environ.pop("UAVMVS_K7_EXACT", None)
+        del c7
+    same7 = bool(np.array_equal(res7["wide"][0].view(np.uint32), res7["exact"][0].view(np.uint32))
+                 and np.array_equal(res7["wide"][1].view(np.uint32), res7["exact"][1].view(np.uint32)))
+    out["k7_closest_hit_rays_per_s"] = rays7 / (ms7["wide"] / 1e3)
+    out["k7"] = {"points": m7, "directions": int(S), "rays": rays7, "ms": ms7["wide"], "ms_reference_order_walk": ms7["exact"],
+                 "bits_equal_to_reference_order_walk": same7,
+                 "what": "kernels.cu:448-494 on the first 2^18 points of the cloud, mesh_size = all faces; best of 3 calls, CUDA events; "
+                         "rays counted on the host (ctheta >= 0.087, float64 dot products: +- a few of 1e8)"}
+    if not same7:
+        print("bench.py: K7 wide-node walk differs from the reference-order walk", file=sys.stderr)
+        sys.exit(1)
     line["extra"] = out
 
 
