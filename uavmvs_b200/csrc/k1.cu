@@ -53,8 +53,24 @@ constexpr int K1_STEPS = K1_STEPS_N;     // node steps between two rounds of war
 // (centre c, radius r) can pass the exact cull of kernels.cu:164-167 (range, image bounds).
 // Margins are 100x above fp32 rounding of the exact test, so a rejected group is rejected
 // point by point by the exact arithmetic as well.
+// Upper bound of sigma_max(R)^2, R = the 3 x 3 part of w2c: largest Gershgorin row sum of R^T R.  A point at distance <= r
+// from the sphere's centre moves by at most sigma_max r in camera space; for a rotation R^T R = I and the bound is 1 (the
+// Frobenius norm used before is sqrt 3: every block counted as 1.73x its size, and 41 % of the pairs queued for the exact
+// cull then failed its image test).  Valid for any matrix; the caller's 1.001 covers the rounding.
+__device__ __forceinline__ float view_sigma2(const float * __restrict__ view)
+{
+    const float * W = view + 3;
+    const float m00 = W[0] * W[0] + W[4] * W[4] + W[8] * W[8], m11 = W[1] * W[1] + W[5] * W[5] + W[9] * W[9];
+    const float m22 = W[2] * W[2] + W[6] * W[6] + W[10] * W[10];
+    const float m01 = fabsf(W[0] * W[1] + W[4] * W[5] + W[8] * W[9]), m02 = fabsf(W[0] * W[2] + W[4] * W[6] + W[8] * W[10]);
+    const float m12 = fabsf(W[1] * W[2] + W[5] * W[6] + W[9] * W[10]);
+    const float g = fmaxf(fmaxf(m00 + m01 + m02, m01 + m11 + m12), m02 + m12 + m22);
+    return (g == g) ? g : UAV_INF;                        // NaN: no bound, nothing is ever rejected
+}
+
+// sig2 = view_sigma2(view) (a per-view constant: k_view_masks computes it once per view and hands it round by shuffle)
 __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view, float4 sph,
-    float max_distance, int width, int height, bool * inside = nullptr)
+    float max_distance, int width, int height, float sig2, bool * inside = nullptr)
 {
     if (inside) *inside = false;
     float dx = view[0] - sph.x, dy = view[1] - sph.y, dz = view[2] - sph.z;
@@ -62,17 +78,16 @@ __device__ __forceinline__ bool block_view_maybe(const float * __restrict__ view
     if (D * 0.99999f - sph.w >= max_distance * 1.00001f) return false;
     if (width <= 0) return true;                          // bare candidate position (histogram jobs): no image test
     const float * W = view + 3; const float * K = view + 19;
-    float q[3], e2 = 0.0f, fro2 = 0.0f;
+    float q[3], e2 = 0.0f;
     #pragma unroll
     for (int i = 0; i < 3; ++i) {
         float a = W[4 * i] * sph.x, b = W[4 * i + 1] * sph.y, c = W[4 * i + 2] * sph.z, d = W[4 * i + 3];
         q[i] = a + b + c + d;
         float e = 1e-6f * (fabsf(a) + fabsf(b) + fabsf(c) + fabsf(d));
         e2 += e * e;
-        fro2 += W[4 * i] * W[4 * i] + W[4 * i + 1] * W[4 * i + 1] + W[4 * i + 2] * W[4 * i + 2];
     }
     float qn = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);
-    float rho = sph.w * sqrtf(fro2) * 1.001f + sqrtf(e2) + 1e-4f * (qn + 1.0f);
+    float rho = sph.w * sqrtf(sig2) * 1.001f + sqrtf(e2) + 1e-4f * (qn + 1.0f);
     float k2n = sqrtf(K[6] * K[6] + K[7] * K[7] + K[8] * K[8]);
     float p2 = K[6] * q[0] + K[7] * q[1] + K[8] * q[2];
     if (!(p2 - k2n * rho > 0.0f)) return true;          // ball not entirely in front: undecided
@@ -128,8 +143,9 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
         float4 t = __ldg(reinterpret_cast<const float4 *>(src) + i);
         view[4 * i] = t.x; view[4 * i + 1] = t.y; view[4 * i + 2] = t.z; view[4 * i + 3] = t.w;
     }
+    const float sig2 = width > 0 ? view_sigma2(view) : 0.0f;          // bare positions (histogram jobs) have no camera
     for (uint32_t sb = sb0; sb < min(sb0 + K1_SB_PER_WARP, num_super); ++sb) {
-        bool cand = v < num_views && block_view_maybe(view, __ldg(super_spheres + sb), max_distance, width, height);
+        bool cand = v < num_views && block_view_maybe(view, __ldg(super_spheres + sb), max_distance, width, height, sig2);
         uint32_t m = __ballot_sync(0xffffffffu, cand);
         uint32_t mine = 0, mine_in = 0;
         const uint32_t b = sb * 32 + lane;
@@ -140,7 +156,8 @@ k_view_masks(const float * __restrict__ views, uint32_t num_views, const float4 
             const int j = __ffs(m) - 1; m &= m - 1;
             const float * vj = views + (size_t)(blockIdx.x * 32 + j) * UAVMVS_VIEW_FLOATS;   // uniform address
             bool in = false;
-            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height, &in)
+            const float sj = __shfl_sync(0xffffffffu, sig2, j);
+            bool c = b < num_blocks && block_view_maybe(vj, bs, max_distance, width, height, sj, &in)
                 && !block_backfacing(vj, bs, bc, bn);
             uint32_t word = __ballot_sync(0xffffffffu, c);
             uint32_t word_in = __ballot_sync(0xffffffffu, c && in);
