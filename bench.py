@@ -39,7 +39,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "occlusion_rays_per_s"
 UNIT = "rays/s"
-CHUNK = 1024          # points per interleaved shard chunk of the strong-scaling split (= one 1024-point super-block)
+CHUNK = 1024          # --shard-chunk's natural unit (one 1024-point super-block); tools/dev_shard_cull.py's default
 L2_NOTE = "GPU arm: L2 flushed between steps (256 MiB fill, outside the events); CPU arm: n/a"
 CONFIGS = {
     2: dict(tris=1_000_000, points=1_000_000, views=2000, extent=256.0, scaling="weak"),
@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--strong-steps", type=int, default=5)
     ap.add_argument("--positions", type=int, default=0, help="config 4: number of candidate positions (0 = steps x 8192)")
     ap.add_argument("--grid", type=int, default=128, help="config 4: voxels per axis")
+    ap.add_argument("--shard-chunk", type=int, default=0, help="strong scaling: 0 = contiguous Z-order ranges per rank, C = interleaved C-point chunks")
     a = ap.parse_args()
     c = CONFIGS[a.config]
     a.tris, a.points, a.views = a.tris or c["tris"], a.points or c["points"], a.views or c["views"]
@@ -99,18 +100,26 @@ def make_scene(a):
 
 def rank_cloud(a, sc, rank, world):
     """This rank's proxy points.  weak: an independent area-weighted sample of the SAME mesh per rank (rank 0's is
-    the N = 1 cloud), so every rank has the N = 1 workload.  strong: interleaved Z-order chunks of the one cloud,
-    every run of `world` consecutive chunks giving one chunk to each rank with a rotating owner."""
+    the N = 1 cloud), so every rank has the N = 1 workload.  strong: contiguous ranges of the Z-ordered cloud, ceil(N / G)
+    points rounded up to whole 32-point blocks (SURVEY.md 8e's partition; each rank then works on one region of the city and
+    of the tree: k_trace 1.44 ms per rank against 1.54 with interleaved 1024-point chunks, tools/dev_shard_cull.py), or with
+    --shard-chunk C interleaved C-point chunks, every run of `world` consecutive chunks giving one chunk to each rank with
+    a rotating owner (for clouds whose ray density varies over the scene)."""
     from uavmvs_b200 import scenes
     if a.scaling == "weak":
         return scenes.sample_cloud(sc.verts, sc.faces, a.points, 2 + 1000 * rank)
     n = sc.num_points
     if world == 1:
         return sc.points, sc.normals
-    chunks = np.arange((n + CHUNK - 1) // CHUNK, dtype=np.uint64)
+    chunk = int(getattr(a, "shard_chunk", 0))
+    if chunk <= 0:
+        per = ((n + world - 1) // world + 31) // 32 * 32
+        lo, hi = min(n, rank * per), min(n, (rank + 1) * per)
+        return np.ascontiguousarray(sc.points[lo:hi]), np.ascontiguousarray(sc.normals[lo:hi])
+    chunks = np.arange((n + chunk - 1) // chunk, dtype=np.uint64)
     rot = ((chunks // np.uint64(world)) * np.uint64(2654435761) >> np.uint64(7)) % np.uint64(world)
     mine = chunks[(chunks + rot) % np.uint64(world) == np.uint64(rank)].astype(np.int64)
-    idx = (mine[:, None] * CHUNK + np.arange(CHUNK)[None, :]).reshape(-1)
+    idx = (mine[:, None] * chunk + np.arange(chunk)[None, :]).reshape(-1)
     idx = idx[idx < n]
     return np.ascontiguousarray(sc.points[idx]), np.ascontiguousarray(sc.normals[idx])
 
@@ -738,7 +747,8 @@ def run_b200(a, rank, local_rank, world):
             "dtype": "f32", "data": "synthetic", "config": config_dict(a, world),
             "setup": {"tree": "GPU %s (uavmvs_bvh_build_%s, %.3f s, not timed)" % (a.tree.upper(), a.tree, blk["build_s"]),
                       "sharding": ("weak: every rank its own %d-point sample of the same mesh" % a.points) if a.scaling == "weak" else
-                                  ("strong: interleaved %d-point Z-order chunks of one %d-point cloud, rotating owner" % (CHUNK, a.points)),
+                                  (("strong: contiguous Z-order ranges of one %d-point cloud, ceil(N / G) points per rank" % a.points) if a.shard_chunk <= 0 else
+                                   ("strong: interleaved %d-point Z-order chunks of one %d-point cloud, rotating owner" % (a.shard_chunk, a.points))),
                       "collective": "ncclAllGather of one 64-byte score record per rank + fold in rank order, enqueued after K9 on the "
                                     "evaluation's stream inside uavmvs_evaluate_trajectory_sharded (inside the timed region)"
                                     if world > 1 else "none (single GPU): pack + fold kernels only"},

@@ -20,7 +20,10 @@ def main():
     ap.add_argument("--ranks", default="0,1")
     ap.add_argument("--debug", action="store_true", help="one more evaluation with UAVMVS_K1_DEBUG=1 (per-block cull cycles)")
     ap.add_argument("--reps", type=int, default=4)
+    ap.add_argument("--chunk", type=int, default=0, help="points per interleaved chunk (0: bench.py's CHUNK)")
     a = ap.parse_args()
+    if a.chunk:
+        bench.CHUNK = a.chunk
     from uavmvs_b200 import api, scenes
     sc = scenes.urban(10_000_000, 8_000_000, 10_000, 800.0, seed=1)
     t0 = time.time()
@@ -30,6 +33,7 @@ def main():
 
     class A:
         scaling = "strong"
+        shard_chunk = bench.CHUNK if bench.CHUNK < 1000000 else 0      # >= 1M: contiguous ranges
     for r in [int(x) for x in a.ranks.split(",")]:
         p, n = bench.rank_cloud(A, sc, r, a.world)
         cloud = api.PointCloud.create(p, n)
@@ -43,6 +47,7 @@ def main():
             ms = api.profile_k1()
             if i and (best is None or sum(ms) < sum(best)):
                 best = ms
+        print("chunk %d " % bench.CHUNK, end="")
         print("rank %d of %d: %d points  masks %.3f caps %.3f cull %.3f trace %.3f retire %.3f  K1 %.3f" %
               (r, a.world, p.shape[0], *best, sum(best)), flush=True)
         if a.debug:
