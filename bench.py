@@ -39,7 +39,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "occlusion_rays_per_s"
 UNIT = "rays/s"
-CHUNK = 1024          # --shard-chunk's natural unit (one 1024-point super-block); tools/dev_shard_cull.py's default
+CHUNK = 1024          # default --shard-chunk: points per interleaved chunk of the strong-scaling split (= one 1024-point super-block)
 L2_NOTE = "GPU arm: L2 flushed between steps (256 MiB fill, outside the events); CPU arm: n/a"
 CONFIGS = {
     2: dict(tris=1_000_000, points=1_000_000, views=2000, extent=256.0, scaling="weak"),
@@ -68,7 +68,7 @@ def parse():
     ap.add_argument("--strong-steps", type=int, default=5)
     ap.add_argument("--positions", type=int, default=0, help="config 4: number of candidate positions (0 = steps x 8192)")
     ap.add_argument("--grid", type=int, default=128, help="config 4: voxels per axis")
-    ap.add_argument("--shard-chunk", type=int, default=0, help="strong scaling: 0 = contiguous Z-order ranges per rank, C = interleaved C-point chunks")
+    ap.add_argument("--shard-chunk", type=int, default=CHUNK, help="strong scaling: C = interleaved C-point Z-order chunks (default 1024), 0 = contiguous ranges per rank")
     a = ap.parse_args()
     c = CONFIGS[a.config]
     a.tris, a.points, a.views = a.tris or c["tris"], a.points or c["points"], a.views or c["views"]
@@ -100,18 +100,19 @@ def make_scene(a):
 
 def rank_cloud(a, sc, rank, world):
     """This rank's proxy points.  weak: an independent area-weighted sample of the SAME mesh per rank (rank 0's is
-    the N = 1 cloud), so every rank has the N = 1 workload.  strong: contiguous ranges of the Z-ordered cloud, ceil(N / G)
-    points rounded up to whole 32-point blocks (SURVEY.md 8e's partition; each rank then works on one region of the city and
-    of the tree: k_trace 1.44 ms per rank against 1.54 with interleaved 1024-point chunks, tools/dev_shard_cull.py), or with
-    --shard-chunk C interleaved C-point chunks, every run of `world` consecutive chunks giving one chunk to each rank with
-    a rotating owner (for clouds whose ray density varies over the scene)."""
+    the N = 1 cloud), so every rank has the N = 1 workload.  strong: interleaved --shard-chunk C-point chunks of the Z-ordered
+    cloud, every run of `world` consecutive chunks giving one chunk to each rank with a rotating owner; C = 0: contiguous
+    ranges of ceil(N / G) points (SURVEY.md 8e's partition).  Measured on config 5 at N = 8 (profiles/r02_fin3_strong_split.txt):
+    1024-point chunks 3.198 ms, 8192-point chunks 3.206 ms, contiguous ranges 3.208 ms (each rank then works on one region of
+    the city and of the tree, k_trace 1.38 - 1.62 ms, but the ranks hold 11.05 M to 12.79 M rays and the slowest sets the
+    time).  The split is not what limits strong scaling; the default stays 1024."""
     from uavmvs_b200 import scenes
     if a.scaling == "weak":
         return scenes.sample_cloud(sc.verts, sc.faces, a.points, 2 + 1000 * rank)
     n = sc.num_points
     if world == 1:
         return sc.points, sc.normals
-    chunk = int(getattr(a, "shard_chunk", 0))
+    chunk = int(getattr(a, "shard_chunk", CHUNK))
     if chunk <= 0:
         per = ((n + world - 1) // world + 31) // 32 * 32
         lo, hi = min(n, rank * per), min(n, (rank + 1) * per)
