@@ -111,6 +111,35 @@ def _gloo_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("chunk", [1024, 8192, 0])
+@pytest.mark.parametrize("world", [2, 8])
+def test_bench_strong_split_is_a_partition(chunk, world):
+    """bench.py's strong-scaling split (--shard-chunk: interleaved chunks with a rotating owner, 0 = contiguous Z-order
+    ranges): every point of the cloud belongs to exactly one rank, ragged tail included, and the ranks are balanced."""
+    import types
+    import bench
+    n = 100_000 + 37
+    pts = np.arange(3 * n, dtype=np.float32).reshape(n, 3)                    # a point's x identifies it
+    sc = types.SimpleNamespace(points=pts, normals=-pts, num_points=n)
+    a = types.SimpleNamespace(scaling="strong", shard_chunk=chunk)
+    seen = np.zeros(n, np.int32)
+    sizes = []
+    for r in range(world):
+        p, nr = bench.rank_cloud(a, sc, r, world)
+        assert p.shape == nr.shape and np.array_equal(nr, -p) and p.flags.c_contiguous
+        ids = (p[:, 0] / 3).astype(np.int64)
+        assert np.array_equal(pts[ids], p)
+        if chunk == 0:
+            assert np.all(np.diff(ids) == 1)                                   # one contiguous range
+        seen[ids] += 1
+        sizes.append(len(ids))
+    assert np.all(seen == 1)
+    assert max(sizes) - min(sizes) <= max(chunk, 32) * 2
+    # one rank: the whole cloud, untouched
+    p, _ = bench.rank_cloud(a, sc, 0, 1)
+    assert p is pts
+
+
 def test_point_sharding_world2_gloo(tmp_path, oracle, tiny_scene, tiny_tree):
     import torch.multiprocessing as mp
     port = _free_port()
