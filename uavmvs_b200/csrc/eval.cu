@@ -454,8 +454,11 @@ static int run_evaluation(const EvalCall & c, float out3[3], uint64_t stats[4], 
         UAV_CUDA(cudaMemcpyAsync(c.h_num_rows, c.obs->num_rows, 4 * (size_t)c.obs->num_cols, cudaMemcpyDeviceToHost, g.copy_stream));
     }
     const uint32_t nblocks = divup(c.obs->num_cols, 32), chunks = overlap ? 0 : (c.h_recons && nblocks >= 64 ? 4 : 1);
+    // four ranges of decreasing size: what stays exposed at the end is the copy of the LAST range only (10 % of the points)
+    static const uint32_t cut4[5] = {0u, 36u, 66u, 90u, 100u};
     for (uint32_t k = 0; k < chunks; ++k) {
-        const uint32_t b0 = (uint32_t)((uint64_t)nblocks * k / chunks), b1 = (uint32_t)((uint64_t)nblocks * (k + 1) / chunks);
+        const uint32_t b0 = chunks == 4 ? (uint32_t)((uint64_t)nblocks * cut4[k] / 100u) : (uint32_t)((uint64_t)nblocks * k / chunks);
+        const uint32_t b1 = chunks == 4 ? (uint32_t)((uint64_t)nblocks * cut4[k + 1] / 100u) : (uint32_t)((uint64_t)nblocks * (k + 1) / chunks);
         rc = launch_sort_eval(s, true, true, c.obs, c.recons, c.target_recon, c.wrecons, false, b0, b1 - b0);
         if (rc) return rc;
         if (c.h_recons) {
